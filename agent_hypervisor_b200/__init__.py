@@ -1,0 +1,23 @@
+"""agent_hypervisor_b200 - B200-native drop-in for agent-hypervisor's audit/Merkle and
+sigma_eff/ring-gating hot path.  Class names and signatures follow
+``hypervisor/__init__.py:56-82`` of the reference for the classes on the path.
+
+Importing this package loads nothing native; the first call that needs the GPU loads
+``libahv_b200.so`` and raises ``NativeUnavailable`` if it (or a CUDA device) is missing.
+"""
+
+from ._native import Context, NativeError, NativeUnavailable, get_context, load_library
+from .audit import (ArenaBuilder, BatchAuditor, CommitmentEngine, CommitmentRecord, DeltaEngine, PackedSessions,
+                    SemanticDelta, VFSChange)
+from .liability import VouchGraphCSR, VouchingEngine, VouchingError, VouchRecord
+from .models import ActionDescriptor, ExecutionRing, ReversibilityLevel
+from .rings import RingCheckResult, RingEnforcer
+
+__version__ = "0.1.0"
+
+__all__ = [
+    "Context", "NativeError", "NativeUnavailable", "get_context", "load_library",
+    "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions",
+    "SemanticDelta", "VFSChange", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
+    "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer",
+]

@@ -1,0 +1,7 @@
+from .delta import DeltaEngine, SemanticDelta, VFSChange
+from .commitment import CommitmentEngine, CommitmentRecord
+from .packing import ArenaBuilder, PackedSessions, canonical_preimage, classify_parent
+from .batch import BatchAuditor
+
+__all__ = ["DeltaEngine", "SemanticDelta", "VFSChange", "CommitmentEngine", "CommitmentRecord",
+           "ArenaBuilder", "PackedSessions", "canonical_preimage", "classify_parent", "BatchAuditor"]

@@ -1,0 +1,74 @@
+"""Batched audit over many sessions: what ``Hypervisor.terminate_session`` (core.py:204) and an
+auditor calling ``verify_chain`` + ``CommitmentEngine.verify`` do one session at a time in the
+reference, done for all sessions in one GPU pass each.
+"""
+
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import numpy as np
+
+from .. import _native as nat
+from .packing import PackedSessions, pack_sessions
+
+
+class BatchAuditor:
+    def __init__(self, ctx: Optional[nat.Context] = None) -> None:
+        self.ctx = ctx or nat.get_context()
+
+    def pack(self, engines: Sequence) -> PackedSessions:
+        """engines: DeltaEngine objects (or lists of SemanticDelta)."""
+        return pack_sessions([getattr(e, "_deltas", e) for e in engines])
+
+    def commit(self, packed: PackedSessions):
+        """-> (leaf digests [n,32], roots as hex or None per session)."""
+        fixed, uni = packed.uniform_shape()
+        digs, roots, empty = self.ctx.commit(
+            packed.arena, None if fixed else packed.offsets, None if uni else packed.session_rowptr,
+            fixed_len=fixed if fixed else 0, uniform_leaves=uni, n_sessions=packed.n_sessions)
+        return digs, [None if empty[s] else roots[s].tobytes().hex() for s in range(packed.n_sessions)]
+
+    def commit_engines(self, engines: Sequence, commitment_engine=None, participants=None) -> list:
+        """Roots for many DeltaEngines at once; also refreshes nothing (pure read), like
+        compute_merkle_root.  Optionally records them in a CommitmentEngine."""
+        packed = self.pack(engines)
+        _, roots = self.commit(packed)
+        if commitment_engine is not None:
+            for e, r in zip(engines, roots):
+                if r is not None:
+                    commitment_engine.commit(e.session_id, r, list(participants or []), len(e._deltas))
+        return roots
+
+    def verify(self, packed: PackedSessions, expected_roots_hex: Optional[Sequence[Optional[str]]] = None):
+        """-> dict(verdict bool[S], first_bad int[S], digests, root_match bool[S] or None)."""
+        fixed, uni = packed.uniform_shape()
+        exp = None
+        if expected_roots_hex is not None:
+            exp = np.zeros((packed.n_sessions, 32), dtype=np.uint8)
+            known = np.zeros(packed.n_sessions, dtype=bool)
+            for s, r in enumerate(expected_roots_hex):
+                if r:
+                    exp[s] = np.frombuffer(bytes.fromhex(r), dtype=np.uint8)
+                    known[s] = True
+        res = self.ctx.verify_chains(
+            packed.arena, None if fixed else packed.offsets, packed.parents, packed.parent_kind,
+            None if uni else packed.session_rowptr, fixed_len=fixed if fixed else 0, uniform_leaves=uni,
+            n_sessions=packed.n_sessions, expected_roots=exp)
+        if exp is not None:
+            res["root_match"] = (res["root_match"].astype(bool)) & known   # commitment.py:61-63
+        res["verdict"] = res["verdict"].astype(bool)
+        return res
+
+    def verify_engines(self, engines: Sequence) -> list[bool]:
+        """verify_chain for many DeltaEngines, including the reference's delta_hash write-back."""
+        packed = self.pack(engines)
+        res = self.verify(packed)
+        rp = packed.session_rowptr
+        for s, e in enumerate(engines):
+            deltas = getattr(e, "_deltas", e)
+            last = len(deltas) - 1 if res["verdict"][s] else int(res["first_bad"][s])
+            base = int(rp[s])
+            for i in range(last + 1):
+                deltas[i].delta_hash = res["digests"][base + i].tobytes().hex()
+        return [bool(v) for v in res["verdict"]]

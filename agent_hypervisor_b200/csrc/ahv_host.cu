@@ -1,0 +1,318 @@
+// ahv_host.cu - host-pointer entry points: stage caller buffers on the device, run the
+// device-pointer entry point, copy results back, synchronise.  These are what the Python
+// shim (agent_hypervisor_b200/_native.py) binds; the reference-side call each replaces is
+// cited in include/ahv.h.
+#include "ahv_internal.cuh"
+
+using namespace ahv;
+
+namespace {
+
+struct Stager {
+    ahv_ctx *ctx;
+    int rc = AHV_OK;
+    explicit Stager(ahv_ctx *c) : ctx(c) {}
+
+    template <class T>
+    T *in(const T *h, uint64_t count)
+    {
+        if (rc != AHV_OK || !h || count == 0) return nullptr;
+        T *d = (T *)io_take(ctx, count * sizeof(T));
+        if (!d) {
+            set_error("internal: staging slab too small");
+            rc = AHV_E_NOMEM;
+            return nullptr;
+        }
+        cudaError_t e = cudaMemcpyAsync(d, h, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream);
+        if (e != cudaSuccess) {
+            set_error("H2D copy failed: %s", cudaGetErrorString(e));
+            rc = AHV_E_CUDA;
+        }
+        return d;
+    }
+    template <class T>
+    T *out(T *h, uint64_t count)
+    {
+        if (rc != AHV_OK || !h || count == 0) return nullptr;
+        T *d = (T *)io_take(ctx, count * sizeof(T));
+        if (!d) {
+            set_error("internal: staging slab too small");
+            rc = AHV_E_NOMEM;
+        }
+        return d;
+    }
+    template <class T>
+    void back(T *h, const T *d, uint64_t count)
+    {
+        if (rc != AHV_OK || !h || !d || count == 0) return;
+        cudaError_t e = cudaMemcpyAsync(h, d, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e != cudaSuccess) {
+            set_error("D2H copy failed: %s", cudaGetErrorString(e));
+            rc = AHV_E_CUDA;
+        }
+    }
+    int finish()
+    {
+        if (rc != AHV_OK) return rc;
+        AHV_CUDA(cudaStreamSynchronize(ctx->stream));
+        return AHV_OK;
+    }
+};
+
+uint64_t p256(uint64_t b) { return pad256(b ? b : 1); }
+
+// message count and arena size from (offsets | fixed_len)
+int arena_extent(const uint64_t *offsets, uint64_t n, uint64_t fixed_len, uint64_t *bytes)
+{
+    if (offsets) {
+        AHV_REQUIRE(offsets[0] <= offsets[n], "offsets must be non-decreasing");
+        *bytes = offsets[n];
+    } else {
+        *bytes = n * fixed_len;
+    }
+    return AHV_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ahv_sha256_batch(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t n, uint64_t fixed_len,
+                     uint8_t *out_digests)
+{
+    AHV_TRY(use_device(ctx));
+    if (n == 0) return AHV_OK;
+    AHV_REQUIRE(out_digests, "out_digests is null");
+    AHV_REQUIRE(offsets || fixed_len > 0, "offsets is NULL and fixed_len is 0");
+    uint64_t ab = 0;
+    AHV_TRY(arena_extent(offsets, n, fixed_len, &ab));
+    AHV_REQUIRE(arena || ab == 0, "arena is null");
+    AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(32 * n)));
+    Stager st(ctx);
+    uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);       // slack: aligned reads may touch the last word
+    if (ab) AHV_CUDA(cudaMemcpyAsync(d_arena, arena, ab, cudaMemcpyHostToDevice, ctx->stream));
+    uint64_t *d_off = st.in(offsets, offsets ? n + 1 : 0);
+    uint8_t *d_out = st.out(out_digests, 32 * n);
+    if (st.rc != AHV_OK) return st.rc;
+    AHV_TRY(ahv_sha256_batch_dev(ctx, d_arena, ab, d_off, n, fixed_len, d_out));
+    st.back(out_digests, d_out, 32 * n);
+    return st.finish();
+}
+
+int ahv_merkle_roots(ahv_ctx *ctx, const uint8_t *digests, const uint64_t *rowptr, uint64_t S, uint8_t *out_roots,
+                     uint8_t *out_empty)
+{
+    AHV_TRY(use_device(ctx));
+    if (S == 0) return AHV_OK;
+    AHV_REQUIRE(rowptr && out_roots, "session_rowptr / out_roots is null");
+    const uint64_t n = rowptr[S] - rowptr[0];
+    AHV_REQUIRE(rowptr[0] == 0, "session_rowptr[0] must be 0");
+    AHV_REQUIRE(digests || n == 0, "digests is null");
+    uint64_t maxl = 0;
+    for (uint64_t s = 0; s < S; ++s) {
+        AHV_REQUIRE(rowptr[s + 1] >= rowptr[s], "session_rowptr must be non-decreasing");
+        uint64_t c = rowptr[s + 1] - rowptr[s];
+        if (c > maxl) maxl = c;
+    }
+    AHV_TRY(io_reserve(ctx, p256(32 * n) + p256(8 * (S + 1)) + p256(32 * S) + p256(S)));
+    Stager st(ctx);
+    uint8_t *d_dig = st.in(digests, 32 * n);
+    uint64_t *d_rp = st.in(rowptr, S + 1);
+    uint8_t *d_roots = st.out(out_roots, 32 * S);
+    uint8_t *d_empty = (uint8_t *)io_take(ctx, S);
+    if (st.rc != AHV_OK) return st.rc;
+    if (!d_dig) d_dig = d_roots;   // n == 0: never dereferenced, keeps alignment checks happy
+    AHV_TRY(ahv_merkle_roots_dev(ctx, d_dig, d_rp, S, n, maxl ? maxl : 1, d_roots, d_empty));
+    st.back(out_roots, d_roots, 32 * S);
+    st.back(out_empty, d_empty, S);
+    return st.finish();
+}
+
+static int session_shape(const uint64_t *rowptr, uint64_t S, uint64_t uniform, uint64_t *n, uint64_t *maxl)
+{
+    if (uniform) {
+        *n = S * uniform;
+        *maxl = uniform;
+        return AHV_OK;
+    }
+    AHV_REQUIRE(rowptr || S == 0, "session_rowptr is NULL and uniform_leaves is 0");
+    *n = S ? rowptr[S] : 0;
+    *maxl = 0;
+    if (S) AHV_REQUIRE(rowptr[0] == 0, "session_rowptr[0] must be 0");
+    for (uint64_t s = 0; s < S; ++s) {
+        AHV_REQUIRE(rowptr[s + 1] >= rowptr[s], "session_rowptr must be non-decreasing");
+        uint64_t c = rowptr[s + 1] - rowptr[s];
+        if (c > *maxl) *maxl = c;
+    }
+    if (*maxl == 0) *maxl = 1;
+    return AHV_OK;
+}
+
+int ahv_commit(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
+               const uint64_t *rowptr, uint64_t S, uint64_t uniform, uint8_t *out_digests, uint8_t *out_roots,
+               uint8_t *out_empty)
+{
+    AHV_TRY(use_device(ctx));
+    if (S == 0) return AHV_OK;
+    AHV_REQUIRE(out_roots, "out_roots is null");
+    uint64_t n = 0, maxl = 0, ab = 0;
+    AHV_TRY(session_shape(rowptr, S, uniform, &n, &maxl));
+    AHV_REQUIRE(offsets || fixed_len > 0 || n == 0, "offsets is NULL and fixed_len is 0");
+    AHV_TRY(arena_extent(offsets, n, fixed_len, &ab));
+    AHV_REQUIRE(arena || ab == 0, "arena is null");
+    AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(8 * (S + 1)) + p256(32 * n) + p256(32 * S) + p256(S)));
+    Stager st(ctx);
+    uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);
+    if (ab) AHV_CUDA(cudaMemcpyAsync(d_arena, arena, ab, cudaMemcpyHostToDevice, ctx->stream));
+    uint64_t *d_off = st.in(offsets, offsets ? n + 1 : 0);
+    uint64_t *d_rp = uniform ? nullptr : st.in(rowptr, S + 1);
+    uint8_t *d_dig = st.out(out_digests, 32 * n);
+    uint8_t *d_roots = st.out(out_roots, 32 * S);
+    uint8_t *d_empty = (uint8_t *)io_take(ctx, S);
+    if (st.rc != AHV_OK) return st.rc;
+    AHV_TRY(ahv_commit_dev(ctx, d_arena, ab, d_off, fixed_len, d_rp, S, n, uniform, maxl, d_dig, d_roots, d_empty));
+    st.back(out_digests, d_dig, 32 * n);
+    st.back(out_roots, d_roots, 32 * S);
+    st.back(out_empty, d_empty, S);
+    return st.finish();
+}
+
+int ahv_verify_chains(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
+                      const uint8_t *parents, const uint8_t *kind, const uint64_t *rowptr, uint64_t S,
+                      uint64_t uniform, const uint8_t *expected_roots, uint8_t *out_verdict, int64_t *out_first_bad,
+                      uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_match)
+{
+    AHV_TRY(use_device(ctx));
+    if (S == 0) return AHV_OK;
+    uint64_t n = 0, maxl = 0, ab = 0;
+    AHV_TRY(session_shape(rowptr, S, uniform, &n, &maxl));
+    AHV_REQUIRE(offsets || fixed_len > 0 || n == 0, "offsets is NULL and fixed_len is 0");
+    AHV_REQUIRE((parents && kind) || n == 0, "parent_digests / parent_kind is null");
+    AHV_REQUIRE(!out_match || expected_roots, "out_root_match needs expected_roots");
+    AHV_TRY(arena_extent(offsets, n, fixed_len, &ab));
+    AHV_REQUIRE(arena || ab == 0, "arena is null");
+    AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(8 * (S + 1)) + 2 * p256(32 * n) + p256(n) +
+                                3 * p256(32 * S) + 2 * p256(S) + p256(8 * S)));
+    Stager st(ctx);
+    uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);
+    if (ab) AHV_CUDA(cudaMemcpyAsync(d_arena, arena, ab, cudaMemcpyHostToDevice, ctx->stream));
+    uint64_t *d_off = st.in(offsets, offsets ? n + 1 : 0);
+    uint64_t *d_rp = uniform ? nullptr : st.in(rowptr, S + 1);
+    uint8_t *d_par = st.in(parents, 32 * n);
+    uint8_t *d_kind = st.in(kind, n);
+    uint8_t *d_exp = st.in(expected_roots, 32 * S);
+    uint8_t *d_verdict = st.out(out_verdict, S);
+    int64_t *d_fb = st.out(out_first_bad, S);
+    uint8_t *d_dig = st.out(out_digests, 32 * n);
+    uint8_t *d_roots = st.out(out_roots, 32 * S);
+    uint8_t *d_match = st.out(out_match, S);
+    if (st.rc != AHV_OK) return st.rc;
+    if (n == 0) {   // only empty sessions: verify_chain's loop body never runs -> True
+        if (out_verdict) memset(out_verdict, 1, S);
+        if (out_first_bad) for (uint64_t s = 0; s < S; ++s) out_first_bad[s] = -1;
+        if (out_roots) memset(out_roots, 0, 32 * S);
+        if (out_match) memset(out_match, 0, S);
+        return AHV_OK;
+    }
+    AHV_TRY(ahv_verify_chains_dev(ctx, d_arena, ab, d_off, fixed_len, d_par, d_kind, d_rp, S, n, uniform, maxl, d_exp,
+                                  d_verdict, d_fb, d_dig, d_roots, d_match));
+    st.back(out_verdict, d_verdict, S);
+    st.back(out_first_bad, d_fb, S);
+    st.back(out_digests, d_dig, 32 * n);
+    st.back(out_roots, d_roots, 32 * S);
+    st.back(out_match, d_match, S);
+    return st.finish();
+}
+
+int ahv_chain_capture(ahv_ctx *ctx, uint8_t *arena, const uint64_t *offsets, const uint32_t *hexpos,
+                      const uint64_t *rowptr, uint64_t S, uint8_t *out_digests, uint8_t *out_parents,
+                      uint8_t *out_kind)
+{
+    AHV_TRY(use_device(ctx));
+    if (S == 0) return AHV_OK;
+    AHV_REQUIRE(arena && offsets && hexpos && rowptr, "arena / offsets / hexpos / session_rowptr is null");
+    uint64_t n = 0, maxl = 0;
+    AHV_TRY(session_shape(rowptr, S, 0, &n, &maxl));
+    if (n == 0) return AHV_OK;
+    const uint64_t ab = offsets[n];
+    for (uint64_t i = 0; i < n; ++i)
+        if (hexpos[i] != 0xffffffffu)
+            AHV_REQUIRE((uint64_t)hexpos[i] + 64 <= offsets[i + 1] - offsets[i], "hexpos outside its message");
+    AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(4 * n) + p256(8 * (S + 1)) + 2 * p256(32 * n) + p256(n)));
+    Stager st(ctx);
+    uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);
+    AHV_CUDA(cudaMemcpyAsync(d_arena, arena, ab, cudaMemcpyHostToDevice, ctx->stream));
+    uint64_t *d_off = st.in(offsets, n + 1);
+    uint32_t *d_hp = st.in(hexpos, n);
+    uint64_t *d_rp = st.in(rowptr, S + 1);
+    uint8_t *d_dig = st.out(out_digests, 32 * n);
+    uint8_t *d_par = st.out(out_parents, 32 * n);
+    uint8_t *d_kind = st.out(out_kind, n);
+    if (st.rc != AHV_OK) return st.rc;
+    AHV_TRY(ahv_chain_capture_dev(ctx, d_arena, ab, d_off, d_hp, d_rp, S, n, d_dig, d_par, d_kind));
+    st.back(arena, d_arena, ab);
+    st.back(out_digests, d_dig, 32 * n);
+    st.back(out_parents, d_par, 32 * n);
+    st.back(out_kind, d_kind, n);
+    return st.finish();
+}
+
+int ahv_sigma_eff_rings(ahv_ctx *ctx, const uint32_t *rowptr, const double *bonded, const uint8_t *active,
+                        const int64_t *expiry, int64_t now, const double *sigma, const double *omega,
+                        const uint8_t *consensus, const uint8_t *current_ring, uint64_t A, double *out_sigma,
+                        uint8_t *out_ring, uint8_t *out_demote, uint8_t *out_near)
+{
+    AHV_TRY(use_device(ctx));
+    if (A == 0) return AHV_OK;
+    AHV_REQUIRE(rowptr && sigma && omega && out_sigma, "rowptr / sigma / omega / out_sigma_eff is null");
+    const uint64_t E = rowptr[A];
+    AHV_REQUIRE(E == 0 || (bonded && active && expiry), "edge arrays are null");
+    AHV_TRY(io_reserve(ctx, p256(4 * (A + 1)) + p256(8 * E) + p256(E) + p256(8 * E) + 3 * p256(8 * A) + 5 * p256(A)));
+    Stager st(ctx);
+    uint32_t *d_rp = st.in(rowptr, A + 1);
+    double *d_b = st.in(bonded, E);
+    uint8_t *d_a = st.in(active, E);
+    int64_t *d_e = st.in(expiry, E);
+    double *d_s = st.in(sigma, A);
+    double *d_o = st.in(omega, A);
+    uint8_t *d_c = st.in(consensus, A);
+    uint8_t *d_r = st.in(current_ring, A);
+    double *d_os = st.out(out_sigma, A);
+    uint8_t *d_or = st.out(out_ring, A);
+    uint8_t *d_od = st.out(out_demote, A);
+    uint8_t *d_on = st.out(out_near, A);
+    if (st.rc != AHV_OK) return st.rc;
+    AHV_TRY(ahv_sigma_eff_rings_dev(ctx, d_rp, d_b, d_a, d_e, now, d_s, d_o, d_c, d_r, A, d_os, d_or, d_od, d_on));
+    st.back(out_sigma, d_os, A);
+    st.back(out_ring, d_or, A);
+    st.back(out_demote, d_od, A);
+    st.back(out_near, d_on, A);
+    return st.finish();
+}
+
+int ahv_ring_check(ahv_ctx *ctx, const uint8_t *agent_ring, const uint8_t *flags, const double *sigma,
+                   const uint8_t *consensus, const uint8_t *witness, uint64_t n, uint8_t *out_allowed,
+                   uint8_t *out_reason, uint8_t *out_required)
+{
+    AHV_TRY(use_device(ctx));
+    if (n == 0) return AHV_OK;
+    AHV_REQUIRE(agent_ring && flags && sigma && consensus && witness, "an input array is null");
+    AHV_TRY(io_reserve(ctx, 7 * p256(n) + p256(8 * n)));
+    Stager st(ctx);
+    uint8_t *d_ar = st.in(agent_ring, n);
+    uint8_t *d_fl = st.in(flags, n);
+    double *d_s = st.in(sigma, n);
+    uint8_t *d_c = st.in(consensus, n);
+    uint8_t *d_w = st.in(witness, n);
+    uint8_t *d_al = st.out(out_allowed, n);
+    uint8_t *d_re = st.out(out_reason, n);
+    uint8_t *d_rq = st.out(out_required, n);
+    if (st.rc != AHV_OK) return st.rc;
+    AHV_TRY(ahv_ring_check_dev(ctx, d_ar, d_fl, d_s, d_c, d_w, n, d_al, d_re, d_rq));
+    st.back(out_allowed, d_al, n);
+    st.back(out_reason, d_re, n);
+    st.back(out_required, d_rq, n);
+    return st.finish();
+}
+
+}  // extern "C"

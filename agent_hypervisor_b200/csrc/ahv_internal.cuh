@@ -1,0 +1,92 @@
+// ahv_internal.cuh - context, error plumbing and launch helpers shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/ahv.h"
+
+#define AHV_MAX_TIMERS 64
+
+struct ahv_ctx {
+    int device;
+    cudaStream_t stream;
+    cudaStream_t copy_stream;     // H2D/D2H of the pipelined host entry points
+    cudaEvent_t ev_copy[4];       // chunk hand-off between copy_stream and stream
+    int sm_count;
+    int clock_khz;
+    uint64_t total_mem;
+    // device scratch: one growable slab, bump-allocated inside each _dev entry point
+    uint8_t *scratch;
+    uint64_t scratch_cap;
+    uint64_t scratch_used;
+    // device staging for the host-pointer entry points (inputs/outputs of the _dev call)
+    uint8_t *io;
+    uint64_t io_cap;
+    uint64_t io_used;
+    uint64_t launches;
+    cudaEvent_t t_start[AHV_MAX_TIMERS], t_stop[AHV_MAX_TIMERS];
+    // tuning options (ahv_set_option)
+    int64_t opt_sort;          // 1: length-sort variable-length batches (default 1)
+    int64_t opt_fixed_k;       // log2 leaves per thread in the fused fixed-size kernel (default 3)
+    int64_t opt_block;         // threads per block for SHA kernels (default 128)
+    int64_t opt_fixed_variant; // 0: direct LDG.128, 1: smem-staged (cp.async)
+    int64_t opt_tree_k;        // log2 leaves per thread in the digest-tree kernel
+    int64_t opt_leaf_timer;    // >0: bracket every leaf-hash launch with timer slots base..base+15 (round robin)
+    uint64_t leaf_launches;    // leaf-hash kernel launches so far (indexes the round robin)
+};
+
+namespace ahv {
+
+void set_error(const char *fmt, ...);
+
+#define AHV_CUDA(call)                                                                          \
+    do {                                                                                        \
+        cudaError_t e_ = (call);                                                                \
+        if (e_ != cudaSuccess) {                                                                \
+            ahv::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return (e_ == cudaErrorMemoryAllocation) ? AHV_E_NOMEM : AHV_E_CUDA;                \
+        }                                                                                       \
+    } while (0)
+
+#define AHV_CHECK_LAUNCH(ctx)                                                                   \
+    do {                                                                                        \
+        (ctx)->launches++;                                                                      \
+        cudaError_t e_ = cudaGetLastError();                                                    \
+        if (e_ != cudaSuccess) {                                                                \
+            ahv::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return AHV_E_CUDA;                                                                  \
+        }                                                                                       \
+    } while (0)
+
+#define AHV_REQUIRE(cond, msg)                                                                  \
+    do {                                                                                        \
+        if (!(cond)) {                                                                          \
+            ahv::set_error("invalid argument: %s", msg);                                        \
+            return AHV_E_INVALID;                                                               \
+        }                                                                                       \
+    } while (0)
+
+#define AHV_TRY(expr)                                                                           \
+    do {                                                                                        \
+        int rc_ = (expr);                                                                       \
+        if (rc_ != AHV_OK) return rc_;                                                          \
+    } while (0)
+
+// scratch slab --------------------------------------------------------------
+int scratch_reserve(ahv_ctx *ctx, uint64_t bytes);   // grow (may sync); resets the bump pointer
+void *scratch_take(ahv_ctx *ctx, uint64_t bytes);    // 256-byte aligned; NULL if reserve was too small
+int io_reserve(ahv_ctx *ctx, uint64_t bytes);        // same, for the host entry points' staging slab
+void *io_take(ahv_ctx *ctx, uint64_t bytes);
+static inline uint64_t pad256(uint64_t b) { return (b + 255u) & ~(uint64_t)255u; }
+
+int use_device(ahv_ctx *ctx);
+
+static inline unsigned grid_for(uint64_t threads, unsigned block)
+{
+    uint64_t g = (threads + block - 1) / block;
+    return (unsigned)(g ? g : 1);
+}
+
+}  // namespace ahv

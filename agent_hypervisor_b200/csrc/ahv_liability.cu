@@ -1,0 +1,88 @@
+// ahv_liability.cu - batched sigma_eff over a CSR vouch graph + ring classification,
+// and the batched RingEnforcer gate.  HBM-bound passes (fp64 compare/add only).
+//
+// Reference behaviour (paths under /root/reference/src/hypervisor):
+//   sigma_eff        liability/vouching.py:128-151 (+ :34-38 expiry, :186-197 active filter)
+//   ring             models.py:34-42 ; should_demote rings/enforcer.py:134-137
+//   required_ring    models.py:122-132 ; gate rings/enforcer.py:44-128
+#include "ahv_internal.cuh"
+#include "liability_core.cuh"
+
+using namespace ahv;
+
+namespace {
+
+// One thread per agent row; the row is summed sequentially in insertion order so the
+// result is bit-identical to the reference's Python loop (vouching.py:146-148).
+__global__ void __launch_bounds__(256)
+k_sigma_eff_rings(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
+                  const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
+                  const double *__restrict__ sigma, const double *__restrict__ omega,
+                  const uint8_t *__restrict__ consensus, const uint8_t *__restrict__ current_ring, uint64_t A,
+                  double *__restrict__ out_sigma, uint8_t *__restrict__ out_ring, uint8_t *__restrict__ out_demote,
+                  uint8_t *__restrict__ out_near)
+{
+    uint64_t a = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= A) return;
+    const uint32_t e0 = rowptr[a], e1 = rowptr[a + 1];
+    double contrib = 0.0;
+    for (uint32_t e = e0; e < e1; ++e)
+        contrib = vouch_accumulate(contrib, bonded[e], active[e], expiry[e], now);
+    const double se = sigma_eff_of(sigma[a], omega[a], contrib);
+    out_sigma[a] = se;
+    if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, consensus[a] != 0);
+    if (out_demote) out_demote[a] = (uint8_t)(ring_from_sigma(se, false) > (int)current_ring[a]);
+    if (out_near) out_near[a] = (uint8_t)near_threshold(se);
+}
+
+__global__ void __launch_bounds__(256)
+k_ring_check(const uint8_t *__restrict__ agent_ring, const uint8_t *__restrict__ flags,
+             const double *__restrict__ sigma, const uint8_t *__restrict__ consensus,
+             const uint8_t *__restrict__ witness, uint64_t n, uint8_t *__restrict__ allowed,
+             uint8_t *__restrict__ reason, uint8_t *__restrict__ required)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int req = required_ring(flags[i]);
+    int code = gate_reason(agent_ring[i], req, sigma[i], consensus[i] != 0, witness[i] != 0);
+    if (allowed) allowed[i] = (uint8_t)(code == AHV_REASON_GRANTED);
+    if (reason) reason[i] = (uint8_t)code;
+    if (required) required[i] = (uint8_t)req;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *d_bonded, const uint8_t *d_active,
+                            const int64_t *d_expiry, int64_t now, const double *d_sigma, const double *d_omega,
+                            const uint8_t *d_consensus, const uint8_t *d_current_ring, uint64_t A,
+                            double *d_out_sigma, uint8_t *d_out_ring, uint8_t *d_out_demote, uint8_t *d_out_near)
+{
+    AHV_TRY(use_device(ctx));
+    if (A == 0) return AHV_OK;
+    AHV_REQUIRE(d_rowptr && d_sigma && d_omega && d_out_sigma, "rowptr / sigma / omega / out_sigma_eff is null");
+    AHV_REQUIRE(!d_out_ring || d_consensus, "out_ring needs consensus");
+    AHV_REQUIRE(!d_out_demote || d_current_ring, "out_demote needs current_ring");
+    AHV_REQUIRE(A < 0xffffffffull, "too many agents (limit 2^32-2)");
+    k_sigma_eff_rings<<<grid_for(A, 256), 256, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma,
+                                                                 d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+                                                                 d_out_ring, d_out_demote, d_out_near);
+    AHV_CHECK_LAUNCH(ctx);
+    return AHV_OK;
+}
+
+int ahv_ring_check_dev(ahv_ctx *ctx, const uint8_t *d_agent_ring, const uint8_t *d_flags, const double *d_sigma,
+                       const uint8_t *d_consensus, const uint8_t *d_witness, uint64_t n, uint8_t *d_allowed,
+                       uint8_t *d_reason, uint8_t *d_required)
+{
+    AHV_TRY(use_device(ctx));
+    if (n == 0) return AHV_OK;
+    AHV_REQUIRE(d_agent_ring && d_flags && d_sigma && d_consensus && d_witness, "an input array is null");
+    k_ring_check<<<grid_for(n, 256), 256, 0, ctx->stream>>>(d_agent_ring, d_flags, d_sigma, d_consensus, d_witness, n,
+                                                            d_allowed, d_reason, d_required);
+    AHV_CHECK_LAUNCH(ctx);
+    return AHV_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,307 @@
+// sha256_core.cuh - per-thread SHA-256 building blocks shared by every audit kernel.
+//
+// All functions are __host__ __device__ so that tests/hostemu can run the very same
+// per-thread logic on the CPU (test infrastructure only; the product has no CPU path).
+//
+// Reference behaviour implemented here (paths under /root/reference/src/hypervisor):
+//   sha256 of a byte string        audit/delta.py:63  (hashlib.sha256(payload).hexdigest())
+//   node = sha256(hex(l)+hex(r))   audit/delta.py:130
+//
+// Layout notes: a digest "in registers" is the 8 SHA-256 state words (big-endian
+// interpretation of the 32 digest bytes).  In memory a digest is the 32 raw bytes.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define AHV_HD __host__ __device__ __forceinline__
+#else
+#define AHV_HD inline
+#endif
+
+namespace ahv {
+
+// ---------------------------------------------------------------- primitives
+AHV_HD uint32_t rotr32(uint32_t x, int n)
+{
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(x, x, n);   // SHF.R.W
+#else
+    return (x >> n) | (x << (32 - n));
+#endif
+}
+
+// byte permute: result byte k = byte (sel>>4k & 7) of the 8-byte pool {hi:lo}={b,a}
+AHV_HD uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(a, b, sel);
+#else
+    uint64_t pool = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (int k = 0; k < 4; ++k) {
+        uint32_t s = (sel >> (4 * k)) & 7u;
+        r |= (uint32_t)((pool >> (8 * s)) & 0xffu) << (8 * k);
+    }
+    return r;
+#endif
+}
+
+AHV_HD uint32_t bswap32(uint32_t x) { return prmt(x, 0u, 0x0123u); }
+
+AHV_HD uint32_t Sig0(uint32_t x) { return rotr32(x, 2) ^ rotr32(x, 13) ^ rotr32(x, 22); }
+AHV_HD uint32_t Sig1(uint32_t x) { return rotr32(x, 6) ^ rotr32(x, 11) ^ rotr32(x, 25); }
+AHV_HD uint32_t sig0(uint32_t x) { return rotr32(x, 7) ^ rotr32(x, 18) ^ (x >> 3); }
+AHV_HD uint32_t sig1(uint32_t x) { return rotr32(x, 17) ^ rotr32(x, 19) ^ (x >> 10); }
+AHV_HD uint32_t Ch(uint32_t e, uint32_t f, uint32_t g) { return g ^ (e & (f ^ g)); }          // one LOP3
+AHV_HD uint32_t Maj(uint32_t a, uint32_t b, uint32_t c) { return (a & b) | (c & (a | b)); }   // one LOP3
+
+struct KW64 {
+    uint32_t v[64];
+};
+
+constexpr uint32_t K256_TABLE[64] = {
+    0x428a2f98u, 0x71374491u, 0xb5c0fbcfu, 0xe9b5dba5u, 0x3956c25bu, 0x59f111f1u, 0x923f82a4u, 0xab1c5ed5u,
+    0xd807aa98u, 0x12835b01u, 0x243185beu, 0x550c7dc3u, 0x72be5d74u, 0x80deb1feu, 0x9bdc06a7u, 0xc19bf174u,
+    0xe49b69c1u, 0xefbe4786u, 0x0fc19dc6u, 0x240ca1ccu, 0x2de92c6fu, 0x4a7484aau, 0x5cb0a9dcu, 0x76f988dau,
+    0x983e5152u, 0xa831c66du, 0xb00327c8u, 0xbf597fc7u, 0xc6e00bf3u, 0xd5a79147u, 0x06ca6351u, 0x14292967u,
+    0x27b70a85u, 0x2e1b2138u, 0x4d2c6dfcu, 0x53380d13u, 0x650a7354u, 0x766a0abbu, 0x81c2c92eu, 0x92722c85u,
+    0xa2bfe8a1u, 0xa81a664bu, 0xc24b8b70u, 0xc76c51a3u, 0xd192e819u, 0xd6990624u, 0xf40e3585u, 0x106aa070u,
+    0x19a4c116u, 0x1e376c08u, 0x2748774cu, 0x34b0bcb5u, 0x391c0cb3u, 0x4ed8aa4au, 0x5b9cca4fu, 0x682e6ff3u,
+    0x748f82eeu, 0x78a5636fu, 0x84c87814u, 0x8cc70208u, 0x90befffau, 0xa4506cebu, 0xbef9a3f7u, 0xc67178f2u};
+
+constexpr uint32_t c_rotr(uint32_t x, int n) { return (x >> n) | (x << (32 - n)); }
+
+// K[t] + W[t] for a block that holds only padding: 0x80 then zeros then the bit length.
+// (block 3 of a 128-byte node message: bitlen = 1024; block 5 of a 256-byte delta: 2048)
+constexpr KW64 make_kw_pad(uint64_t bitlen)
+{
+    uint32_t w[64] = {};
+    w[0] = 0x80000000u;
+    w[14] = (uint32_t)(bitlen >> 32);
+    w[15] = (uint32_t)bitlen;
+    for (int t = 16; t < 64; ++t) {
+        uint32_t s0 = c_rotr(w[t - 15], 7) ^ c_rotr(w[t - 15], 18) ^ (w[t - 15] >> 3);
+        uint32_t s1 = c_rotr(w[t - 2], 17) ^ c_rotr(w[t - 2], 19) ^ (w[t - 2] >> 10);
+        w[t] = w[t - 16] + s0 + w[t - 7] + s1;
+    }
+    KW64 r = {};
+    for (int t = 0; t < 64; ++t) r.v[t] = w[t] + K256_TABLE[t];
+    return r;
+}
+
+AHV_HD void sha256_init(uint32_t st[8])
+{
+    st[0] = 0x6a09e667u; st[1] = 0xbb67ae85u; st[2] = 0x3c6ef372u; st[3] = 0xa54ff53au;
+    st[4] = 0x510e527fu; st[5] = 0x9b05688cu; st[6] = 0x1f83d9abu; st[7] = 0x5be0cd19u;
+}
+
+#define AHV_K256_LIST                                                                                       \
+    0x428a2f98u, 0x71374491u, 0xb5c0fbcfu, 0xe9b5dba5u, 0x3956c25bu, 0x59f111f1u, 0x923f82a4u, 0xab1c5ed5u, \
+    0xd807aa98u, 0x12835b01u, 0x243185beu, 0x550c7dc3u, 0x72be5d74u, 0x80deb1feu, 0x9bdc06a7u, 0xc19bf174u, \
+    0xe49b69c1u, 0xefbe4786u, 0x0fc19dc6u, 0x240ca1ccu, 0x2de92c6fu, 0x4a7484aau, 0x5cb0a9dcu, 0x76f988dau, \
+    0x983e5152u, 0xa831c66du, 0xb00327c8u, 0xbf597fc7u, 0xc6e00bf3u, 0xd5a79147u, 0x06ca6351u, 0x14292967u, \
+    0x27b70a85u, 0x2e1b2138u, 0x4d2c6dfcu, 0x53380d13u, 0x650a7354u, 0x766a0abbu, 0x81c2c92eu, 0x92722c85u, \
+    0xa2bfe8a1u, 0xa81a664bu, 0xc24b8b70u, 0xc76c51a3u, 0xd192e819u, 0xd6990624u, 0xf40e3585u, 0x106aa070u, \
+    0x19a4c116u, 0x1e376c08u, 0x2748774cu, 0x34b0bcb5u, 0x391c0cb3u, 0x4ed8aa4au, 0x5b9cca4fu, 0x682e6ff3u, \
+    0x748f82eeu, 0x78a5636fu, 0x84c87814u, 0x8cc70208u, 0x90befffau, 0xa4506cebu, 0xbef9a3f7u, 0xc67178f2u
+
+// One SHA-256 round on rotating names (no register moves after unrolling).
+#define AHV_ROUND(a, b, c, d, e, f, g, h, kw)                              \
+    {                                                                      \
+        uint32_t t1_ = (h) + Sig1(e) + Ch(e, f, g) + (kw);                 \
+        (d) += t1_;                                                        \
+        (h) = t1_ + Sig0(a) + Maj(a, b, c);                                \
+    }
+
+// Compress one 64-byte block given as 16 big-endian words.  w[] is consumed
+// (rolling 16-word schedule kept in registers).
+AHV_HD void sha256_compress(uint32_t st[8], uint32_t w[16])
+{
+    const uint32_t K[64] = {AHV_K256_LIST};
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t += 8) {
+        if (t >= 16) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j;
+                w[i & 15] += sig1(w[(i - 2) & 15]) + w[(i - 7) & 15] + sig0(w[(i - 15) & 15]);
+            }
+        }
+        AHV_ROUND(a, b, c, d, e, f, g, h, K[t + 0] + w[(t + 0) & 15])
+        AHV_ROUND(h, a, b, c, d, e, f, g, K[t + 1] + w[(t + 1) & 15])
+        AHV_ROUND(g, h, a, b, c, d, e, f, K[t + 2] + w[(t + 2) & 15])
+        AHV_ROUND(f, g, h, a, b, c, d, e, K[t + 3] + w[(t + 3) & 15])
+        AHV_ROUND(e, f, g, h, a, b, c, d, K[t + 4] + w[(t + 4) & 15])
+        AHV_ROUND(d, e, f, g, h, a, b, c, K[t + 5] + w[(t + 5) & 15])
+        AHV_ROUND(c, d, e, f, g, h, a, b, K[t + 6] + w[(t + 6) & 15])
+        AHV_ROUND(b, c, d, e, f, g, h, a, K[t + 7] + w[(t + 7) & 15])
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+
+// Compress a block whose K+W values are known constants (padding-only block).
+// kw may live in registers, constant memory or kernel parameters.
+template <class KWT>
+AHV_HD void sha256_compress_kw(uint32_t st[8], const KWT &kw)
+{
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t += 8) {
+        AHV_ROUND(a, b, c, d, e, f, g, h, kw.v[t + 0])
+        AHV_ROUND(h, a, b, c, d, e, f, g, kw.v[t + 1])
+        AHV_ROUND(g, h, a, b, c, d, e, f, kw.v[t + 2])
+        AHV_ROUND(f, g, h, a, b, c, d, e, kw.v[t + 3])
+        AHV_ROUND(e, f, g, h, a, b, c, d, kw.v[t + 4])
+        AHV_ROUND(d, e, f, g, h, a, b, c, kw.v[t + 5])
+        AHV_ROUND(c, d, e, f, g, h, a, b, kw.v[t + 6])
+        AHV_ROUND(b, c, d, e, f, g, h, a, kw.v[t + 7])
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+
+// ---------------------------------------------------------------- hex expansion
+// 4 nibble-valued bytes -> 4 lowercase hex ASCII bytes.
+AHV_HD uint32_t nib2ascii(uint32_t x)
+{
+    uint32_t m = ((x + 0x06060606u) >> 4) & 0x01010101u;   // 1 where nibble >= 10
+    return x + 0x30303030u + m * 0x27u;                    // '0'+n  or  'a'+n-10
+}
+
+// one state word (8 nibbles) -> two big-endian message words of ASCII hex
+AHV_HD void hex_expand(uint32_t v, uint32_t &w0, uint32_t &w1)
+{
+    uint32_t hi = nib2ascii((v >> 4) & 0x0f0f0f0fu);   // chars of nibbles 7,5,3,1
+    uint32_t lo = nib2ascii(v & 0x0f0f0f0fu);          // chars of nibbles 6,4,2,0
+    w0 = prmt(hi, lo, 0x3726u);                        // n7 n6 n5 n4
+    w1 = prmt(hi, lo, 0x1504u);                        // n3 n2 n1 n0
+}
+
+// audit/delta.py:130 : sha256((left_hex + right_hex).encode()) on state-word digests.
+AHV_HD void merkle_node(const uint32_t l[8], const uint32_t r[8], uint32_t out[8])
+{
+    uint32_t st[8], w[16];
+    sha256_init(st);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) hex_expand(l[i], w[2 * i], w[2 * i + 1]);
+    sha256_compress(st, w);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) hex_expand(r[i], w[2 * i], w[2 * i + 1]);
+    sha256_compress(st, w);
+    constexpr KW64 kw = make_kw_pad(1024);
+    sha256_compress_kw(st, kw);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) out[i] = st[i];
+}
+
+// ---------------------------------------------------------------- digest <-> memory
+struct alignas(16) U4 {
+    uint32_t x, y, z, w;
+};
+
+// state words -> the 32 raw digest bytes at a 16-byte aligned address
+AHV_HD void store_digest(uint8_t *dst, const uint32_t st[8])
+{
+    U4 *p = reinterpret_cast<U4 *>(dst);
+    U4 a = {bswap32(st[0]), bswap32(st[1]), bswap32(st[2]), bswap32(st[3])};
+    U4 b = {bswap32(st[4]), bswap32(st[5]), bswap32(st[6]), bswap32(st[7])};
+    p[0] = a;
+    p[1] = b;
+}
+
+AHV_HD void load_digest(const uint8_t *src, uint32_t st[8])
+{
+    const U4 *p = reinterpret_cast<const U4 *>(src);
+    U4 a = p[0], b = p[1];
+    st[0] = bswap32(a.x); st[1] = bswap32(a.y); st[2] = bswap32(a.z); st[3] = bswap32(a.w);
+    st[4] = bswap32(b.x); st[5] = bswap32(b.y); st[6] = bswap32(b.z); st[7] = bswap32(b.w);
+}
+
+AHV_HD bool digest_equal_mem(const uint8_t *src, const uint32_t st[8])
+{
+    uint32_t p[8];
+    load_digest(src, p);
+    uint32_t diff = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) diff |= p[i] ^ st[i];
+    return diff == 0;
+}
+
+// ---------------------------------------------------------------- whole messages
+// Word loader over an arbitrarily aligned byte string.  Reads only 4-byte aligned
+// words that contain at least one byte of [p, p+len); never touches memory past the
+// aligned word holding the last message byte.
+struct MsgReader {
+    const uint32_t *q;   // aligned base
+    uint32_t a;          // p & 3
+    uint32_t sel;        // PRMT selector doing alignment + big-endian swap in one op
+    AHV_HD void init(const uint8_t *p)
+    {
+        a = (uint32_t)(reinterpret_cast<uintptr_t>(p) & 3u);
+        q = reinterpret_cast<const uint32_t *>(p - a);
+        sel = 0x0123u + 0x1111u * a;
+    }
+};
+
+// SHA-256 of len bytes at p (any alignment).  One compress copy: full blocks take the
+// fast word path, the final one or two blocks build padding per word.
+AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8])
+{
+    MsgReader rd;
+    rd.init(p);
+    sha256_init(st);
+    const uint64_t nfull = len >> 6;
+    const uint32_t rem = (uint32_t)(len & 63u);
+    const uint64_t nblk = nfull + ((rem + 9u > 64u) ? 2u : 1u);
+    const bool aligned16 = ((reinterpret_cast<uintptr_t>(p) & 15u) == 0);
+    for (uint64_t b = 0; b < nblk; ++b) {
+        uint32_t w[16];
+        const uint32_t *qb = rd.q + 16 * b;
+        if (b < nfull) {
+            if (aligned16) {
+                const U4 *q4 = reinterpret_cast<const U4 *>(qb);
+                U4 v0 = q4[0], v1 = q4[1], v2 = q4[2], v3 = q4[3];
+                w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
+                w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
+                w[8] = bswap32(v2.x); w[9] = bswap32(v2.y); w[10] = bswap32(v2.z); w[11] = bswap32(v2.w);
+                w[12] = bswap32(v3.x); w[13] = bswap32(v3.y); w[14] = bswap32(v3.z); w[15] = bswap32(v3.w);
+            } else {
+                uint32_t x[17];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) x[j] = qb[j];
+                x[16] = rd.a ? qb[16] : 0u;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) w[j] = prmt(x[j], x[j + 1], rd.sel);
+            }
+        } else {
+            // tail: byte position of word j relative to the start of the tail data
+            const uint32_t tb = (uint32_t)(b - nfull) * 64u;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const uint32_t pos = tb + 4u * j;
+                uint32_t v = 0;
+                if (pos < rem) {
+                    uint32_t x0 = qb[j];
+                    uint32_t x1 = (rd.a && pos + 4u - rd.a < rem) ? qb[j + 1] : 0u;
+                    v = prmt(x0, x1, rd.sel);
+                    const uint32_t nvalid = rem - pos;             // >= 1
+                    if (nvalid < 4u) {
+                        v &= 0xffffffffu << (32u - 8u * nvalid);
+                        v |= 0x80000000u >> (8u * nvalid);
+                    }
+                } else if (pos == rem) {
+                    v = 0x80000000u;
+                }
+                w[j] = v;
+            }
+            if (b == nblk - 1) {
+                const uint64_t bits = len << 3;
+                w[14] = (uint32_t)(bits >> 32);
+                w[15] = (uint32_t)bits;
+            }
+        }
+        sha256_compress(st, w);
+    }
+}
+
+}  // namespace ahv

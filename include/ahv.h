@@ -1,0 +1,230 @@
+/*
+ * ahv.h - C ABI of libahv_b200.so: the B200-native replacement for the one
+ * data-parallel hot path of imran-siddique/agent-hypervisor (Delta Audit
+ * Engine: SHA-256 leaf hashing, Merkle roots, chain verification; plus the
+ * sigma_eff + execution-ring gating pass).
+ *
+ * The reference has no FFI (it is pure Python); the interface each entry point
+ * replaces is therefore a Python method, cited as file:line under
+ * /root/reference/src/hypervisor/.  INTEGRATION.md shows the ctypes binding a
+ * maintainer would add on the reference side.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 (AHV_E_*) on error;
+ *     ahv_last_error() returns a thread-local message for the last failure.
+ *   - the caller owns every buffer it passes.  The library owns only the
+ *     device scratch attached to an ahv_ctx (one ctx per GPU per process).
+ *   - "host" entry points take HOST pointers, copy in/out themselves and
+ *     return after the results are in the caller's buffers.
+ *   - "_dev" entry points take DEVICE pointers, enqueue on the ctx stream and
+ *     return without synchronising (call ahv_sync).
+ *   - digests are raw 32-byte SHA-256 values (hashlib .digest() order).
+ *   - a packed arena is `uint8 arena[]` + `uint64 offsets[n+1]`; message i is
+ *     arena[offsets[i] .. offsets[i+1]).  Sessions are CSR ranges of message
+ *     indices: `uint64 session_rowptr[n_sessions+1]`.
+ *   - no CPU fallback exists: without a CUDA device ahv_create fails.
+ */
+#ifndef AHV_H
+#define AHV_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AHV_ABI_VERSION 1
+
+#define AHV_OK 0
+#define AHV_E_INVALID (-1)  /* bad argument */
+#define AHV_E_CUDA (-2)     /* CUDA runtime error (message has the detail) */
+#define AHV_E_NOMEM (-3)    /* device or pinned-host allocation failed */
+#define AHV_E_NODEVICE (-4) /* no usable CUDA device */
+#define AHV_E_TOOLARGE (-5) /* size beyond a documented limit */
+
+/* parent_kind values (host encoding of SemanticDelta.parent_hash, audit/delta.py:38) */
+#define AHV_PARENT_NONE 0  /* parent_hash is None */
+#define AHV_PARENT_HEX 1   /* 64 lowercase hex chars; raw 32 bytes in parent_digests */
+#define AHV_PARENT_OTHER 2 /* any other string: never equal to a hexdigest */
+
+/* action_flags bits (host encoding of ActionDescriptor, models.py:104-132) */
+#define AHV_ACT_ADMIN 1
+#define AHV_ACT_READ_ONLY 2
+#define AHV_ACT_REV_NONE 4
+
+/* RingEnforcer.check outcome codes, in the order rings/enforcer.py:58-128 tests them */
+#define AHV_REASON_GRANTED 0
+#define AHV_REASON_NEEDS_WITNESS 1
+#define AHV_REASON_RING1_SIGMA 2
+#define AHV_REASON_NEEDS_CONSENSUS 3
+#define AHV_REASON_RING2_SIGMA 4
+#define AHV_REASON_RING_INSUFFICIENT 5
+
+#define AHV_EXPIRY_NONE INT64_MAX /* VouchRecord.expiry is None (liability/vouching.py:30) */
+
+typedef struct ahv_ctx ahv_ctx;
+
+/* ------------------------------------------------------------------ context */
+int ahv_abi_version(void);
+const char *ahv_last_error(void);
+/* One context per GPU per process.  device = CUDA ordinal. */
+int ahv_create(int device, ahv_ctx **out_ctx);
+void ahv_destroy(ahv_ctx *ctx);
+int ahv_sync(ahv_ctx *ctx);
+/* sm_count, max SM clock (kHz), total device memory (bytes); any pointer may be NULL */
+int ahv_device_info(ahv_ctx *ctx, int *sm_count, int *sm_clock_khz, uint64_t *total_mem);
+/* cudaStream_t of the context, as void* (for callers that enqueue their own work) */
+void *ahv_stream(ahv_ctx *ctx);
+/* number of kernels this context has launched since creation */
+uint64_t ahv_launch_count(ahv_ctx *ctx);
+
+/* memory helpers so that callers without a CUDA binding can keep arenas resident */
+int ahv_dev_alloc(ahv_ctx *ctx, uint64_t bytes, void **out_dptr);
+int ahv_dev_free(ahv_ctx *ctx, void *dptr);
+int ahv_host_alloc(ahv_ctx *ctx, uint64_t bytes, void **out_hptr); /* pinned */
+int ahv_host_free(ahv_ctx *ctx, void *hptr);
+int ahv_memcpy_h2d(ahv_ctx *ctx, void *dptr, const void *hptr, uint64_t bytes); /* async on ctx stream */
+int ahv_memcpy_d2h(ahv_ctx *ctx, void *hptr, const void *dptr, uint64_t bytes); /* async on ctx stream */
+int ahv_memset_dev(ahv_ctx *ctx, void *dptr, int value, uint64_t bytes);
+
+/* CUDA-event timers on the ctx stream (slot 0..63): start/stop bracket work, elapsed in ms */
+int ahv_timer_start(ahv_ctx *ctx, int slot);
+int ahv_timer_stop(ahv_ctx *ctx, int slot);
+int ahv_timer_elapsed_ms(ahv_ctx *ctx, int slot, float *out_ms); /* synchronises on the stop event */
+
+/* ------------------------------------------------------------------ audit path
+ *
+ * ahv_sha256_batch: digest[i] = SHA-256(message i).
+ *   replaces SemanticDelta.compute_hash's hashlib call, audit/delta.py:63,
+ *   applied to n pre-images the host serialised per audit/delta.py:43-62.
+ *   offsets may be NULL when fixed_len > 0: message i = arena[i*fixed_len ..).
+ */
+int ahv_sha256_batch(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t n,
+                     uint64_t fixed_len, uint8_t *out_digests /* n*32 */);
+int ahv_sha256_batch_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes,
+                         const uint64_t *d_offsets, uint64_t n, uint64_t fixed_len,
+                         uint8_t *d_out_digests);
+
+/*
+ * ahv_merkle_roots: one Merkle root per session over its leaf digests.
+ *   replaces DeltaEngine.compute_merkle_root, audit/delta.py:117-134:
+ *   node = SHA-256(hex(left) || hex(right)) (128 ASCII bytes), odd level
+ *   duplicates its last node (:129), one leaf -> root is the leaf (:125),
+ *   no leaves -> None (:119-120), reported as out_empty[s] = 1 and a zero root.
+ *   max_session_leaves: the largest session size (0 = let the library find it;
+ *   the _dev variant then synchronises once).
+ */
+int ahv_merkle_roots(ahv_ctx *ctx, const uint8_t *digests /* n*32 */, const uint64_t *session_rowptr,
+                     uint64_t n_sessions, uint8_t *out_roots /* S*32 */, uint8_t *out_empty /* S */);
+int ahv_merkle_roots_dev(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_session_rowptr,
+                         uint64_t n_sessions, uint64_t n_leaves, uint64_t max_session_leaves,
+                         uint8_t *d_out_roots, uint8_t *d_out_empty);
+
+/*
+ * ahv_commit: fused leaf hashing + Merkle roots (what Hypervisor.terminate_session
+ * needs at core.py:204 for many sessions at once): audit/delta.py:63 then :117-134.
+ *   out_digests may be NULL.  uniform_leaves > 0 states that every session has
+ *   exactly that many leaves (session_rowptr may then be NULL).
+ */
+int ahv_commit(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
+               const uint64_t *session_rowptr, uint64_t n_sessions, uint64_t uniform_leaves,
+               uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty);
+int ahv_commit_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                   uint64_t fixed_len, const uint64_t *d_session_rowptr, uint64_t n_sessions,
+                   uint64_t n_leaves, uint64_t uniform_leaves, uint64_t max_session_leaves,
+                   uint8_t *d_out_digests, uint8_t *d_out_roots, uint8_t *d_out_empty);
+
+/*
+ * ahv_verify_chains: DeltaEngine.verify_chain for many sessions, audit/delta.py:136-152.
+ *   Effective rule of the reference (compute_hash at :140 overwrites delta_hash, so
+ *   the test at :141 cannot fail): the first delta's parent must be None (:145-147)
+ *   and every later parent must equal the hash recomputed for the delta before it
+ *   (:149).  out_verdict[s] = 1/0, out_first_bad[s] = index inside the session of the
+ *   first failing delta or -1.  out_digests (optional) receives every recomputed
+ *   leaf digest (the reference writes those back into delta_hash for indices
+ *   <= first_bad).  If expected_roots is given, the Merkle root is rebuilt from the
+ *   recomputed digests and compared on the device (CommitmentEngine.verify,
+ *   audit/commitment.py:59-64): out_root_match[s] = 1/0.  out_roots optional.
+ */
+int ahv_verify_chains(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
+                      const uint8_t *parent_digests /* n*32 */, const uint8_t *parent_kind /* n */,
+                      const uint64_t *session_rowptr, uint64_t n_sessions, uint64_t uniform_leaves,
+                      const uint8_t *expected_roots /* S*32 or NULL */, uint8_t *out_verdict,
+                      int64_t *out_first_bad, uint8_t *out_digests, uint8_t *out_roots,
+                      uint8_t *out_root_match);
+int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes,
+                          const uint64_t *d_offsets, uint64_t fixed_len, const uint8_t *d_parent_digests,
+                          const uint8_t *d_parent_kind, const uint64_t *d_session_rowptr,
+                          uint64_t n_sessions, uint64_t n_leaves, uint64_t uniform_leaves,
+                          uint64_t max_session_leaves, const uint8_t *d_expected_roots,
+                          uint8_t *d_out_verdict, int64_t *d_out_first_bad, uint8_t *d_out_digests,
+                          uint8_t *d_out_roots, uint8_t *d_out_root_match);
+
+/*
+ * ahv_chain_capture: session-parallel replay of DeltaEngine.capture's chaining,
+ * audit/delta.py:101-114: for each session, in order, hash delta i, write its 64 hex
+ * chars into delta i+1's pre-image at byte hexpos[i+1] (the "parent_hash" value the
+ * host left as a 64-char placeholder), then continue.  hexpos[i] = UINT32_MAX for a
+ * delta whose parent is null.  The arena is patched in place; digests and the parent
+ * side arrays (for ahv_verify_chains) are produced.
+ */
+int ahv_chain_capture(ahv_ctx *ctx, uint8_t *arena, const uint64_t *offsets, const uint32_t *hexpos,
+                      const uint64_t *session_rowptr, uint64_t n_sessions, uint8_t *out_digests,
+                      uint8_t *out_parent_digests, uint8_t *out_parent_kind);
+int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                          const uint32_t *d_hexpos, const uint64_t *d_session_rowptr, uint64_t n_sessions,
+                          uint64_t n_leaves, uint8_t *d_out_digests, uint8_t *d_out_parent_digests,
+                          uint8_t *d_out_parent_kind);
+
+/* ------------------------------------------------------------------ liability / rings
+ *
+ * ahv_sigma_eff_rings: VouchingEngine.compute_sigma_eff for every agent of one session
+ * (liability/vouching.py:128-151) over a CSR of vouch records grouped by vouchee in
+ * insertion order (:186-197), then ExecutionRing.from_sigma_eff (models.py:34-42) and
+ * RingEnforcer.should_demote (rings/enforcer.py:134-137).
+ *   record e contributes iff active[e] && !(expiry[e] != AHV_EXPIRY_NONE && now > expiry[e])
+ *   (vouching.py:34-38; times in microseconds since the epoch).
+ *   sum is sequential fp64 from 0.0; sigma_eff = sigma + (omega * sum), two roundings;
+ *   result = (1.0 < x) ? 1.0 : x  (Python min(), NaN kept).
+ *   out_near[a] = 1 when sigma_eff lies within 1e-6 (relative) of 0.60 or 0.95.
+ */
+int ahv_sigma_eff_rings(ahv_ctx *ctx, const uint32_t *rowptr /* A+1 */, const double *bonded,
+                        const uint8_t *active, const int64_t *expiry, int64_t now, const double *sigma,
+                        const double *omega, const uint8_t *consensus, const uint8_t *current_ring,
+                        uint64_t n_agents, double *out_sigma_eff, uint8_t *out_ring, uint8_t *out_demote,
+                        uint8_t *out_near);
+int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *d_bonded,
+                            const uint8_t *d_active, const int64_t *d_expiry, int64_t now,
+                            const double *d_sigma, const double *d_omega, const uint8_t *d_consensus,
+                            const uint8_t *d_current_ring, uint64_t n_agents, double *d_out_sigma_eff,
+                            uint8_t *d_out_ring, uint8_t *d_out_demote, uint8_t *d_out_near);
+
+/*
+ * ahv_ring_check: RingEnforcer.check for n (agent, action) pairs, rings/enforcer.py:44-128,
+ * with ActionDescriptor.required_ring (models.py:122-132) derived from action_flags.
+ */
+int ahv_ring_check(ahv_ctx *ctx, const uint8_t *agent_ring, const uint8_t *action_flags,
+                   const double *sigma_eff, const uint8_t *consensus, const uint8_t *witness, uint64_t n,
+                   uint8_t *out_allowed, uint8_t *out_reason, uint8_t *out_required);
+int ahv_ring_check_dev(ahv_ctx *ctx, const uint8_t *d_agent_ring, const uint8_t *d_action_flags,
+                       const double *d_sigma_eff, const uint8_t *d_consensus, const uint8_t *d_witness,
+                       uint64_t n, uint8_t *d_out_allowed, uint8_t *d_out_reason, uint8_t *d_out_required);
+
+/* ------------------------------------------------------------------ measurement
+ * ahv_int_peak: register-only kernel issuing the SHA-256 instruction mix
+ * (funnel shifts : 3-input logic : 3-input adds = 6:4:4 per round) on every SM;
+ * returns the measured rate in 32-bit integer thread-instructions per second.
+ * No counterpart in the reference (it is the roofline denominator of SURVEY 8d).
+ *   mode 0: ALU-pipe only (SHF/LOP3/IADD3)   mode 1: adds issued as IMAD on the FMA pipe
+ */
+int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, float *out_ms);
+
+/* Selects a kernel variant for experiments (bench/tuning only).  key names are
+ * documented in DESIGN.md; unknown keys return AHV_E_INVALID. */
+int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AHV_H */

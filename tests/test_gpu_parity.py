@@ -1,0 +1,392 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle and the golden
+vectors produced by the real reference.  Bit-exact for digests, roots, verdicts, rings;
+sigma_eff bit-identical (well inside the 1e-6 relative tolerance north_star allows)."""
+
+import hashlib
+
+import numpy as np
+import pytest
+
+import recipes
+import workloads
+from helpers import chain_preimages, config2_session, hexes, pack_sessions
+from oracle import audit_oracle as ao
+from oracle import coracle as co
+from oracle import liability_oracle as lo
+
+pytestmark = pytest.mark.gpu
+
+SIGMA_REL_TOL = 1e-6   # BASELINE.json north_star; we additionally assert bit equality
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from agent_hypervisor_b200 import get_context
+    return get_context()
+
+
+def _tight(msgs):
+    offs = np.zeros(len(msgs) + 1, dtype=np.uint64)
+    np.cumsum([len(m) for m in msgs], out=offs[1:])
+    arena = np.frombuffer(b"".join(msgs), dtype=np.uint8) if offs[-1] else np.zeros(0, np.uint8)
+    return arena, offs
+
+
+# ------------------------------------------------------------------ SHA-256
+def test_sha256_known_answers(ctx, audit_golden):
+    msgs = [v["msg"].encode() for v in audit_golden["nist"]]
+    want = [v["digest"] for v in audit_golden["nist"]]
+    for v in audit_golden["sha_kats"]:
+        msgs.append(recipes.kat_message(v["seed"], v["len"]))
+        want.append(v["digest"])
+    nk = audit_golden["node_kat"]
+    msgs.append((nk["left"] + nk["right"]).encode()); want.append(nk["digest"])
+    arena, offs = _tight(msgs)           # tight packing -> every byte alignment occurs
+    assert hexes(ctx.sha256_batch(arena, offs)) == want
+
+
+@pytest.mark.parametrize("sort", [0, 1])
+def test_sha256_random_lengths_vs_oracle(ctx, sort):
+    rng = np.random.default_rng(11)
+    lens = np.concatenate([np.arange(0, 260), rng.integers(0, 3000, 3000), [16383, 16384, 16385, 70000]])
+    rng.shuffle(lens)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    arena = rng.integers(0, 256, int(offs[-1]), dtype=np.uint8)
+    ctx.set_option("sort", sort)
+    try:
+        got = ctx.sha256_batch(arena, offs)
+    finally:
+        ctx.set_option("sort", 1)
+    assert np.array_equal(got, co.sha256_batch(arena, offs))
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("flen", [64, 128, 256, 320, 100, 55, 1])
+def test_sha256_fixed_len(ctx, flen, variant):
+    rng = np.random.default_rng(flen)
+    n = 2500 + flen % 7            # partial last warp
+    arena = rng.integers(0, 256, n * flen, dtype=np.uint8)
+    ctx.set_option("fixed_variant", variant)
+    try:
+        got = ctx.sha256_batch(arena, None, fixed_len=flen, n=n)
+    finally:
+        ctx.set_option("fixed_variant", 0)
+    offs = (np.arange(n + 1) * flen).astype(np.uint64)
+    assert np.array_equal(got, co.sha256_batch(arena, offs))
+
+
+def test_sha256_empty_batch(ctx):
+    assert ctx.sha256_batch(np.zeros(0, np.uint8), np.zeros(1, np.uint64)).shape == (0, 32)
+
+
+# ------------------------------------------------------------------ Merkle
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 15, 16, 17, 31, 33, 63, 64, 65, 125, 250, 1000])
+def test_golden_session_commit(ctx, audit_golden, n):
+    g = audit_golden["golden_session"][str(n)]
+    arena, offs, par, kind, rp = pack_sessions([chain_preimages(recipes.golden_session(n))])
+    digs, roots, empty = ctx.commit(arena, offs, rp)
+    if n == 0:
+        assert empty[0] == 1 and g["root"] is None
+        return
+    assert empty[0] == 0 and roots[0].tobytes().hex() == g["root"]
+    assert hexes(digs)[-1] == g["last_leaf"]
+    if "leaves" in g:
+        assert hexes(digs) == g["leaves"]
+    r2, e2 = ctx.merkle_roots(digs, rp)           # tree alone over the same digests
+    assert r2[0].tobytes().hex() == g["root"] and e2[0] == 0
+
+
+def test_merkle_sizes_vs_oracle(ctx):
+    """Every size through the in-CTA top kernel (<=256) and the global level steps (>256), ragged."""
+    rng = np.random.default_rng(5)
+    sizes = list(range(0, 70)) + [127, 128, 129, 255, 256, 257, 258, 511, 512, 513, 1000, 1023, 1024, 1025, 2049, 5000]
+    rng.shuffle(sizes)
+    rp = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+    digs = rng.integers(0, 256, (int(rp[-1]), 32), dtype=np.uint8)
+    roots, empty = ctx.merkle_roots(digs, rp)
+    wr, we = co.merkle_roots(digs, rp)
+    assert np.array_equal(empty, we) and np.array_equal(roots, wr)
+    # a subset checked against the hashlib restatement of delta.py:117-134 as well
+    pr, pe = ao.merkle_roots(digs[: int(rp[40])], rp[:41])
+    assert np.array_equal(roots[:40], pr) and np.array_equal(empty[:40], pe)
+
+
+def test_merkle_single_big_tree(ctx):
+    rng = np.random.default_rng(6)
+    n = 100_003
+    digs = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    rp = np.array([0, n], dtype=np.uint64)
+    roots, _ = ctx.merkle_roots(digs, rp)
+    wr, _ = co.merkle_roots(digs, rp)
+    assert np.array_equal(roots, wr)
+
+
+def test_random_sessions_commit_and_verify(ctx, audit_golden):
+    rs = audit_golden["random_sessions"]
+    sessions = [chain_preimages(recipes.random_session(r["seed"])) for r in rs]
+    arena, offs, par, kind, rp = pack_sessions(sessions)
+    digs, roots, empty = ctx.commit(arena, offs, rp)
+    res = ctx.verify_chains(arena, offs, par, kind, rp, expected_roots=roots)
+    for s, r in enumerate(rs):
+        if r["n"] == 0:
+            assert empty[s] == 1
+            assert res["root_match"][s] == 0      # no commitment for an empty session
+        else:
+            assert roots[s].tobytes().hex() == r["root"], r["seed"]
+            assert res["root_match"][s] == 1
+        assert bool(res["verdict"][s]) == r["verify"] and res["first_bad"][s] == -1
+    assert np.array_equal(res["digests"], digs)
+    assert np.array_equal(digs, co.sha256_batch(arena, offs))
+
+
+# ------------------------------------------------------------------ verify_chain semantics
+def test_verify_kats(ctx, audit_golden):
+    from test_oracle_golden import _tampered
+    sessions, meta = [], []
+    for k in audit_golden["verify_kats"]:
+        pre, par, stored = _tampered(k["name"], k["n"])
+        sessions.append(list(zip(pre, par)))
+        meta.append((k, pre, par))
+    arena, offs, parents, kind, rp = pack_sessions(sessions)
+    res = ctx.verify_chains(arena, offs, parents, kind, rp)
+    for s, (k, pre, par) in enumerate(meta):
+        verdict, first_bad, _ = ao.verify_chain_session(pre, par)
+        assert bool(res["verdict"][s]) == k["verdict"] == verdict, k["name"]
+        assert res["first_bad"][s] == first_bad, k["name"]
+
+
+def test_verify_random_tampering_vs_oracle(ctx):
+    rng = np.random.default_rng(21)
+    sessions = []
+    for s in range(300):
+        n = int(rng.integers(0, 30))
+        sess = chain_preimages(recipes.golden_session(n))
+        pre = [p for p, _ in sess]; par = [q for _, q in sess]
+        for _ in range(int(rng.integers(0, 3))):
+            if n == 0: break
+            i = int(rng.integers(0, n)); what = int(rng.integers(0, 4))
+            if what == 0: pre[i] = pre[i] + b" "
+            elif what == 1: par[i] = None
+            elif what == 2: par[i] = "e" * 64
+            else: par[i] = "zz"
+        sessions.append(list(zip(pre, par)))
+    arena, offs, parents, kind, rp = pack_sessions(sessions)
+    res = ctx.verify_chains(arena, offs, parents, kind, rp)
+    v, fb, d = co.verify_chains(arena, offs, parents, kind, rp)
+    assert np.array_equal(res["verdict"], v) and np.array_equal(res["first_bad"], fb)
+    assert np.array_equal(res["digests"], d)
+
+
+# ------------------------------------------------------------------ config 2 shape (fixed 256 B, uniform sessions)
+@pytest.mark.parametrize("variant", [0, 1])
+def test_config2_small_vs_golden_and_oracle(ctx, audit_golden, variant):
+    S, L = 40, 1000
+    first = 1200
+    arena = np.zeros(S * L * 256, np.uint8)
+    offs, hexpos, rp = workloads.config2_fill(arena, first, S, L)
+    digs, par, kind = ctx.chain_capture(arena, offs, hexpos, rp)          # patches arena in place
+    g = audit_golden["config2"]["1234"]
+    s = 1234 - first
+    assert digs[s * L + L - 1].tobytes().hex() == g["last_leaf"]
+    assert digs[s * L].tobytes().hex() == g["leaf0"]
+    want_sess = config2_session(1234)
+    assert arena[s * L * 256:(s + 1) * L * 256].tobytes() == b"".join(p for p, _ in want_sess)
+    ctx.set_option("fixed_variant", variant)
+    try:
+        d2, roots, empty = ctx.commit(arena, None, None, fixed_len=256, uniform_leaves=L, n_sessions=S)
+        res = ctx.verify_chains(arena, None, par, kind, None, fixed_len=256, uniform_leaves=L, n_sessions=S,
+                                expected_roots=roots)
+    finally:
+        ctx.set_option("fixed_variant", 0)
+    assert roots[s].tobytes().hex() == g["root"]
+    assert np.array_equal(d2, digs) and np.array_equal(d2, co.sha256_batch(arena, offs))
+    wr, _ = co.merkle_roots(d2, rp)
+    assert np.array_equal(roots, wr)
+    assert res["verdict"].all() and (res["first_bad"] == -1).all() and res["root_match"].all()
+    # the generic (offsets + rowptr) path must agree with the fixed/uniform fast path
+    d3, r3, _ = ctx.commit(arena, offs, rp)
+    assert np.array_equal(d3, d2) and np.array_equal(r3, roots)
+    # tamper: one byte in the middle of session 7, and the LAST delta of session 9 (not detectable)
+    bad = arena.copy()
+    bad[(7 * L + 500) * 256 + 20] ^= 1
+    bad[(9 * L + L - 1) * 256 + 20] ^= 1
+    res = ctx.verify_chains(bad, None, par, kind, None, fixed_len=256, uniform_leaves=L, n_sessions=S,
+                            expected_roots=roots)
+    assert list(np.nonzero(res["verdict"] == 0)[0]) == [7] and res["first_bad"][7] == 501
+    assert list(np.nonzero(res["root_match"] == 0)[0]) == [7, 9]      # the root compare does see both
+
+
+def test_chain_capture_vs_python_chain(ctx):
+    sessions = [recipes.golden_session(n) for n in (0, 1, 2, 5, 33)]
+    blobs, offs, hexpos, rp = [], [0], [], [0]
+    for fields in sessions:
+        for i, f in enumerate(fields):
+            pre = ao.canonical_preimage(f["delta_id"], f["turn_id"], f["session_id"], f["agent_did"],
+                                        f["timestamp"].isoformat(), f["changes"], None if i == 0 else "0" * 64)
+            hexpos.append(0xFFFFFFFF if i == 0 else pre.index(b'"parent_hash": "') + 16)
+            blobs.append(pre); offs.append(offs[-1] + len(pre))
+        rp.append(len(hexpos))
+    arena = np.frombuffer(b"".join(blobs), dtype=np.uint8).copy()
+    digs, par, kind = ctx.chain_capture(arena, np.array(offs, np.uint64), np.array(hexpos, np.uint32),
+                                        np.array(rp, np.uint64))
+    want = [chain_preimages(f) for f in sessions]
+    assert arena.tobytes() == b"".join(p for s in want for p, _ in s)
+    wa, wo, wp, wk, wr = pack_sessions(want)
+    assert np.array_equal(par, wp) and np.array_equal(kind, wk)
+    assert np.array_equal(digs, co.sha256_batch(wa, wo))
+
+
+# ------------------------------------------------------------------ drop-in classes
+def test_delta_engine_dropin(ctx):
+    from agent_hypervisor_b200 import DeltaEngine, VFSChange
+    from agent_hypervisor_b200.audit.packing import canonical_preimage
+    e = DeltaEngine("session:test-audit")
+    assert e.compute_merkle_root() is None and e.verify_chain()
+    for i in range(10):
+        d = e.capture("did:a", [VFSChange(path=f"/f{i}.txt", operation="add", content_hash=f"h{i}")])
+        assert d.turn_id == i + 1
+        assert d.delta_hash == hashlib.sha256(canonical_preimage(d)).hexdigest()
+    ds = e.deltas
+    assert ds[0].parent_hash is None and all(ds[i].parent_hash == ds[i - 1].delta_hash for i in range(1, 10))
+    root = e.compute_merkle_root()
+    assert root == ao.merkle_root_hex([d.delta_hash for d in ds]) and len(root) == 64
+    assert e.verify_chain() and e.turn_count == 10
+    assert e.compute_merkle_root() == root                            # idempotent (e2e test :443-447)
+    e._deltas[9].agent_did = "did:evil"                               # last delta: NOT detected
+    assert e.verify_chain()
+    e._deltas[5].agent_did = "did:tampered"                           # e2e test :421-423
+    stale6 = e._deltas[6].delta_hash
+    assert not e.verify_chain()
+    assert e._deltas[5].delta_hash == hashlib.sha256(canonical_preimage(e._deltas[5])).hexdigest()
+    assert e._deltas[6].delta_hash == hashlib.sha256(canonical_preimage(e._deltas[6])).hexdigest()  # idx == first_bad
+    assert stale6 == e._deltas[6].delta_hash                           # delta 6 itself was not changed
+    # a delta_hash overwritten with a non-digest string still yields the reference's root
+    e2 = DeltaEngine("s2")
+    for i in range(5):
+        e2.capture("did:a", [])
+    e2._deltas[2].delta_hash = "deadbeef"
+    assert e2.compute_merkle_root() == ao.merkle_root_hex([d.delta_hash for d in e2._deltas])
+    e3 = DeltaEngine("s3"); e3.capture("did:a", [])
+    assert e3.compute_merkle_root() == e3._deltas[0].delta_hash
+
+
+def test_batch_auditor(ctx):
+    from agent_hypervisor_b200 import BatchAuditor, CommitmentEngine, DeltaEngine, VFSChange
+    engines = []
+    for s in range(20):
+        e = DeltaEngine(f"session:{s}")
+        for i in range(s):
+            e.capture("did:a", [VFSChange(path=f"/f{i}", operation="add")])
+        engines.append(e)
+    ba, ce = BatchAuditor(), CommitmentEngine()
+    roots = ba.commit_engines(engines, ce, ["did:a"])
+    for e, r in zip(engines, roots):
+        assert r == ao.merkle_root_hex([d.delta_hash for d in e._deltas])
+        assert (ce.get_commitment(e.session_id) is None) == (r is None)
+    engines[7]._deltas[3].agent_did = "did:evil"
+    assert ba.verify_engines(engines) == [s != 7 for s in range(20)]
+    res = ba.verify(ba.pack(engines), roots)
+    assert [bool(x) for x in res["root_match"]] == [s not in (0, 7) for s in range(20)]
+
+
+# ------------------------------------------------------------------ liability / rings
+def test_sigma_eff_golden_graphs(ctx, liability_golden):
+    from test_oracle_golden import graph_to_csr
+    for gr in liability_golden["graphs"]:
+        g = recipes.random_vouch_graph(gr["seed"], gr["A"], gr["E"])
+        rowptr, bonded, act, exp, now = graph_to_csr(g, gr["A"])
+        se, ring, dem, near = ctx.sigma_eff_rings(rowptr, bonded, act, exp, now, g["sigma"], g["omega"],
+                                                  g["consensus"], g["current_ring"])
+        want = np.array([float.fromhex(x) for x in gr["sigma_eff"]])
+        assert np.allclose(se, want, rtol=SIGMA_REL_TOL, atol=0) and np.array_equal(se, want)
+        assert list(ring) == gr["ring"] and [bool(x) for x in dem] == gr["demote"]
+
+
+def test_sigma_eff_config4_shape_vs_oracle(ctx):
+    g = workloads.config4_graph(50_000, 500_000)
+    got = ctx.sigma_eff_rings(g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"],
+                              g["consensus"], g["current_ring"])
+    want = co.sigma_eff_rings(g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"],
+                              g["consensus"], g["current_ring"])
+    rel = np.abs(got[0] - want[0]) / np.maximum(np.abs(want[0]), 1e-300)
+    assert rel.max() <= SIGMA_REL_TOL
+    assert np.array_equal(got[0], want[0])                 # sequential fp64, no FMA: bit-identical
+    for a, b in zip(got[1:], want[1:]):
+        assert np.array_equal(a, b)                        # rings, demote flags, near-threshold list
+
+
+def test_ring_check_grid_and_dropin(ctx, liability_golden):
+    from agent_hypervisor_b200 import ActionDescriptor, ExecutionRing, ReversibilityLevel, RingEnforcer, VouchingEngine
+    rows = liability_golden["checks"]
+    sig = lambda x: float("nan") if x == "nan" else float.fromhex(x)
+    flags = [(1 if c[0] else 0) | (2 if c[1] else 0) | (4 if c[2] == "none" else 0) for c in rows]
+    al, re, rq = ctx.ring_check([c[3] for c in rows], flags, [sig(c[4]) for c in rows], [c[5] for c in rows],
+                                [c[6] for c in rows])
+    assert list(al) == [c[7] for c in rows] and list(rq) == [c[8] for c in rows]
+    enf = RingEnforcer()
+    for c in rows[::37]:
+        act = ActionDescriptor("a", "n", "/x", reversibility=ReversibilityLevel(c[2]), is_read_only=bool(c[1]),
+                               is_admin=bool(c[0]))
+        r = enf.check(ExecutionRing(c[3]), act, sig(c[4]), bool(c[5]), bool(c[6]))
+        assert (int(r.allowed), int(r.required_ring.value), r.reason, int(r.requires_consensus),
+                int(r.requires_sre_witness)) == (c[7], c[8], c[9], c[10], c[11])
+        assert act.required_ring.value == c[8]
+    for r in liability_golden["ring_grid"]:
+        assert enf.compute_ring(sig(r["sigma"]), r["consensus"]).value == r["ring"]
+    assert enf.should_demote(ExecutionRing.RING_1_PRIVILEGED, 0.99)        # computed without consensus
+    assert not enf.should_demote(ExecutionRing.RING_2_STANDARD, 0.85)
+    # reference's own pinned points (tests/unit/test_liability.py:39-67)
+    pts = [float.fromhex(p["value"]) for p in liability_golden["pinned_points"]]
+    ve = VouchingEngine(); ve.vouch("did:h", "did:l", "s1", 0.9, bond_pct=0.2)
+    assert ve.compute_sigma_eff("did:l", "s1", 0.4, 0.5) == pts[0]
+    ve = VouchingEngine(); ve.vouch("did:h", "did:l", "s1", 1.0, bond_pct=0.8)
+    assert ve.compute_sigma_eff("did:l", "s1", 0.9, 1.0) == pts[1] == 1.0
+    ve = VouchingEngine(); ve.vouch("did:h1", "did:l", "s1", 0.9, bond_pct=0.2); ve.vouch("did:h2", "did:l", "s1", 0.8, bond_pct=0.2)
+    assert ve.compute_sigma_eff("did:l", "s1", 0.3, 0.5) == pts[2]
+    out = ve.compute_sigma_eff_batch("s1", ["did:l", "did:nobody"], [0.3, 0.6], [0.5, 0.5])
+    assert out["sigma_eff"][0] == pts[2] and out["sigma_eff"][1] == 0.6 and out["near_threshold"] == ["did:nobody"]
+
+
+# ------------------------------------------------------------------ full size (BASELINE config 2), properties
+def test_config2_full_size_properties(ctx):
+    """10k sessions x 1k x 256 B on the device: chain -> commit -> verify, checked through
+    size-independent properties plus a sample of sessions against the oracle."""
+    S, L, FL = 10_000, 1000, 256
+    n = S * L
+    arena = np.empty(n * FL, np.uint8)
+    offs, hexpos, rp = workloads.config2_fill(arena, 0, S, L)
+    d = {k: ctx.dev_alloc(v) for k, v in dict(arena=arena.nbytes, offs=offs.nbytes, hexpos=hexpos.nbytes,
+                                               rp=rp.nbytes, digs=32 * n, par=32 * n, kind=n, roots=32 * S,
+                                               roots2=32 * S, empty=S, verdict=S, fb=8 * S, match=S, digs2=32 * n).items()}
+    try:
+        ctx.h2d(d["arena"], arena); ctx.h2d(d["offs"], offs); ctx.h2d(d["hexpos"], hexpos); ctx.h2d(d["rp"], rp)
+        ctx.chain_capture_dev(d["arena"], arena.nbytes, d["offs"], d["hexpos"], d["rp"], S, n, d["digs"], d["par"], d["kind"])
+        ctx.commit_dev(d["arena"], arena.nbytes, 0, FL, 0, S, n, L, L, d["digs2"], d["roots"], d["empty"])
+        ctx.verify_chains_dev(d["arena"], arena.nbytes, 0, FL, d["par"], d["kind"], 0, S, n, L, L, d["roots"],
+                              d["verdict"], d["fb"], 0, d["roots2"], d["match"])
+        # generic path (offsets + rowptr, length-sorted var kernel, ragged tree) on the same data
+        roots3 = ctx.dev_alloc(32 * S)
+        ctx.commit_dev(d["arena"], arena.nbytes, d["offs"], 0, d["rp"], S, n, 0, L, 0, roots3, d["empty"])
+        h = {k: np.empty(sz, np.uint8) for k, sz in dict(digs=32 * n, digs2=32 * n, roots=32 * S, roots2=32 * S,
+                                                         verdict=S, match=S, roots3=32 * S).items()}
+        fb = np.empty(S, np.int64)
+        for k in ("digs", "digs2", "roots", "roots2", "verdict", "match"):
+            ctx.d2h(h[k], d[k])
+        ctx.d2h(h["roots3"], roots3); ctx.d2h(fb, d["fb"]); ctx.d2h(arena, d["arena"])
+        ctx.sync()
+        ctx.dev_free(roots3)
+    finally:
+        for p in d.values():
+            ctx.dev_free(p)
+    assert np.array_equal(h["digs"], h["digs2"])                    # capture digests == commit digests
+    assert h["verdict"].all() and (fb == -1).all() and h["match"].all()
+    assert np.array_equal(h["roots"], h["roots2"]) and np.array_equal(h["roots"], h["roots3"])
+    assert len({h["roots"][i * 32:(i + 1) * 32].tobytes() for i in range(S)}) == S   # all sessions distinct
+    rng = np.random.default_rng(1)
+    for s in rng.integers(0, S, 12):                                # sample vs the C oracle
+        sl = slice(int(s) * L * FL, (int(s) + 1) * L * FL)
+        o = (np.arange(L + 1) * FL).astype(np.uint64)
+        dg = co.sha256_batch(arena[sl], o)
+        assert np.array_equal(dg.reshape(-1), h["digs"][int(s) * L * 32:(int(s) + 1) * L * 32])
+        r, _ = co.merkle_roots(dg, np.array([0, L], np.uint64))
+        assert np.array_equal(r[0], h["roots"][int(s) * 32:(int(s) + 1) * 32])

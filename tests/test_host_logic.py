@@ -1,0 +1,140 @@
+"""CPU-only tests of the host side: canonical packer vs the reference's pre-images (golden),
+side-array encoding, the C-ABI library loads and exports every declared symbol, and the
+product fails loudly without a GPU (no CPU fallback)."""
+
+import hashlib
+import os
+import re
+
+import numpy as np
+import pytest
+
+import recipes
+from agent_hypervisor_b200 import SemanticDelta, VFSChange, _native as nat
+from agent_hypervisor_b200.audit.packing import ArenaBuilder, canonical_preimage, classify_parent, pack_sessions
+from agent_hypervisor_b200.liability.vouching import VouchGraphCSR, VouchRecord, _to_us
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def build_deltas(fields):
+    """Shim SemanticDelta objects chained like DeltaEngine.capture, hashes via hashlib (test only)."""
+    out, parent = [], None
+    for f in fields:
+        d = SemanticDelta(delta_id=f["delta_id"], turn_id=f["turn_id"], session_id=f["session_id"],
+                          agent_did=f["agent_did"], timestamp=f["timestamp"],
+                          changes=[VFSChange(**c) for c in f["changes"]], parent_hash=parent)
+        d.delta_hash = hashlib.sha256(canonical_preimage(d)).hexdigest()
+        parent = d.delta_hash
+        out.append(d)
+    return out
+
+
+def test_packer_matches_reference_preimages(audit_golden):
+    for r in audit_golden["random_sessions"]:
+        ds = build_deltas(recipes.random_session(r["seed"]))
+        pre = b"".join(canonical_preimage(d) for d in ds)
+        assert hashlib.sha256(pre).hexdigest() == r["preimages_sha"], r["seed"]
+        if ds:
+            assert ds[-1].delta_hash == r["last_leaf"]
+    g = audit_golden["golden_session"]["2"]
+    ds = build_deltas(recipes.golden_session(2))
+    assert canonical_preimage(ds[0]).decode() == g["preimage0"]
+    assert canonical_preimage(ds[1]).decode() == g["preimage1"]
+
+
+def test_packer_non_string_fields_match_json():
+    import json
+    from datetime import datetime, timezone
+    d = SemanticDelta(delta_id=17, turn_id=True, session_id=None, agent_did=1.5,
+                      timestamp=datetime(2026, 1, 1, tzinfo=timezone.utc),
+                      changes=[VFSChange(path={"b": 1, "a": [1, "x"]}, operation="é", content_hash=3)],
+                      parent_hash=None)
+    want = json.dumps({"delta_id": 17, "turn_id": True, "session_id": None, "agent_did": 1.5,
+                       "timestamp": d.timestamp.isoformat(),
+                       "changes": [{"path": {"b": 1, "a": [1, "x"]}, "operation": "é", "content_hash": 3,
+                                    "previous_hash": None}],
+                       "parent_hash": None}, sort_keys=True).encode()
+    assert canonical_preimage(d) == want
+
+
+def test_pack_sessions_layout():
+    s1 = build_deltas(recipes.golden_session(3))
+    s2 = []
+    s3 = build_deltas(recipes.golden_session(1))
+    s3[0].parent_hash = "NOTHEX"
+    p = pack_sessions([s1, s2, s3])
+    assert list(p.session_rowptr) == [0, 3, 3, 4]
+    assert p.n == 4 and p.n_sessions == 3
+    assert list(p.parent_kind) == [nat.PARENT_NONE, nat.PARENT_HEX, nat.PARENT_HEX, nat.PARENT_OTHER]
+    assert p.parents[1].tobytes().hex() == s1[0].delta_hash
+    for i, d in enumerate(s1):
+        assert p.arena[int(p.offsets[i]):int(p.offsets[i + 1])].tobytes() == canonical_preimage(d)
+    assert p.uniform_shape() == (0, 0)
+
+
+def test_classify_parent():
+    assert classify_parent(None)[0] == nat.PARENT_NONE
+    assert classify_parent("a" * 64) == (nat.PARENT_HEX, bytes.fromhex("a" * 64))
+    assert classify_parent("A" * 64)[0] == nat.PARENT_OTHER
+    assert classify_parent("a" * 63)[0] == nat.PARENT_OTHER
+    assert classify_parent("")[0] == nat.PARENT_OTHER
+
+
+def test_vouch_csr_insertion_order_and_session_filter():
+    from datetime import datetime, timedelta, timezone
+    t = datetime(2030, 1, 1, 12, 0, 0, 123456, tzinfo=timezone.utc)
+    recs = [
+        VouchRecord("v1", "a", "x", "s", 0.2, 0.11),
+        VouchRecord("v2", "b", "y", "s", 0.2, 0.22, expiry=t),
+        VouchRecord("v3", "c", "x", "other", 0.2, 0.33),
+        VouchRecord("v4", "d", "x", "s", 0.2, 0.44, is_active=False),
+        VouchRecord("v5", "e", "zz", "s", 0.2, 0.55),
+    ]
+    g = VouchGraphCSR.from_records(recs, "s", ["x", "y", "nobody"])
+    assert list(g.rowptr) == [0, 2, 3, 3]
+    assert list(g.bonded) == [0.11, 0.44, 0.22]
+    assert list(g.active) == [1, 0, 1]
+    assert g.expiry[0] == nat.EXPIRY_NONE and g.expiry[2] == _to_us(t)
+    assert _to_us(t) == int(t.timestamp()) * 10**6 + 123456
+    assert _to_us(t + timedelta(microseconds=1)) == _to_us(t) + 1
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "ahv.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(ahv_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 30
+    lib = nat.load_library()                       # dlopen only; no CUDA call
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in ahv.h but not exported"
+        assert name in nat.SIGNATURES, f"{name} has no ctypes signature"
+    assert set(nat.SIGNATURES) <= declared
+    assert lib.ahv_abi_version() == 1
+
+
+def test_no_cpu_fallback_without_gpu():
+    """Without a CUDA device every product call must raise, never compute on the CPU."""
+    lib = nat.load_library()
+    import ctypes as C
+    h = C.c_void_p()
+    rc = lib.ahv_create(0, C.byref(h))
+    if rc == 0:                                    # running on the GPU box
+        lib.ahv_destroy(h)
+        pytest.skip("CUDA device present")
+    assert rc == -4 and b"no CPU path" in lib.ahv_last_error()
+    from agent_hypervisor_b200 import DeltaEngine, NativeUnavailable
+    nat._default_ctx = None
+    with pytest.raises(NativeUnavailable):
+        DeltaEngine("s").capture("did:a", [VFSChange(path="/f", operation="add")])
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "agent_hypervisor_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, fn), encoding="utf-8").read()
+                assert "oracle" not in src.lower(), f"{fn} mentions the oracle"
+                if fn.endswith(".py"):
+                    assert "hashlib" not in src.replace("no hashlib path", ""), f"{fn} uses hashlib"
