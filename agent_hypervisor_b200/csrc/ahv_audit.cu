@@ -574,24 +574,18 @@ int run_leaves(ahv_ctx *ctx, const uint8_t *d_arena, const uint64_t *d_offsets, 
     return AHV_OK;
 }
 
-uint32_t levels_for(uint64_t max_leaves)
-{
-    uint32_t L = 0;
-    while ((1ull << L) < max_leaves) ++L;
-    return L;
-}
-
 // levels reduced by global level steps before the in-CTA top kernel takes over
-uint32_t global_levels(uint64_t max_leaves)
+uint32_t global_levels(const ahv_ctx *ctx, uint64_t max_leaves)
 {
+    const uint64_t top = (ctx->opt_top_max >= 2 && ctx->opt_top_max <= TOP_MAX) ? (uint64_t)ctx->opt_top_max : TOP_MAX;
     uint32_t l = 0;
-    while (((max_leaves + ((1ull << l) - 1)) >> l) > TOP_MAX) ++l;
+    while (((max_leaves + ((1ull << l) - 1)) >> l) > top) ++l;
     return l;
 }
 
-uint64_t tree_scratch_bytes(uint64_t n, uint64_t S, uint64_t max_leaves, bool uniform)
+uint64_t tree_scratch_bytes(const ahv_ctx *ctx, uint64_t n, uint64_t S, uint64_t max_leaves, bool uniform)
 {
-    const uint32_t G = global_levels(max_leaves);
+    const uint32_t G = global_levels(ctx, max_leaves);
     if (G == 0) return 0;
     uint64_t b = 2 * pad256(32ull * (n / 2 + S + 1));
     if (!uniform) b += pad256(8ull * G * (S + 1));
@@ -603,7 +597,7 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
              uint64_t uniform, uint64_t max_leaves, uint8_t *d_roots, uint8_t *d_empty)
 {
     if (S == 0) return AHV_OK;
-    const uint32_t G = global_levels(max_leaves);
+    const uint32_t G = global_levels(ctx, max_leaves);
     const uint8_t *cur = d_digests;
     const uint64_t *rp_cur = d_rowptr;
     uint32_t c_cur = (uint32_t)uniform;
@@ -708,7 +702,7 @@ int ahv_merkle_roots_dev(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t 
         AHV_TRY(scratch_reserve(ctx, 256));
         AHV_TRY(device_max_session(ctx, d_rowptr, S, &max_leaves));
     }
-    AHV_TRY(scratch_reserve(ctx, tree_scratch_bytes(n, S, max_leaves, false)));
+    AHV_TRY(scratch_reserve(ctx, tree_scratch_bytes(ctx, n, S, max_leaves, false)));
     return run_tree(ctx, d_digests, d_rowptr, S, n, 0, max_leaves, d_roots, d_empty);
 }
 
@@ -726,7 +720,7 @@ int ahv_commit_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes, c
         AHV_TRY(device_max_session(ctx, d_rowptr, S, &max_leaves));
     }
     const bool sorted = d_offsets && ctx->opt_sort && n > 1024;
-    uint64_t need = leaf_scratch_bytes(n, sorted) + tree_scratch_bytes(n, S, max_leaves, uniform != 0) +
+    uint64_t need = leaf_scratch_bytes(n, sorted) + tree_scratch_bytes(ctx, n, S, max_leaves, uniform != 0) +
                     (d_digests ? 0 : pad256(32ull * n));
     AHV_TRY(scratch_reserve(ctx, need));
     uint8_t *dig = d_digests;
@@ -763,7 +757,7 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
     const bool sorted = d_offsets && ctx->opt_sort && n > 1024;
     const bool need_dig = want_tree && !d_digests;
     uint64_t need = leaf_scratch_bytes(n, sorted) + pad256(8ull * S) + (uniform ? 0 : pad256(n)) +
-                    (want_tree ? tree_scratch_bytes(n, S, max_leaves, uniform != 0) + pad256(32ull * S) + pad256(S) : 0) +
+                    (want_tree ? tree_scratch_bytes(ctx, n, S, max_leaves, uniform != 0) + pad256(32ull * S) + pad256(S) : 0) +
                     (need_dig ? pad256(32ull * n) : 0);
     AHV_TRY(scratch_reserve(ctx, need));
     unsigned long long *fb = (unsigned long long *)scratch_take(ctx, 8ull * S);

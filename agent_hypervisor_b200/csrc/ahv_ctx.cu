@@ -141,6 +141,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_block = 128;
     c->opt_fixed_variant = 0;
     c->opt_tree_k = 0;
+    c->opt_top_max = 256;
     *out_ctx = c;
     return AHV_OK;
 }
@@ -287,6 +288,9 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "tree_k")) {
         AHV_REQUIRE(value >= 0 && value <= 3, "tree_k must be 0..3");
         ctx->opt_tree_k = value;
+    } else if (!strcmp(key, "top_max")) {
+        AHV_REQUIRE(value >= 2 && value <= 256, "top_max must be 2..256");
+        ctx->opt_top_max = value;
     } else if (!strcmp(key, "leaf_timer")) {
         AHV_REQUIRE(value == 0 || (value > 0 && value + 16 <= AHV_MAX_TIMERS), "leaf_timer base must leave 16 slots");
         ctx->opt_leaf_timer = value;

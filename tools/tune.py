@@ -77,6 +77,16 @@ def main():
     best, avg = timed(ctx, lambda: ctx.commit_dev(d["arena"], arena.nbytes, 0, FL, 0, S, n, L, L, d["digs"], d["roots"], d["empty"]))
     res["commit_uniform"] = {"best_ms": best, "avg_ms": avg}
     print(f"commit (leaf+tree uniform): best {best:.3f} ms", flush=True)
+    ctx.sha256_batch_dev(d["arena"], arena.nbytes, 0, n, FL, d["digs"])
+    for top in (256, 128, 64, 32, 16):
+        ctx.set_option("top_max", top)
+        # tree alone = commit minus leaves is not separable through the ABI; time the ragged tree and the uniform commit
+        best, avg = timed(ctx, lambda: ctx.commit_dev(d["arena"], arena.nbytes, 0, FL, 0, S, n, L, L, d["digs"], d["roots"], d["empty"]), reps=3)
+        res[f"commit_uniform_top{top}"] = {"best_ms": best}
+        b2, _ = timed(ctx, lambda: ctx.merkle_roots_dev(d["digs"], d["rp"], S, n, L, d["roots2"], d["empty"]), reps=3)
+        res[f"tree_ragged_top{top}"] = {"best_ms": b2, "Gcomp_s": node_c / b2 / 1e6}
+        print(f"top_max {top}: commit {best:.3f} ms, ragged tree {b2:.3f} ms ({node_c/b2/1e6:.2f} Gcomp/s)", flush=True)
+    ctx.set_option("top_max", 256)
     best, avg = timed(ctx, lambda: ctx.merkle_roots_dev(d["digs"], d["rp"], S, n, L, d["roots2"], d["empty"]))
     res["tree_ragged"] = {"best_ms": best, "avg_ms": avg, "Gcomp_s": node_c / best / 1e6}
     print(f"tree ragged path: best {best:.3f} ms -> {node_c/best/1e6:.2f} Gcomp/s", flush=True)
