@@ -63,6 +63,7 @@ SIGNATURES = {
     "ahv_sha256_batch_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _u64, _vp]),
     "ahv_merkle_roots": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp]),
     "ahv_merkle_roots_dev": (C.c_int, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp]),
+    "ahv_merkle_roots_noalloc_dev": (C.c_int, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp]),
     "ahv_commit": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _u64, _u64, _vp, _vp, _vp]),
     "ahv_commit_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _u64, _u64, _u64, _vp, _vp, _vp]),
     "ahv_verify_chains": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
@@ -336,6 +337,11 @@ class Context:
     def merkle_roots_dev(self, d_digests, d_rowptr, S, n, max_leaves, d_roots, d_empty):
         self._check(self.lib.ahv_merkle_roots_dev(self.h, _vp(d_digests), _vp(d_rowptr), S, n, max_leaves,
                                                   _vp(d_roots), _vp(d_empty)), "ahv_merkle_roots_dev")
+
+    def merkle_roots_noalloc_dev(self, d_digests, d_rowptr, S, n, max_leaves, d_roots, d_empty):
+        """Same as merkle_roots_dev, but never allocates: scratch is a fixed 8 MiB array in the library."""
+        self._check(self.lib.ahv_merkle_roots_noalloc_dev(self.h, _vp(d_digests), _vp(d_rowptr), S, n, max_leaves,
+                                                          _vp(d_roots), _vp(d_empty)), "ahv_merkle_roots_noalloc_dev")
 
     def chain_capture_dev(self, d_arena, arena_bytes, d_offsets, d_hexpos, d_rowptr, S, n, d_digests, d_par, d_kind):
         self._check(self.lib.ahv_chain_capture_dev(self.h, _vp(d_arena), arena_bytes, _vp(d_offsets), _vp(d_hexpos),

@@ -819,3 +819,121 @@ int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, 
 }
 
 }  // extern "C"
+
+// =================================================================== allocation-free Merkle roots
+//
+// ahv_merkle_roots_noalloc_dev: same result as ahv_merkle_roots_dev, for callers that must not
+// allocate device memory while they run.  Two kinds of caller are in that position:
+//   * a service that shares the GPU with another framework whose allocator already owns the rest
+//     of HBM (a fixed budget carved up at start-up): a cudaMalloc issued later, when a bigger
+//     batch happens to arrive, can fail or fragment the other tenant's pool;
+//   * a latency-sensitive loop: cudaMalloc / cudaFree synchronise the whole device, so the
+//     growable slab behind ahv_merkle_roots_dev can stall every other stream the first time a
+//     larger batch shows up.
+// Here the level buffers and per-level row pointers live in ONE fixed array inside the library
+// image (AHV_NOALLOC_SCRATCH_BYTES = 8 MiB).  Every GPU that loads the library holds that array
+// from load until the process exits, whether or not this entry point is ever called.
+//
+// Rules for users:
+//   * Batches whose scratch need exceeds the array are refused with AHV_E_TOOLARGE before anything
+//     is launched.  The need is 2 * 32 * (n_leaves/2 + n_sessions + 1) bytes for the two level
+//     buffers plus 8 * (n_sessions + 1) bytes per level reduced outside the in-CTA finish, each
+//     part rounded up to 256 bytes; roughly 32 bytes per leaf + 72 bytes per session, i.e. about
+//     250 000 leaves in a handful of sessions.  max_session_leaves must be given (> 0): finding it
+//     would need a device-to-host read back.
+//   * The first call on each device looks up the array's device address (cudaGetSymbolAddress,
+//     with that device current) and remembers it; make that first call before any stream capture
+//     begins on that device.  No call, first or later, uses cudaMalloc, cudaFree or any other
+//     allocating routine.
+//   * All calls on a device share the one array, and it still holds whatever the previous call left
+//     there.  Nothing in it has to start at zero: every byte a call reads it has written earlier in
+//     the same call (each level is produced in full before the next level reads it), so no clearing
+//     is needed between calls.  For the same reason two calls whose kernels overlap on the GPU
+//     (different streams, contexts or host threads) race on the array; run them one after another.
+namespace {
+
+constexpr uint64_t AHV_NOALLOC_SCRATCH_BYTES = 8ull << 20;
+constexpr int AHV_NOALLOC_MAX_DEVICES = 64;
+
+// In host code this name is only a handle for the runtime, never an address to hand to a kernel.
+static __device__ __align__(256) uint8_t g_noalloc_scratch[AHV_NOALLOC_SCRATCH_BYTES];
+
+// device address of g_noalloc_scratch on each device, looked up once per device
+uint8_t *g_noalloc_addr[AHV_NOALLOC_MAX_DEVICES] = {};
+
+int noalloc_base(ahv_ctx *ctx, uint8_t **out)
+{
+    if (ctx->device < 0 || ctx->device >= AHV_NOALLOC_MAX_DEVICES) {
+        set_error("device ordinal %d not supported by the allocation-free entry point (limit %d)", ctx->device,
+                  AHV_NOALLOC_MAX_DEVICES - 1);
+        return AHV_E_INVALID;
+    }
+    uint8_t *p = __atomic_load_n(&g_noalloc_addr[ctx->device], __ATOMIC_ACQUIRE);
+    if (!p) {
+        // use_device() has already made ctx->device current on this thread
+        void *sym = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&sym, g_noalloc_scratch);
+        if (e != cudaSuccess || !sym) {
+            cudaGetLastError();
+            set_error("cudaGetSymbolAddress(static scratch) failed on device %d: %s", ctx->device,
+                      cudaGetErrorString(e));
+            return AHV_E_CUDA;
+        }
+        p = (uint8_t *)sym;
+        __atomic_store_n(&g_noalloc_addr[ctx->device], p, __ATOMIC_RELEASE);   // same value from any thread
+    }
+    *out = p;
+    return AHV_OK;
+}
+
+}  // namespace
+
+extern "C" int ahv_merkle_roots_noalloc_dev(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr,
+                                            uint64_t S, uint64_t n, uint64_t max_leaves, uint8_t *d_roots,
+                                            uint8_t *d_empty)
+{
+    AHV_TRY(use_device(ctx));
+    AHV_REQUIRE(d_roots || S == 0, "out_roots is null");
+    AHV_REQUIRE(d_rowptr || S == 0, "session_rowptr is null");
+    AHV_REQUIRE((reinterpret_cast<uintptr_t>(d_digests) & 15u) == 0 && (reinterpret_cast<uintptr_t>(d_roots) & 15u) == 0,
+                "digest buffers must be 16-byte aligned");
+    AHV_REQUIRE(max_leaves > 0 || S == 0, "max_session_leaves must be given (> 0) for the allocation-free entry point");
+    AHV_TRY(check_sizes(n, S));
+    if (S == 0) return AHV_OK;
+
+    const uint32_t G = global_levels(ctx, max_leaves);
+    const uint64_t lvl_bytes = pad256(32ull * (n / 2 + S + 1));
+    const uint64_t rp_bytes = G ? pad256(8ull * G * (S + 1)) : 0;
+    const uint64_t need = G ? 2 * lvl_bytes + rp_bytes : 0;
+    if (need > AHV_NOALLOC_SCRATCH_BYTES) {
+        set_error("batch needs %llu bytes of scratch but the allocation-free entry point has a fixed %llu-byte array "
+                  "(n_leaves=%llu, n_sessions=%llu); use ahv_merkle_roots_dev or split the batch",
+                  (unsigned long long)need, (unsigned long long)AHV_NOALLOC_SCRATCH_BYTES, (unsigned long long)n,
+                  (unsigned long long)S);
+        return AHV_E_TOOLARGE;
+    }
+    uint8_t *base = nullptr;
+    AHV_TRY(noalloc_base(ctx, &base));
+
+    const uint8_t *cur = d_digests;
+    const uint64_t *rp_cur = d_rowptr;
+    if (G > 0) {
+        uint8_t *bufA = base;
+        uint8_t *bufB = base + lvl_bytes;
+        uint64_t *lvl_rp = reinterpret_cast<uint64_t *>(base + 2 * lvl_bytes);
+        k_level_rowptrs<<<G, 1024, 0, ctx->stream>>>(d_rowptr, S, lvl_rp);
+        AHV_CHECK_LAUNCH(ctx);
+        for (uint32_t l = 1; l <= G; ++l) {
+            uint8_t *dst = (l & 1) ? bufA : bufB;
+            const uint64_t *rp_out = lvl_rp + (uint64_t)(l - 1) * (S + 1);
+            const uint64_t bound = ((n + ((1ull << l) - 1)) >> l) + S;
+            k_merkle_level<false><<<grid_for(bound, 128), 128, 0, ctx->stream>>>(cur, dst, S, 0, 0, rp_cur, rp_out);
+            AHV_CHECK_LAUNCH(ctx);
+            rp_cur = rp_out;
+            cur = dst;
+        }
+    }
+    k_merkle_top<false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty);
+    AHV_CHECK_LAUNCH(ctx);
+    return AHV_OK;
+}

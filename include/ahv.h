@@ -122,6 +122,21 @@ int ahv_merkle_roots_dev(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t 
                          uint8_t *d_out_roots, uint8_t *d_out_empty);
 
 /*
+ * ahv_merkle_roots_noalloc_dev: ahv_merkle_roots_dev for callers that must not allocate device memory
+ * while running (a GPU shared with another framework's allocator under a fixed memory budget; loops
+ * that cannot afford the device-wide synchronisation of cudaMalloc/cudaFree).  No counterpart in the
+ * reference.  Its scratch is one fixed 8 MiB array inside the library image, held by every GPU that loads
+ * the library until the process exits.  Batches needing more (about 32 bytes per leaf + 72 bytes per
+ * session; roughly 250 000 leaves) are refused with AHV_E_TOOLARGE; max_session_leaves must be > 0.
+ * The first call on a device looks up the array's address and should come before any stream capture on
+ * that device.  Calls share the array (nothing in it needs clearing between calls), so calls that
+ * overlap on the GPU race: issue them one after another.
+ */
+int ahv_merkle_roots_noalloc_dev(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_session_rowptr,
+                                 uint64_t n_sessions, uint64_t n_leaves, uint64_t max_session_leaves,
+                                 uint8_t *d_out_roots, uint8_t *d_out_empty);
+
+/*
  * ahv_commit: fused leaf hashing + Merkle roots (what Hypervisor.terminate_session
  * needs at core.py:204 for many sessions at once): audit/delta.py:63 then :117-134.
  *   out_digests may be NULL.  uniform_leaves > 0 states that every session has
