@@ -75,13 +75,30 @@ __device__ __forceinline__ void verify_epilogue(const VerifyArgs &va, uint64_t i
     }
 }
 
+// compression policy selected at compile time per kernel instance (see sha256_core.cuh)
+template <bool SC> struct Pol;
+template <> struct Pol<false> {
+    typedef CompressNative type;
+    static __device__ __forceinline__ CompressNative make(uint32_t) { return CompressNative(); }
+};
+template <> struct Pol<true> {
+    typedef CompressScaled type;
+    static __device__ __forceinline__ CompressScaled make(uint32_t rc)
+    {
+        CompressScaled p;
+        p.rc = rc;
+        return p;
+    }
+};
+
 // ------------------------------------------------------------------ leaf kernels
 // General path: any length, any alignment, optional length-sorted permutation.
-template <bool VERIFY>
+template <bool VERIFY, bool SC>
 __global__ void __launch_bounds__(256)
 k_sha256_var(const uint8_t *__restrict__ arena, const uint64_t *__restrict__ offsets, uint64_t fixed_len,
-             uint64_t n, const uint32_t *__restrict__ perm, uint8_t *__restrict__ out, VerifyArgs va)
+             uint64_t n, const uint32_t *__restrict__ perm, uint8_t *__restrict__ out, uint32_t rc, VerifyArgs va)
 {
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     uint64_t i = perm ? perm[t] : t;
@@ -94,7 +111,7 @@ k_sha256_var(const uint8_t *__restrict__ arena, const uint64_t *__restrict__ off
         len = fixed_len;
     }
     uint32_t st[8];
-    sha256_message(arena + off, len, st);
+    sha256_message(arena + off, len, st, cp);
     if (out) store_digest(out + 32 * i, st);
     if (VERIFY) verify_epilogue(va, i, n, st);
 }
@@ -118,11 +135,12 @@ __device__ __forceinline__ void words_from_u4(uint32_t w[16], const U4 &v0, cons
 // The padding block is the same for every message, so its K+W values arrive as a
 // kernel parameter (constant-bank operands, no schedule work).  Next block's 64 bytes
 // are prefetched into registers while the current block is compressed.
-template <bool VERIFY>
+template <bool VERIFY, bool SC>
 __global__ void __launch_bounds__(256)
 k_sha256_fixed(const uint8_t *__restrict__ arena, uint32_t nb, uint64_t n, uint8_t *__restrict__ out,
-               const __grid_constant__ KW64 kwpad, VerifyArgs va)
+               const __grid_constant__ KW64 kwpad, uint32_t rc, VerifyArgs va)
 {
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const U4 *p = reinterpret_cast<const U4 *>(arena + i * (uint64_t)nb * 64u);
@@ -137,9 +155,9 @@ k_sha256_fixed(const uint8_t *__restrict__ arena, uint32_t nb, uint64_t n, uint8
             p += 4;
             v0 = ldg_u4(p); v1 = ldg_u4(p + 1); v2 = ldg_u4(p + 2); v3 = ldg_u4(p + 3);
         }
-        sha256_compress(st, w);
+        cp.block(st, w);
     }
-    sha256_compress_kw(st, kwpad);
+    cp.pad(st, kwpad);
     if (out) store_digest(out + 32 * i, st);
     if (VERIFY) verify_epilogue(va, i, n, st);
 }
@@ -148,11 +166,12 @@ k_sha256_fixed(const uint8_t *__restrict__ arena, uint32_t nb, uint64_t n, uint8
 // blocks with fully coalesced 16-byte cp.async (512 contiguous bytes per instruction
 // when messages are 64 bytes; whole 128-byte lines otherwise), double buffered, then
 // every lane reads its own block from a padded (conflict-free) slot.
-template <bool VERIFY>
+template <bool VERIFY, bool SC>
 __global__ void __launch_bounds__(256)
 k_sha256_fixed_smem(const uint8_t *__restrict__ arena, uint32_t nb, uint64_t n, uint8_t *__restrict__ out,
-                    const __grid_constant__ KW64 kwpad, VerifyArgs va)
+                    const __grid_constant__ KW64 kwpad, uint32_t rc, VerifyArgs va)
 {
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     // per warp: 2 stages x 32 lanes x 80 bytes (64 data + 16 pad -> LDS.128 conflict-free)
     extern __shared__ __align__(16) uint8_t smem[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -197,10 +216,10 @@ k_sha256_fixed_smem(const uint8_t *__restrict__ arena, uint32_t nb, uint64_t n, 
         __syncwarp();     // all lanes have read stage b&1 before it is refilled two iterations later
         uint32_t w[16];
         words_from_u4(w, v0, v1, v2, v3);
-        sha256_compress(st, w);
+        cp.block(st, w);
     }
     if (i < n) {
-        sha256_compress_kw(st, kwpad);
+        cp.pad(st, kwpad);
         if (out) store_digest(out + 32 * i, st);
         if (VERIFY) verify_epilogue(va, i, n, st);
     }
@@ -321,12 +340,13 @@ k_level_rowptrs(const uint64_t *__restrict__ rowptr, uint64_t S, uint64_t *__res
 // ------------------------------------------------------------------ Merkle level step
 // One thread per output node (audit/delta.py:127-131).  Sessions that are already down
 // to one node carry it forward unchanged (the reference loop stops at len == 1, :125).
-template <bool UNIFORM>
+template <bool UNIFORM, bool SC>
 __global__ void __launch_bounds__(256)
 k_merkle_level(const uint8_t *__restrict__ in, uint8_t *__restrict__ out, uint64_t S,
                uint32_t c_in_u, uint32_t c_out_u,                       // uniform counts per session
-               const uint64_t *__restrict__ rp_in, const uint64_t *__restrict__ rp_out)
+               const uint64_t *__restrict__ rp_in, const uint64_t *__restrict__ rp_out, uint32_t rc)
 {
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint64_t in0, k, c_in;
     if (UNIFORM) {
@@ -357,7 +377,7 @@ k_merkle_level(const uint8_t *__restrict__ in, uint8_t *__restrict__ out, uint64
 #pragma unroll
         for (int q = 0; q < 8; ++q) r[q] = l[q];          // odd level: duplicate the last node (:129)
     }
-    merkle_node(l, r, d);
+    merkle_node(l, r, d, cp);
     store_digest(out + 32 * j, d);
 }
 
@@ -365,11 +385,12 @@ k_merkle_level(const uint8_t *__restrict__ in, uint8_t *__restrict__ out, uint64
 // pair-hashed level by level in shared memory.  Cuts the launch count for deep trees and
 // is the whole tree for small sessions.
 constexpr uint32_t TOP_MAX = 256;
-template <bool UNIFORM>
+template <bool UNIFORM, bool SC>
 __global__ void __launch_bounds__(128)
 k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const uint64_t *__restrict__ rp_in,
-             uint8_t *__restrict__ roots, uint8_t *__restrict__ empty)
+             uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc)
 {
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     __shared__ uint32_t buf[2][TOP_MAX / 2 + 1][8 + 1];   // +1 word pad against bank conflicts
     const uint64_t s = blockIdx.x;
     if (s >= S) return;
@@ -405,7 +426,7 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
 #pragma unroll
             for (int q = 0; q < 8; ++q) r[q] = l[q];
         }
-        merkle_node(l, r, d);
+        merkle_node(l, r, d, cp);
 #pragma unroll
         for (int q = 0; q < 8; ++q) buf[cur][k][q] = d[q];
     }
@@ -421,7 +442,7 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
                 l[q] = buf[cur][2 * k][q];
                 r[q] = buf[cur][kr][q];
             }
-            merkle_node(l, r, d);
+            merkle_node(l, r, d, cp);
 #pragma unroll
             for (int q = 0; q < 8; ++q) buf[cur ^ 1][k][q] = d[q];
         }
@@ -433,6 +454,80 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
         uint32_t d[8];
 #pragma unroll
         for (int q = 0; q < 8; ++q) d[q] = buf[cur][0][q];
+        store_digest(roots + 32 * s, d);
+    }
+}
+
+// Same finish, one WARP per session (4 sessions per CTA) for levels of <= 64 nodes: no idle
+// warps, no block-wide barriers; the level is pair-hashed in the warp's shared-memory slot.
+template <bool UNIFORM, bool SC>
+__global__ void __launch_bounds__(128)
+k_merkle_top_warp(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const uint64_t *__restrict__ rp_in,
+                  uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc)
+{
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
+    __shared__ uint32_t buf[4][2][32][8 + 1];
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint64_t s = (uint64_t)blockIdx.x * 4 + wid;
+    if (s >= S) return;
+    uint64_t in0;
+    uint32_t c;
+    if (UNIFORM) {
+        in0 = s * c_in_u;
+        c = c_in_u;
+    } else {
+        in0 = rp_in[s];
+        c = (uint32_t)(rp_in[s + 1] - in0);
+    }
+    if (c == 0) {
+        roots[32 * s + lane] = 0;
+        if (lane == 0 && empty) empty[s] = 1;
+        return;
+    }
+    if (lane == 0 && empty) empty[s] = 0;
+    if (c == 1) {
+        if (lane < 8)
+            reinterpret_cast<uint32_t *>(roots + 32 * s)[lane] = reinterpret_cast<const uint32_t *>(in + 32 * in0)[lane];
+        return;
+    }
+    uint32_t cur = 0;
+    uint32_t c_out = (c + 1) >> 1;                       // <= 32: one node per lane
+    if (lane < c_out) {
+        uint32_t l[8], r[8], d[8];
+        load_digest(in + 32 * (in0 + 2 * lane), l);
+        if (2 * lane + 1 < c) load_digest(in + 32 * (in0 + 2 * lane + 1), r);
+        else {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) r[q] = l[q];
+        }
+        merkle_node(l, r, d, cp);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) buf[wid][cur][lane][q] = d[q];
+    }
+    c = c_out;
+    __syncwarp();
+    while (c > 1) {
+        c_out = (c + 1) >> 1;
+        if (lane < c_out) {
+            uint32_t l[8], r[8], d[8];
+            const uint32_t kr = (2 * lane + 1 < c) ? 2 * lane + 1 : 2 * lane;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                l[q] = buf[wid][cur][2 * lane][q];
+                r[q] = buf[wid][cur][kr][q];
+            }
+            merkle_node(l, r, d, cp);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) buf[wid][cur ^ 1][lane][q] = d[q];
+        }
+        cur ^= 1;
+        c = c_out;
+        __syncwarp();
+    }
+    if (lane == 0) {
+        uint32_t d[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) d[q] = buf[wid][cur][0][q];
         store_digest(roots + 32 * s, d);
     }
 }
@@ -466,11 +561,13 @@ __global__ void k_root_compare(const uint8_t *__restrict__ roots, const uint8_t 
 // One thread per session walks its chain (audit/delta.py:101-114): hash delta i, write the
 // 64 hex characters into delta i+1's pre-image, continue.  Plain (coherent) loads only:
 // the thread re-reads bytes it has just written.
+template <bool SC>
 __global__ void __launch_bounds__(128)
 k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint32_t *__restrict__ hexpos,
                 const uint64_t *__restrict__ rowptr, uint64_t S, uint8_t *__restrict__ out_digests,
-                uint8_t *__restrict__ out_parents, uint8_t *__restrict__ out_kind)
+                uint8_t *__restrict__ out_parents, uint8_t *__restrict__ out_kind, uint32_t rc)
 {
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= S) return;
     uint32_t prev[8];
@@ -497,7 +594,7 @@ k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint
             }
             if (out_kind) out_kind[i] = AHV_PARENT_NONE;
         }
-        sha256_message(arena + off, len, prev);
+        sha256_message(arena + off, len, prev, cp);
         if (out_digests) store_digest(out_digests + 32 * i, prev);
     }
 }
@@ -530,17 +627,24 @@ int run_leaves(ahv_ctx *ctx, const uint8_t *d_arena, const uint64_t *d_offsets, 
     const bool fixed_fast = (!d_offsets && fixed_len > 0 && (fixed_len & 63u) == 0 &&
                              (reinterpret_cast<uintptr_t>(d_arena) & 15u) == 0 && fixed_len / 64 < 0xffffffffull);
     const int tslot = ctx->opt_leaf_timer ? (int)(ctx->opt_leaf_timer + (ctx->leaf_launches++ & 15u)) : -1;
+    const bool sc = ctx->opt_compress != 0;
+    const uint32_t rc = SHA_SC;
     if (fixed_fast) {
-        const KW64 kw = make_kw_pad(fixed_len * 8);
+        const KW64 kw = sc ? make_kw_pad_scaled(fixed_len * 8) : make_kw_pad(fixed_len * 8);
         const uint32_t nb = (uint32_t)(fixed_len / 64);
         if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_start[tslot], ctx->stream));
         if (ctx->opt_fixed_variant == 1) {
             size_t smem = (size_t)(block / 32) * 2 * 32 * 80;
-            if (va) k_sha256_fixed_smem<true><<<grid_for(n, block), block, smem, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
-            else k_sha256_fixed_smem<false><<<grid_for(n, block), block, smem, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
+#define AHV_LAUNCH_LEAF(KERNEL, SMEM, ...)                                                                  \
+    do {                                                                                                   \
+        if (va && sc) KERNEL<true, true><<<grid_for(n, block), block, SMEM, ctx->stream>>>(__VA_ARGS__);    \
+        else if (va) KERNEL<true, false><<<grid_for(n, block), block, SMEM, ctx->stream>>>(__VA_ARGS__);    \
+        else if (sc) KERNEL<false, true><<<grid_for(n, block), block, SMEM, ctx->stream>>>(__VA_ARGS__);    \
+        else KERNEL<false, false><<<grid_for(n, block), block, SMEM, ctx->stream>>>(__VA_ARGS__);           \
+    } while (0)
+            AHV_LAUNCH_LEAF(k_sha256_fixed_smem, smem, d_arena, nb, n, d_out, kw, rc, v);
         } else {
-            if (va) k_sha256_fixed<true><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
-            else k_sha256_fixed<false><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, nb, n, d_out, kw, v);
+            AHV_LAUNCH_LEAF(k_sha256_fixed, 0, d_arena, nb, n, d_out, kw, rc, v);
         }
         AHV_CHECK_LAUNCH(ctx);
         if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_stop[tslot], ctx->stream));
@@ -567,8 +671,7 @@ int run_leaves(ahv_ctx *ctx, const uint8_t *d_arena, const uint64_t *d_offsets, 
         perm = p;
     }
     if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_start[tslot], ctx->stream));
-    if (va) k_sha256_var<true><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, d_offsets, fixed_len, n, perm, d_out, v);
-    else k_sha256_var<false><<<grid_for(n, block), block, 0, ctx->stream>>>(d_arena, d_offsets, fixed_len, n, perm, d_out, v);
+    AHV_LAUNCH_LEAF(k_sha256_var, 0, d_arena, d_offsets, fixed_len, n, perm, d_out, rc, v);
     AHV_CHECK_LAUNCH(ctx);
     if (tslot >= 0) AHV_CUDA(cudaEventRecord(ctx->t_stop[tslot], ctx->stream));
     return AHV_OK;
@@ -601,6 +704,8 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
     const uint8_t *cur = d_digests;
     const uint64_t *rp_cur = d_rowptr;
     uint32_t c_cur = (uint32_t)uniform;
+    const bool sc = ctx->opt_compress != 0;
+    const uint32_t rc = SHA_SC;
     if (G > 0) {
         uint8_t *bufA = (uint8_t *)scratch_take(ctx, 32ull * (n / 2 + S + 1));
         uint8_t *bufB = (uint8_t *)scratch_take(ctx, 32ull * (n / 2 + S + 1));
@@ -619,20 +724,32 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
             if (uniform) {
                 uint32_t c_out = (c_cur + 1) >> 1;
                 uint64_t total = S * (uint64_t)c_out;
-                k_merkle_level<true><<<grid_for(total, 128), 128, 0, ctx->stream>>>(cur, dst, S, c_cur, c_out, nullptr, nullptr);
+                if (sc) k_merkle_level<true, true><<<grid_for(total, 128), 128, 0, ctx->stream>>>(cur, dst, S, c_cur, c_out, nullptr, nullptr, rc);
+                else k_merkle_level<true, false><<<grid_for(total, 128), 128, 0, ctx->stream>>>(cur, dst, S, c_cur, c_out, nullptr, nullptr, rc);
                 c_cur = c_out;
             } else {
                 const uint64_t *rp_out = lvl_rp + (uint64_t)(l - 1) * (S + 1);
                 uint64_t bound = ((n + ((1ull << l) - 1)) >> l) + S;   // >= sum ceil(n_s/2^l)
-                k_merkle_level<false><<<grid_for(bound, 128), 128, 0, ctx->stream>>>(cur, dst, S, 0, 0, rp_cur, rp_out);
+                if (sc) k_merkle_level<false, true><<<grid_for(bound, 128), 128, 0, ctx->stream>>>(cur, dst, S, 0, 0, rp_cur, rp_out, rc);
+                else k_merkle_level<false, false><<<grid_for(bound, 128), 128, 0, ctx->stream>>>(cur, dst, S, 0, 0, rp_cur, rp_out, rc);
                 rp_cur = rp_out;
             }
             AHV_CHECK_LAUNCH(ctx);
             cur = dst;
         }
     }
-    if (uniform) k_merkle_top<true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty);
-    else k_merkle_top<false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty);
+    const uint64_t top = (ctx->opt_top_max >= 2 && ctx->opt_top_max <= TOP_MAX) ? (uint64_t)ctx->opt_top_max : TOP_MAX;
+    if (top <= 64) {
+        const unsigned g4 = (unsigned)((S + 3) / 4);
+        if (uniform && sc) k_merkle_top_warp<true, true><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
+        else if (uniform) k_merkle_top_warp<true, false><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
+        else if (sc) k_merkle_top_warp<false, true><<<g4, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
+        else k_merkle_top_warp<false, false><<<g4, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
+    } else
+    if (uniform && sc) k_merkle_top<true, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
+    else if (uniform) k_merkle_top<true, false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
+    else if (sc) k_merkle_top<false, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
+    else k_merkle_top<false, false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
@@ -812,8 +929,12 @@ int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, 
     AHV_REQUIRE((d_offsets && d_hexpos && d_rowptr) || n == 0, "offsets / hexpos / session_rowptr is null");
     AHV_TRY(check_sizes(n, S));
     if (S == 0 || n == 0) return AHV_OK;
-    k_chain_capture<<<grid_for(S, 64), 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests,
-                                                             d_parents, d_kind);
+    if (ctx->opt_compress)
+        k_chain_capture<true><<<grid_for(S, 64), 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests,
+                                                                       d_parents, d_kind, SHA_SC);
+    else
+        k_chain_capture<false><<<grid_for(S, 64), 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests,
+                                                                        d_parents, d_kind, SHA_SC);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
@@ -927,13 +1048,13 @@ extern "C" int ahv_merkle_roots_noalloc_dev(ahv_ctx *ctx, const uint8_t *d_diges
             uint8_t *dst = (l & 1) ? bufA : bufB;
             const uint64_t *rp_out = lvl_rp + (uint64_t)(l - 1) * (S + 1);
             const uint64_t bound = ((n + ((1ull << l) - 1)) >> l) + S;
-            k_merkle_level<false><<<grid_for(bound, 128), 128, 0, ctx->stream>>>(cur, dst, S, 0, 0, rp_cur, rp_out);
+            k_merkle_level<false, true><<<grid_for(bound, 128), 128, 0, ctx->stream>>>(cur, dst, S, 0, 0, rp_cur, rp_out, SHA_SC);
             AHV_CHECK_LAUNCH(ctx);
             rp_cur = rp_out;
             cur = dst;
         }
     }
-    k_merkle_top<false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty);
+    k_merkle_top<false, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, SHA_SC);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

@@ -141,7 +141,9 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_block = 128;
     c->opt_fixed_variant = 0;
     c->opt_tree_k = 0;
-    c->opt_top_max = 256;
+    c->opt_top_max = 32;
+    c->opt_compress = 1;
+    c->opt_sigma_variant = 1;
     *out_ctx = c;
     return AHV_OK;
 }
@@ -288,6 +290,12 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "tree_k")) {
         AHV_REQUIRE(value >= 0 && value <= 3, "tree_k must be 0..3");
         ctx->opt_tree_k = value;
+    } else if (!strcmp(key, "sigma_variant")) {
+        AHV_REQUIRE(value == 0 || value == 1, "sigma_variant must be 0 or 1");
+        ctx->opt_sigma_variant = value;
+    } else if (!strcmp(key, "compress")) {
+        AHV_REQUIRE(value == 0 || value == 1, "compress must be 0 or 1");
+        ctx->opt_compress = value;
     } else if (!strcmp(key, "top_max")) {
         AHV_REQUIRE(value >= 2 && value <= 256, "top_max must be 2..256");
         ctx->opt_top_max = value;

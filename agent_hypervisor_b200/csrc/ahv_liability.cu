@@ -35,6 +35,49 @@ k_sigma_eff_rings(const uint32_t *__restrict__ rowptr, const double *__restrict_
     if (out_near) out_near[a] = (uint8_t)near_threshold(se);
 }
 
+// Tiled form (default): a CTA owns 256 consecutive agent rows.  Their edges are one contiguous
+// CSR range, streamed through shared memory in chunks with fully coalesced loads (phase 1: each
+// edge becomes its contribution, bonded or +0.0 when inactive/expired); then every thread adds
+// up the slice of its own row inside the chunk, in CSR order (phase 2).  Order of additions per
+// row is exactly the reference's, so results stay bit-identical; x + (+0.0) == x for every x the
+// running sum can hold (it starts at +0.0 and can never become -0.0).
+constexpr int SIG_ROWS = 256;
+constexpr int SIG_CHUNK = 2048;
+
+__global__ void __launch_bounds__(SIG_ROWS)
+k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
+                  const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
+                  const double *__restrict__ sigma, const double *__restrict__ omega,
+                  const uint8_t *__restrict__ consensus, const uint8_t *__restrict__ current_ring, uint64_t A,
+                  double *__restrict__ out_sigma, uint8_t *__restrict__ out_ring, uint8_t *__restrict__ out_demote,
+                  uint8_t *__restrict__ out_near)
+{
+    __shared__ double v[SIG_CHUNK];
+    const uint32_t tid = threadIdx.x;
+    const uint64_t a0 = (uint64_t)blockIdx.x * SIG_ROWS;
+    const uint64_t a = a0 + tid;
+    const bool valid = a < A;
+    const uint64_t a_last = (a0 + SIG_ROWS < A) ? a0 + SIG_ROWS : A;
+    const uint32_t e_begin = rowptr[a0], e_end = rowptr[a_last];
+    const uint32_t my0 = valid ? rowptr[a] : e_end, my1 = valid ? rowptr[a + 1] : e_end;
+    double contrib = 0.0;
+    for (uint32_t c0 = e_begin; c0 < e_end; c0 += SIG_CHUNK) {
+        const uint32_t c1 = (e_end - c0 > (uint32_t)SIG_CHUNK) ? c0 + SIG_CHUNK : e_end;
+        for (uint32_t e = c0 + tid; e < c1; e += SIG_ROWS)
+            v[e - c0] = vouch_accumulate(0.0, bonded[e], active[e], expiry[e], now);
+        __syncthreads();
+        const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
+        for (uint32_t e = lo; e < hi; ++e) contrib = __dadd_rn(contrib, v[e - c0]);
+        __syncthreads();
+    }
+    if (!valid) return;
+    const double se = sigma_eff_of(sigma[a], omega[a], contrib);
+    out_sigma[a] = se;
+    if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, consensus[a] != 0);
+    if (out_demote) out_demote[a] = (uint8_t)(ring_from_sigma(se, false) > (int)current_ring[a]);
+    if (out_near) out_near[a] = (uint8_t)near_threshold(se);
+}
+
 __global__ void __launch_bounds__(256)
 k_ring_check(const uint8_t *__restrict__ agent_ring, const uint8_t *__restrict__ flags,
              const double *__restrict__ sigma, const uint8_t *__restrict__ consensus,
@@ -65,9 +108,15 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
     AHV_REQUIRE(!d_out_ring || d_consensus, "out_ring needs consensus");
     AHV_REQUIRE(!d_out_demote || d_current_ring, "out_demote needs current_ring");
     AHV_REQUIRE(A < 0xffffffffull, "too many agents (limit 2^32-2)");
-    k_sigma_eff_rings<<<grid_for(A, 256), 256, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma,
-                                                                 d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-                                                                 d_out_ring, d_out_demote, d_out_near);
+    if (ctx->opt_sigma_variant == 0)
+        k_sigma_eff_rings<<<grid_for(A, 256), 256, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma,
+                                                                     d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+                                                                     d_out_ring, d_out_demote, d_out_near);
+    else
+        k_sigma_eff_tiled<<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now,
+                                                                               d_sigma, d_omega, d_consensus, d_current_ring,
+                                                                               A, d_out_sigma, d_out_ring, d_out_demote,
+                                                                               d_out_near);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

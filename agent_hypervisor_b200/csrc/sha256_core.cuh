@@ -160,6 +160,388 @@ AHV_HD void sha256_compress_kw(uint32_t st[8], const KWT &kw)
     st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
 }
 
+// ---------------------------------------------------------------- FMA-pipe variants
+// The ALU pipe (SHF/LOP3/IADD3/PRMT, 64 lanes/clk/SM) is the binding resource of SHA-256 on
+// sm_100; IMAD issues on the FMA pipe and co-issues with it.  These variants move work there.
+// Multipliers arrive at run time (kernel parameter) so ptxas cannot turn them back into
+// shifts/adds.
+struct ShaMults {
+    uint32_t one;              // 1          : a*1 + b      = add
+    uint32_t m25, m14, m29;    // sigma0     : x*2^25 -> (x<<25 | x>>7), x*2^14 -> rotr18, hi(x*2^29) = x>>3
+    uint32_t m15, m13, m22;    // sigma1     : rotr17, rotr19, x>>10
+    uint32_t c;                // SHA_SC (scale constant of sha256_compress_scaled) as a run-time value
+};
+
+inline ShaMults make_sha_mults()
+{
+    ShaMults m = {1u, 1u << 25, 1u << 14, 1u << 29, 1u << 15, 1u << 13, 1u << 22, 0x9E3779B1u};
+    return m;
+}
+
+AHV_HD uint32_t madd(uint32_t a, uint32_t b, uint32_t one)
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+    return d;
+#else
+    return a * one + b;
+#endif
+}
+
+// xor of the two halves of x * m (m = 2^(32-n)) is rotr(x, n)
+AHV_HD void mulwide(uint32_t x, uint32_t m, uint32_t &lo, uint32_t &hi)
+{
+#if defined(__CUDA_ARCH__)
+    unsigned long long p;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(p) : "r"(x), "r"(m));
+    lo = (uint32_t)p;
+    hi = (uint32_t)(p >> 32);
+#else
+    uint64_t p = (uint64_t)x * m;
+    lo = (uint32_t)p;
+    hi = (uint32_t)(p >> 32);
+#endif
+}
+
+AHV_HD uint32_t mulhi(uint32_t x, uint32_t m)
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(d) : "r"(x), "r"(m));
+    return d;
+#else
+    return (uint32_t)(((uint64_t)x * m) >> 32);
+#endif
+}
+
+AHV_HD uint32_t sig0_wide(uint32_t x, const ShaMults &mu)
+{
+    uint32_t l1, h1, l2, h2;
+    mulwide(x, mu.m25, l1, h1);
+    mulwide(x, mu.m14, l2, h2);
+    return (l1 ^ h1 ^ l2) ^ (h2 ^ mulhi(x, mu.m29));
+}
+
+AHV_HD uint32_t sig1_wide(uint32_t x, const ShaMults &mu)
+{
+    uint32_t l1, h1, l2, h2;
+    mulwide(x, mu.m15, l1, h1);
+    mulwide(x, mu.m13, l2, h2);
+    return (l1 ^ h1 ^ l2) ^ (h2 ^ mulhi(x, mu.m22));
+}
+
+// a + b as IMAD.IADD with an immediate multiplier (two register reads, FMA pipe)
+AHV_HD uint32_t madd1(uint32_t a, uint32_t b)
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, 1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+#else
+    return a + b;
+#endif
+}
+
+// Add-site selector: bit set -> that addition is issued as IMAD.IADD (FMA pipe), clear -> plain
+// C addition (the compiler fuses neighbours into IADD3 on the ALU pipe).
+//   round:    bit0 w+K   bit1 h+(w+K)   bit2 +Ch   bit3 +Sig1   bit4 d+=t1   bit5 Sig0+Maj   bit6 t1+t2
+//   schedule: bit7 w+sig1   bit8 +w[i-7]   bit9 +sig0      bit10: sigmas through IMAD.WIDE/HI
+//   bit11: state feed-forward adds      bit12: schedule's plain right shifts as IMAD.HI
+template <uint32_t MASK, int BIT>
+AHV_HD uint32_t add_site(uint32_t a, uint32_t b)
+{
+    return (MASK >> BIT) & 1u ? madd1(a, b) : a + b;
+}
+
+#define AHV_ROUND_SEL(a, b, c, d, e, f, g, h, k, w)                                        \
+    {                                                                                      \
+        uint32_t t1_ = add_site<MASK, 1>(h, add_site<MASK, 0>(w, k));                      \
+        t1_ = add_site<MASK, 2>(t1_, Ch(e, f, g));                                         \
+        t1_ = add_site<MASK, 3>(t1_, Sig1(e));                                             \
+        (d) = add_site<MASK, 4>(d, t1_);                                                   \
+        (h) = add_site<MASK, 6>(t1_, add_site<MASK, 5>(Sig0(a), Maj(a, b, c)));            \
+    }
+
+template <uint32_t MASK>
+AHV_HD void sha256_compress_sel(uint32_t st[8], uint32_t w[16], const ShaMults &mu)
+{
+    const uint32_t K[64] = {AHV_K256_LIST};
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t += 8) {
+        if (t >= 16) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j;
+                const bool wide = (MASK >> 10) & 1u;
+                const bool shr_hi = (MASK >> 12) & 1u;     // plain right shifts as IMAD.HI (FMA pipe)
+                const uint32_t x2 = w[(i - 2) & 15], x15 = w[(i - 15) & 15];
+                const uint32_t s1v = wide ? sig1_wide(x2, mu)
+                                          : (shr_hi ? (rotr32(x2, 17) ^ rotr32(x2, 19) ^ mulhi(x2, mu.m22)) : sig1(x2));
+                const uint32_t s0v = wide ? sig0_wide(x15, mu)
+                                          : (shr_hi ? (rotr32(x15, 7) ^ rotr32(x15, 18) ^ mulhi(x15, mu.m29)) : sig0(x15));
+                w[i & 15] = add_site<MASK, 9>(add_site<MASK, 8>(add_site<MASK, 7>(w[i & 15], s1v), w[(i - 7) & 15]), s0v);
+            }
+        }
+        AHV_ROUND_SEL(a, b, c, d, e, f, g, h, K[t + 0], w[(t + 0) & 15])
+        AHV_ROUND_SEL(h, a, b, c, d, e, f, g, K[t + 1], w[(t + 1) & 15])
+        AHV_ROUND_SEL(g, h, a, b, c, d, e, f, K[t + 2], w[(t + 2) & 15])
+        AHV_ROUND_SEL(f, g, h, a, b, c, d, e, K[t + 3], w[(t + 3) & 15])
+        AHV_ROUND_SEL(e, f, g, h, a, b, c, d, K[t + 4], w[(t + 4) & 15])
+        AHV_ROUND_SEL(d, e, f, g, h, a, b, c, K[t + 5], w[(t + 5) & 15])
+        AHV_ROUND_SEL(c, d, e, f, g, h, a, b, K[t + 6], w[(t + 6) & 15])
+        AHV_ROUND_SEL(b, c, d, e, f, g, h, a, K[t + 7], w[(t + 7) & 15])
+    }
+    st[0] = add_site<MASK, 11>(st[0], a); st[1] = add_site<MASK, 11>(st[1], b);
+    st[2] = add_site<MASK, 11>(st[2], c); st[3] = add_site<MASK, 11>(st[3], d);
+    st[4] = add_site<MASK, 11>(st[4], e); st[5] = add_site<MASK, 11>(st[5], f);
+    st[6] = add_site<MASK, 11>(st[6], g); st[7] = add_site<MASK, 11>(st[7], h);
+}
+
+// ---------------------------------------------------------------- scaled-sum compression
+// ptxas turns "a*1+b" back into an add and then places it itself (mostly IADD3 on the ALU
+// pipe, which SHA-256 already saturates).  To move the additions to the FMA pipe for real,
+// sums are accumulated in a scaled domain: with C odd and C*CI = 1 (mod 2^32),
+//     (x1 + x2 + ... + xn) * C   is a chain of   acc = x_i * C + acc      (IMAD, immediate C)
+// and the final  acc * CI + y  both unscales and adds one more term.  Every step is an IMAD
+// with an immediate multiplier (two register reads), which co-issues with the ALU pipe at
+// ~0.96 IPC (measured), and none of them can be rewritten as an add.
+constexpr uint32_t SHA_SC = 0x9E3779B1u;
+constexpr uint32_t inv32(uint32_t c)
+{
+    uint32_t x = c;                         // Newton: x <- x * (2 - c*x), doubles correct bits
+    for (int i = 0; i < 5; ++i) x *= 2u - c * x;
+    return x;
+}
+constexpr uint32_t SHA_SCI = inv32(SHA_SC);
+static_assert(SHA_SC * SHA_SCI == 1u, "scale constant must be invertible");
+
+AHV_HD uint32_t imad_c(uint32_t a, uint32_t b)        // a*C + b
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, 0x9E3779B1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+#else
+    return a * SHA_SC + b;
+#endif
+}
+
+AHV_HD uint32_t imad_ci(uint32_t a, uint32_t b)       // a*CI + b
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "n"(SHA_SCI), "r"(b));
+    return d;
+#else
+    return a * SHA_SCI + b;
+#endif
+}
+
+AHV_HD uint32_t imad_rk(uint32_t a, uint32_t rc, uint32_t kc)   // a*rc + kc, rc = C at run time, kc immediate
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(rc), "r"(kc));
+    return d;
+#else
+    return a * rc + kc;
+#endif
+}
+
+AHV_HD uint32_t mul_c(uint32_t a)                     // a*C
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mul.lo.u32 %0, %1, 0x9E3779B1;" : "=r"(d) : "r"(a));
+    return d;
+#else
+    return a * SHA_SC;
+#endif
+}
+
+// t1*C = (h + K + w + Ch + Sig1)*C ; e' = d + t1 ; a' = t1 + Maj + Sig0
+#define AHV_ROUND_SC(a, b, c, d, e, f, g, h, k, w)                                 \
+    {                                                                              \
+        uint32_t s_;                                                               \
+        if (VAR & 4) {                                                             \
+            s_ = imad_c(w, imad_rk(h, rc_, kct_.v[ti_]));                          \
+        } else if (VAR & 8) {                                                      \
+            s_ = imad_c((w) + (k), imad_c(h, rc_));                                \
+        } else if (VAR & 2) {                                                      \
+            s_ = imad_c((w) + (k), imad_rk(h, rc_, 0u));                           \
+        } else {                                                                   \
+            s_ = imad_rk(h, rc_, (k) * SHA_SC);                                    \
+            s_ = imad_c(w, s_);                                                    \
+        }                                                                          \
+        s_ = imad_c(Ch(e, f, g), s_);                                              \
+        s_ = imad_c(Sig1(e), s_);                                                  \
+        (d) = imad_ci(s_, d);                                                      \
+        (h) = imad_ci(imad_c(Maj(a, b, c), s_), Sig0(a));                          \
+    }
+
+// rc must hold SHA_SC at run time (kernel parameter), so that the K*C immediates can ride along.
+template <int VAR, class KCT>
+AHV_HD void sha256_compress_scaled_t(uint32_t st[8], uint32_t w[16], uint32_t rc_, const KCT &kct_)
+{
+    const uint32_t K[64] = {AHV_K256_LIST};
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t += 8) {
+        if (t >= 16) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j;
+                if (VAR & 1) {
+                    // w[i] = w[i-16] + (w[i-7] + sig1 + sig0): inner sum scaled, unscale adds w[i-16]
+                    uint32_t z = (VAR & 8) ? imad_c(w[(i - 7) & 15], rc_)       // run-time ZERO addend
+                                           : imad_rk(w[(i - 7) & 15], rc_, 0u); // run-time C: ptxas must not fold C*CI
+                    z = imad_c(sig1(w[(i - 2) & 15]), z);
+                    z = imad_c(sig0(w[(i - 15) & 15]), z);
+                    w[i & 15] = imad_ci(z, w[i & 15]);
+                } else {
+                    w[i & 15] += sig1(w[(i - 2) & 15]) + w[(i - 7) & 15] + sig0(w[(i - 15) & 15]);
+                }
+            }
+        }
+        { const int ti_ = t + 0; AHV_ROUND_SC(a, b, c, d, e, f, g, h, K[t + 0], w[(t + 0) & 15]) }
+        { const int ti_ = t + 1; AHV_ROUND_SC(h, a, b, c, d, e, f, g, K[t + 1], w[(t + 1) & 15]) }
+        { const int ti_ = t + 2; AHV_ROUND_SC(g, h, a, b, c, d, e, f, K[t + 2], w[(t + 2) & 15]) }
+        { const int ti_ = t + 3; AHV_ROUND_SC(f, g, h, a, b, c, d, e, K[t + 3], w[(t + 3) & 15]) }
+        { const int ti_ = t + 4; AHV_ROUND_SC(e, f, g, h, a, b, c, d, K[t + 4], w[(t + 4) & 15]) }
+        { const int ti_ = t + 5; AHV_ROUND_SC(d, e, f, g, h, a, b, c, K[t + 5], w[(t + 5) & 15]) }
+        { const int ti_ = t + 6; AHV_ROUND_SC(c, d, e, f, g, h, a, b, K[t + 6], w[(t + 6) & 15]) }
+        { const int ti_ = t + 7; AHV_ROUND_SC(b, c, d, e, f, g, h, a, K[t + 7], w[(t + 7) & 15]) }
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+
+struct NoKCT {
+    uint32_t v[1];
+};
+
+template <int VAR>
+AHV_HD void sha256_compress_scaled_v(uint32_t st[8], uint32_t w[16], uint32_t rc_)
+{
+    const NoKCT none = {{0u}};
+    sha256_compress_scaled_t<VAR>(st, w, rc_, none);
+}
+
+AHV_HD void sha256_compress_scaled(uint32_t st[8], uint32_t w[16], uint32_t rc_)
+{
+    sha256_compress_scaled_v<1>(st, w, rc_);
+}
+
+// K[t]*C table for the VAR&4 form (K folded into the chain's first IMAD as a constant-bank addend)
+constexpr KW64 make_kc_table()
+{
+    KW64 r = {};
+    for (int t = 0; t < 64; ++t) r.v[t] = K256_TABLE[t] * SHA_SC;
+    return r;
+}
+
+// (K+W)*C table for a padding-only block, for sha256_compress_kw_scaled
+constexpr KW64 make_kw_pad_scaled(uint64_t bitlen)
+{
+    KW64 r = make_kw_pad(bitlen);
+    for (int t = 0; t < 64; ++t) r.v[t] *= SHA_SC;
+    return r;
+}
+
+#define AHV_ROUND_SCKW(a, b, c, d, e, f, g, h, kwc)                                \
+    {                                                                              \
+        uint32_t s_ = imad_rk(h, rc_, 0u) + (kwc);                                 \
+        s_ = imad_c(Ch(e, f, g), s_);                                              \
+        s_ = imad_c(Sig1(e), s_);                                                  \
+        (d) = imad_ci(s_, d);                                                      \
+        (h) = imad_ci(imad_c(Maj(a, b, c), s_), Sig0(a));                          \
+    }
+
+// Padding-only block in the scaled-sum formulation; kwc.v[t] = (K[t] + W[t]) * C.
+template <class KWT>
+AHV_HD void sha256_compress_kw_scaled(uint32_t st[8], const KWT &kwc, uint32_t rc_)
+{
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t += 8) {
+        AHV_ROUND_SCKW(a, b, c, d, e, f, g, h, kwc.v[t + 0])
+        AHV_ROUND_SCKW(h, a, b, c, d, e, f, g, kwc.v[t + 1])
+        AHV_ROUND_SCKW(g, h, a, b, c, d, e, f, kwc.v[t + 2])
+        AHV_ROUND_SCKW(f, g, h, a, b, c, d, e, kwc.v[t + 3])
+        AHV_ROUND_SCKW(e, f, g, h, a, b, c, d, kwc.v[t + 4])
+        AHV_ROUND_SCKW(d, e, f, g, h, a, b, c, kwc.v[t + 5])
+        AHV_ROUND_SCKW(c, d, e, f, g, h, a, b, kwc.v[t + 6])
+        AHV_ROUND_SCKW(b, c, d, e, f, g, h, a, kwc.v[t + 7])
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+
+// Compression policies: which formulation a kernel uses.  Native = plain additions (ptxas keeps
+// most of them on the ALU pipe); Scaled = additions as IMAD chains on the FMA pipe (rc = SHA_SC
+// passed at run time).  Both give identical results (tests/test_hostemu.py, GPU parity tests).
+struct CompressNative {
+    AHV_HD void block(uint32_t st[8], uint32_t w[16]) const { sha256_compress(st, w); }
+    template <class KWT>
+    AHV_HD void pad(uint32_t st[8], const KWT &kw) const { sha256_compress_kw(st, kw); }
+    AHV_HD void node_pad(uint32_t st[8]) const
+    {
+        constexpr KW64 kw = make_kw_pad(1024);
+        sha256_compress_kw(st, kw);
+    }
+    static constexpr bool scaled = false;
+};
+
+struct CompressScaled {
+    uint32_t rc;
+    AHV_HD void block(uint32_t st[8], uint32_t w[16]) const { sha256_compress_scaled_v<3>(st, w, rc); }
+    template <class KWT>
+    AHV_HD void pad(uint32_t st[8], const KWT &kwc) const { sha256_compress_kw_scaled(st, kwc, rc); }
+    AHV_HD void node_pad(uint32_t st[8]) const
+    {
+        constexpr KW64 kwc = make_kw_pad_scaled(1024);
+        sha256_compress_kw_scaled(st, kwc, rc);
+    }
+    static constexpr bool scaled = true;
+};
+
+// 3-register IMAD form (multiplier in a register): measured slower (dispatch stalls), kept for the lab
+#define AHV_ROUND_IMAD(a, b, c, d, e, f, g, h, k, w)                       \
+    {                                                                      \
+        uint32_t t1_ = madd(h, madd(w, k, one_), one_);                    \
+        t1_ = madd(t1_, Ch(e, f, g), one_);                                \
+        t1_ = madd(t1_, Sig1(e), one_);                                    \
+        (d) = madd(d, t1_, one_);                                          \
+        (h) = madd(t1_, madd(Sig0(a), Maj(a, b, c), one_), one_);          \
+    }
+
+AHV_HD void sha256_compress_imad(uint32_t st[8], uint32_t w[16], const ShaMults &mu)
+{
+    const uint32_t K[64] = {AHV_K256_LIST};
+    const uint32_t one_ = mu.one;
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+    for (int t = 0; t < 64; t += 8) {
+        if (t >= 16) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j;
+                w[i & 15] = madd(madd(madd(w[i & 15], sig1(w[(i - 2) & 15]), one_), w[(i - 7) & 15], one_),
+                                 sig0(w[(i - 15) & 15]), one_);
+            }
+        }
+        AHV_ROUND_IMAD(a, b, c, d, e, f, g, h, K[t + 0], w[(t + 0) & 15])
+        AHV_ROUND_IMAD(h, a, b, c, d, e, f, g, K[t + 1], w[(t + 1) & 15])
+        AHV_ROUND_IMAD(g, h, a, b, c, d, e, f, K[t + 2], w[(t + 2) & 15])
+        AHV_ROUND_IMAD(f, g, h, a, b, c, d, e, K[t + 3], w[(t + 3) & 15])
+        AHV_ROUND_IMAD(e, f, g, h, a, b, c, d, K[t + 4], w[(t + 4) & 15])
+        AHV_ROUND_IMAD(d, e, f, g, h, a, b, c, K[t + 5], w[(t + 5) & 15])
+        AHV_ROUND_IMAD(c, d, e, f, g, h, a, b, K[t + 6], w[(t + 6) & 15])
+        AHV_ROUND_IMAD(b, c, d, e, f, g, h, a, K[t + 7], w[(t + 7) & 15])
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+
 // ---------------------------------------------------------------- hex expansion
 // 4 nibble-valued bytes -> 4 lowercase hex ASCII bytes.
 AHV_HD uint32_t nib2ascii(uint32_t x)
@@ -178,20 +560,25 @@ AHV_HD void hex_expand(uint32_t v, uint32_t &w0, uint32_t &w1)
 }
 
 // audit/delta.py:130 : sha256((left_hex + right_hex).encode()) on state-word digests.
-AHV_HD void merkle_node(const uint32_t l[8], const uint32_t r[8], uint32_t out[8])
+template <class P>
+AHV_HD void merkle_node(const uint32_t l[8], const uint32_t r[8], uint32_t out[8], const P &cp)
 {
     uint32_t st[8], w[16];
     sha256_init(st);
 #pragma unroll
     for (int i = 0; i < 8; ++i) hex_expand(l[i], w[2 * i], w[2 * i + 1]);
-    sha256_compress(st, w);
+    cp.block(st, w);
 #pragma unroll
     for (int i = 0; i < 8; ++i) hex_expand(r[i], w[2 * i], w[2 * i + 1]);
-    sha256_compress(st, w);
-    constexpr KW64 kw = make_kw_pad(1024);
-    sha256_compress_kw(st, kw);
+    cp.block(st, w);
+    cp.node_pad(st);
 #pragma unroll
     for (int i = 0; i < 8; ++i) out[i] = st[i];
+}
+
+AHV_HD void merkle_node(const uint32_t l[8], const uint32_t r[8], uint32_t out[8])
+{
+    merkle_node(l, r, out, CompressNative());
 }
 
 // ---------------------------------------------------------------- digest <-> memory
@@ -245,7 +632,8 @@ struct MsgReader {
 
 // SHA-256 of len bytes at p (any alignment).  One compress copy: full blocks take the
 // fast word path, the final one or two blocks build padding per word.
-AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8])
+template <class P>
+AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8], const P &cp)
 {
     MsgReader rd;
     rd.init(p);
@@ -300,8 +688,13 @@ AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8])
                 w[15] = (uint32_t)bits;
             }
         }
-        sha256_compress(st, w);
+        cp.block(st, w);
     }
+}
+
+AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8])
+{
+    sha256_message(p, len, st, CompressNative());
 }
 
 }  // namespace ahv

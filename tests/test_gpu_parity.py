@@ -96,8 +96,18 @@ def test_golden_session_commit(ctx, audit_golden, n):
     assert r2[0].tobytes().hex() == g["root"] and e2[0] == 0
 
 
-def test_merkle_sizes_vs_oracle(ctx):
-    """Every size through the in-CTA top kernel (<=256) and the global level steps (>256), ragged."""
+@pytest.mark.parametrize("top_max,compress", [(32, 1), (256, 1), (2, 1), (64, 0), (128, 0)])
+def test_merkle_sizes_vs_oracle(ctx, top_max, compress):
+    """Every size through both tree-finish kernels (warp per session <=64, CTA per session <=256),
+    the global level steps, and both compression formulations; ragged sessions."""
+    ctx.set_option("top_max", top_max); ctx.set_option("compress", compress)
+    try:
+        _merkle_sizes(ctx)
+    finally:
+        ctx.set_option("top_max", 32); ctx.set_option("compress", 1)
+
+
+def _merkle_sizes(ctx):
     rng = np.random.default_rng(5)
     sizes = list(range(0, 70)) + [127, 128, 129, 255, 256, 257, 258, 511, 512, 513, 1000, 1023, 1024, 1025, 2049, 5000]
     rng.shuffle(sizes)
@@ -302,17 +312,48 @@ def test_sigma_eff_golden_graphs(ctx, liability_golden):
         assert list(ring) == gr["ring"] and [bool(x) for x in dem] == gr["demote"]
 
 
-def test_sigma_eff_config4_shape_vs_oracle(ctx):
+@pytest.mark.parametrize("variant", [1, 0])
+def test_sigma_eff_config4_shape_vs_oracle(ctx, variant):
     g = workloads.config4_graph(50_000, 500_000)
-    got = ctx.sigma_eff_rings(g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"],
-                              g["consensus"], g["current_ring"])
+    # a few very long rows (beyond one shared-memory chunk) and NaN / inf / -0.0 amounts
+    g["bonded"][:20] = [float("nan"), float("inf"), -0.0, 0.0, 1e308, 1e308, -1e308, 5e-324, 1.0, -1.0] * 2
+    ctx.set_option("sigma_variant", variant)
+    try:
+        got = ctx.sigma_eff_rings(g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"],
+                                  g["consensus"], g["current_ring"])
+    finally:
+        ctx.set_option("sigma_variant", 1)
     want = co.sigma_eff_rings(g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"],
                               g["consensus"], g["current_ring"])
-    rel = np.abs(got[0] - want[0]) / np.maximum(np.abs(want[0]), 1e-300)
+    fin = np.isfinite(want[0])
+    rel = np.abs(got[0][fin] - want[0][fin]) / np.maximum(np.abs(want[0][fin]), 1e-300)
     assert rel.max() <= SIGMA_REL_TOL
-    assert np.array_equal(got[0], want[0])                 # sequential fp64, no FMA: bit-identical
+    assert np.array_equal(got[0], want[0], equal_nan=True)  # sequential fp64, no FMA: bit-identical
     for a, b in zip(got[1:], want[1:]):
         assert np.array_equal(a, b)                        # rings, demote flags, near-threshold list
+
+
+def test_sigma_eff_long_and_empty_rows(ctx):
+    """Rows far longer than one shared-memory chunk (2048 edges), empty rows, a partial last CTA."""
+    rng = np.random.default_rng(4)
+    deg = np.concatenate([[5000, 0, 0, 3000, 1, 2047, 2048, 2049, 0, 9000], rng.integers(0, 30, 700)])
+    A = len(deg)
+    rowptr = np.concatenate([[0], np.cumsum(deg)]).astype(np.uint32)
+    E = int(rowptr[-1])
+    bonded = rng.uniform(0, 1e-3, E)
+    active = (rng.random(E) < 0.8).astype(np.uint8)
+    expiry = np.where(rng.random(E) < 0.5, lo.EXPIRY_NONE, rng.integers(0, 2000, E)).astype(np.int64)
+    args = (rowptr, bonded, active, expiry, 1000, rng.random(A), rng.choice([0.2, 0.65, 0.95], A),
+            (rng.random(A) < 0.5).astype(np.uint8), rng.integers(1, 4, A).astype(np.uint8))
+    want = co.sigma_eff_rings(*args)
+    for variant in (1, 0):
+        ctx.set_option("sigma_variant", variant)
+        try:
+            got = ctx.sigma_eff_rings(*args)
+        finally:
+            ctx.set_option("sigma_variant", 1)
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b)
 
 
 def test_ring_check_grid_and_dropin(ctx, liability_golden):

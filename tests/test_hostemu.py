@@ -94,3 +94,33 @@ def test_device_liability_arithmetic(emu, liability_golden):
                                 expiry.ctypes.data_as(C.POINTER(C.c_int64)), n, 1000, sigma, omega)
         assert got == want[0]
     assert emu.emu_near(0.6) and emu.emu_near(0.95) and emu.emu_near(0.6000003) and not emu.emu_near(0.61)
+
+
+def test_compress_variants_agree(emu):
+    """The FMA-pipe formulations (adds as IMAD, sigmas as IMAD.WIDE/HI) are the same function."""
+    rng = np.random.default_rng(9)
+    for _ in range(200):
+        blk = rng.integers(0, 2**32, 16, dtype=np.uint32)
+        out = np.zeros(40, np.uint32)
+        emu.emu_compress_variants(blk.ctypes.data_as(C.POINTER(C.c_uint32)), out.ctypes.data_as(C.POINTER(C.c_uint32)))
+        for v in (1, 2, 3, 4):    # IMAD adds, WIDE/HI sigmas, scaled-sum, scaled-sum with K table
+            assert np.array_equal(out[:8], out[8 * v:8 * v + 8]), v
+
+
+def test_scaled_policy_matches_hashlib(emu):
+    """The scaled-sum compression policy (what the kernels run by default) end to end."""
+    rng = np.random.default_rng(17)
+    buf = rng.integers(0, 256, 40000, dtype=np.uint8)
+    out = np.zeros(32, np.uint8)
+    for ln in list(range(0, 130)) + [255, 256, 257, 1000, 4096, 16384]:
+        for a in (0, 1, 3, 16):
+            emu.emu_sha256_scaled(C.cast(buf.ctypes.data + a, u8p), ln, out.ctypes.data_as(u8p))
+            assert out.tobytes() == hashlib.sha256(buf[a:a + ln].tobytes()).digest(), (ln, a)
+    for _ in range(20):
+        l = rng.integers(0, 256, 32, dtype=np.uint8); r = rng.integers(0, 256, 32, dtype=np.uint8)
+        emu.emu_node_scaled(l.ctypes.data_as(u8p), r.ctypes.data_as(u8p), out.ctypes.data_as(u8p))
+        assert out.tobytes() == hashlib.sha256((l.tobytes().hex() + r.tobytes().hex()).encode()).digest()
+        m = rng.integers(0, 256, 256, dtype=np.uint8)
+        for scaled in (0, 1):
+            emu.emu_sha256_fixed256(m.ctypes.data_as(u8p), scaled, out.ctypes.data_as(u8p))
+            assert out.tobytes() == hashlib.sha256(m.tobytes()).digest()

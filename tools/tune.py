@@ -58,6 +58,15 @@ def main():
     comp_leaf = n * 5
 
     res = {}
+    for comp in (0, 1):
+        ctx.set_option("compress", comp)
+        best, avg = timed(ctx, lambda: ctx.sha256_batch_dev(d["arena"], arena.nbytes, 0, n, FL, d["digs"]))
+        res[f"leaf_fixed_compress{comp}"] = {"best_ms": best, "Gcomp_s": comp_leaf / best / 1e6}
+        b2, _ = timed(ctx, lambda: ctx.commit_dev(d["arena"], arena.nbytes, 0, FL, 0, S, n, L, L, d["digs"], d["roots"], d["empty"]), reps=3)
+        b3, _ = timed(ctx, lambda: ctx.sha256_batch_dev(d["arena"], arena.nbytes, d["offs"], n, 0, d["digs"]), reps=3)
+        print(f"compress={comp}: leaf fixed {best:.3f} ms ({comp_leaf/best/1e6:.2f} Gcomp/s), commit {b2:.3f} ms, leaf var {b3:.3f} ms", flush=True)
+        res[f"commit_compress{comp}"] = {"best_ms": b2}
+        res[f"leaf_var_compress{comp}"] = {"best_ms": b3}
     for variant in (0, 1):
         for block in (64, 128, 256):
             ctx.set_option("fixed_variant", variant); ctx.set_option("block", block)
@@ -78,7 +87,7 @@ def main():
     res["commit_uniform"] = {"best_ms": best, "avg_ms": avg}
     print(f"commit (leaf+tree uniform): best {best:.3f} ms", flush=True)
     ctx.sha256_batch_dev(d["arena"], arena.nbytes, 0, n, FL, d["digs"])
-    for top in (256, 128, 64, 32, 16):
+    for top in (256, 64, 32, 16, 8, 4, 2):
         ctx.set_option("top_max", top)
         # tree alone = commit minus leaves is not separable through the ABI; time the ragged tree and the uniform commit
         best, avg = timed(ctx, lambda: ctx.commit_dev(d["arena"], arena.nbytes, 0, FL, 0, S, n, L, L, d["digs"], d["roots"], d["empty"]), reps=3)
@@ -86,7 +95,7 @@ def main():
         b2, _ = timed(ctx, lambda: ctx.merkle_roots_dev(d["digs"], d["rp"], S, n, L, d["roots2"], d["empty"]), reps=3)
         res[f"tree_ragged_top{top}"] = {"best_ms": b2, "Gcomp_s": node_c / b2 / 1e6}
         print(f"top_max {top}: commit {best:.3f} ms, ragged tree {b2:.3f} ms ({node_c/b2/1e6:.2f} Gcomp/s)", flush=True)
-    ctx.set_option("top_max", 256)
+    ctx.set_option("top_max", 32)
     best, avg = timed(ctx, lambda: ctx.merkle_roots_dev(d["digs"], d["rp"], S, n, L, d["roots2"], d["empty"]))
     res["tree_ragged"] = {"best_ms": best, "avg_ms": avg, "Gcomp_s": node_c / best / 1e6}
     print(f"tree ragged path: best {best:.3f} ms -> {node_c/best/1e6:.2f} Gcomp/s", flush=True)
