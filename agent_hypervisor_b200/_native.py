@@ -69,6 +69,7 @@ SIGNATURES = {
     "ahv_verify_chains": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahv_verify_chains_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _u64, _u64, _vp,
                                         _vp, _vp, _vp, _vp, _vp]),
+    "ahv_audit_sessions": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahv_chain_capture": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_chain_capture_dev": (C.c_int, [_vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp]),
     "ahv_sigma_eff_rings": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,
@@ -275,6 +276,31 @@ class Context:
                 int(uniform_leaves), _ptr(exp), _ptr(verdict), _ptr(first_bad), _ptr(digs), _ptr(roots),
                 _ptr(match)), "ahv_verify_chains")
         return {"verdict": verdict, "first_bad": first_bad, "digests": digs, "roots": roots, "root_match": match}
+
+    def audit_sessions(self, arena, offsets, parent_digests, parent_kind, session_rowptr=None, fixed_len: int = 0,
+                       uniform_leaves: int = 0, n_sessions: Optional[int] = None, want_digests: bool = True, out=None):
+        """Commit + verify on one upload (ahv_audit_sessions).  ``out`` may supply preallocated
+        (e.g. pinned) result arrays: dict with digests/roots/empty/verdict/first_bad/root_match."""
+        arena = _arr(arena, np.uint8)
+        offsets = _arr(offsets, np.uint64)
+        par = _arr(parent_digests, np.uint8)
+        kind = _arr(parent_kind, np.uint8)
+        rp = _arr(session_rowptr, np.uint64)
+        S = (len(rp) - 1) if rp is not None else int(n_sessions)
+        n = int(rp[-1]) if rp is not None else S * int(uniform_leaves)
+        o = dict(out or {})
+        o.setdefault("digests", np.empty((n, 32), dtype=np.uint8) if want_digests else None)
+        o.setdefault("roots", np.zeros((S, 32), dtype=np.uint8))
+        o.setdefault("empty", np.zeros(S, dtype=np.uint8))
+        o.setdefault("verdict", np.ones(S, dtype=np.uint8))
+        o.setdefault("first_bad", np.full(S, -1, dtype=np.int64))
+        o.setdefault("root_match", np.zeros(S, dtype=np.uint8))
+        with self._lock:
+            self._check(self.lib.ahv_audit_sessions(
+                self.h, _ptr(arena), _ptr(offsets), int(fixed_len), _ptr(par), _ptr(kind), _ptr(rp), S,
+                int(uniform_leaves), _ptr(o["digests"]), _ptr(o["roots"]), _ptr(o["empty"]), _ptr(o["verdict"]),
+                _ptr(o["first_bad"]), _ptr(o["root_match"])), "ahv_audit_sessions")
+        return o
 
     def chain_capture(self, arena: np.ndarray, offsets, hexpos, session_rowptr):
         """Patches ``arena`` IN PLACE; returns (digests, parent_digests, parent_kind)."""

@@ -391,7 +391,7 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
              uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc)
 {
     const typename Pol<SC>::type cp = Pol<SC>::make(rc);
-    __shared__ uint32_t buf[2][TOP_MAX / 2 + 1][8 + 1];   // +1 word pad against bank conflicts
+    __shared__ uint32_t buf[2][TOP_MAX][8 + 1];   // +1 word pad against bank conflicts
     const uint64_t s = blockIdx.x;
     if (s >= S) return;
     uint64_t in0;
@@ -415,25 +415,17 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
                 reinterpret_cast<const uint32_t *>(in + 32 * in0)[threadIdx.x];
         return;
     }
-    // first step reads global memory, later steps ping-pong in shared memory
+    // stage the level in shared memory, then pair-hash level by level (one copy of the node code)
     uint32_t cur = 0;
-    uint32_t c_out = (c + 1) >> 1;
-    for (uint32_t k = threadIdx.x; k < c_out; k += blockDim.x) {
-        uint32_t l[8], r[8], d[8];
-        load_digest(in + 32 * (in0 + 2 * k), l);
-        if (2 * k + 1 < c) load_digest(in + 32 * (in0 + 2 * k + 1), r);
-        else {
-#pragma unroll
-            for (int q = 0; q < 8; ++q) r[q] = l[q];
-        }
-        merkle_node(l, r, d, cp);
+    for (uint32_t k = threadIdx.x; k < c; k += blockDim.x) {
+        uint32_t d[8];
+        load_digest(in + 32 * (in0 + k), d);
 #pragma unroll
         for (int q = 0; q < 8; ++q) buf[cur][k][q] = d[q];
     }
-    c = c_out;
     __syncthreads();
     while (c > 1) {
-        c_out = (c + 1) >> 1;
+        const uint32_t c_out = (c + 1) >> 1;
         for (uint32_t k = threadIdx.x; k < c_out; k += blockDim.x) {
             uint32_t l[8], r[8], d[8];
             const uint32_t kr = (2 * k + 1 < c) ? 2 * k + 1 : 2 * k;
@@ -466,7 +458,7 @@ k_merkle_top_warp(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, c
                   uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc)
 {
     const typename Pol<SC>::type cp = Pol<SC>::make(rc);
-    __shared__ uint32_t buf[4][2][32][8 + 1];
+    __shared__ uint32_t buf[4][2][64][8 + 1];
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint64_t s = (uint64_t)blockIdx.x * 4 + wid;
     if (s >= S) return;
@@ -491,23 +483,15 @@ k_merkle_top_warp(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, c
         return;
     }
     uint32_t cur = 0;
-    uint32_t c_out = (c + 1) >> 1;                       // <= 32: one node per lane
-    if (lane < c_out) {
-        uint32_t l[8], r[8], d[8];
-        load_digest(in + 32 * (in0 + 2 * lane), l);
-        if (2 * lane + 1 < c) load_digest(in + 32 * (in0 + 2 * lane + 1), r);
-        else {
+    for (uint32_t k = lane; k < c; k += 32) {            // c <= 64
+        uint32_t d[8];
+        load_digest(in + 32 * (in0 + k), d);
 #pragma unroll
-            for (int q = 0; q < 8; ++q) r[q] = l[q];
-        }
-        merkle_node(l, r, d, cp);
-#pragma unroll
-        for (int q = 0; q < 8; ++q) buf[wid][cur][lane][q] = d[q];
+        for (int q = 0; q < 8; ++q) buf[wid][cur][k][q] = d[q];
     }
-    c = c_out;
     __syncwarp();
     while (c > 1) {
-        c_out = (c + 1) >> 1;
+        const uint32_t c_out = (c + 1) >> 1;             // <= 32: one node per lane
         if (lane < c_out) {
             uint32_t l[8], r[8], d[8];
             const uint32_t kr = (2 * lane + 1 < c) ? 2 * lane + 1 : 2 * lane;
@@ -678,9 +662,19 @@ int run_leaves(ahv_ctx *ctx, const uint8_t *d_arena, const uint64_t *d_offsets, 
 }
 
 // levels reduced by global level steps before the in-CTA top kernel takes over
-uint32_t global_levels(const ahv_ctx *ctx, uint64_t max_leaves)
+// Level width at which a session's tree is finished inside one warp / CTA.  Dense global level
+// steps run at full ALU rate as long as a level still has tens of thousands of nodes over all
+// sessions, so with many sessions the hand-over comes late (2 nodes), with few it comes early (64).
+uint64_t tree_top(const ahv_ctx *ctx, uint64_t S)
 {
-    const uint64_t top = (ctx->opt_top_max >= 2 && ctx->opt_top_max <= TOP_MAX) ? (uint64_t)ctx->opt_top_max : TOP_MAX;
+    if (ctx->opt_top_max >= 2 && ctx->opt_top_max <= (int64_t)TOP_MAX) return (uint64_t)ctx->opt_top_max;
+    uint64_t t = 16384 / (S ? S : 1);
+    return t < 2 ? 2 : (t > 64 ? 64 : t);
+}
+
+uint32_t global_levels(const ahv_ctx *ctx, uint64_t S, uint64_t max_leaves)
+{
+    const uint64_t top = tree_top(ctx, S);
     uint32_t l = 0;
     while (((max_leaves + ((1ull << l) - 1)) >> l) > top) ++l;
     return l;
@@ -688,7 +682,7 @@ uint32_t global_levels(const ahv_ctx *ctx, uint64_t max_leaves)
 
 uint64_t tree_scratch_bytes(const ahv_ctx *ctx, uint64_t n, uint64_t S, uint64_t max_leaves, bool uniform)
 {
-    const uint32_t G = global_levels(ctx, max_leaves);
+    const uint32_t G = global_levels(ctx, S, max_leaves);
     if (G == 0) return 0;
     uint64_t b = 2 * pad256(32ull * (n / 2 + S + 1));
     if (!uniform) b += pad256(8ull * G * (S + 1));
@@ -700,7 +694,7 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
              uint64_t uniform, uint64_t max_leaves, uint8_t *d_roots, uint8_t *d_empty)
 {
     if (S == 0) return AHV_OK;
-    const uint32_t G = global_levels(ctx, max_leaves);
+    const uint32_t G = global_levels(ctx, S, max_leaves);
     const uint8_t *cur = d_digests;
     const uint64_t *rp_cur = d_rowptr;
     uint32_t c_cur = (uint32_t)uniform;
@@ -738,7 +732,7 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
             cur = dst;
         }
     }
-    const uint64_t top = (ctx->opt_top_max >= 2 && ctx->opt_top_max <= TOP_MAX) ? (uint64_t)ctx->opt_top_max : TOP_MAX;
+    const uint64_t top = tree_top(ctx, S);
     if (top <= 64) {
         const unsigned g4 = (unsigned)((S + 3) / 4);
         if (uniform && sc) k_merkle_top_warp<true, true><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
@@ -1022,7 +1016,7 @@ extern "C" int ahv_merkle_roots_noalloc_dev(ahv_ctx *ctx, const uint8_t *d_diges
     AHV_TRY(check_sizes(n, S));
     if (S == 0) return AHV_OK;
 
-    const uint32_t G = global_levels(ctx, max_leaves);
+    const uint32_t G = global_levels(ctx, S, max_leaves);
     const uint64_t lvl_bytes = pad256(32ull * (n / 2 + S + 1));
     const uint64_t rp_bytes = G ? pad256(8ull * G * (S + 1)) : 0;
     const uint64_t need = G ? 2 * lvl_bytes + rp_bytes : 0;

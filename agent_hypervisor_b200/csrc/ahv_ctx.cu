@@ -131,6 +131,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->total_mem = prop.totalGlobalMem;
     AHV_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     AHV_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    AHV_CUDA(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 4; ++i) AHV_CUDA(cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming));
     for (int i = 0; i < AHV_MAX_TIMERS; ++i) {
         AHV_CUDA(cudaEventCreate(&c->t_start[i]));
@@ -141,7 +142,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_block = 128;
     c->opt_fixed_variant = 0;
     c->opt_tree_k = 0;
-    c->opt_top_max = 32;
+    c->opt_top_max = 0;
     c->opt_compress = 1;
     c->opt_sigma_variant = 1;
     *out_ctx = c;
@@ -154,6 +155,7 @@ void ahv_destroy(ahv_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaStreamSynchronize(ctx->copy_stream);
+    cudaStreamSynchronize(ctx->d2h_stream);
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->io) cudaFree(ctx->io);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(ctx->ev_copy[i]);
@@ -163,6 +165,7 @@ void ahv_destroy(ahv_ctx *ctx)
     }
     cudaStreamDestroy(ctx->stream);
     cudaStreamDestroy(ctx->copy_stream);
+    cudaStreamDestroy(ctx->d2h_stream);
     delete ctx;
 }
 
@@ -171,6 +174,7 @@ int ahv_sync(ahv_ctx *ctx)
     AHV_TRY(use_device(ctx));
     AHV_CUDA(cudaStreamSynchronize(ctx->copy_stream));
     AHV_CUDA(cudaStreamSynchronize(ctx->stream));
+    AHV_CUDA(cudaStreamSynchronize(ctx->d2h_stream));
     return AHV_OK;
 }
 
@@ -297,7 +301,7 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
         AHV_REQUIRE(value == 0 || value == 1, "compress must be 0 or 1");
         ctx->opt_compress = value;
     } else if (!strcmp(key, "top_max")) {
-        AHV_REQUIRE(value >= 2 && value <= 256, "top_max must be 2..256");
+        AHV_REQUIRE(value == 0 || (value >= 2 && value <= 256), "top_max must be 0 (auto) or 2..256");
         ctx->opt_top_max = value;
     } else if (!strcmp(key, "leaf_timer")) {
         AHV_REQUIRE(value == 0 || (value > 0 && value + 16 <= AHV_MAX_TIMERS), "leaf_timer base must leave 16 slots");

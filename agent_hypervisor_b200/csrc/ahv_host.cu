@@ -224,6 +224,130 @@ int ahv_verify_chains(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offset
     return st.finish();
 }
 
+// Commit + verify of one batch on ONE upload: leaf digests and Merkle roots (audit/delta.py:63,
+// 117-134), then a full verify pass (re-hash, parent links, root rebuild and compare against the
+// roots just committed; audit/delta.py:136-152, audit/commitment.py:59-64).  For fixed-size deltas
+// in uniform sessions the batch is cut into session chunks and pipelined: chunk k+1 is copied in
+// while chunk k is hashed and chunk k-1's results are copied out (three streams, PCIe full duplex).
+int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
+                       const uint8_t *parents, const uint8_t *kind, const uint64_t *rowptr, uint64_t S,
+                       uint64_t uniform, uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty,
+                       uint8_t *out_verdict, int64_t *out_first_bad, uint8_t *out_match)
+{
+    AHV_TRY(use_device(ctx));
+    if (S == 0) return AHV_OK;
+    AHV_REQUIRE(out_roots && out_verdict, "out_roots / out_verdict is null");
+    uint64_t n = 0, maxl = 0, ab = 0;
+    AHV_TRY(session_shape(rowptr, S, uniform, &n, &maxl));
+    AHV_REQUIRE(offsets || fixed_len > 0 || n == 0, "offsets is NULL and fixed_len is 0");
+    AHV_REQUIRE((parents && kind) || n == 0, "parent_digests / parent_kind is null");
+    AHV_TRY(arena_extent(offsets, n, fixed_len, &ab));
+    AHV_REQUIRE(arena || ab == 0, "arena is null");
+    if (n == 0) {   // only empty sessions
+        memset(out_roots, 0, 32 * S);
+        if (out_empty) memset(out_empty, 1, S);
+        memset(out_verdict, 1, S);
+        if (out_first_bad) for (uint64_t s = 0; s < S; ++s) out_first_bad[s] = -1;
+        if (out_match) memset(out_match, 0, S);
+        return AHV_OK;
+    }
+    AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(8 * (S + 1)) + 2 * p256(32 * n) + p256(n) +
+                                2 * p256(32 * S) + 3 * p256(S) + p256(8 * S)));
+    uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);
+    uint64_t *d_off = offsets ? (uint64_t *)io_take(ctx, 8 * (n + 1)) : nullptr;
+    uint64_t *d_rp = uniform ? nullptr : (uint64_t *)io_take(ctx, 8 * (S + 1));
+    uint8_t *d_par = (uint8_t *)io_take(ctx, 32 * n);
+    uint8_t *d_kind = (uint8_t *)io_take(ctx, n);
+    uint8_t *d_dig = (uint8_t *)io_take(ctx, 32 * n);
+    uint8_t *d_roots = (uint8_t *)io_take(ctx, 32 * S);
+    uint8_t *d_roots_v = (uint8_t *)io_take(ctx, 32 * S);
+    uint8_t *d_empty = (uint8_t *)io_take(ctx, S);
+    uint8_t *d_verdict = (uint8_t *)io_take(ctx, S);
+    uint8_t *d_match = (uint8_t *)io_take(ctx, S);
+    int64_t *d_fb = (int64_t *)io_take(ctx, 8 * S);
+    if (!d_arena || (offsets && !d_off) || (!uniform && !d_rp) || !d_par || !d_kind || !d_dig || !d_roots ||
+        !d_roots_v || !d_empty || !d_verdict || !d_match || !d_fb) {
+        set_error("internal: staging slab too small");
+        return AHV_E_NOMEM;
+    }
+
+    const bool pipelined = uniform && !offsets && fixed_len > 0 && S >= 64;
+    if (!pipelined) {
+        cudaStream_t st = ctx->stream;
+        AHV_CUDA(cudaMemcpyAsync(d_arena, arena, ab, cudaMemcpyHostToDevice, st));
+        if (offsets) AHV_CUDA(cudaMemcpyAsync(d_off, offsets, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+        if (!uniform) AHV_CUDA(cudaMemcpyAsync(d_rp, rowptr, 8 * (S + 1), cudaMemcpyHostToDevice, st));
+        AHV_CUDA(cudaMemcpyAsync(d_par, parents, 32 * n, cudaMemcpyHostToDevice, st));
+        AHV_CUDA(cudaMemcpyAsync(d_kind, kind, n, cudaMemcpyHostToDevice, st));
+        AHV_TRY(ahv_commit_dev(ctx, d_arena, ab, d_off, fixed_len, d_rp, S, n, uniform, maxl, d_dig, d_roots, d_empty));
+        AHV_TRY(ahv_verify_chains_dev(ctx, d_arena, ab, d_off, fixed_len, d_par, d_kind, d_rp, S, n, uniform, maxl,
+                                      d_roots, d_verdict, d_fb, nullptr, d_roots_v, d_match));
+        if (out_digests) AHV_CUDA(cudaMemcpyAsync(out_digests, d_dig, 32 * n, cudaMemcpyDeviceToHost, st));
+        AHV_CUDA(cudaMemcpyAsync(out_roots, d_roots, 32 * S, cudaMemcpyDeviceToHost, st));
+        if (out_empty) AHV_CUDA(cudaMemcpyAsync(out_empty, d_empty, S, cudaMemcpyDeviceToHost, st));
+        AHV_CUDA(cudaMemcpyAsync(out_verdict, d_verdict, S, cudaMemcpyDeviceToHost, st));
+        if (out_first_bad) AHV_CUDA(cudaMemcpyAsync(out_first_bad, d_fb, 8 * S, cudaMemcpyDeviceToHost, st));
+        if (out_match) AHV_CUDA(cudaMemcpyAsync(out_match, d_match, S, cudaMemcpyDeviceToHost, st));
+        AHV_CUDA(cudaStreamSynchronize(st));
+        return AHV_OK;
+    }
+
+    // ---- pipelined: sessions are independent, so each chunk is a complete sub-batch
+    constexpr int MAXC = 32;
+    int nchunk = (int)(S / 512);
+    if (nchunk < 2) nchunk = 2;
+    if (nchunk > MAXC) nchunk = MAXC;
+    const uint64_t per = (S + nchunk - 1) / nchunk;
+    cudaEvent_t ev_in[MAXC], ev_done[MAXC];
+    const int created = nchunk;
+    for (int k = 0; k < nchunk; ++k) {
+        AHV_CUDA(cudaEventCreateWithFlags(&ev_in[k], cudaEventDisableTiming));
+        AHV_CUDA(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
+    }
+    // (the first chunk may grow the scratch slab, which synchronises once; later chunks reuse it)
+    int rc = AHV_OK;
+    for (int k = 0; k < nchunk && rc == AHV_OK; ++k) {
+        const uint64_t s0 = (uint64_t)k * per, s1 = (s0 + per < S) ? s0 + per : S;
+        if (s0 >= s1) { nchunk = k; break; }
+        const uint64_t Sc = s1 - s0, l0 = s0 * uniform, nc = Sc * uniform, b0 = l0 * fixed_len, bc = nc * fixed_len;
+        cudaStream_t hs = ctx->copy_stream;
+        AHV_CUDA(cudaMemcpyAsync(d_arena + b0, arena + b0, bc, cudaMemcpyHostToDevice, hs));
+        AHV_CUDA(cudaMemcpyAsync(d_par + 32 * l0, parents + 32 * l0, 32 * nc, cudaMemcpyHostToDevice, hs));
+        AHV_CUDA(cudaMemcpyAsync(d_kind + l0, kind + l0, nc, cudaMemcpyHostToDevice, hs));
+        AHV_CUDA(cudaEventRecord(ev_in[k], hs));
+        AHV_CUDA(cudaStreamWaitEvent(ctx->stream, ev_in[k], 0));
+        rc = ahv_commit_dev(ctx, d_arena + b0, bc, nullptr, fixed_len, nullptr, Sc, nc, uniform, maxl, d_dig + 32 * l0,
+                            d_roots + 32 * s0, d_empty + s0);
+        if (rc == AHV_OK)
+            rc = ahv_verify_chains_dev(ctx, d_arena + b0, bc, nullptr, fixed_len, d_par + 32 * l0, d_kind + l0, nullptr, Sc,
+                                       nc, uniform, maxl, d_roots + 32 * s0, d_verdict + s0, d_fb + s0, nullptr,
+                                       d_roots_v + 32 * s0, d_match + s0);
+        if (rc != AHV_OK) break;
+        AHV_CUDA(cudaEventRecord(ev_done[k], ctx->stream));
+        cudaStream_t ds = ctx->d2h_stream;
+        AHV_CUDA(cudaStreamWaitEvent(ds, ev_done[k], 0));
+        if (out_digests) AHV_CUDA(cudaMemcpyAsync(out_digests + 32 * l0, d_dig + 32 * l0, 32 * nc, cudaMemcpyDeviceToHost, ds));
+        AHV_CUDA(cudaMemcpyAsync(out_roots + 32 * s0, d_roots + 32 * s0, 32 * Sc, cudaMemcpyDeviceToHost, ds));
+        if (out_empty) AHV_CUDA(cudaMemcpyAsync(out_empty + s0, d_empty + s0, Sc, cudaMemcpyDeviceToHost, ds));
+        AHV_CUDA(cudaMemcpyAsync(out_verdict + s0, d_verdict + s0, Sc, cudaMemcpyDeviceToHost, ds));
+        if (out_first_bad) AHV_CUDA(cudaMemcpyAsync(out_first_bad + s0, d_fb + s0, 8 * Sc, cudaMemcpyDeviceToHost, ds));
+        if (out_match) AHV_CUDA(cudaMemcpyAsync(out_match + s0, d_match + s0, Sc, cudaMemcpyDeviceToHost, ds));
+    }
+    cudaStreamSynchronize(ctx->copy_stream);
+    cudaStreamSynchronize(ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->d2h_stream);
+    for (int k = 0; k < created; ++k) {
+        cudaEventDestroy(ev_in[k]);
+        cudaEventDestroy(ev_done[k]);
+    }
+    if (rc != AHV_OK) return rc;
+    if (e != cudaSuccess) {
+        set_error("pipelined audit failed: %s", cudaGetErrorString(e));
+        return AHV_E_CUDA;
+    }
+    return AHV_OK;
+}
+
 int ahv_chain_capture(ahv_ctx *ctx, uint8_t *arena, const uint64_t *offsets, const uint32_t *hexpos,
                       const uint64_t *rowptr, uint64_t S, uint8_t *out_digests, uint8_t *out_parents,
                       uint8_t *out_kind)

@@ -12,7 +12,8 @@
 struct ahv_ctx {
     int device;
     cudaStream_t stream;
-    cudaStream_t copy_stream;     // H2D/D2H of the pipelined host entry points
+    cudaStream_t copy_stream;     // H2D of the pipelined host entry point
+    cudaStream_t d2h_stream;      // D2H of the pipelined host entry point (PCIe is full duplex)
     cudaEvent_t ev_copy[4];       // chunk hand-off between copy_stream and stream
     int sm_count;
     int clock_khz;
@@ -35,7 +36,7 @@ struct ahv_ctx {
     int64_t opt_tree_k;        // log2 leaves per thread in the digest-tree kernel
     int64_t opt_sigma_variant; // 1: tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
-    int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (2..256, default 32; <= 64 uses the warp-per-session finish)
+    int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)
     int64_t opt_leaf_timer;    // >0: bracket every leaf-hash launch with timer slots base..base+15 (round robin)
     uint64_t leaf_launches;    // leaf-hash kernel launches so far (indexes the round robin)
 };

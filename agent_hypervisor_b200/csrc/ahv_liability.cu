@@ -63,8 +63,21 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
     double contrib = 0.0;
     for (uint32_t c0 = e_begin; c0 < e_end; c0 += SIG_CHUNK) {
         const uint32_t c1 = (e_end - c0 > (uint32_t)SIG_CHUNK) ? c0 + SIG_CHUNK : e_end;
-        for (uint32_t e = c0 + tid; e < c1; e += SIG_ROWS)
-            v[e - c0] = vouch_accumulate(0.0, bonded[e], active[e], expiry[e], now);
+        // phase 1: issue every load of this thread's 8 edges before using any (memory-level parallelism)
+        double b_[SIG_CHUNK / SIG_ROWS];
+        int64_t x_[SIG_CHUNK / SIG_ROWS];
+        uint8_t a_[SIG_CHUNK / SIG_ROWS];
+#pragma unroll
+        for (int k = 0; k < SIG_CHUNK / SIG_ROWS; ++k) {
+            const uint32_t e = c0 + tid + k * SIG_ROWS;
+            const bool in = e < c1;
+            b_[k] = in ? __ldg(bonded + e) : 0.0;
+            x_[k] = in ? __ldg(expiry + e) : AHV_EXPIRY_NONE;
+            a_[k] = in ? __ldg(active + e) : (uint8_t)0;
+        }
+#pragma unroll
+        for (int k = 0; k < SIG_CHUNK / SIG_ROWS; ++k)
+            v[tid + k * SIG_ROWS] = vouch_accumulate(0.0, b_[k], a_[k], x_[k], now);
         __syncthreads();
         const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
         for (uint32_t e = lo; e < hi; ++e) contrib = __dadd_rn(contrib, v[e - c0]);

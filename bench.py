@@ -45,7 +45,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
@@ -287,16 +287,15 @@ def run_cuda(args):
     lib, H = ctx.lib, ctx.h
     import ctypes as C
     vp = C.c_void_p
-    h_roots_e = np.zeros(32 * S, np.uint8); h_empty_e = np.zeros(S, np.uint8)
-    h_verdict_e = np.zeros(S, np.uint8); h_fb_e = np.zeros(S, np.int64); h_match_e = np.zeros(S, np.uint8)
+    h_roots_e = ctx.host_alloc(32 * S); h_empty_e = ctx.host_alloc(S)
+    h_verdict_e = ctx.host_alloc(S); h_fb_e = ctx.host_alloc(8 * S, np.int64); h_match_e = ctx.host_alloc(S)
 
     def e2e_step():
-        rc = lib.ahv_commit(H, vp(h_arena.ctypes.data), None, FL, None, S, L, vp(h_digs.ctypes.data),
-                            vp(h_roots_e.ctypes.data), vp(h_empty_e.ctypes.data))
-        assert rc == 0, lib.ahv_last_error()
-        rc = lib.ahv_verify_chains(H, vp(h_arena.ctypes.data), None, FL, vp(h_par.ctypes.data), vp(h_kind.ctypes.data),
-                                   None, S, L, vp(h_roots_e.ctypes.data), vp(h_verdict_e.ctypes.data),
-                                   vp(h_fb_e.ctypes.data), None, None, vp(h_match_e.ctypes.data))
+        # one upload of the batch, then the commit pass and the verify pass on the device, results back
+        rc = lib.ahv_audit_sessions(H, vp(h_arena.ctypes.data), None, FL, vp(h_par.ctypes.data), vp(h_kind.ctypes.data),
+                                    None, S, L, vp(h_digs.ctypes.data), vp(h_roots_e.ctypes.data),
+                                    vp(h_empty_e.ctypes.data), vp(h_verdict_e.ctypes.data), vp(h_fb_e.ctypes.data),
+                                    vp(h_match_e.ctypes.data))
         assert rc == 0, lib.ahv_last_error()
 
     e2e_step()                                   # warm-up (sizes the staging slab)
@@ -311,7 +310,7 @@ def run_cuda(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     verified = verified and bool(h_verdict_e.all() and h_match_e.all()) and np.array_equal(h_roots_e, h_roots)
-    h2d = 2 * arena_bytes + 32 * n + n + 32 * S          # arena twice (commit, verify) + parents + kinds + roots
+    h2d = arena_bytes + 32 * n + n                       # arena + parent digests + parent kinds, once per step
     d2h = 32 * n + 32 * S + S + S + 8 * S + S            # digests, roots, empty, verdict, first_bad, match
 
     if rank != 0:
@@ -320,9 +319,11 @@ def run_cuda(args):
         return 0
 
     # ---- roofline of the dominant kernel (leaf SHA-256; 2 launches per step)
-    peak_rounds, _ = ctx.int_peak(1, 3000)        # SHA round mix, whatever pipes the compiler uses
-    peak_alu, _ = ctx.int_peak(0, 30000)          # SHF+LOP3 only: the ALU pipe alone
-    peak_comp, _ = ctx.int_peak(2, 3000)          # whole compressions on registers (kernel-level ceiling)
+    # integer ceilings measured live by register-only kernels on all SMs (csrc/ahv_peak.cu)
+    peak_alu, _ = ctx.int_peak(0, 30000)          # SHF+LOP3 only: the ALU pipe alone (64 lanes/clk/SM)
+    peak_dual, _ = ctx.int_peak(10, 30000)        # SHF+LOP3 co-issued with IMAD: both integer-capable pipes
+    peak_native, _ = ctx.int_peak(2, 3000)        # whole compressions, plain additions (compiler's placement)
+    peak_scaled, _ = ctx.int_peak(15, 3000)       # whole compressions, additions as IMAD chains (what the kernels run)
     comp_per_launch = n * ((FL + 9 + 63) // 64)
     algo_instr = comp_per_launch * ALGO_INSTR_PER_COMPRESSION
     achieved = algo_instr / (leaf_avg_ms * 1e-3)
@@ -339,15 +340,25 @@ def run_cuda(args):
         traffic = json.load(open(os.path.join(ROOT, "profiles", "leaf_kernel_traffic.json")))["dram_bytes_per_launch"]
     except Exception:
         pass
+    # instructions SHA-256 can only issue on the ALU pipe (funnel shifts, 3-input logic, byte swaps):
+    # 1040 per data block, 656 for the constant-schedule padding block
+    alu_only = n * (4 * 1040 + 656)
     roofline = {
         "kernel": "k_sha256_fixed (leaf SHA-256, one 256 B delta per thread)",
-        "bound": "int32-pipe", "achieved": achieved / 1e12, "peak": peak_rounds / 1e12, "unit": "Tinstr/s",
-        "frac": achieved / peak_rounds, "traffic": traffic,
+        "bound": "int32-pipe", "achieved": achieved / 1e12, "peak": peak_dual / 1e12, "unit": "Tinstr/s",
+        "frac": achieved / peak_dual, "traffic": traffic,
         "algorithmic": f"{ALGO_INSTR_PER_COMPRESSION} int instr/compression x {comp_per_launch} compressions/launch",
         "launch_ms": leaf_avg_ms, "launches_timed": n_leaf,
-        "peak_source": "measured live: ahv_int_peak mode 1 (SHA-256 round instruction mix, register only)",
+        "peak_source": "measured live: ahv_int_peak mode 10 (SHF+LOP3 on the ALU pipe co-issued with IMAD on the FMA "
+                       "pipe = every pipe that executes 32-bit integer work)",
+        "binding_pipe": {"pipe": "alu", "peak_tinstr": peak_alu / 1e12,
+                         "alu_only_instr_per_launch": alu_only,
+                         "frac": alu_only / (leaf_avg_ms * 1e-3) / peak_alu,
+                         "note": "shift/logic instructions that cannot leave the ALU pipe, over its measured peak; "
+                                 "additions run as IMAD on the FMA pipe"},
         "alu_pipe_peak_tinstr": peak_alu / 1e12, "frac_of_alu_pipe": achieved / peak_alu,
-        "compress_ceiling_tinstr": peak_comp / 1e12, "frac_of_compress_ceiling": achieved / peak_comp,
+        "compress_ceiling_native_tinstr": peak_native / 1e12, "compress_ceiling_scaled_tinstr": peak_scaled / 1e12,
+        "frac_of_compress_ceiling": achieved / peak_scaled,
         "hbm": {"achieved": hbm_bytes / (leaf_avg_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": hbm_bytes / (leaf_avg_ms * 1e-3) / 1e9 / hbm_peak,
                 "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback"},
@@ -387,7 +398,7 @@ def run_cuda(args):
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "e2e": {"value": world * n * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                "api": "ahv_commit + ahv_verify_chains (host-pointer C ABI, pinned host buffers)"},
+                "api": "ahv_audit_sessions (host-pointer C ABI, pinned host buffers; commit pass + verify pass on one upload, pipelined in session chunks)"},
         "verified": verified, "device": info,
     }
     print(json.dumps(line))
@@ -399,7 +410,7 @@ def run_cuda(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--sessions", type=int, default=SESSIONS_PER_GPU, help="sessions per GPU (default: configs[1])")

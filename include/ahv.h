@@ -177,6 +177,20 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
                           uint8_t *d_out_roots, uint8_t *d_out_root_match);
 
 /*
+ * ahv_audit_sessions: ahv_commit followed by ahv_verify_chains against the roots just committed, on a
+ * single upload of the batch (what an auditor does when sessions arrive from the host: terminate_session's
+ * root, core.py:204, then verify_chain, audit/delta.py:136-152, then CommitmentEngine.verify,
+ * audit/commitment.py:59-64).  Both device passes run in full (the verify pass re-hashes).  Fixed-size
+ * deltas in uniform sessions are pipelined in session chunks (copy-in / hash / copy-out overlap); pass
+ * pinned host buffers (ahv_host_alloc) for that overlap to happen.  Host pointers only.
+ */
+int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
+                       const uint8_t *parent_digests, const uint8_t *parent_kind,
+                       const uint64_t *session_rowptr, uint64_t n_sessions, uint64_t uniform_leaves,
+                       uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty, uint8_t *out_verdict,
+                       int64_t *out_first_bad, uint8_t *out_root_match);
+
+/*
  * ahv_chain_capture: session-parallel replay of DeltaEngine.capture's chaining,
  * audit/delta.py:101-114: for each session, in order, hash delta i, write its 64 hex
  * chars into delta i+1's pre-image at byte hexpos[i+1] (the "parent_hash" value the

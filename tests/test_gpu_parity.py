@@ -104,7 +104,7 @@ def test_merkle_sizes_vs_oracle(ctx, top_max, compress):
     try:
         _merkle_sizes(ctx)
     finally:
-        ctx.set_option("top_max", 32); ctx.set_option("compress", 1)
+        ctx.set_option("top_max", 0); ctx.set_option("compress", 1)
 
 
 def _merkle_sizes(ctx):
@@ -224,6 +224,36 @@ def test_config2_small_vs_golden_and_oracle(ctx, audit_golden, variant):
                             expected_roots=roots)
     assert list(np.nonzero(res["verdict"] == 0)[0]) == [7] and res["first_bad"][7] == 501
     assert list(np.nonzero(res["root_match"] == 0)[0]) == [7, 9]      # the root compare does see both
+
+
+def test_audit_sessions_pipelined_and_ragged(ctx, audit_golden):
+    """ahv_audit_sessions (commit + verify on one upload): pipelined uniform path and ragged path."""
+    S, L = 1500, 100                              # 1500 sessions -> 2 pipelined chunks, last one partial
+    arena = ctx.host_alloc(S * L * 256)
+    offs, hexpos, rp = workloads.config2_fill(arena, 7, S, L)
+    digs, par, kind = ctx.chain_capture(arena, offs, hexpos, rp)
+    bad = np.array(arena)
+    bad[(700 * L + 50) * 256 + 30] ^= 4           # a middle delta of session 700
+    bad[(1499 * L + L - 1) * 256 + 30] ^= 4       # the last delta of the last session (links still fine)
+    for data, bad_sessions in ((arena, []), (bad, [700])):
+        o = ctx.audit_sessions(data, None, par, kind, None, fixed_len=256, uniform_leaves=L, n_sessions=S)
+        want_d = co.sha256_batch(np.asarray(data), offs)
+        want_r, _ = co.merkle_roots(want_d, rp)
+        v, fb, _ = co.verify_chains(np.asarray(data), offs, par, kind, rp)
+        assert np.array_equal(o["digests"], want_d) and np.array_equal(o["roots"], want_r)
+        assert np.array_equal(o["verdict"], v) and np.array_equal(o["first_bad"], fb)
+        assert list(np.nonzero(o["verdict"] == 0)[0]) == bad_sessions
+        assert o["root_match"].all() and not o["empty"].any()      # compared with the roots of the same upload
+    ctx.host_free(arena)
+    rs = audit_golden["random_sessions"][:300]
+    sessions = [chain_preimages(recipes.random_session(r["seed"])) for r in rs]
+    a2, o2, p2, k2, rp2 = pack_sessions(sessions)
+    o = ctx.audit_sessions(a2, o2, p2, k2, rp2)
+    for s, r in enumerate(rs):
+        assert bool(o["empty"][s]) == (r["n"] == 0)
+        if r["n"]:
+            assert o["roots"][s].tobytes().hex() == r["root"] and o["root_match"][s] == 1
+        assert o["verdict"][s] == 1 and o["first_bad"][s] == -1
 
 
 def test_chain_capture_vs_python_chain(ctx):

@@ -95,7 +95,7 @@ def main():
         b2, _ = timed(ctx, lambda: ctx.merkle_roots_dev(d["digs"], d["rp"], S, n, L, d["roots2"], d["empty"]), reps=3)
         res[f"tree_ragged_top{top}"] = {"best_ms": b2, "Gcomp_s": node_c / b2 / 1e6}
         print(f"top_max {top}: commit {best:.3f} ms, ragged tree {b2:.3f} ms ({node_c/b2/1e6:.2f} Gcomp/s)", flush=True)
-    ctx.set_option("top_max", 32)
+    ctx.set_option("top_max", 0)
     best, avg = timed(ctx, lambda: ctx.merkle_roots_dev(d["digs"], d["rp"], S, n, L, d["roots2"], d["empty"]))
     res["tree_ragged"] = {"best_ms": best, "avg_ms": avg, "Gcomp_s": node_c / best / 1e6}
     print(f"tree ragged path: best {best:.3f} ms -> {node_c/best/1e6:.2f} Gcomp/s", flush=True)
@@ -140,6 +140,17 @@ def main():
     by = workloads.config4_bytes(A, E)
     out["sigma_eff"] = {"best_ms": best, "avg_ms": avg, "GBps": by / best / 1e6, "bytes": by, "A": A, "E": E}
     print(f"sigma_eff A={A} E={E}: best {best:.4f} ms -> {by/best/1e6:.1f} GB/s", flush=True)
+    # same sizes, every row exactly 10 edges (no long-row tail): the bulk streaming rate
+    rp_u = (np.arange(A + 1, dtype=np.uint64) * (E // A)).astype(np.uint32)
+    ctx.h2d(dd["rowptr"], rp_u); ctx.sync()
+    E_u = (E // A) * A
+    best, avg = timed(ctx, lambda: ctx.sigma_eff_rings_dev(dd["rowptr"], dd["bonded"], dd["active"], dd["expiry"], g["now"],
+                                                          dd["sigma"], dd["omega"], dd["consensus"], dd["current_ring"], A,
+                                                          o["se"], o["ring"], o["dem"], o["near"]), reps=10)
+    by_u = workloads.config4_bytes(A, min(E_u, E))
+    out["sigma_eff_uniform10"] = {"best_ms": best, "GBps": by_u / best / 1e6}
+    print(f"sigma_eff uniform degree 10: best {best:.4f} ms -> {by_u/best/1e6:.1f} GB/s", flush=True)
+    print("max degree in config-4 graph:", int(np.diff(g["rowptr"].astype(np.int64)).max()), flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(out, open(os.path.join(ROOT, "gpurun_out", "tune.json"), "w"), indent=1)
 
