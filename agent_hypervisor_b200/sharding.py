@@ -1,0 +1,135 @@
+"""Multi-GPU sharding of the audit path: one process per GPU (torchrun), plumbing over
+``torch.distributed`` (NCCL on GPUs; gloo in the CPU tests).
+
+Two schemes:
+
+* **Sessions** are independent trees, so ranks own contiguous session ranges and nothing is
+  exchanged until the results are collected: one all-gather of 32-byte roots and 1-byte verdicts.
+* **One giant tree** (a single chain of n leaves) is cut at multiples of 2^k leaves.  Every full
+  sub-tree has exactly 2^k leaves, so no odd-node duplication happens inside it and its root is
+  the level-k node of the global tree.  Only the ragged tail is special: its nodes are always the
+  last of their level, and the global level width there is odd, so the reference's rule
+  (audit/delta.py:129) duplicates it at every level up to k ("lifting").  The ceil(n/2^k) sub-roots
+  are all-gathered and every rank finishes the top of the tree.
+
+torch is imported lazily and only by the collective helpers; hashing is done by the callable
+passed in (default: the GPU context's ``merkle_roots``).
+"""
+
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import numpy as np
+
+
+def shard_range(n_items: int, world: int, rank: int) -> tuple[int, int]:
+    """Contiguous, balanced [lo, hi) of n_items for this rank (first n_items % world ranks get one more)."""
+    base, extra = divmod(n_items, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def subtree_log2(n_leaves: int, world: int, min_subtrees_per_rank: int = 8, max_log2: int = 24) -> int:
+    """k such that there are at least world * min_subtrees_per_rank sub-trees of 2^k leaves (k >= 0)."""
+    k = max_log2
+    while k > 0 and (n_leaves + (1 << k) - 1) >> k < world * min_subtrees_per_rank:
+        k -= 1
+    return k
+
+
+def plan_tree(n_leaves: int, world: int, k: Optional[int] = None) -> dict:
+    """Sub-tree layout of one n-leaf tree: k, number of sub-trees, and each rank's sub-tree range."""
+    if k is None:
+        k = subtree_log2(n_leaves, world)
+    n_sub = (n_leaves + (1 << k) - 1) >> k
+    ranges = [shard_range(n_sub, world, r) for r in range(world)]
+    return {"k": k, "n_sub": n_sub, "ranges": ranges, "n_leaves": n_leaves}
+
+
+def _default_merkle() -> Callable:
+    from ._native import get_context
+    return get_context().merkle_roots
+
+
+def local_subroots(digests: np.ndarray, first_leaf: int, plan: dict, rank: int,
+                   merkle_fn: Optional[Callable] = None) -> np.ndarray:
+    """Level-k nodes of this rank's sub-trees.  ``digests`` are the rank's leaves, leaf ``first_leaf``
+    (= range start * 2^k) first.  Returns uint8[n_local_sub, 32]."""
+    merkle_fn = merkle_fn or _default_merkle()
+    k, n = plan["k"], plan["n_leaves"]
+    lo, hi = plan["ranges"][rank]
+    if hi <= lo:
+        return np.zeros((0, 32), np.uint8)
+    size = 1 << k
+    assert first_leaf == lo * size
+    n_local = min(hi * size, n) - first_leaf
+    digests = np.ascontiguousarray(digests, dtype=np.uint8).reshape(-1, 32)[:n_local]
+    rowptr = np.minimum(np.arange(hi - lo + 1, dtype=np.uint64) * np.uint64(size), np.uint64(n_local))
+    roots, _ = merkle_fn(digests, rowptr)
+    roots = np.array(roots, dtype=np.uint8).reshape(-1, 32)
+    # the ragged tail (only the globally last sub-tree can be short): lift it to level k
+    tail = int(rowptr[-1] - rowptr[-2])
+    if tail < size and plan["n_sub"] > 1:
+        depth = 0
+        while (1 << depth) < tail:
+            depth += 1
+        x = roots[-1:].copy()
+        for _ in range(k - depth):
+            pair = np.concatenate([x, x])                      # H(hex(x) + hex(x)), audit/delta.py:129-130
+            x, _ = merkle_fn(pair, np.array([0, 2], dtype=np.uint64))
+            x = np.array(x, dtype=np.uint8).reshape(1, 32)
+        roots[-1] = x[0]
+    return roots
+
+
+def finish_tree(subroots: np.ndarray, merkle_fn: Optional[Callable] = None) -> Optional[bytes]:
+    """Top of the tree over all sub-roots in order (the ordinary rule of audit/delta.py:125-134)."""
+    merkle_fn = merkle_fn or _default_merkle()
+    subroots = np.ascontiguousarray(subroots, dtype=np.uint8).reshape(-1, 32)
+    if len(subroots) == 0:
+        return None
+    roots, _ = merkle_fn(subroots, np.array([0, len(subroots)], dtype=np.uint64))
+    return bytes(np.array(roots, dtype=np.uint8).reshape(-1, 32)[0])
+
+
+# ---------------------------------------------------------------------------- collectives
+def all_gather_bytes(local: np.ndarray, counts: list[int], device=None, group=None) -> np.ndarray:
+    """All-gather rows of a uint8 [rows, width] array whose row counts per rank are ``counts``
+    (known to every rank from the plan).  One collective; padded to the largest count."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    width = local.shape[1] if local.ndim == 2 else 1
+    cap = max(counts) if counts else 0
+    buf = torch.zeros((cap, width), dtype=torch.uint8, device=device)
+    if len(local):
+        buf[: len(local)] = torch.from_numpy(np.ascontiguousarray(local).reshape(len(local), width)).to(buf.device)
+    out = torch.empty((world * cap, width), dtype=torch.uint8, device=buf.device)
+    dist.all_gather_into_tensor(out, buf, group=group)
+    out = out.cpu().numpy().reshape(world, cap, width)
+    return np.concatenate([out[r, : counts[r]] for r in range(world)], axis=0)
+
+
+def sharded_tree_root(local_leaf_digests: np.ndarray, n_leaves: int, rank: int, world: int,
+                      k: Optional[int] = None, merkle_fn: Optional[Callable] = None, device=None, group=None):
+    """Root of one n-leaf tree whose leaves are spread over the ranks by ``plan_tree``."""
+    plan = plan_tree(n_leaves, world, k)
+    lo, hi = plan["ranges"][rank]
+    sub = local_subroots(local_leaf_digests, lo << plan["k"], plan, rank, merkle_fn)
+    counts = [h - l for (l, h) in plan["ranges"]]
+    allsub = all_gather_bytes(sub, counts, device=device, group=group) if world > 1 else sub
+    return finish_tree(allsub, merkle_fn), plan
+
+
+def gather_session_results(local_roots: np.ndarray, local_verdicts: np.ndarray, n_sessions: int, rank: int,
+                           world: int, device=None, group=None):
+    """Roots [S,32] and verdicts [S] of all sessions, sessions sharded by ``shard_range``."""
+    counts = [shard_range(n_sessions, world, r)[1] - shard_range(n_sessions, world, r)[0] for r in range(world)]
+    if world == 1:
+        return local_roots, local_verdicts
+    packed = np.concatenate([np.ascontiguousarray(local_roots, dtype=np.uint8).reshape(-1, 32),
+                             np.ascontiguousarray(local_verdicts, dtype=np.uint8).reshape(-1, 1)], axis=1)
+    allp = all_gather_bytes(packed, counts, device=device, group=group)
+    return allp[:, :32].copy(), allp[:, 32].copy()

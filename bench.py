@@ -35,41 +35,73 @@ ALGO_INSTR_PER_COMPRESSION = 1400
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle-reason samples DURING the timed region: NVML in-process every 10 ms (a few
+    microseconds per query, measured not to perturb the step); `nvidia-smi -lms 200` is the fallback."""
 
     def __init__(self, device: int):
-        self.device, self.rows, self.proc = device, [], None
+        self.device, self.rows, self.proc, self._stop, self._thr, self.max_mhz = device, [], None, False, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "20", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.device)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            bits = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+
+            def loop():
+                while not self._stop:
+                    try:
+                        mhz = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                        r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                        pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                        self.rows.append((time.perf_counter(), mhz, [k for k, b in bits.items() if r & b], pw))
+                    except Exception:
+                        pass
+                    time.sleep(0.01)
+
+            self._thr = threading.Thread(target=loop, daemon=True)
+            self._thr.start()
+            self.source = "nvml"
         except Exception:
-            self.proc = None
+            self.source = "nvidia-smi"
+            try:
+                q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+                     "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+                     "clocks_event_reasons.sw_power_cap")
+                self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                              "-lms", "200", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
+                threading.Thread(target=self._read, daemon=True).start()
+            except Exception:
+                self.proc = None
 
     def _read(self):
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         for line in self.proc.stdout:
-            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+            f = [x.strip() for x in line.split(",")]
+            try:
+                self.max_mhz = float(f[1])
+                self.rows.append((time.perf_counter(), float(f[0]),
+                                  [n for n, v in zip(names, f[3:7]) if v.lower().startswith("active")], float(f[2])))
+            except Exception:
+                pass
 
     def stop(self):
+        self._stop = True
         if self.proc:
             self.proc.terminate()
 
     def summary(self, t0, t1):
-        rows = [r for t, r in self.rows if t0 <= t <= t1] or [r for _, r in self.rows[-3:]]
+        rows = [r for r in self.rows if t0 <= r[0] <= t1] or self.rows[-3:]
         if not rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        sm = sorted(float(r[1]) for r in rows)
-        reasons = set()
-        for r in rows:
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][2]), "reasons": sorted(reasons),
-                "power_w_max": max(float(r[3]) for r in rows), "samples": len(rows)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampling unavailable"]}
+        sm = sorted(r[1] for r in rows)
+        reasons = sorted({x for r in rows for x in r[2]})
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "power_w_max": max(r[3] for r in rows), "samples": len(rows), "source": self.source}
 
 
 # ----------------------------------------------------------------------------- CPU arm (oracle port)
@@ -213,6 +245,7 @@ def run_cuda(args):
         t_verdict = torch.empty(S, dtype=torch.uint8, device=f"cuda:{local}")
         t_all_verdict = torch.empty(S * world, dtype=torch.uint8, device=f"cuda:{local}")
         d_roots, d_verdict = t_roots.data_ptr(), t_verdict.data_ptr()
+        ext_stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local))
     else:
         d_roots, d_verdict = ctx.dev_alloc(32 * S), d["verdict"]
     ctx.h2d(d["arena"], h_arena); ctx.h2d(d["offs"], offs); ctx.h2d(d["hexpos"], hexpos); ctx.h2d(d["rp"], rp)
@@ -227,21 +260,22 @@ def run_cuda(args):
         ctx.commit_dev(d["arena"], arena_bytes, 0, FL, 0, S, n, L, L, d["digs"], d_roots, d["empty"])
         ctx.verify_chains_dev(d["arena"], arena_bytes, 0, FL, d["par"], d["kind"], 0, S, n, L, L, d_roots,
                               d_verdict, d["fb"], 0, d["roots_v"], d["match"])
-        if world > 1:
-            ctx.sync()                    # ctx stream -> torch stream hand-off
-            dist.all_gather_into_tensor(t_all_roots, t_roots)        # 32 B x S sub-roots per rank over NVLink
-            dist.all_gather_into_tensor(t_all_verdict, t_verdict)
+        if world > 1 and not args.no_gather:
+            # the collectives are ordered after the kernels on the library's own stream (wrapped as a
+            # torch ExternalStream): no host synchronisation inside a step
+            with torch.cuda.stream(ext_stream):
+                dist.all_gather_into_tensor(t_all_roots, t_roots)        # 32 B x S sub-roots per rank over NVLink
+                dist.all_gather_into_tensor(t_all_verdict, t_verdict)
 
     for _ in range(max(args.warmup, 3)):
         step()
     ctx.sync()
-    if world > 1:
-        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
-
     sampler = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and not args.no_clocks:
         sampler.start()
-        time.sleep(0.3)
+        time.sleep(0.1)
+    if world > 1:          # every rank enters the timed region together (after rank 0 started its sampler)
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
     ctx.set_option("leaf_timer", 32)
     launches0 = ctx.launch_count()
     t_wall0 = time.perf_counter()
@@ -410,11 +444,13 @@ def run_cuda(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--sessions", type=int, default=SESSIONS_PER_GPU, help="sessions per GPU (default: configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-clocks", action="store_true", help="diagnostic: do not poll nvidia-smi during the timed region")
+    ap.add_argument("--no-gather", action="store_true", help="diagnostic: skip the per-step all-gather")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

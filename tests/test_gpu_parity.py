@@ -418,6 +418,23 @@ def test_ring_check_grid_and_dropin(ctx, liability_golden):
     assert out["sigma_eff"][0] == pts[2] and out["sigma_eff"][1] == 0.6 and out["near_threshold"] == ["did:nobody"]
 
 
+def test_sharded_single_tree_matches_whole_tree(ctx):
+    """one big tree cut at 2^k-aligned leaves across 8 emulated ranks (sub-roots, lifted tail,
+    top finish) gives the same root as hashing the whole tree, on the CUDA path."""
+    from agent_hypervisor_b200 import sharding
+    rng = np.random.default_rng(8)
+    n = 1_000_003
+    digs = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    whole, _ = ctx.merkle_roots(digs, np.array([0, n], np.uint64))
+    want, _ = co.merkle_roots(digs, np.array([0, n], np.uint64))
+    assert np.array_equal(whole, want)
+    for world, k in ((8, None), (3, 10), (8, 17)):
+        plan = sharding.plan_tree(n, world, k)
+        subs = [sharding.local_subroots(digs[(lo << plan["k"]): min(hi << plan["k"], n)], lo << plan["k"], plan, r)
+                for r, (lo, hi) in enumerate(plan["ranges"])]
+        assert sharding.finish_tree(np.concatenate(subs)) == bytes(want[0]), (world, k)
+
+
 # ------------------------------------------------------------------ full size (BASELINE config 2), properties
 def test_config2_full_size_properties(ctx):
     """10k sessions x 1k x 256 B on the device: chain -> commit -> verify, checked through

@@ -1,0 +1,85 @@
+"""N>1 host logic on CPU: world_size-2 (and 3) gloo process groups.  Hashing is done by the oracle
+here (test infrastructure); on the GPU box the same helpers call the CUDA context."""
+
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from agent_hypervisor_b200 import sharding
+from oracle import coracle as co
+
+
+def test_shard_range_covers_everything():
+    for n in (0, 1, 7, 10, 10000, 12345):
+        for world in (1, 2, 3, 8):
+            spans = [sharding.shard_range(n, world, r) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+@pytest.mark.parametrize("n,k", [(1, 0), (2, 1), (37, 3), (64, 3), (65, 3), (1000, 5), (1001, 5), (4097, 6), (5000, 4)])
+def test_subtree_plan_matches_whole_tree_single_process(n, k):
+    """Sub-roots at 2^k-aligned cuts + lifted tail + top finish == the reference's whole-tree root."""
+    rng = np.random.default_rng(n)
+    digs = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    want, _ = co.merkle_roots(digs, np.array([0, n], np.uint64))
+    for world in (1, 2, 3, 8):
+        plan = sharding.plan_tree(n, world, k)
+        subs = []
+        for r in range(world):
+            lo, hi = plan["ranges"][r]
+            first = lo << k
+            subs.append(sharding.local_subroots(digs[first: min(hi << k, n)], first, plan, r, co.merkle_roots))
+        root = sharding.finish_tree(np.concatenate(subs), co.merkle_roots)
+        assert root == bytes(want[0]), (n, k, world)
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, n, n_sessions, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(99)
+        digs = rng.integers(0, 256, (n, 32), dtype=np.uint8)            # every rank can regenerate the input
+        plan = sharding.plan_tree(n, world)
+        lo, hi = plan["ranges"][rank]
+        mine = digs[lo << plan["k"]: min(hi << plan["k"], n)]
+        root, _ = sharding.sharded_tree_root(mine, n, rank, world, merkle_fn=co.merkle_roots)
+        # session sharding: each rank "computes" roots/verdicts of its own sessions, then one gather
+        sess_roots = rng.integers(0, 256, (n_sessions, 32), dtype=np.uint8)
+        sess_verd = (rng.random(n_sessions) < 0.9).astype(np.uint8)
+        s0, s1 = sharding.shard_range(n_sessions, world, rank)
+        all_r, all_v = sharding.gather_session_results(sess_roots[s0:s1], sess_verd[s0:s1], n_sessions, rank, world)
+        ok = np.array_equal(all_r, sess_roots) and np.array_equal(all_v, sess_verd)
+        q.put((rank, root, ok))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_sharded_tree_and_session_gather(world):
+    import torch.multiprocessing as mp
+    n, n_sessions = 10_007, 101
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, n_sessions, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    rng = np.random.default_rng(99)
+    digs = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    want, _ = co.merkle_roots(digs, np.array([0, n], np.uint64))
+    for rank, root, ok in res:
+        assert root == bytes(want[0]) and ok
