@@ -9,7 +9,7 @@ Importing this package loads nothing native; the first call that needs the GPU l
 from ._native import Context, NativeError, NativeUnavailable, get_context, load_library
 from .audit import (ArenaBuilder, BatchAuditor, CommitmentEngine, CommitmentRecord, DeltaEngine, PackedSessions,
                     SemanticDelta, VFSChange)
-from .liability import VouchGraphCSR, VouchingEngine, VouchingError, VouchRecord
+from .liability import LiabilityEdge, LiabilityMatrix, VouchGraphCSR, VouchingEngine, VouchingError, VouchRecord
 from .models import ActionDescriptor, ExecutionRing, ReversibilityLevel
 from .rings import RingCheckResult, RingEnforcer
 
@@ -18,6 +18,6 @@ __version__ = "0.1.0"
 __all__ = [
     "Context", "NativeError", "NativeUnavailable", "get_context", "load_library",
     "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions",
-    "SemanticDelta", "VFSChange", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
+    "SemanticDelta", "VFSChange", "LiabilityEdge", "LiabilityMatrix", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
     "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer",
 ]

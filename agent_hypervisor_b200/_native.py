@@ -76,6 +76,8 @@ SIGNATURES = {
                                       _vp, _vp, _vp, _vp]),
     "ahv_sigma_eff_rings_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,
                                           _vp, _vp, _vp, _vp]),
+    "ahv_exposure_sums": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _u64, C.c_int, _vp]),
+    "ahv_exposure_sums_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _u64, C.c_int, _vp]),
     "ahv_ring_check": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_ring_check_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_int_peak": (C.c_int, [_vp, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
@@ -331,6 +333,21 @@ class Context:
                 _ptr(consensus), _ptr(current_ring), A, _ptr(o_s), _ptr(o_r), _ptr(o_d), _ptr(o_n)),
                 "ahv_sigma_eff_rings")
         return o_s, o_r, o_d, o_n
+
+    def exposure_sums(self, rowptr, bonded, active, expiry, now: int, compensated: Optional[bool] = None) -> np.ndarray:
+        """Per-row live sums.  compensated=None picks what Python's sum() does under THIS interpreter
+        (Neumaier compensation since CPython 3.12), i.e. what the reference would return here."""
+        import sys
+        if compensated is None:
+            compensated = sys.version_info >= (3, 12)
+        rp = _arr(rowptr, np.uint32)
+        R = len(rp) - 1
+        bonded = _arr(bonded, np.float64); active = _arr(active, np.uint8); expiry = _arr(expiry, np.int64)
+        out = np.zeros(R, np.float64)
+        with self._lock:
+            self._check(self.lib.ahv_exposure_sums(self.h, _ptr(rp), _ptr(bonded), _ptr(active), _ptr(expiry), int(now),
+                                                   R, 1 if compensated else 0, _ptr(out)), "ahv_exposure_sums")
+        return out
 
     def ring_check(self, agent_ring, action_flags, sigma, consensus, witness):
         ar = _arr(agent_ring, np.uint8); fl = _arr(action_flags, np.uint8); sg = _arr(sigma, np.float64)

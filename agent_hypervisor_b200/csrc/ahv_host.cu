@@ -414,6 +414,27 @@ int ahv_sigma_eff_rings(ahv_ctx *ctx, const uint32_t *rowptr, const double *bond
     return st.finish();
 }
 
+int ahv_exposure_sums(ahv_ctx *ctx, const uint32_t *rowptr, const double *bonded, const uint8_t *active,
+                      const int64_t *expiry, int64_t now, uint64_t n_rows, int compensated, double *out_sum)
+{
+    AHV_TRY(use_device(ctx));
+    if (n_rows == 0) return AHV_OK;
+    AHV_REQUIRE(rowptr && out_sum, "rowptr / out_sum is null");
+    const uint64_t E = rowptr[n_rows];
+    AHV_REQUIRE(E == 0 || (bonded && active && expiry), "edge arrays are null");
+    AHV_TRY(io_reserve(ctx, p256(4 * (n_rows + 1)) + 2 * p256(8 * E) + p256(E) + p256(8 * n_rows)));
+    Stager st(ctx);
+    uint32_t *d_rp = st.in(rowptr, n_rows + 1);
+    double *d_b = st.in(bonded, E);
+    uint8_t *d_a = st.in(active, E);
+    int64_t *d_e = st.in(expiry, E);
+    double *d_o = st.out(out_sum, n_rows);
+    if (st.rc != AHV_OK) return st.rc;
+    AHV_TRY(ahv_exposure_sums_dev(ctx, d_rp, d_b, d_a, d_e, now, n_rows, compensated, d_o));
+    st.back(out_sum, d_o, n_rows);
+    return st.finish();
+}
+
 int ahv_ring_check(ahv_ctx *ctx, const uint8_t *agent_ring, const uint8_t *flags, const double *sigma,
                    const uint8_t *consensus, const uint8_t *witness, uint64_t n, uint8_t *out_allowed,
                    uint8_t *out_reason, uint8_t *out_required)

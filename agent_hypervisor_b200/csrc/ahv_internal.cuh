@@ -34,7 +34,7 @@ struct ahv_ctx {
     int64_t opt_block;         // threads per block for SHA kernels (default 128)
     int64_t opt_fixed_variant; // 0: direct LDG.128, 1: smem-staged (cp.async)
     int64_t opt_tree_k;        // log2 leaves per thread in the digest-tree kernel
-    int64_t opt_sigma_variant; // 1: tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
+    int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)
     int64_t opt_leaf_timer;    // >0: bracket every leaf-hash launch with timer slots base..base+15 (round robin)

@@ -41,9 +41,38 @@ k_sigma_eff_rings(const uint32_t *__restrict__ rowptr, const double *__restrict_
 // up the slice of its own row inside the chunk, in CSR order (phase 2).  Order of additions per
 // row is exactly the reference's, so results stay bit-identical; x + (+0.0) == x for every x the
 // running sum can hold (it starts at +0.0 and can never become -0.0).
+// A row of d edges is d dependent fp64 additions: the longest row bounds the kernel from below
+// (measured ~17 cycles per element), which is what the Zipf-shaped config-4 graph runs into.
 constexpr int SIG_ROWS = 256;
 constexpr int SIG_CHUNK = 2048;
 
+// Running sum of one row.  Plain: left-to-right fp64 additions (the explicit += loop of
+// vouching.py:146-148, and Python's sum() up to CPython 3.11).  Compensated: CPython >= 3.12's
+// sum() of floats (Neumaier's variant of Kahan-Babuska, Python/bltinmodule.c), which is what
+// get_total_exposure / total_exposure evaluate to under the interpreter the reference runs on.
+template <bool COMPENSATED> struct RowSum;
+template <> struct RowSum<false> {
+    double f = 0.0;
+    __device__ __forceinline__ void add(double x) { f = __dadd_rn(f, x); }
+    __device__ __forceinline__ double result() const { return f; }
+};
+template <> struct RowSum<true> {
+    double f = 0.0, c = 0.0;
+    __device__ __forceinline__ void add(double x)
+    {
+        const double t = __dadd_rn(f, x);
+        if (fabs(f) >= fabs(x)) c = __dadd_rn(c, __dadd_rn(__dsub_rn(f, t), x));
+        else c = __dadd_rn(c, __dadd_rn(__dsub_rn(x, t), f));
+        f = t;
+    }
+    __device__ __forceinline__ double result() const
+    {
+        return (c != 0.0 && isfinite(c)) ? __dadd_rn(f, c) : f;
+    }
+};
+
+// MODE 0: sigma_eff + rings.  MODE 1: plain live sum of each row.  MODE 2: compensated live sum.
+template <int MODE>
 __global__ void __launch_bounds__(SIG_ROWS)
 k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
                   const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
@@ -60,7 +89,7 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
     const uint64_t a_last = (a0 + SIG_ROWS < A) ? a0 + SIG_ROWS : A;
     const uint32_t e_begin = rowptr[a0], e_end = rowptr[a_last];
     const uint32_t my0 = valid ? rowptr[a] : e_end, my1 = valid ? rowptr[a + 1] : e_end;
-    double contrib = 0.0;
+    RowSum<MODE == 2> acc;
     for (uint32_t c0 = e_begin; c0 < e_end; c0 += SIG_CHUNK) {
         const uint32_t c1 = (e_end - c0 > (uint32_t)SIG_CHUNK) ? c0 + SIG_CHUNK : e_end;
         // phase 1: issue every load of this thread's 8 edges before using any (memory-level parallelism)
@@ -80,10 +109,15 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
             v[tid + k * SIG_ROWS] = vouch_accumulate(0.0, b_[k], a_[k], x_[k], now);
         __syncthreads();
         const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
-        for (uint32_t e = lo; e < hi; ++e) contrib = __dadd_rn(contrib, v[e - c0]);
+        for (uint32_t e = lo; e < hi; ++e) acc.add(v[e - c0]);
         __syncthreads();
     }
     if (!valid) return;
+    const double contrib = acc.result();
+    if (MODE != 0) {
+        out_sigma[a] = contrib;
+        return;
+    }
     const double se = sigma_eff_of(sigma[a], omega[a], contrib);
     out_sigma[a] = se;
     if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, consensus[a] != 0);
@@ -126,10 +160,30 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
                                                                      d_omega, d_consensus, d_current_ring, A, d_out_sigma,
                                                                      d_out_ring, d_out_demote, d_out_near);
     else
-        k_sigma_eff_tiled<<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now,
+        k_sigma_eff_tiled<0><<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now,
                                                                                d_sigma, d_omega, d_consensus, d_current_ring,
                                                                                A, d_out_sigma, d_out_ring, d_out_demote,
                                                                                d_out_near);
+    AHV_CHECK_LAUNCH(ctx);
+    return AHV_OK;
+}
+
+int ahv_exposure_sums_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *d_bonded, const uint8_t *d_active,
+                          const int64_t *d_expiry, int64_t now, uint64_t n_rows, int compensated, double *d_out_sum)
+{
+    AHV_TRY(use_device(ctx));
+    if (n_rows == 0) return AHV_OK;
+    AHV_REQUIRE(d_rowptr && d_out_sum, "rowptr / out_sum is null");
+    AHV_REQUIRE(n_rows < 0xffffffffull, "too many rows (limit 2^32-2)");
+    const unsigned g = grid_for(n_rows, SIG_ROWS);
+    if (compensated)
+        k_sigma_eff_tiled<2><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr, nullptr,
+                                                              nullptr, nullptr, n_rows, d_out_sum, nullptr, nullptr,
+                                                              nullptr);
+    else
+        k_sigma_eff_tiled<1><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr, nullptr,
+                                                              nullptr, nullptr, n_rows, d_out_sum, nullptr, nullptr,
+                                                              nullptr);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

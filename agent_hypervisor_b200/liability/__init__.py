@@ -1,3 +1,4 @@
+from .matrix import LiabilityEdge, LiabilityMatrix
 from .vouching import VouchRecord, VouchingEngine, VouchingError, VouchGraphCSR
 
-__all__ = ["VouchRecord", "VouchingEngine", "VouchingError", "VouchGraphCSR"]
+__all__ = ["LiabilityEdge", "LiabilityMatrix", "VouchRecord", "VouchingEngine", "VouchingError", "VouchGraphCSR"]

@@ -177,6 +177,25 @@ class VouchingEngine:
         out = self.compute_sigma_eff_batch(session_id, [vouchee_did], [vouchee_sigma], [risk_weight])
         return float(out["sigma_eff"][0])
 
+    def get_total_exposure_batch(self, voucher_dids: Sequence[str], session_id: str, now: Optional[datetime] = None,
+                                 ctx: Optional[nat.Context] = None) -> np.ndarray:
+        """get_total_exposure (vouching.py:157-166) for many vouchers in one launch."""
+        ctx = ctx or nat.get_context()
+        index = {v: i for i, v in enumerate(voucher_dids)}
+        rows: list[list] = [[] for _ in voucher_dids]
+        for v in self._vouches.values():
+            if v.session_id == session_id:
+                r = index.get(v.voucher_did)
+                if r is not None:
+                    rows[r].append(v)
+        rowptr = np.zeros(len(voucher_dids) + 1, dtype=np.uint32)
+        np.cumsum([len(r) for r in rows], out=rowptr[1:])
+        flat = [v for r in rows for v in r]
+        bonded = np.array([v.bonded_amount for v in flat], dtype=np.float64)
+        active = np.array([1 if v.is_active else 0 for v in flat], dtype=np.uint8)
+        expiry = np.array([nat.EXPIRY_NONE if v.expiry is None else _to_us(v.expiry) for v in flat], dtype=np.int64)
+        return ctx.exposure_sums(rowptr, bonded, active, expiry, _to_us(now or datetime.now(timezone.utc)))
+
     def build_csr(self, session_id: str, agents: Sequence[str]) -> VouchGraphCSR:
         return VouchGraphCSR.from_records(self._vouches.values(), session_id, agents)
 

@@ -230,6 +230,21 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
                             uint8_t *d_out_ring, uint8_t *d_out_demote, uint8_t *d_out_near);
 
 /*
+ * ahv_exposure_sums: per-row sequential fp64 sum of the live bonded amounts of a CSR (rows = vouchers,
+ * out-edges in insertion order): VouchingEngine.get_total_exposure (liability/vouching.py:157-166) and
+ * LiabilityMatrix.total_exposure (liability/__init__.py:64-66) for every voucher at once.  Same edge
+ * predicate as ahv_sigma_eff_rings; no cap.  Both reference methods use Python's built-in sum(), whose
+ * float arithmetic depends on the interpreter: compensated = 1 reproduces CPython >= 3.12 (Neumaier
+ * compensated summation, Python/bltinmodule.c), compensated = 0 the plain left-to-right additions of
+ * CPython <= 3.11.  The Python shim passes the flag of the interpreter it runs under.
+ */
+int ahv_exposure_sums(ahv_ctx *ctx, const uint32_t *rowptr /* R+1 */, const double *bonded, const uint8_t *active,
+                      const int64_t *expiry, int64_t now, uint64_t n_rows, int compensated, double *out_sum);
+int ahv_exposure_sums_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *d_bonded, const uint8_t *d_active,
+                          const int64_t *d_expiry, int64_t now, uint64_t n_rows, int compensated,
+                          double *d_out_sum);
+
+/*
  * ahv_ring_check: RingEnforcer.check for n (agent, action) pairs, rings/enforcer.py:44-128,
  * with ActionDescriptor.required_ring (models.py:122-132) derived from action_flags.
  */

@@ -230,6 +230,31 @@ void orc_sigma_eff_rings(const uint32_t *rowptr, const double *bonded, const uin
     }
 }
 
+/* Python sum() over the live bonded amounts of each row (vouching.py:157-166, liability/__init__.py:64-66).
+ * compensated != 0: CPython >= 3.12 (Neumaier, Python/bltinmodule.c); else plain left-to-right. */
+void orc_exposure_sums(const uint32_t *rowptr, const double *bonded, const uint8_t *active, const int64_t *expiry,
+                       int64_t now, uint64_t n_rows, int compensated, double *out_sum)
+{
+    for (uint64_t r = 0; r < n_rows; ++r) {
+        volatile double f = 0.0, c = 0.0;
+        for (uint32_t e = rowptr[r]; e < rowptr[r + 1]; ++e) {
+            int expired = (expiry[e] != INT64_MAX) && (now > expiry[e]);
+            if (!active[e] || expired) continue;
+            double x = bonded[e];
+            if (compensated) {
+                volatile double t = f + x;
+                if (fabs(f) >= fabs(x)) { volatile double u = f - t; u = u + x; c = c + u; }
+                else { volatile double u = x - t; u = u + f; c = c + u; }
+                f = t;
+            } else {
+                f = f + x;
+            }
+        }
+        if (compensated && c != 0.0 && isfinite(c)) f = f + c;
+        out_sum[r] = f;
+    }
+}
+
 /* action_flags: bit0 is_admin, bit1 is_read_only, bit2 reversibility==NONE */
 void orc_ring_check(const uint8_t *agent_ring, const uint8_t *action_flags, const double *sigma,
                     const uint8_t *consensus, const uint8_t *witness, uint64_t n,

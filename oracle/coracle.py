@@ -45,6 +45,7 @@ def lib():
             _u32p, _f64p, _u8p, _i64p, C.c_int64, _f64p, _f64p, _u8p, _u8p, C.c_uint64,
             _f64p, _u8p, _u8p, _u8p,
         ]
+        L.orc_exposure_sums.argtypes = [_u32p, _f64p, _u8p, _i64p, C.c_int64, C.c_uint64, C.c_int, _f64p]
         L.orc_ring_check.argtypes = [_u8p, _u8p, _f64p, _u8p, _u8p, C.c_uint64, _u8p, _u8p, _u8p]
         L.orc_num_threads.restype = C.c_int
         L.orc_set_threads.argtypes = [C.c_int]
@@ -158,3 +159,15 @@ def ring_check(agent_ring, action_flags, sigma, consensus, witness):
     lib().orc_ring_check(_p(agent_ring, _u8p), _p(action_flags, _u8p), _p(sigma, _f64p),
                          _p(consensus, _u8p), _p(witness, _u8p), n, _p(al, _u8p), _p(re, _u8p), _p(rq, _u8p))
     return al, re, rq
+
+
+def exposure_sums(rowptr, bonded, active, expiry, now, compensated):
+    rowptr = _c(rowptr, np.uint32)
+    R = len(rowptr) - 1
+    bonded = _c(bonded, np.float64); active = _c(active, np.uint8); expiry = _c(expiry, np.int64)
+    if bonded.size == 0:
+        bonded = np.zeros(1); active = np.zeros(1, np.uint8); expiry = np.zeros(1, np.int64)
+    out = np.zeros(R, np.float64)
+    lib().orc_exposure_sums(_p(rowptr, _u32p), _p(bonded, _f64p), _p(active, _u8p), _p(expiry, _i64p), int(now), R,
+                            1 if compensated else 0, _p(out, _f64p))
+    return out

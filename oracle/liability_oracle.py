@@ -115,3 +115,32 @@ def ring_check(agent_ring, action_flags, sigma, consensus, witness):
             reason[i] = REASON_GRANTED
             allowed[i] = 1
     return allowed, reason, req_out
+
+
+def exposure_sums(rowptr, bonded, active, expiry, now, compensated):
+    """Per-row sum of live bonded amounts: VouchingEngine.get_total_exposure (vouching.py:157-166) and
+    LiabilityMatrix.total_exposure (liability/__init__.py:64-66), both written with Python's built-in
+    sum().  compensated=True restates CPython >= 3.12's float sum (Neumaier, Python/bltinmodule.c);
+    False the plain left-to-right additions of CPython <= 3.11."""
+    rowptr = np.asarray(rowptr)
+    R = len(rowptr) - 1
+    out = np.zeros(R, dtype=np.float64)
+    for r in range(R):
+        f, c = 0.0, 0.0
+        for e in range(int(rowptr[r]), int(rowptr[r + 1])):
+            if not (active[e] and not (expiry[e] != EXPIRY_NONE and now > expiry[e])):
+                continue
+            x = float(bonded[e])
+            if compensated:
+                t = f + x
+                if abs(f) >= abs(x):
+                    c += (f - t) + x
+                else:
+                    c += (x - t) + f
+                f = t
+            else:
+                f = f + x
+        if compensated and c and np.isfinite(c):
+            f += c
+        out[r] = f
+    return out

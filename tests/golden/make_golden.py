@@ -244,6 +244,28 @@ def liability_golden() -> dict:
                                                int(r.allowed), int(r.required_ring.value), r.reason,
                                                int(r.requires_consensus), int(r.requires_sre_witness)])
     out["checks"] = checks
+    # -- LiabilityMatrix (liability/__init__.py:24-139)
+    import random
+    from hypervisor.liability import LiabilityMatrix
+    rng = random.Random(3)
+    m = LiabilityMatrix("s")
+    edges = []
+    for k in range(400):
+        a, b = rng.randrange(40), rng.randrange(40)
+        amt = rng.choice([rng.uniform(0, 0.8), 0.0, -0.0, 1e-300, 0.1])
+        edges.append((f"did:{a}", f"did:{b}", amt, f"v{k}"))
+        m.add_edge(*edges[-1])
+    mat = {"edges": [[e[0], e[1], float(e[2]).hex(), e[3]] for e in edges],
+           "exposure": {f"did:{i}": float(m.total_exposure(f"did:{i}")).hex() for i in range(42)},
+           "has_cycle": m.has_cycle()}
+    m2 = LiabilityMatrix("t")
+    for a, b in [("a", "b"), ("b", "c"), ("c", "d"), ("a", "e")]:
+        m2.add_edge(a, b, 0.1, a + b)
+    mat["acyclic"] = {"has_cycle": m2.has_cycle(), "cascade_a": m2.cascade_path("a"),
+                      "cascade_a3": m2.cascade_path("a", 3), "cascade_d": m2.cascade_path("d")}
+    m2.add_edge("d", "a", 0.1, "da")
+    mat["cyclic"] = {"has_cycle": m2.has_cycle(), "cascade_a": m2.cascade_path("a", 4)}
+    out["matrix"] = mat
     out["risk_weights"] = {lv.value: float(lv.default_risk_weight).hex() for lv in ReversibilityLevel}
     return out
 

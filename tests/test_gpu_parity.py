@@ -386,6 +386,49 @@ def test_sigma_eff_long_and_empty_rows(ctx):
             assert np.array_equal(a, b)
 
 
+def test_liability_matrix_and_exposure(ctx, liability_golden):
+    from agent_hypervisor_b200 import LiabilityMatrix, VouchingEngine
+    g = liability_golden["matrix"]
+    m = LiabilityMatrix("s")
+    for a, b, amt, vid in g["edges"]:
+        m.add_edge(a, b, float.fromhex(amt), vid)
+    names = list(g["exposure"])
+    got = m.total_exposure_batch(names)
+    for i, nm in enumerate(names):
+        want = float.fromhex(g["exposure"][nm])
+        assert got[i] == want and float(m.total_exposure(nm)) == want, nm
+    assert m.total_exposure("did:nobody") == 0
+    rng = np.random.default_rng(0)
+    deg = np.concatenate([[4, 0, 3000, 1], rng.integers(0, 40, 600)])
+    rp = np.concatenate([[0], np.cumsum(deg)]).astype(np.uint32)
+    vals = rng.uniform(-1, 1, int(rp[-1])) * 10.0 ** rng.integers(-8, 8, int(rp[-1]))
+    vals[:4] = [1e16, 1.0, -1e16, 1.0]
+    act = (rng.random(len(vals)) < 0.9).astype(np.uint8); act[:4] = 1
+    exp = np.where(rng.random(len(vals)) < 0.7, lo.EXPIRY_NONE, rng.integers(0, 2000, len(vals))).astype(np.int64)
+    exp[:4] = lo.EXPIRY_NONE
+    for comp in (True, False):                      # CPython >= 3.12 sum() and the plain loop
+        gpu = ctx.exposure_sums(rp, vals, act, exp, 1000, compensated=comp)
+        assert np.array_equal(gpu, co.exposure_sums(rp, vals, act, exp, 1000, comp))
+        assert gpu[0] == (2.0 if comp else 1.0)
+    # VouchingEngine.get_total_exposure for many vouchers == the per-voucher host scan
+    ve = VouchingEngine(max_exposure=1.0)
+    for k in range(60):
+        ve.vouch(f"did:h{k % 7}", f"did:l{k}", "s1", 0.9, bond_pct=0.01 + 0.001 * k)
+    list(ve._vouches.values())[5].is_active = False
+    vs = [f"did:h{i}" for i in range(8)]
+    batch = ve.get_total_exposure_batch(vs, "s1")
+    for i, v in enumerate(vs):
+        assert batch[i] == float(ve.get_total_exposure(v, "s1"))
+    # sigma_eff straight from the matrix's vouchee-grouped CSR
+    agents = [f"did:{i}" for i in range(40)]
+    rowptr, bonded, active, expiry = m.to_vouch_csr(agents)
+    se, *_ = ctx.sigma_eff_rings(rowptr, bonded, active, expiry, 0, np.full(40, 0.1), np.full(40, 0.5),
+                                 np.zeros(40, np.uint8), np.full(40, 3, np.uint8))
+    want, *_ = co.sigma_eff_rings(rowptr, bonded, active, expiry, 0, np.full(40, 0.1), np.full(40, 0.5),
+                                  np.zeros(40, np.uint8), np.full(40, 3, np.uint8))
+    assert np.array_equal(se, want)
+
+
 def test_ring_check_grid_and_dropin(ctx, liability_golden):
     from agent_hypervisor_b200 import ActionDescriptor, ExecutionRing, ReversibilityLevel, RingEnforcer, VouchingEngine
     rows = liability_golden["checks"]

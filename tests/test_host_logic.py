@@ -100,6 +100,30 @@ def test_vouch_csr_insertion_order_and_session_filter():
     assert _to_us(t + timedelta(microseconds=1)) == _to_us(t) + 1
 
 
+def test_liability_matrix_graph_walks(liability_golden):
+    from agent_hypervisor_b200 import LiabilityMatrix
+    g = liability_golden["matrix"]
+    m = LiabilityMatrix("s")
+    for a, b, amt, vid in g["edges"]:
+        m.add_edge(a, b, float.fromhex(amt), vid)
+    assert m.has_cycle() == g["has_cycle"] and len(m.edges) == 400
+    assert len(m.who_vouches_for("did:3")) == sum(1 for e in g["edges"] if e[1] == "did:3")
+    m.remove_edge("v0")
+    assert len(m.edges) == 399
+    m2 = LiabilityMatrix("t")
+    for a, b in [("a", "b"), ("b", "c"), ("c", "d"), ("a", "e")]:
+        m2.add_edge(a, b, 0.1, a + b)
+    assert m2.has_cycle() == g["acyclic"]["has_cycle"]
+    assert m2.cascade_path("a") == g["acyclic"]["cascade_a"]
+    assert m2.cascade_path("a", 3) == g["acyclic"]["cascade_a3"]
+    assert m2.cascade_path("d") == g["acyclic"]["cascade_d"]
+    m2.add_edge("d", "a", 0.1, "da")
+    assert m2.has_cycle() == g["cyclic"]["has_cycle"]
+    assert m2.cascade_path("a", 4) == g["cyclic"]["cascade_a"]
+    m2.clear()
+    assert m2.edges == [] and not m2.has_cycle()
+
+
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "ahv.h")).read()
     hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)

@@ -245,3 +245,40 @@ def test_ring_grid_and_checks(liability_golden):
             assert (code == lo.REASON_NEEDS_CONSENSUS) == bool(c[10])
             assert (code == lo.REASON_NEEDS_WITNESS) == bool(c[11])
             assert (code == lo.REASON_GRANTED) == (c[9] == "Access granted")
+
+
+def test_exposure_sums_match_python_sum_and_reference(liability_golden):
+    """total_exposure / get_total_exposure are Python sum(): compensated since CPython 3.12."""
+    import sys
+    g = liability_golden["matrix"]
+    names = list(g["exposure"])
+    idx = {n: i for i, n in enumerate(names)}
+    rows = [[] for _ in names]
+    for a, b, amt, vid in g["edges"]:
+        if a in idx:
+            rows[idx[a]].append(float.fromhex(amt))
+    rowptr = np.concatenate([[0], np.cumsum([len(r) for r in rows])]).astype(np.uint32)
+    bonded = np.array([x for r in rows for x in r])
+    ones = np.ones(len(bonded), np.uint8); none = np.full(len(bonded), lo.EXPIRY_NONE, np.int64)
+    want_ref = np.array([float.fromhex(g["exposure"][n]) for n in names])      # produced by the reference on CPython 3.12
+    for impl in (lo.exposure_sums, co.exposure_sums):
+        assert np.array_equal(impl(rowptr, bonded, ones, none, 0, True), want_ref)
+        plain = impl(rowptr, bonded, ones, none, 0, False)
+        want_plain = []
+        for r in rows:
+            f = 0.0
+            for x in r:
+                f += x
+            want_plain.append(f)
+        assert np.array_equal(plain, np.array(want_plain))
+    if sys.version_info >= (3, 12):
+        assert [sum(r) for r in rows] == list(want_ref)
+    # ill-conditioned rows where the two summations differ visibly
+    rng = np.random.default_rng(0)
+    vals = np.concatenate([[1e16, 1.0, -1e16, 1.0], rng.uniform(-1, 1, 500) * 10.0 ** rng.integers(-8, 8, 500)])
+    rp = np.array([0, 4, len(vals)], np.uint32)
+    o = np.ones(len(vals), np.uint8); nn = np.full(len(vals), lo.EXPIRY_NONE, np.int64)
+    a = lo.exposure_sums(rp, vals, o, nn, 0, True); b = co.exposure_sums(rp, vals, o, nn, 0, True)
+    assert np.array_equal(a, b) and a[0] == 2.0
+    assert lo.exposure_sums(rp, vals, o, nn, 0, False)[0] == 1.0          # plain summation loses the first 1.0
+    assert np.array_equal(lo.exposure_sums(rp, vals, o, nn, 0, False), co.exposure_sums(rp, vals, o, nn, 0, False))
