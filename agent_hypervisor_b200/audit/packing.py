@@ -126,3 +126,109 @@ def pack_sessions(sessions: Sequence[Sequence]) -> PackedSessions:
     for s in sessions:
         b.add_session(s)
     return b.finish()
+
+
+# ---------------------------------------------------------------------------------------------
+# Columnar path: the C++ host packer (ahv_pack_deltas) for bulk import / replay, where deltas
+# arrive as columns rather than Python objects.  ``columns_from_deltas`` exists for tests and
+# small batches; a bulk producer fills the same arrays directly.
+# ---------------------------------------------------------------------------------------------
+import ctypes as _C
+from datetime import datetime as _dt, timezone as _tz
+
+_EPOCH = _dt(1970, 1, 1, tzinfo=_tz.utc)
+_NAIVE = -(2 ** 31)
+
+
+class _DeltaColumns(_C.Structure):
+    _fields_ = [("n", _C.c_uint64)] + [(nm, _C.c_void_p) for nm in (
+        "delta_id_blob", "delta_id_off", "session_id_blob", "session_id_off", "agent_did_blob", "agent_did_off",
+        "turn_id", "timestamp_us", "timestamp_utcoffset_s", "parent_kind", "parent_digest",
+        "parent_other_blob", "parent_other_off", "change_rowptr",
+        "change_path_blob", "change_path_off", "change_op_blob", "change_op_off",
+        "change_content_blob", "change_content_off", "change_content_null",
+        "change_prev_blob", "change_prev_off", "change_prev_null")]
+
+
+def _str_col(values):
+    enc = [b"" if v is None else v.encode("utf-8", "surrogatepass") for v in values]
+    off = np.zeros(len(enc) + 1, dtype=np.uint64)
+    if enc:
+        np.cumsum([len(e) for e in enc], out=off[1:])
+    blob = np.frombuffer(b"".join(enc) or b"\0", dtype=np.uint8)
+    null = np.array([1 if v is None else 0 for v in values], dtype=np.uint8) if values else np.zeros(1, np.uint8)
+    return blob, off, null
+
+
+def columns_from_deltas(deltas) -> dict:
+    """Columnar form of SemanticDelta-like objects with string ids (ints/other JSON types in id fields
+    are not representable as columns: use canonical_preimage for those)."""
+    changes = [c for d in deltas for c in d.changes]
+    ts_us, ts_off = [], []
+    for d in deltas:
+        t = d.timestamp
+        if t.tzinfo is None:
+            delta = t - _EPOCH.replace(tzinfo=None)
+            ts_off.append(_NAIVE)
+        else:
+            delta = t - _EPOCH
+            ts_off.append(int(t.utcoffset().total_seconds()))
+        ts_us.append((delta.days * 86400 + delta.seconds) * 1_000_000 + delta.microseconds)
+    kinds, digs, others = [], bytearray(), []
+    for d in deltas:
+        k, raw = classify_parent(d.parent_hash)
+        kinds.append(k); digs += raw
+        others.append(d.parent_hash if k == nat.PARENT_OTHER else "")
+    rowptr = np.zeros(len(deltas) + 1, dtype=np.uint64)
+    if deltas:
+        np.cumsum([len(d.changes) for d in deltas], out=rowptr[1:])
+    return {
+        "n": len(deltas),
+        "delta_id": _str_col([d.delta_id for d in deltas]), "session_id": _str_col([d.session_id for d in deltas]),
+        "agent_did": _str_col([d.agent_did for d in deltas]),
+        "turn_id": np.array([d.turn_id for d in deltas], dtype=np.int64),
+        "timestamp_us": np.array(ts_us, dtype=np.int64), "timestamp_utcoffset_s": np.array(ts_off, dtype=np.int32),
+        "parent_kind": np.array(kinds, dtype=np.uint8),
+        "parent_digest": np.frombuffer(bytes(digs) or b"\0" * 32, dtype=np.uint8),
+        "parent_other": _str_col(others), "change_rowptr": rowptr,
+        "change_path": _str_col([c.path for c in changes]), "change_op": _str_col([c.operation for c in changes]),
+        "change_content": _str_col([c.content_hash for c in changes]),
+        "change_prev": _str_col([c.previous_hash for c in changes]),
+    }
+
+
+def pack_columns(cols: dict, arena: Optional[np.ndarray] = None):
+    """Canonical pre-images of ``cols['n']`` deltas via the C++ packer -> (arena u8[], offsets u64[n+1])."""
+    lib = nat.load_library()
+    keep = []
+
+    def ptr(a):
+        a = np.ascontiguousarray(a)
+        keep.append(a)
+        return a.ctypes.data
+
+    st = _DeltaColumns()
+    st.n = cols["n"]
+    for nm in ("delta_id", "session_id", "agent_did", "parent_other"):
+        blob, off, _ = cols[nm]
+        setattr(st, nm + "_blob", ptr(blob)); setattr(st, nm + "_off", ptr(off))
+    for nm in ("turn_id", "timestamp_us", "timestamp_utcoffset_s", "parent_kind", "parent_digest", "change_rowptr"):
+        setattr(st, nm, ptr(cols[nm]))
+    for nm, key in (("change_path", "change_path"), ("change_op", "change_op")):
+        blob, off, _ = cols[key]
+        setattr(st, nm + "_blob", ptr(blob)); setattr(st, nm + "_off", ptr(off))
+    for nm in ("change_content", "change_prev"):
+        blob, off, null = cols[nm]
+        setattr(st, nm + "_blob", ptr(blob)); setattr(st, nm + "_off", ptr(off)); setattr(st, nm + "_null", ptr(null))
+    n = cols["n"]
+    offsets = np.zeros(n + 1, dtype=np.uint64)
+    nbytes = _C.c_uint64()
+    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, None, 0, _C.byref(nbytes))
+    if rc:
+        raise nat.NativeError(lib.ahv_last_error().decode())
+    if arena is None:
+        arena = np.empty(max(int(nbytes.value), 1), dtype=np.uint8)
+    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, arena.ctypes.data, arena.nbytes, _C.byref(nbytes))
+    if rc:
+        raise nat.NativeError(lib.ahv_last_error().decode())
+    return arena[: int(nbytes.value)], offsets

@@ -633,8 +633,28 @@ struct MsgReader {
     }
 };
 
-// SHA-256 of len bytes at p (any alignment).  One compress copy: full blocks take the
-// fast word path, the final one or two blocks build padding per word.
+// 17 raw aligned words covering one 64-byte block at any byte alignment: four 16-byte loads when the
+// block is 16-byte aligned, else 4-byte loads (the 17th only when the block really spills into it).
+AHV_HD void load_block_raw(const uint32_t *qb, bool aligned16, uint32_t a, uint32_t x[17])
+{
+    if (aligned16) {
+        const U4 *q4 = reinterpret_cast<const U4 *>(qb);
+        const U4 v0 = q4[0], v1 = q4[1], v2 = q4[2], v3 = q4[3];
+        x[0] = v0.x; x[1] = v0.y; x[2] = v0.z; x[3] = v0.w;
+        x[4] = v1.x; x[5] = v1.y; x[6] = v1.z; x[7] = v1.w;
+        x[8] = v2.x; x[9] = v2.y; x[10] = v2.z; x[11] = v2.w;
+        x[12] = v3.x; x[13] = v3.y; x[14] = v3.z; x[15] = v3.w;
+        x[16] = 0u;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) x[j] = qb[j];
+        x[16] = a ? qb[16] : 0u;
+    }
+}
+
+// SHA-256 of len bytes at p (any alignment).  One compress copy: full blocks take the fast word
+// path (next block's raw words are fetched before the current block is compressed), the final
+// one or two blocks build padding per word.
 template <class P>
 AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8], const P &cp)
 {
@@ -645,25 +665,15 @@ AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8], const
     const uint32_t rem = (uint32_t)(len & 63u);
     const uint64_t nblk = nfull + ((rem + 9u > 64u) ? 2u : 1u);
     const bool aligned16 = ((reinterpret_cast<uintptr_t>(p) & 15u) == 0);
+    uint32_t x[17];
+    if (nfull) load_block_raw(rd.q, aligned16, rd.a, x);
     for (uint64_t b = 0; b < nblk; ++b) {
         uint32_t w[16];
         const uint32_t *qb = rd.q + 16 * b;
         if (b < nfull) {
-            if (aligned16) {
-                const U4 *q4 = reinterpret_cast<const U4 *>(qb);
-                U4 v0 = q4[0], v1 = q4[1], v2 = q4[2], v3 = q4[3];
-                w[0] = bswap32(v0.x); w[1] = bswap32(v0.y); w[2] = bswap32(v0.z); w[3] = bswap32(v0.w);
-                w[4] = bswap32(v1.x); w[5] = bswap32(v1.y); w[6] = bswap32(v1.z); w[7] = bswap32(v1.w);
-                w[8] = bswap32(v2.x); w[9] = bswap32(v2.y); w[10] = bswap32(v2.z); w[11] = bswap32(v2.w);
-                w[12] = bswap32(v3.x); w[13] = bswap32(v3.y); w[14] = bswap32(v3.z); w[15] = bswap32(v3.w);
-            } else {
-                uint32_t x[17];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) x[j] = qb[j];
-                x[16] = rd.a ? qb[16] : 0u;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) w[j] = prmt(x[j], x[j + 1], rd.sel);
-            }
+            for (int j = 0; j < 16; ++j) w[j] = prmt(x[j], x[j + 1], rd.sel);
+            if (b + 1 < nfull) load_block_raw(qb + 16, aligned16, rd.a, x);
         } else {
             // tail: byte position of word j relative to the start of the tail data
             const uint32_t tb = (uint32_t)(b - nfull) * 64u;

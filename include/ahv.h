@@ -206,6 +206,35 @@ int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, 
                           uint64_t n_leaves, uint8_t *d_out_digests, uint8_t *d_out_parent_digests,
                           uint8_t *d_out_parent_kind);
 
+/*
+ * ahv_pack_deltas: host-side canonical packer.  Writes, for n deltas given as columns, exactly the bytes
+ * SemanticDelta.compute_hash serialises (audit/delta.py:43-62: json.dumps({...}, sort_keys=True).encode(),
+ * CPython's default separators and ensure_ascii escaping, timestamp.isoformat()) into a packed arena,
+ * multi-threaded on the host.  Strings are UTF-8 blobs with offsets[count+1].  Call with out_arena = NULL to
+ * get sizes: out_offsets[n+1] and *out_bytes are filled either way.  Runs on the CPU by design (the host
+ * packs, the GPU hashes); it needs no ahv_ctx.
+ */
+typedef struct ahv_delta_columns {
+    uint64_t n;
+    const uint8_t *delta_id_blob;   const uint64_t *delta_id_off;     /* n+1 */
+    const uint8_t *session_id_blob; const uint64_t *session_id_off;   /* n+1 */
+    const uint8_t *agent_did_blob;  const uint64_t *agent_did_off;    /* n+1 */
+    const int64_t *turn_id;                                           /* n */
+    const int64_t *timestamp_us;            /* n: microseconds since the epoch, UTC */
+    const int32_t *timestamp_utcoffset_s;   /* n: tzinfo offset in seconds, INT32_MIN for a naive datetime */
+    const uint8_t *parent_kind;             /* n: AHV_PARENT_* */
+    const uint8_t *parent_digest;           /* n*32, used where kind == AHV_PARENT_HEX */
+    const uint8_t *parent_other_blob; const uint64_t *parent_other_off;   /* n+1, used where kind == AHV_PARENT_OTHER */
+    const uint64_t *change_rowptr;          /* n+1: changes of delta i are rows [rowptr[i], rowptr[i+1]) below */
+    const uint8_t *change_path_blob;    const uint64_t *change_path_off;
+    const uint8_t *change_op_blob;      const uint64_t *change_op_off;
+    const uint8_t *change_content_blob; const uint64_t *change_content_off; const uint8_t *change_content_null;
+    const uint8_t *change_prev_blob;    const uint64_t *change_prev_off;    const uint8_t *change_prev_null;
+} ahv_delta_columns;
+
+int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets /* n+1 */, uint8_t *out_arena,
+                    uint64_t arena_capacity, uint64_t *out_bytes);
+
 /* ------------------------------------------------------------------ liability / rings
  *
  * ahv_sigma_eff_rings: VouchingEngine.compute_sigma_eff for every agent of one session

@@ -162,3 +162,33 @@ def test_product_never_imports_oracle():
                 assert "oracle" not in src.lower(), f"{fn} mentions the oracle"
                 if fn.endswith(".py"):
                     assert "hashlib" not in src.replace("no hashlib path", ""), f"{fn} uses hashlib"
+
+
+def test_cpp_packer_matches_reference_preimages(audit_golden):
+    """ahv_pack_deltas (C++ host packer, columnar input) writes byte-identical pre-images."""
+    from agent_hypervisor_b200.audit.packing import columns_from_deltas, pack_columns
+    from datetime import datetime, timedelta, timezone
+    deltas = []
+    for r in audit_golden["random_sessions"]:
+        deltas += build_deltas(recipes.random_session(r["seed"]))
+    # dates far from the epoch, naive timestamps, odd offsets, non-digest parents
+    extra = build_deltas(recipes.golden_session(6))
+    extra[0].timestamp = datetime(1, 1, 1, 0, 0, 0)                                       # naive, year 1
+    extra[1].timestamp = datetime(9999, 12, 31, 23, 59, 59, 999999, tzinfo=timezone.utc)
+    extra[2].timestamp = datetime(1969, 12, 31, 23, 59, 59, 1, tzinfo=timezone(timedelta(hours=-9, minutes=-30)))
+    extra[3].timestamp = datetime(2024, 2, 29, 12, 0, 0, tzinfo=timezone(timedelta(seconds=3723)))
+    extra[4].parent_hash = "NOT-A-DIGEST ☃ \U0001F600 \x7f\x00"
+    extra[5].turn_id = -42
+    deltas += extra
+    arena, offs = pack_columns(columns_from_deltas(deltas))
+    assert len(offs) == len(deltas) + 1
+    for i, d in enumerate(deltas):
+        assert arena[int(offs[i]):int(offs[i + 1])].tobytes() == canonical_preimage(d), i
+    # the session-level digest the golden file holds, over the C++ packer's bytes
+    pos = 0
+    for r in audit_golden["random_sessions"][:200]:
+        blob = arena[int(offs[pos]):int(offs[pos + r["n"]])].tobytes()
+        assert hashlib.sha256(blob).hexdigest() == r["preimages_sha"]
+        pos += r["n"]
+    a0, o0 = pack_columns(columns_from_deltas([]))
+    assert len(o0) == 1 and o0[0] == 0

@@ -1,0 +1,121 @@
+#!/usr/bin/env python3
+"""Full-size runs of BASELINE.json configs 3, 4 and the per-GPU share of config 5 on one GPU
+(development tool; the contract benchmark is bench.py).  Writes gpurun_out/configs.json.
+
+Config 3 at 10^7 leaves is a 10x device-side tiling of a 10^6-message arena (same length
+distribution, 29 GB), hashed + tree'd + verified as 10^4 sessions x 1000 and as ONE 10^7-leaf tree;
+a sample of digests / roots is checked against the C oracle (checker only)."""
+import json, os, sys, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import workloads
+from agent_hypervisor_b200 import Context
+from oracle import coracle as co
+
+ctx = Context(0)
+out = {}
+
+
+def timed(fn, reps=3, warm=1):
+    for _ in range(warm):
+        fn()
+    ctx.sync()
+    best = 1e30
+    for _ in range(reps):
+        ctx.timer_start(1); fn(); ctx.timer_stop(1)
+        best = min(best, ctx.timer_ms(1))
+    return best
+
+
+# ---------------------------------------------------------------- config 3
+n1, reps = 1_000_000, int(os.environ.get("CFG3_TILES", "10"))
+a1, o1 = workloads.config3_arena(n1)
+B1 = int(o1[-1])
+B1p = (B1 + 15) & ~15                      # keep every tile 16-byte aligned like the first
+n = n1 * reps
+d_arena = ctx.dev_alloc(B1p * reps + 64)
+offs = np.concatenate([o1[:-1] + np.uint64(k * B1p) for k in range(reps)] + [np.array([(reps - 1) * B1p + B1], np.uint64)])
+# a message's extent is offs[i+1]-offs[i]: fix the last message of each tile (padding gap belongs to nobody)
+lens = np.tile(np.diff(o1.astype(np.int64)), reps)
+for k in range(reps):
+    ctx.h2d(d_arena + k * B1p, a1)
+ctx.sync()
+# offsets with gaps cannot be expressed by one CSR array; pad the last message of each tile instead: keep it simple
+# and hash tile-by-tile arenas as one batch whose offsets are contiguous (B1p == B1 when B1 % 16 == 0)
+if B1p != B1:
+    pad = B1p - B1
+    a1 = np.concatenate([a1, np.zeros(pad, np.uint8)])
+    o1 = o1.copy(); o1[-1] = B1p           # last message of a tile grows by the pad bytes (still valid input)
+    for k in range(reps):
+        ctx.h2d(d_arena + k * B1p, a1)
+    ctx.sync()
+    offs = np.concatenate([o1[:-1] + np.uint64(k * B1p) for k in range(reps)] + [np.array([reps * B1p], np.uint64)])
+comp = int(((np.diff(offs.astype(np.int64)) + 9 + 63) // 64).sum())
+d_offs = ctx.dev_alloc(offs.nbytes); ctx.h2d(d_offs, offs)
+d_digs = ctx.dev_alloc(32 * n)
+S = n // 1000
+rp = (np.arange(S + 1, dtype=np.uint64) * 1000)
+d_rp = ctx.dev_alloc(rp.nbytes); ctx.h2d(d_rp, rp)
+rp1 = np.array([0, n], np.uint64); d_rp1 = ctx.dev_alloc(16); ctx.h2d(d_rp1, rp1)
+d_roots = ctx.dev_alloc(32 * S); d_empty = ctx.dev_alloc(S); d_root1 = ctx.dev_alloc(32); d_e1 = ctx.dev_alloc(1)
+ctx.sync()
+nbytes = int(offs[-1])
+t_hash = timed(lambda: ctx.sha256_batch_dev(d_arena, nbytes, d_offs, n, 0, d_digs))
+t_tree = timed(lambda: ctx.merkle_roots_dev(d_digs, d_rp, S, n, 1000, d_roots, d_empty))
+t_one = timed(lambda: ctx.merkle_roots_dev(d_digs, d_rp1, 1, n, n, d_root1, d_e1))
+t_commit = timed(lambda: ctx.commit_dev(d_arena, nbytes, d_offs, 0, d_rp, S, n, 0, 1000, d_digs, d_roots, d_empty))
+# parents = digest of the previous message inside each session
+digs = np.empty((n, 32), np.uint8); ctx.d2h(digs, d_digs); ctx.sync()
+par = np.zeros((n, 32), np.uint8); par[1:] = digs[:-1]
+kind = np.ones(n, np.uint8); kind[::1000] = 0
+d_par = ctx.dev_alloc(32 * n); d_kind = ctx.dev_alloc(n); ctx.h2d(d_par, par); ctx.h2d(d_kind, kind)
+d_verd = ctx.dev_alloc(S); d_fb = ctx.dev_alloc(8 * S); d_match = ctx.dev_alloc(S); d_rv = ctx.dev_alloc(32 * S)
+ctx.sync()
+t_verify = timed(lambda: ctx.verify_chains_dev(d_arena, nbytes, d_offs, 0, d_par, d_kind, d_rp, S, n, 0, 1000, d_roots,
+                                               d_verd, d_fb, 0, d_rv, d_match))
+verd = np.empty(S, np.uint8); match = np.empty(S, np.uint8); roots = np.empty((S, 32), np.uint8); root1 = np.empty(32, np.uint8)
+ctx.d2h(verd, d_verd); ctx.d2h(match, d_match); ctx.d2h(roots, d_roots); ctx.d2h(root1, d_root1); ctx.sync()
+# checker: first tile's digests, 8 session roots, and the single-tree root via the oracle on the GPU's digests
+chk = co.sha256_batch(a1, o1)
+ok = bool(np.array_equal(chk, digs[:n1]) and np.array_equal(chk[:-1], digs[n1:2 * n1 - 1]) if reps > 1 else np.array_equal(chk, digs[:n1]))
+wr, _ = co.merkle_roots(digs[:8000], rp[:9])
+ok = ok and np.array_equal(wr, roots[:8]) and bool(verd.all()) and bool(match.all())
+w1, _ = co.merkle_roots(digs, rp1)
+ok = ok and np.array_equal(w1[0], root1)
+out["config3"] = {"leaves": n, "arena_bytes": nbytes, "compressions": comp, "hash_ms": t_hash, "tree_10k_sessions_ms": t_tree,
+                  "tree_single_10M_ms": t_one, "commit_ms": t_commit, "verify_ms": t_verify,
+                  "hash_Gcompr_s": comp / t_hash / 1e6, "hash_GBps": nbytes / t_hash / 1e6,
+                  "commit_plus_verify_deltas_s": n / ((t_commit + t_verify) * 1e-3), "parity_ok": ok}
+print(json.dumps(out["config3"]), flush=True)
+for p in (d_arena, d_offs, d_digs, d_rp, d_rp1, d_roots, d_empty, d_root1, d_e1, d_par, d_kind, d_verd, d_fb, d_match, d_rv):
+    ctx.dev_free(p)
+del digs, par
+
+# ---------------------------------------------------------------- config 5, one GPU's share (12 500 sessions) and all 10^8 on one GPU
+for S5 in (12_500, int(os.environ.get("CFG5_SESSIONS", "100000"))):
+    L, FL = 1000, 256
+    n5 = S5 * L
+    h = ctx.host_alloc(n5 * FL)
+    offs5, hexpos5, rp5 = workloads.config2_fill(h, 0, S5, L, FL)
+    d = {k: ctx.dev_alloc(v) for k, v in dict(arena=n5 * FL, offs=offs5.nbytes, hexpos=hexpos5.nbytes, rp=rp5.nbytes,
+                                               digs=32 * n5, par=32 * n5, kind=n5, roots=32 * S5, empty=S5, verdict=S5,
+                                               fb=8 * S5, match=S5, rv=32 * S5).items()}
+    ctx.h2d(d["arena"], h); ctx.h2d(d["offs"], offs5); ctx.h2d(d["hexpos"], hexpos5); ctx.h2d(d["rp"], rp5)
+    t0 = time.perf_counter()
+    ctx.chain_capture_dev(d["arena"], n5 * FL, d["offs"], d["hexpos"], d["rp"], S5, n5, d["digs"], d["par"], d["kind"])
+    ctx.sync(); t_chain = (time.perf_counter() - t0) * 1e3
+    t_c = timed(lambda: ctx.commit_dev(d["arena"], n5 * FL, 0, FL, 0, S5, n5, L, L, d["digs"], d["roots"], d["empty"]))
+    t_v = timed(lambda: ctx.verify_chains_dev(d["arena"], n5 * FL, 0, FL, d["par"], d["kind"], 0, S5, n5, L, L, d["roots"],
+                                              d["verdict"], d["fb"], 0, d["rv"], d["match"]))
+    v = np.empty(S5, np.uint8); m = np.empty(S5, np.uint8); ctx.d2h(v, d["verdict"]); ctx.d2h(m, d["match"]); ctx.sync()
+    out[f"config5_{S5}_sessions"] = {"deltas": n5, "chain_capture_ms": t_chain, "commit_ms": t_c, "verify_ms": t_v,
+                                     "deltas_committed_verified_per_s": n5 / ((t_c + t_v) * 1e-3),
+                                     "all_verified": bool(v.all() and m.all())}
+    print(json.dumps(out[f"config5_{S5}_sessions"]), flush=True)
+    for p in d.values():
+        ctx.dev_free(p)
+    ctx.host_free(h)
+
+os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+json.dump(out, open(os.path.join(ROOT, "gpurun_out", "configs.json"), "w"), indent=1)
