@@ -12,6 +12,7 @@ from .audit import (ArenaBuilder, BatchAuditor, CommitmentEngine, CommitmentReco
 from .liability import LiabilityEdge, LiabilityMatrix, VouchGraphCSR, VouchingEngine, VouchingError, VouchRecord
 from .models import ActionDescriptor, ExecutionRing, ReversibilityLevel
 from .rings import RingCheckResult, RingEnforcer
+from .vfs import content_hashes
 
 __version__ = "0.1.0"
 
@@ -19,5 +20,5 @@ __all__ = [
     "Context", "NativeError", "NativeUnavailable", "get_context", "load_library",
     "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions",
     "SemanticDelta", "VFSChange", "LiabilityEdge", "LiabilityMatrix", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
-    "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer",
+    "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer", "content_hashes",
 ]

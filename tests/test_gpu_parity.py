@@ -79,6 +79,16 @@ def test_sha256_empty_batch(ctx):
     assert ctx.sha256_batch(np.zeros(0, np.uint8), np.zeros(1, np.uint64)).shape == (0, 32)
 
 
+def test_vfs_content_hashes(ctx):
+    """session/sso.py:214-216 for a batch of file contents (incl. empty, unicode, large)."""
+    from agent_hypervisor_b200 import content_hashes
+    rng = np.random.default_rng(12)
+    contents = ["", "hello", "héllo ☃ \U0001F600", "x" * 55, "y" * 64, "z" * 1_000_000]
+    contents += ["".join(chr(int(c)) for c in rng.integers(32, 0x2000, int(n))) for n in rng.integers(0, 3000, 200)]
+    assert content_hashes(contents) == [hashlib.sha256(c.encode()).hexdigest() for c in contents]
+    assert content_hashes([]) == []
+
+
 # ------------------------------------------------------------------ Merkle
 @pytest.mark.parametrize("n", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 15, 16, 17, 31, 33, 63, 64, 65, 125, 250, 1000])
 def test_golden_session_commit(ctx, audit_golden, n):
