@@ -341,7 +341,7 @@ k_level_rowptrs(const uint64_t *__restrict__ rowptr, uint64_t S, uint64_t *__res
 // One thread per output node (audit/delta.py:127-131).  Sessions that are already down
 // to one node carry it forward unchanged (the reference loop stops at len == 1, :125).
 template <bool UNIFORM, bool SC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128, 8)
 k_merkle_level(const uint8_t *__restrict__ in, uint8_t *__restrict__ out, uint64_t S,
                uint32_t c_in_u, uint32_t c_out_u,                       // uniform counts per session
                const uint64_t *__restrict__ rp_in, const uint64_t *__restrict__ rp_out, uint32_t rc)
@@ -366,18 +366,17 @@ k_merkle_level(const uint8_t *__restrict__ in, uint8_t *__restrict__ out, uint64
         in0 = rp_in[lo];
         c_in = rp_in[lo + 1] - in0;
     }
-    uint32_t l[8], r[8], d[8];
-    load_digest(in + 32 * (in0 + 2 * k), l);
+    const uint8_t *lp = in + 32 * (in0 + 2 * k);
     if (c_in == 1) {
-        store_digest(out + 32 * j, l);
+        const uint4 *src = reinterpret_cast<const uint4 *>(lp);
+        uint4 *dst = reinterpret_cast<uint4 *>(out + 32 * j);
+        dst[0] = src[0];
+        dst[1] = src[1];
         return;
     }
-    if (2 * k + 1 < c_in) load_digest(in + 32 * (in0 + 2 * k + 1), r);
-    else {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) r[q] = l[q];          // odd level: duplicate the last node (:129)
-    }
-    merkle_node(l, r, d, cp);
+    const uint8_t *rp = (2 * k + 1 < c_in) ? lp + 32 : lp;    // odd level: duplicate the last node (:129)
+    uint32_t d[8];
+    merkle_node_mem(lp, rp, d, cp);
     store_digest(out + 32 * j, d);
 }
 

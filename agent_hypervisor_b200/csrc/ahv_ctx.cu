@@ -138,10 +138,8 @@ int ahv_create(int device, ahv_ctx **out_ctx)
         AHV_CUDA(cudaEventCreate(&c->t_stop[i]));
     }
     c->opt_sort = 1;
-    c->opt_fixed_k = 3;
     c->opt_block = 128;
     c->opt_fixed_variant = 0;
-    c->opt_tree_k = 0;
     c->opt_top_max = 0;
     c->opt_compress = 1;
     c->opt_sigma_variant = 1;
@@ -284,17 +282,11 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     AHV_TRY(use_device(ctx));
     AHV_REQUIRE(key, "key is null");
     if (!strcmp(key, "sort")) ctx->opt_sort = value;
-    else if (!strcmp(key, "fixed_k")) {
-        AHV_REQUIRE(value >= 0 && value <= 3, "fixed_k must be 0..3");
-        ctx->opt_fixed_k = value;
-    } else if (!strcmp(key, "block")) {
+    else if (!strcmp(key, "block")) {
         AHV_REQUIRE(value == 64 || value == 128 || value == 256, "block must be 64/128/256");
         ctx->opt_block = value;
     } else if (!strcmp(key, "fixed_variant")) ctx->opt_fixed_variant = value;
-    else if (!strcmp(key, "tree_k")) {
-        AHV_REQUIRE(value >= 0 && value <= 3, "tree_k must be 0..3");
-        ctx->opt_tree_k = value;
-    } else if (!strcmp(key, "sigma_variant")) {
+    else if (!strcmp(key, "sigma_variant")) {
         AHV_REQUIRE(value == 0 || value == 1, "sigma_variant must be 0 or 1");
         ctx->opt_sigma_variant = value;
     } else if (!strcmp(key, "compress")) {

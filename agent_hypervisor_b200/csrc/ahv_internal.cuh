@@ -30,10 +30,8 @@ struct ahv_ctx {
     cudaEvent_t t_start[AHV_MAX_TIMERS], t_stop[AHV_MAX_TIMERS];
     // tuning options (ahv_set_option)
     int64_t opt_sort;          // 1: length-sort variable-length batches (default 1)
-    int64_t opt_fixed_k;       // log2 leaves per thread in the fused fixed-size kernel (default 3)
     int64_t opt_block;         // threads per block for SHA kernels (default 128)
     int64_t opt_fixed_variant; // 0: direct LDG.128, 1: smem-staged (cp.async)
-    int64_t opt_tree_k;        // log2 leaves per thread in the digest-tree kernel
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)

@@ -617,6 +617,26 @@ AHV_HD bool digest_equal_mem(const uint8_t *src, const uint32_t st[8])
     return diff == 0;
 }
 
+// Same node hash with the children still in memory (raw 32-byte digests): the right child is
+// fetched only when its block is due, which keeps 8 registers free in the level kernel.
+template <class P>
+AHV_HD void merkle_node_mem(const uint8_t *lp, const uint8_t *rp, uint32_t out[8], const P &cp)
+{
+    uint32_t st[8], w[16];
+    sha256_init(st);
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+        uint32_t x[8];
+        load_digest(half ? rp : lp, x);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) hex_expand(x[i], w[2 * i], w[2 * i + 1]);
+        cp.block(st, w);
+    }
+    cp.node_pad(st);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) out[i] = st[i];
+}
+
 // ---------------------------------------------------------------- whole messages
 // Word loader over an arbitrarily aligned byte string.  Reads only 4-byte aligned
 // words that contain at least one byte of [p, p+len); never touches memory past the

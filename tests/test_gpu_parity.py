@@ -32,6 +32,37 @@ def _tight(msgs):
     return arena, offs
 
 
+# ------------------------------------------------------------------ C ABI error behaviour
+def test_c_abi_error_codes(ctx):
+    import ctypes as C
+    from agent_hypervisor_b200 import NativeError
+    lib, h = ctx.lib, ctx.h
+    vp = C.c_void_p
+    out = np.zeros(64, np.uint8)
+    a = np.zeros(64, np.uint8)
+    assert lib.ahv_sha256_batch(h, vp(a.ctypes.data), None, 1, 0, vp(out.ctypes.data)) == -1       # no offsets, no fixed_len
+    assert b"offsets is NULL" in lib.ahv_last_error()
+    assert lib.ahv_sha256_batch(h, vp(a.ctypes.data), None, 1, 64, None) == -1                      # null output
+    assert lib.ahv_sha256_batch(None, vp(a.ctypes.data), None, 1, 64, vp(out.ctypes.data)) == -1    # null context
+    assert lib.ahv_sha256_batch(h, None, None, 0, 0, None) == 0                                     # empty batch is fine
+    rp = np.array([0, 2, 1], np.uint64)                                                             # decreasing rowptr
+    assert lib.ahv_merkle_roots(h, vp(a.ctypes.data), vp(rp.ctypes.data), 2, vp(out.ctypes.data), None) == -1
+    d = ctx.dev_alloc(256)
+    try:
+        with pytest.raises(NativeError, match="16-byte aligned"):
+            ctx.sha256_batch_dev(d, 64, 0, 1, 64, d + 8)
+        with pytest.raises(NativeError, match="n_sessions \\* uniform_leaves"):
+            ctx.commit_dev(d, 128, 0, 64, 0, 2, 3, 1, 1, d, d, d)
+    finally:
+        ctx.dev_free(d)
+    with pytest.raises(NativeError, match="unknown option"):
+        ctx.set_option("no_such_option", 1)
+    with pytest.raises(NativeError, match="top_max"):
+        ctx.set_option("top_max", 1)
+    c2 = C.c_void_p()
+    assert lib.ahv_create(4096, C.byref(c2)) == -1 and b"out of range" in lib.ahv_last_error()
+
+
 # ------------------------------------------------------------------ SHA-256
 def test_sha256_known_answers(ctx, audit_golden):
     msgs = [v["msg"].encode() for v in audit_golden["nist"]]
