@@ -160,6 +160,17 @@ __global__ void __launch_bounds__(256) k_peak_kct(int iters, const __grid_consta
     if (r == 0x12345678u) out[0] = r;
 }
 
+// dependent fp64 additions: latency of the serial chain a sequential row sum is made of
+__global__ void __launch_bounds__(256) k_peak_dadd_chain(int iters, double x, double *out)
+{
+    double acc = (double)threadIdx.x;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) acc = __dadd_rn(acc, x);
+    }
+    if (acc == -1.0) out[0] = acc;
+}
+
 template <int VARIANT>
 __global__ void __launch_bounds__(256) k_peak_compress(int iters, const __grid_constant__ ShaMults mu, uint32_t *out)
 {
@@ -192,10 +203,10 @@ __global__ void __launch_bounds__(256) k_peak_compress(int iters, const __grid_c
 extern "C" int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, float *out_ms)
 {
     AHV_TRY(use_device(ctx));
-    AHV_REQUIRE(((mode >= 0 && mode <= 19) || (mode >= 100 && mode < 100 + 18) || (mode >= 200 && mode < 200 + 18)) &&
+    AHV_REQUIRE(((mode >= 0 && mode <= 20) || (mode >= 100 && mode < 100 + 18) || (mode >= 200 && mode < 200 + 18)) &&
                     iters > 0 && out_instr_per_s, "bad ahv_int_peak arguments");
     AHV_TRY(scratch_reserve(ctx, 256));
-    uint32_t *d = (uint32_t *)scratch_take(ctx, 4);
+    uint32_t *d = (uint32_t *)scratch_take(ctx, 8);
     const unsigned grid = (unsigned)ctx->sm_count * 4, block = 256;
     const ShaMults mu = make_sha_mults();
     cudaEvent_t e0, e1;
@@ -225,6 +236,10 @@ extern "C" int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr
         case 17: { const KW64 kct = make_kc_table(); k_peak_kct<5><<<grid, block, 0, ctx->stream>>>(iters, mu, kct, d); per_thread = (double)iters * 1400.0; break; }
         case 18: k_peak_compress<7><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
         case 19: k_peak_compress<8><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
+        case 20:   // one warp per SM: nothing hides the latency; "instr/s" = additions per second per thread x threads
+            k_peak_dadd_chain<<<(unsigned)ctx->sm_count, 32, 0, ctx->stream>>>(iters, 1e-9, (double *)d);
+            per_thread = (double)iters * 16.0 * ((double)ctx->sm_count * 32.0) / ((double)grid * block);
+            break;
         case 9: k_peak_compress<2><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
 #define SEL_CASE(idx, mask)                                                                                              \
         case 100 + idx: k_peak_sel<mask, 1><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break; \

@@ -13,3 +13,8 @@ for mode, nm in ((0, "ALU only"), (2, "compress native"), (12, "scaled rounds+sc
         v, ms = ctx.int_peak(mode, int(os.environ.get('LAB_ITERS', '3000')))
         best = max(best, v)
     print(f"mode {mode} {nm}: {best/1e12:.3f} Tinstr/s = {best/1400/1e9:.2f} Gcomp/s", flush=True)
+
+v, ms = ctx.int_peak(20, 20000)
+adds = 20000 * 16
+info = ctx.device_info()
+print(f"dependent DADD chain: {ms*1e-3/adds*1e9:.2f} ns per addition = {ms*1e-3/adds*info['sm_clock_khz']*1e3:.1f} cycles at {info['sm_clock_khz']/1e3:.0f} MHz", flush=True)
