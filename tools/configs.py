@@ -28,6 +28,38 @@ def timed(fn, reps=3, warm=1):
     return best
 
 
+# ---------------------------------------------------------------- config 1: one session, 1000 benchmark-shaped deltas
+# (the reference's own CPU-runnable case: capture x1000, compute_merkle_root, verify_chain; median of 20)
+def config1():
+    import statistics
+    from agent_hypervisor_b200 import DeltaEngine, VFSChange
+    from oracle import audit_oracle as ao
+    import hashlib
+    def med(fn, reps=20, warm=2):
+        ts = []
+        for i in range(reps + warm):
+            t0 = time.perf_counter(); r = fn(); dt = time.perf_counter() - t0
+            if i >= warm: ts.append(dt)
+        return statistics.median(ts) * 1e3, r
+    def build():
+        de = DeltaEngine("bench-session")
+        for i in range(1000):
+            de.capture("did:mesh:a", [VFSChange(path=f"/f{i}", operation="add", content_hash=f"h{i}")])
+        return de
+    t_cap, de = med(build, reps=3, warm=1)
+    t_root, root = med(de.compute_merkle_root)
+    t_ver, ok = med(de.verify_chain)
+    hexes = [d.delta_hash for d in de.deltas]
+    t_root_cpu, root_cpu = med(lambda: ao.merkle_root_hex(hexes))
+    pre = [d.preimage() for d in de.deltas]; par = [d.parent_hash for d in de.deltas]
+    t_ver_cpu, v_cpu = med(lambda: ao.verify_chain_session(pre, par)[0])
+    return {"capture_1000_ms_gpu_dropin": t_cap, "merkle_root_ms_gpu_dropin": t_root, "verify_chain_ms_gpu_dropin": t_ver,
+            "merkle_root_ms_cpu_port": t_root_cpu, "verify_chain_ms_cpu_port_prepacked": t_ver_cpu,
+            "root_equal": root == root_cpu, "verify": bool(ok) and bool(v_cpu),
+            "note": "drop-in classes, one GPU call per capture (latency-bound); verify_chain includes the Python packer"}
+out["config1"] = config1()
+print(json.dumps(out["config1"]), flush=True)
+
 # ---------------------------------------------------------------- config 3
 n1, reps = 1_000_000, int(os.environ.get("CFG3_TILES", "10"))
 a1, o1 = workloads.config3_arena(n1)
