@@ -296,7 +296,7 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
 /* Selects a kernel variant for experiments (bench/tuning only); unknown keys return AHV_E_INVALID.
  *   "sort" 0/1          length-sort variable-length batches (default 1)
  *   "block" 64/128/256  threads per block of the leaf kernels (default 128)
- *   "fixed_variant" 0/1 fixed-size leaf kernel: direct 16-byte loads (default) / shared-memory staged
+ *   "fixed_variant" 0/1/2 fixed-size leaf kernel: direct 16-byte loads (default) / cp.async staged / TMA bulk-copy staged
  *   "compress" 0/1      plain additions / scaled-sum compression with additions on the FMA pipe (default 1)
  *   "top_max" 0,2..256  level width at which a session's tree is finished in one warp/CTA (0 = auto)
  *   "sigma_variant" 0/1 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1)

@@ -91,8 +91,8 @@ def test_sha256_random_lengths_vs_oracle(ctx, sort):
     assert np.array_equal(got, co.sha256_batch(arena, offs))
 
 
-@pytest.mark.parametrize("variant", [0, 1])
-@pytest.mark.parametrize("flen", [64, 128, 256, 320, 100, 55, 1])
+@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("flen", [64, 128, 256, 320, 384, 100, 55, 1])
 def test_sha256_fixed_len(ctx, flen, variant):
     rng = np.random.default_rng(flen)
     n = 2500 + flen % 7            # partial last warp
@@ -229,7 +229,7 @@ def test_verify_random_tampering_vs_oracle(ctx):
 
 
 # ------------------------------------------------------------------ config 2 shape (fixed 256 B, uniform sessions)
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 2])
 def test_config2_small_vs_golden_and_oracle(ctx, audit_golden, variant):
     S, L = 40, 1000
     first = 1200

@@ -67,7 +67,7 @@ def main():
         print(f"compress={comp}: leaf fixed {best:.3f} ms ({comp_leaf/best/1e6:.2f} Gcomp/s), commit {b2:.3f} ms, leaf var {b3:.3f} ms", flush=True)
         res[f"commit_compress{comp}"] = {"best_ms": b2}
         res[f"leaf_var_compress{comp}"] = {"best_ms": b3}
-    for variant in (0, 1):
+    for variant in (0, 1, 2):
         for block in (64, 128, 256):
             ctx.set_option("fixed_variant", variant); ctx.set_option("block", block)
             best, avg = timed(ctx, lambda: ctx.sha256_batch_dev(d["arena"], arena.nbytes, 0, n, FL, d["digs"]))
