@@ -22,7 +22,11 @@ from typing import Optional
 import numpy as np
 
 from .. import _native as nat
-from .packing import ArenaBuilder, canonical_preimage, is_hexdigest
+import re
+
+from .packing import ArenaBuilder, canonical_preimage
+
+_LOWER_HEX = re.compile(r"[0-9a-f]*")
 
 
 @dataclass
@@ -73,8 +77,9 @@ def _merkle_root_of_strings(hashes: list[str]) -> Optional[str]:
     if len(hashes) == 1:
         return hashes[0]
     ctx = nat.get_context()
-    if all(is_hexdigest(h) for h in hashes):
-        digs = np.frombuffer(bytes.fromhex("".join(hashes)), dtype=np.uint8).reshape(-1, 32)
+    joined = "".join(hashes) if all(type(h) is str for h in hashes) else ""
+    if len(joined) == 64 * len(hashes) and set(map(len, hashes)) == {64} and _LOWER_HEX.fullmatch(joined):
+        digs = np.frombuffer(bytes.fromhex(joined), dtype=np.uint8).reshape(-1, 32)
     else:
         msgs = []
         for i in range(0, len(hashes), 2):
