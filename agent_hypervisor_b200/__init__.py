@@ -13,6 +13,7 @@ from .liability import LiabilityEdge, LiabilityMatrix, VouchGraphCSR, VouchingEn
 from .models import ActionDescriptor, ExecutionRing, ReversibilityLevel
 from .rings import RingCheckResult, RingEnforcer
 from .vfs import content_hashes
+from .install import install, uninstall
 
 __version__ = "0.1.0"
 
@@ -20,5 +21,5 @@ __all__ = [
     "Context", "NativeError", "NativeUnavailable", "get_context", "load_library",
     "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions",
     "SemanticDelta", "VFSChange", "LiabilityEdge", "LiabilityMatrix", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
-    "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer", "content_hashes",
+    "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer", "content_hashes", "install", "uninstall",
 ]

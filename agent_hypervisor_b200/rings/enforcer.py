@@ -60,8 +60,20 @@ def check_batch(agent_ring, action_flags, sigma_eff, has_consensus, has_sre_witn
     return ctx.ring_check(agent_ring, action_flags, sigma_eff, has_consensus, has_sre_witness)
 
 
+def _flags_of(action) -> int:
+    """AHV_ACT_* bits of an ActionDescriptor - ours or the reference's (models.py:104-132)."""
+    f = getattr(action, "action_flags", None)
+    if f is not None:
+        return int(f)
+    rev = getattr(action.reversibility, "value", action.reversibility)
+    return ((nat.ACT_ADMIN if action.is_admin else 0) | (nat.ACT_READ_ONLY if action.is_read_only else 0)
+            | (nat.ACT_REV_NONE if rev == "none" else 0))
+
+
 class RingEnforcer:
-    """4-ring privilege gate (rings/enforcer.py:28-137)."""
+    """4-ring privilege gate (rings/enforcer.py:28-137).  Works with this package's model types and,
+    after ``install()``, with the reference's own ``ExecutionRing`` / ``ActionDescriptor``: rings
+    come back as members of the enum class the caller passed in."""
 
     RING_1_THRESHOLD = 0.95
     RING_2_THRESHOLD = 0.60
@@ -85,18 +97,19 @@ class RingEnforcer:
 
     def check(self, agent_ring: ExecutionRing, action: ActionDescriptor, sigma_eff: float,
               has_consensus: bool = False, has_sre_witness: bool = False) -> RingCheckResult:
-        al, code, req = check_batch([int(agent_ring.value)], [action.action_flags], [sigma_eff],
+        al, code, req = check_batch([int(agent_ring.value)], [_flags_of(action)], [sigma_eff],
                                     [bool(has_consensus)], [bool(has_sre_witness)])
         code, req = int(code[0]), int(req[0])
+        ring_cls = type(agent_ring) if hasattr(type(agent_ring), "RING_0_ROOT") else ExecutionRing
         return RingCheckResult(
-            allowed=bool(al[0]), required_ring=ExecutionRing(req), agent_ring=agent_ring, sigma_eff=sigma_eff,
+            allowed=bool(al[0]), required_ring=ring_cls(req), agent_ring=agent_ring, sigma_eff=sigma_eff,
             reason=self._reason_text(code, int(agent_ring.value), req, sigma_eff),
             requires_consensus=(code == nat.REASON_NEEDS_CONSENSUS),
             requires_sre_witness=(code == nat.REASON_NEEDS_WITNESS))
 
     def check_many(self, agent_rings, actions: Sequence[ActionDescriptor], sigma_eff, has_consensus,
                    has_sre_witness) -> list[RingCheckResult]:
-        al, code, req = check_batch([int(r.value) for r in agent_rings], [a.action_flags for a in actions],
+        al, code, req = check_batch([int(r.value) for r in agent_rings], [_flags_of(a) for a in actions],
                                     sigma_eff, has_consensus, has_sre_witness)
         return [RingCheckResult(bool(al[i]), ExecutionRing(int(req[i])), agent_rings[i], sigma_eff[i],
                                 self._reason_text(int(code[i]), int(agent_rings[i].value), int(req[i]), sigma_eff[i]),

@@ -106,6 +106,26 @@ def test_sha256_fixed_len(ctx, flen, variant):
     assert np.array_equal(got, co.sha256_batch(arena, offs))
 
 
+def test_config3_shape_vs_oracle(ctx):
+    """Config-3 shape (log-uniform 64 B..16 KB, tightly packed, every alignment), 2x10^5 messages = 0.6 GB:
+    hash + 200 trees + verify against the C oracle, sorted and unsorted launch order."""
+    n = 200_000
+    arena, offs = workloads.config3_arena(n, seed=0xA6E27)
+    want = co.sha256_batch(arena, offs)
+    got = ctx.sha256_batch(arena, offs)
+    assert np.array_equal(got, want)
+    rp = (np.arange(201, dtype=np.uint64) * 1000)
+    par = np.zeros((n, 32), np.uint8); par[1:] = want[:-1]
+    kind = np.ones(n, np.uint8); kind[::1000] = 0
+    par[123_456] ^= 1                                        # one broken link: session 123, position 456
+    res = ctx.verify_chains(arena, offs, par, kind, rp, want_roots=True)
+    wr, _ = co.merkle_roots(want, rp)
+    assert np.array_equal(res["roots"], wr) and np.array_equal(res["digests"], want)
+    assert list(np.nonzero(res["verdict"] == 0)[0]) == [123] and res["first_bad"][123] == 456
+    lens = np.diff(offs.astype(np.int64))
+    assert lens.min() >= 64 and lens.max() <= 16384 and 2000 < lens.mean() < 4000
+
+
 def test_sha256_empty_batch(ctx):
     assert ctx.sha256_batch(np.zeros(0, np.uint8), np.zeros(1, np.uint64)).shape == (0, 32)
 

