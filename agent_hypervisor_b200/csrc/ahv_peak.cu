@@ -171,6 +171,25 @@ __global__ void __launch_bounds__(256) k_peak_dadd_chain(int iters, double x, do
     if (acc == -1.0) out[0] = acc;
 }
 
+template <int A, int B, int C, int D>
+__global__ void __launch_bounds__(256) k_peak_search(int iters, uint32_t rc, uint32_t *out)
+{
+    uint32_t st[8];
+    sha256_init(st);
+    st[0] ^= threadIdx.x;
+    st[1] ^= blockIdx.x;
+    for (int it = 0; it < iters; ++it) {
+        uint32_t w[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) w[k] = st[k & 7] ^ (0x01010101u * k);
+        sha256_compress_search<A, B, C, D>(st, w, rc);
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r ^= st[k];
+    if (r == 0x12345678u) out[0] = r;
+}
+
 template <int VARIANT>
 __global__ void __launch_bounds__(256) k_peak_compress(int iters, const __grid_constant__ ShaMults mu, uint32_t *out)
 {
@@ -203,7 +222,7 @@ __global__ void __launch_bounds__(256) k_peak_compress(int iters, const __grid_c
 extern "C" int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, float *out_ms)
 {
     AHV_TRY(use_device(ctx));
-    AHV_REQUIRE(((mode >= 0 && mode <= 20) || (mode >= 100 && mode < 100 + 18) || (mode >= 200 && mode < 200 + 18)) &&
+    AHV_REQUIRE(((mode >= 0 && mode <= 20) || (mode >= 100 && mode < 100 + 18) || (mode >= 200 && mode < 200 + 18) || (mode >= 300 && mode < 348)) &&
                     iters > 0 && out_instr_per_s, "bad ahv_int_peak arguments");
     AHV_TRY(scratch_reserve(ctx, 256));
     uint32_t *d = (uint32_t *)scratch_take(ctx, 8);
@@ -240,6 +259,54 @@ extern "C" int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr
             k_peak_dadd_chain<<<(unsigned)ctx->sm_count, 32, 0, ctx->stream>>>(iters, 1e-9, (double *)d);
             per_thread = (double)iters * 16.0 * ((double)ctx->sm_count * 32.0) / ((double)grid * block);
             break;
+        case 300: k_peak_search<0, 0, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 301: k_peak_search<0, 0, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 302: k_peak_search<0, 0, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 303: k_peak_search<0, 0, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 304: k_peak_search<0, 0, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 305: k_peak_search<0, 0, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 306: k_peak_search<0, 1, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 307: k_peak_search<0, 1, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 308: k_peak_search<0, 1, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 309: k_peak_search<0, 1, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 310: k_peak_search<0, 1, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 311: k_peak_search<0, 1, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 312: k_peak_search<1, 0, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 313: k_peak_search<1, 0, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 314: k_peak_search<1, 0, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 315: k_peak_search<1, 0, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 316: k_peak_search<1, 0, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 317: k_peak_search<1, 0, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 318: k_peak_search<1, 1, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 319: k_peak_search<1, 1, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 320: k_peak_search<1, 1, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 321: k_peak_search<1, 1, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 322: k_peak_search<1, 1, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 323: k_peak_search<1, 1, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 324: k_peak_search<2, 0, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 325: k_peak_search<2, 0, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 326: k_peak_search<2, 0, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 327: k_peak_search<2, 0, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 328: k_peak_search<2, 0, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 329: k_peak_search<2, 0, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 330: k_peak_search<2, 1, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 331: k_peak_search<2, 1, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 332: k_peak_search<2, 1, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 333: k_peak_search<2, 1, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 334: k_peak_search<2, 1, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 335: k_peak_search<2, 1, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 336: k_peak_search<3, 0, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 337: k_peak_search<3, 0, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 338: k_peak_search<3, 0, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 339: k_peak_search<3, 0, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 340: k_peak_search<3, 0, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 341: k_peak_search<3, 0, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 342: k_peak_search<3, 1, 0, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 343: k_peak_search<3, 1, 0, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 344: k_peak_search<3, 1, 0, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 345: k_peak_search<3, 1, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 346: k_peak_search<3, 1, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 347: k_peak_search<3, 1, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
         case 9: k_peak_compress<2><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
 #define SEL_CASE(idx, mask)                                                                                              \
         case 100 + idx: k_peak_sel<mask, 1><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break; \

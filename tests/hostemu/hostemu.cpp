@@ -125,3 +125,15 @@ void emu_sha256_fixed256(const uint8_t *p, int scaled, uint8_t *out32)
     memcpy(out32, tmp, 32);
 }
 }
+
+extern "C" void emu_compress_search(const uint32_t *block16, uint32_t *out16)
+{
+    for (int v = 0; v < 2; ++v) {
+        uint32_t st[8], w[16];
+        ahv::sha256_init(st);
+        for (int i = 0; i < 16; ++i) w[i] = block16[i];
+        if (v == 0) ahv::sha256_compress(st, w);
+        else ahv::sha256_compress_search<3, 1, 1, 2>(st, w, ahv::SHA_SC);
+        for (int i = 0; i < 8; ++i) out16[8 * v + i] = st[i];
+    }
+}

@@ -124,3 +124,12 @@ def test_scaled_policy_matches_hashlib(emu):
         for scaled in (0, 1):
             emu.emu_sha256_fixed256(m.ctypes.data_as(u8p), scaled, out.ctypes.data_as(u8p))
             assert out.tobytes() == hashlib.sha256(m.tobytes()).digest()
+
+
+def test_search_formulation_is_the_same_function(emu):
+    rng = np.random.default_rng(23)
+    for _ in range(100):
+        blk = rng.integers(0, 2**32, 16, dtype=np.uint32)
+        out = np.zeros(16, np.uint32)
+        emu.emu_compress_search(blk.ctypes.data_as(C.POINTER(C.c_uint32)), out.ctypes.data_as(C.POINTER(C.c_uint32)))
+        assert np.array_equal(out[:8], out[8:])
