@@ -11,7 +11,7 @@
 //   mode 8: full compressions with every add issued as IMAD (sha256_compress_imad)
 //   mode 9: mode 8 + message-schedule sigmas through IMAD.WIDE (sha256_compress_wide)
 #include "ahv_internal.cuh"
-#include "sha256_core.cuh"
+#include "sha256_lab.cuh"
 
 using namespace ahv;
 
@@ -209,7 +209,10 @@ __global__ void __launch_bounds__(256) k_peak_compress(int iters, const __grid_c
         else if (VARIANT == 5) sha256_compress_scaled_v<2>(st, w, mu.c);
         else if (VARIANT == 6) sha256_compress_scaled_v<3>(st, w, mu.c);
         else if (VARIANT == 7) sha256_compress_scaled_v<8 + 1>(st, w, mu.one - 1u);   // run-time zero addend
-        else sha256_compress_scaled_v<8>(st, w, mu.one - 1u);
+        else if (VARIANT == 8) sha256_compress_scaled_v<8>(st, w, mu.one - 1u);
+        else if (VARIANT == 9) sha256_compress_scaled_v<3 + 16>(st, w, mu.c);    // + plain shifts as IMAD.HI
+        else if (VARIANT == 10) sha256_compress_scaled_v<3 + 32>(st, w, mu.c);   // h+K+w as one IADD3
+        else sha256_compress_scaled_v<3 + 16 + 32>(st, w, mu.c);                 // both
     }
     uint32_t r = 0;
 #pragma unroll
@@ -222,7 +225,7 @@ __global__ void __launch_bounds__(256) k_peak_compress(int iters, const __grid_c
 extern "C" int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, float *out_ms)
 {
     AHV_TRY(use_device(ctx));
-    AHV_REQUIRE(((mode >= 0 && mode <= 20) || (mode >= 100 && mode < 100 + 18) || (mode >= 200 && mode < 200 + 18) || (mode >= 300 && mode < 348)) &&
+    AHV_REQUIRE(((mode >= 0 && mode <= 23) || (mode >= 100 && mode < 100 + 18) || (mode >= 200 && mode < 200 + 18) || (mode >= 300 && mode < 348)) &&
                     iters > 0 && out_instr_per_s, "bad ahv_int_peak arguments");
     AHV_TRY(scratch_reserve(ctx, 256));
     uint32_t *d = (uint32_t *)scratch_take(ctx, 8);
@@ -307,6 +310,9 @@ extern "C" int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr
         case 345: k_peak_search<3, 1, 1, 0><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
         case 346: k_peak_search<3, 1, 1, 1><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
         case 347: k_peak_search<3, 1, 1, 2><<<grid, block, 0, ctx->stream>>>(iters, mu.c, d); per_thread = (double)iters * 1400.0; break;
+        case 21: k_peak_compress<9><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
+        case 22: k_peak_compress<10><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
+        case 23: k_peak_compress<11><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
         case 9: k_peak_compress<2><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break;
 #define SEL_CASE(idx, mask)                                                                                              \
         case 100 + idx: k_peak_sel<mask, 1><<<grid, block, 0, ctx->stream>>>(iters, mu, d); per_thread = (double)iters * 1400.0; break; \

@@ -3,7 +3,7 @@
 // errors are caught in the CPU-only container before a GPU run.  Never loaded by
 // the product package.
 #include <cstring>
-#include "../../agent_hypervisor_b200/csrc/sha256_core.cuh"
+#include "../../agent_hypervisor_b200/csrc/sha256_lab.cuh"
 
 extern "C" {
 void emu_sha256(const uint8_t *p, uint64_t len, uint8_t *out32)
@@ -133,7 +133,7 @@ extern "C" void emu_compress_search(const uint32_t *block16, uint32_t *out16)
         ahv::sha256_init(st);
         for (int i = 0; i < 16; ++i) w[i] = block16[i];
         if (v == 0) ahv::sha256_compress(st, w);
-        else ahv::sha256_compress_search<3, 1, 1, 2>(st, w, ahv::SHA_SC);
+        else ahv::sha256_compress_scaled_v<3 + 16 + 32>(st, w, ahv::SHA_SC);
         for (int i = 0; i < 8; ++i) out16[8 * v + i] = st[i];
     }
 }

@@ -7,7 +7,8 @@ ctx = Context(0)
 for mode, nm in ((0, "ALU only"), (2, "compress native"), (12, "scaled rounds+sched"), (13, "scaled rounds, native sched"),
                  (14, "scaled rounds (K native), native sched"), (15, "scaled rounds (K native) + sched"),
                  (16, "scaled rounds (K const-bank), native sched"), (17, "scaled rounds (K const-bank) + sched"),
-                 (18, "rt-zero addend: rounds (K native) + sched"), (19, "rt-zero addend: rounds (K native), native sched")):
+                 (21, "mode 15 + plain shifts as IMAD.HI (immediate)"), (22, "mode 15 with h+K+w as one IADD3"),
+                 (23, "mode 15 + IMAD.HI shifts + IADD3 h+K+w"), (18, "rt-zero addend: rounds (K native) + sched"), (19, "rt-zero addend: rounds (K native), native sched")):
     best = 0
     for _ in range(3):
         v, ms = ctx.int_peak(mode, int(os.environ.get('LAB_ITERS', '3000')))
