@@ -295,6 +295,9 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     } else if (!strcmp(key, "top_max")) {
         AHV_REQUIRE(value == 0 || (value >= 2 && value <= 256), "top_max must be 0 (auto) or 2..256");
         ctx->opt_top_max = value;
+    } else if (!strcmp(key, "peak_ctas")) {
+        AHV_REQUIRE(value >= 1 && value <= 8, "peak_ctas must be 1..8");
+        ctx->opt_peak_ctas = value;
     } else if (!strcmp(key, "leaf_timer")) {
         AHV_REQUIRE(value == 0 || (value > 0 && value + 16 <= AHV_MAX_TIMERS), "leaf_timer base must leave 16 slots");
         ctx->opt_leaf_timer = value;

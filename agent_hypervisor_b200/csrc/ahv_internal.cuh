@@ -35,6 +35,7 @@ struct ahv_ctx {
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)
+    int64_t opt_peak_ctas;     // CTAs of 256 threads per SM in the ahv_int_peak kernels (default 4)
     int64_t opt_leaf_timer;    // >0: bracket every leaf-hash launch with timer slots base..base+15 (round robin)
     uint64_t leaf_launches;    // leaf-hash kernel launches so far (indexes the round robin)
 };

@@ -229,7 +229,7 @@ extern "C" int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr
                     iters > 0 && out_instr_per_s, "bad ahv_int_peak arguments");
     AHV_TRY(scratch_reserve(ctx, 256));
     uint32_t *d = (uint32_t *)scratch_take(ctx, 8);
-    const unsigned grid = (unsigned)ctx->sm_count * 4, block = 256;
+    const unsigned grid = (unsigned)ctx->sm_count * (unsigned)(ctx->opt_peak_ctas > 0 ? ctx->opt_peak_ctas : 4), block = 256;
     const ShaMults mu = make_sha_mults();
     cudaEvent_t e0, e1;
     AHV_CUDA(cudaEventCreate(&e0));
