@@ -133,6 +133,7 @@ class Context:
         self.h = h
         self.device = int(device)
         self._lock = threading.Lock()   # one host thread per call
+        self._pinned: dict[int, int] = {}   # numpy data address -> pinned allocation
 
     # -- plumbing -----------------------------------------------------------
     def _check(self, rc: int, what: str):
@@ -182,11 +183,11 @@ class Context:
         buf = (C.c_uint8 * int(nbytes)).from_address(p.value)
         a = np.frombuffer(buf, dtype=np.uint8).view(dtype)
         a.flags.writeable = True
-        self.__dict__.setdefault("_pinned", {})[a.ctypes.data] = p.value
+        self._pinned[a.ctypes.data] = p.value
         return a
 
     def host_free(self, arr: np.ndarray):
-        p = self.__dict__.get("_pinned", {}).pop(arr.ctypes.data, None)
+        p = self._pinned.pop(arr.ctypes.data, None)
         if p is not None:
             self._check(self.lib.ahv_host_free(self.h, _vp(p)), "ahv_host_free")
 

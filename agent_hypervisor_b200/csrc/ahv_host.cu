@@ -298,11 +298,27 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
     if (nchunk < 2) nchunk = 2;
     if (nchunk > MAXC) nchunk = MAXC;
     const uint64_t per = (S + nchunk - 1) / nchunk;
-    cudaEvent_t ev_in[MAXC], ev_done[MAXC];
-    const int created = nchunk;
+    struct Events {                       // destroyed on every exit path, after the streams have drained
+        ahv_ctx *ctx;
+        cudaEvent_t in[MAXC], done[MAXC];
+        int n = 0;
+        ~Events()
+        {
+            cudaStreamSynchronize(ctx->copy_stream);
+            cudaStreamSynchronize(ctx->stream);
+            cudaStreamSynchronize(ctx->d2h_stream);
+            for (int k = 0; k < n; ++k) {
+                cudaEventDestroy(in[k]);
+                cudaEventDestroy(done[k]);
+            }
+        }
+    } ev;
+    ev.ctx = ctx;
+    cudaEvent_t *ev_in = ev.in, *ev_done = ev.done;
     for (int k = 0; k < nchunk; ++k) {
         AHV_CUDA(cudaEventCreateWithFlags(&ev_in[k], cudaEventDisableTiming));
         AHV_CUDA(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
+        ev.n = k + 1;
     }
     // (the first chunk may grow the scratch slab, which synchronises once; later chunks reuse it)
     int rc = AHV_OK;
@@ -336,10 +352,6 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
     cudaStreamSynchronize(ctx->copy_stream);
     cudaStreamSynchronize(ctx->stream);
     cudaError_t e = cudaStreamSynchronize(ctx->d2h_stream);
-    for (int k = 0; k < created; ++k) {
-        cudaEventDestroy(ev_in[k]);
-        cudaEventDestroy(ev_done[k]);
-    }
     if (rc != AHV_OK) return rc;
     if (e != cudaSuccess) {
         set_error("pipelined audit failed: %s", cudaGetErrorString(e));
