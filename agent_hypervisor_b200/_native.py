@@ -69,10 +69,11 @@ SIGNATURES = {
     "ahv_verify_chains": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahv_verify_chains_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _u64, _u64, _vp,
                                         _vp, _vp, _vp, _vp, _vp]),
-    "ahv_audit_sessions": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahv_audit_sessions": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahv_extract_parents_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _vp]),
     "ahv_chain_capture": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_chain_capture_dev": (C.c_int, [_vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp]),
-    "ahv_pack_deltas": (C.c_int, [_vp, _vp, _vp, _u64, _u64p]),
+    "ahv_pack_deltas": (C.c_int, [_vp, _vp, _vp, _u64, _u64p, _vp]),
     "ahv_sigma_eff_rings": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,
                                       _vp, _vp, _vp, _vp]),
     "ahv_sigma_eff_rings_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,
@@ -282,13 +283,15 @@ class Context:
         return {"verdict": verdict, "first_bad": first_bad, "digests": digs, "roots": roots, "root_match": match}
 
     def audit_sessions(self, arena, offsets, parent_digests, parent_kind, session_rowptr=None, fixed_len: int = 0,
-                       uniform_leaves: int = 0, n_sessions: Optional[int] = None, want_digests: bool = True, out=None):
+                       uniform_leaves: int = 0, n_sessions: Optional[int] = None, want_digests: bool = True, out=None,
+                       parent_pos=None):
         """Commit + verify on one upload (ahv_audit_sessions).  ``out`` may supply preallocated
         (e.g. pinned) result arrays: dict with digests/roots/empty/verdict/first_bad/root_match."""
         arena = _arr(arena, np.uint8)
         offsets = _arr(offsets, np.uint64)
         par = _arr(parent_digests, np.uint8)
         kind = _arr(parent_kind, np.uint8)
+        ppos = _arr(parent_pos, np.uint32)
         rp = _arr(session_rowptr, np.uint64)
         S = (len(rp) - 1) if rp is not None else int(n_sessions)
         n = int(rp[-1]) if rp is not None else S * int(uniform_leaves)
@@ -301,7 +304,7 @@ class Context:
         o.setdefault("root_match", np.zeros(S, dtype=np.uint8))
         with self._lock:
             self._check(self.lib.ahv_audit_sessions(
-                self.h, _ptr(arena), _ptr(offsets), int(fixed_len), _ptr(par), _ptr(kind), _ptr(rp), S,
+                self.h, _ptr(arena), _ptr(offsets), int(fixed_len), _ptr(par), _ptr(kind), _ptr(ppos), _ptr(rp), S,
                 int(uniform_leaves), _ptr(o["digests"]), _ptr(o["roots"]), _ptr(o["empty"]), _ptr(o["verdict"]),
                 _ptr(o["first_bad"]), _ptr(o["root_match"])), "ahv_audit_sessions")
         return o
@@ -392,6 +395,33 @@ class Context:
         self._check(self.lib.ahv_chain_capture_dev(self.h, _vp(d_arena), arena_bytes, _vp(d_offsets), _vp(d_hexpos),
                                                    _vp(d_rowptr), S, n, _vp(d_digests), _vp(d_par), _vp(d_kind)),
                     "ahv_chain_capture_dev")
+
+    def extract_parents_dev(self, d_arena, arena_bytes, d_offsets, fixed_len, d_parent_pos, n, d_par, d_kind):
+        self._check(self.lib.ahv_extract_parents_dev(self.h, _vp(d_arena), arena_bytes, _vp(d_offsets), int(fixed_len),
+                                                     _vp(d_parent_pos), n, _vp(d_par), _vp(d_kind)),
+                    "ahv_extract_parents_dev")
+
+    def extract_parents(self, arena, offsets, parent_pos, fixed_len: int = 0):
+        """(parent_digests [n,32], parent_kind [n]) read out of the pre-images on the device."""
+        arena = _arr(arena, np.uint8); offsets = _arr(offsets, np.uint64); ppos = _arr(parent_pos, np.uint32)
+        n = len(ppos)
+        par = np.zeros((n, 32), dtype=np.uint8); kind = np.zeros(n, dtype=np.uint8)
+        if n == 0:
+            return par, kind
+        bufs = [self.dev_alloc(max(arena.nbytes, 1) + 16), self.dev_alloc(8 * (n + 1)), self.dev_alloc(4 * n),
+                self.dev_alloc(32 * n), self.dev_alloc(n)]
+        try:
+            self.h2d(bufs[0], arena); self.h2d(bufs[2], ppos)
+            if offsets is not None:
+                self.h2d(bufs[1], offsets)
+            self.extract_parents_dev(bufs[0], arena.nbytes, bufs[1] if offsets is not None else None, fixed_len,
+                                     bufs[2], n, bufs[3], bufs[4])
+            self.d2h(par, bufs[3]); self.d2h(kind, bufs[4])
+            self.sync()
+        finally:
+            for b in bufs:
+                self.dev_free(b)
+        return par, kind
 
     def sigma_eff_rings_dev(self, d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_cons, d_ring, A,
                             d_os, d_or, d_od, d_on):

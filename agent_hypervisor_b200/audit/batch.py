@@ -60,6 +60,22 @@ class BatchAuditor:
         res["verdict"] = res["verdict"].astype(bool)
         return res
 
+    def audit(self, packed: PackedSessions):
+        """Commit + verify on ONE upload (``ahv_audit_sessions``): what an auditor replaying stored sessions
+        needs - every Merkle root (core.py:204-207) and every verify_chain verdict (audit/delta.py:136-152).
+        The parents are read out of the pre-images on the device when the packer recorded their positions.
+        -> dict(digests, roots hex|None per session, verdict bool[S], first_bad int[S], root_match)."""
+        fixed, uni = packed.uniform_shape()
+        by_pos = packed.parent_pos is not None
+        o = self.ctx.audit_sessions(
+            packed.arena, None if fixed else packed.offsets,
+            None if by_pos else packed.parents, None if by_pos else packed.parent_kind,
+            None if uni else packed.session_rowptr, fixed_len=fixed if fixed else 0, uniform_leaves=uni,
+            n_sessions=packed.n_sessions, parent_pos=packed.parent_pos if by_pos else None)
+        o["roots"] = [None if o["empty"][s] else o["roots"][s].tobytes().hex() for s in range(packed.n_sessions)]
+        o["verdict"] = o["verdict"].astype(bool)
+        return o
+
     def verify_engines(self, engines: Sequence) -> list[bool]:
         """verify_chain for many DeltaEngines, including the reference's delta_hash write-back."""
         packed = self.pack(engines)

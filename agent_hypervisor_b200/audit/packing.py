@@ -30,17 +30,30 @@ def _enc(v) -> str:
     return json.dumps(v, sort_keys=True)              # ints, floats, bools, nested containers
 
 
-def canonical_preimage(delta) -> bytes:
-    """Pre-image of ``SemanticDelta.compute_hash`` (audit/delta.py:43-62) as bytes."""
+PARENT_POS_NONE = 0xFFFFFFFF     # parent_pos of a delta whose parent_hash is None
+
+
+def canonical_preimage_pos(delta) -> tuple[bytes, int]:
+    """Pre-image of ``SemanticDelta.compute_hash`` (audit/delta.py:43-62) as bytes, and the position in it
+    of the first character of the ``parent_hash`` value (past the opening quote of a string;
+    ``PARENT_POS_NONE`` for None): the ``parent_pos`` entry ``ahv_audit_sessions`` reads the parent from."""
     changes = ", ".join(
         '{"content_hash": %s, "operation": %s, "path": %s, "previous_hash": %s}'
         % (_enc(c.content_hash), _enc(c.operation), _enc(c.path), _enc(c.previous_hash))
         for c in delta.changes)
-    text = ('{"agent_did": %s, "changes": [%s], "delta_id": %s, "parent_hash": %s, '
-            '"session_id": %s, "timestamp": %s, "turn_id": %s}'
-            % (_enc(delta.agent_did), changes, _enc(delta.delta_id), _enc(delta.parent_hash),
-               _enc(delta.session_id), _enc(delta.timestamp.isoformat()), _enc(delta.turn_id)))
-    return text.encode()
+    head = ('{"agent_did": %s, "changes": [%s], "delta_id": %s, "parent_hash": '
+            % (_enc(delta.agent_did), changes, _enc(delta.delta_id)))
+    ph = delta.parent_hash
+    text = (head + '%s, "session_id": %s, "timestamp": %s, "turn_id": %s}'
+            % (_enc(ph), _enc(delta.session_id), _enc(delta.timestamp.isoformat()), _enc(delta.turn_id)))
+    # ensure_ascii: every character is one byte, so string positions are byte positions
+    pos = PARENT_POS_NONE if ph is None else len(head) + (1 if type(ph) is str else 0)
+    return text.encode(), pos
+
+
+def canonical_preimage(delta) -> bytes:
+    """Pre-image of ``SemanticDelta.compute_hash`` (audit/delta.py:43-62) as bytes."""
+    return canonical_preimage_pos(delta)[0]
 
 
 def classify_parent(parent_hash) -> tuple[int, bytes]:
@@ -63,6 +76,7 @@ class PackedSessions:
     parents: np.ndarray          # uint8[n,32]
     parent_kind: np.ndarray      # uint8[n]
     session_rowptr: np.ndarray   # uint64[S+1]
+    parent_pos: Optional[np.ndarray] = None   # uint32[n]; None when a pre-image was added without its position
 
     @property
     def n(self) -> int:
@@ -90,16 +104,22 @@ class ArenaBuilder:
         self._parents = bytearray()
         self._kind = bytearray()
         self._rowptr = [0]
+        self._pos: Optional[list] = []
 
-    def add_preimage(self, preimage: bytes, parent_hash) -> None:
+    def add_preimage(self, preimage: bytes, parent_hash, parent_pos: Optional[int] = None) -> None:
         self._buf += preimage
         self._offsets.append(len(self._buf))
         k, raw = classify_parent(parent_hash)
         self._kind.append(k)
         self._parents += raw
+        if parent_pos is None:
+            self._pos = None                       # positions unknown: callers use the side arrays
+        elif self._pos is not None:
+            self._pos.append(parent_pos)
 
     def add_delta(self, delta) -> None:
-        self.add_preimage(canonical_preimage(delta), delta.parent_hash)
+        pre, pos = canonical_preimage_pos(delta)
+        self.add_preimage(pre, delta.parent_hash, pos)
 
     def end_session(self) -> None:
         self._rowptr.append(len(self._kind))
@@ -118,7 +138,8 @@ class ArenaBuilder:
             offsets=np.array(self._offsets, dtype=np.uint64),
             parents=np.frombuffer(bytes(self._parents), dtype=np.uint8).reshape(n, 32),
             parent_kind=np.frombuffer(bytes(self._kind), dtype=np.uint8),
-            session_rowptr=np.array(self._rowptr, dtype=np.uint64))
+            session_rowptr=np.array(self._rowptr, dtype=np.uint64),
+            parent_pos=None if self._pos is None else np.array(self._pos, dtype=np.uint32))
 
 
 def pack_sessions(sessions: Sequence[Sequence]) -> PackedSessions:
@@ -197,8 +218,9 @@ def columns_from_deltas(deltas) -> dict:
     }
 
 
-def pack_columns(cols: dict, arena: Optional[np.ndarray] = None):
-    """Canonical pre-images of ``cols['n']`` deltas via the C++ packer -> (arena u8[], offsets u64[n+1])."""
+def pack_columns(cols: dict, arena: Optional[np.ndarray] = None, want_parent_pos: bool = False):
+    """Canonical pre-images of ``cols['n']`` deltas via the C++ packer -> (arena u8[], offsets u64[n+1])
+    and, with ``want_parent_pos``, the uint32[n] positions of the parent values as a third element."""
     lib = nat.load_library()
     keep = []
 
@@ -223,12 +245,16 @@ def pack_columns(cols: dict, arena: Optional[np.ndarray] = None):
     n = cols["n"]
     offsets = np.zeros(n + 1, dtype=np.uint64)
     nbytes = _C.c_uint64()
-    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, None, 0, _C.byref(nbytes))
+    ppos = np.zeros(max(n, 1), dtype=np.uint32) if want_parent_pos else None
+    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, None, 0, _C.byref(nbytes),
+                             ppos.ctypes.data if want_parent_pos else None)
     if rc:
         raise nat.NativeError(lib.ahv_last_error().decode())
     if arena is None:
         arena = np.empty(max(int(nbytes.value), 1), dtype=np.uint8)
-    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, arena.ctypes.data, arena.nbytes, _C.byref(nbytes))
+    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, arena.ctypes.data, arena.nbytes, _C.byref(nbytes), None)
     if rc:
         raise nat.NativeError(lib.ahv_last_error().decode())
+    if want_parent_pos:
+        return arena[: int(nbytes.value)], offsets, ppos[:n]
     return arena[: int(nbytes.value)], offsets

@@ -597,6 +597,55 @@ __global__ void k_root_compare(const uint8_t *__restrict__ roots, const uint8_t 
     match[s] = (diff == 0 && !(empty && empty[s])) ? 1 : 0;
 }
 
+// ------------------------------------------------------------------ parents from the pre-images
+// The claimed parent of a delta is already inside its canonical pre-image ("parent_hash": "<64 hex>"
+// or null, audit/delta.py:61).  Given the byte position of that value, this fills the parent side
+// arrays on the device, so a host batch needs 4 bytes per delta instead of 33.
+__global__ void __launch_bounds__(256)
+k_extract_parents(const uint8_t *__restrict__ arena, const uint64_t *__restrict__ offsets, uint64_t fixed_len,
+                  const uint32_t *__restrict__ pos, uint64_t n, uint8_t *__restrict__ parents,
+                  uint8_t *__restrict__ kind)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t off, len;
+    if (offsets) {
+        off = offsets[i];
+        len = offsets[i + 1] - off;
+    } else {
+        off = i * fixed_len;
+        len = fixed_len;
+    }
+    const uint32_t p = pos[i];
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint8_t k = AHV_PARENT_NONE;
+    if (p != 0xffffffffu) {
+        k = AHV_PARENT_OTHER;
+        // the value must be exactly "<64 lowercase hex>": quotes on both sides, 64 valid characters
+        if (p >= 1 && (uint64_t)p + 65 <= len) {
+            const uint8_t *b = arena + off + p;
+            bool ok = (b[-1] == '"') && (b[64] == '"');
+#pragma unroll 4
+            for (int q = 0; q < 32 && ok; ++q) {
+                const uint32_t hi = b[2 * q], lo = b[2 * q + 1];
+                const uint32_t vh = (hi - '0' < 10u) ? hi - '0' : ((hi - 'a' < 6u) ? hi - 'a' + 10 : 0xffu);
+                const uint32_t vl = (lo - '0' < 10u) ? lo - '0' : ((lo - 'a' < 6u) ? lo - 'a' + 10 : 0xffu);
+                ok = (vh | vl) < 16u;
+                w[q >> 2] |= ((vh << 4) | (vl & 15u)) << (8 * (q & 3));     // memory byte order
+            }
+            if (ok) k = AHV_PARENT_HEX;
+        }
+        if (k != AHV_PARENT_HEX) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) w[q] = 0;
+        }
+    }
+    uint4 *dst = reinterpret_cast<uint4 *>(parents + 32 * i);
+    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    kind[i] = k;
+}
+
 // ------------------------------------------------------------------ chained capture
 // One thread per session walks its chain (audit/delta.py:101-114): hash delta i, write the
 // 64 hex characters into delta i+1's pre-image, continue.  Plain (coherent) loads only:
@@ -971,6 +1020,23 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
             AHV_CHECK_LAUNCH(ctx);
         }
     }
+    return AHV_OK;
+}
+
+int ahv_extract_parents_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                            uint64_t fixed_len, const uint32_t *d_parent_pos, uint64_t n, uint8_t *d_out_parents,
+                            uint8_t *d_out_kind)
+{
+    AHV_TRY(use_device(ctx));
+    (void)arena_bytes;
+    if (n == 0) return AHV_OK;
+    AHV_REQUIRE(d_parent_pos && d_out_parents && d_out_kind, "parent_pos / out_parent_digests / out_parent_kind is null");
+    AHV_REQUIRE(d_offsets || fixed_len > 0, "offsets is NULL and fixed_len is 0");
+    AHV_REQUIRE((reinterpret_cast<uintptr_t>(d_out_parents) & 15u) == 0, "out_parent_digests must be 16-byte aligned");
+    AHV_TRY(check_sizes(n, 0));
+    k_extract_parents<<<grid_for(n, 256), 256, 0, ctx->stream>>>(d_arena, d_offsets, fixed_len, d_parent_pos, n, d_out_parents,
+                                                                 d_out_kind);
+    AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
 

@@ -230,8 +230,8 @@ int ahv_verify_chains(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offset
 // in uniform sessions the batch is cut into session chunks and pipelined: chunk k+1 is copied in
 // while chunk k is hashed and chunk k-1's results are copied out (three streams, PCIe full duplex).
 int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
-                       const uint8_t *parents, const uint8_t *kind, const uint64_t *rowptr, uint64_t S,
-                       uint64_t uniform, uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty,
+                       const uint8_t *parents, const uint8_t *kind, const uint32_t *parent_pos,
+                       const uint64_t *rowptr, uint64_t S, uint64_t uniform, uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty,
                        uint8_t *out_verdict, int64_t *out_first_bad, uint8_t *out_match)
 {
     AHV_TRY(use_device(ctx));
@@ -240,7 +240,9 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
     uint64_t n = 0, maxl = 0, ab = 0;
     AHV_TRY(session_shape(rowptr, S, uniform, &n, &maxl));
     AHV_REQUIRE(offsets || fixed_len > 0 || n == 0, "offsets is NULL and fixed_len is 0");
-    AHV_REQUIRE((parents && kind) || n == 0, "parent_digests / parent_kind is null");
+    AHV_REQUIRE((parents && kind) || parent_pos || n == 0,
+                "give parent_digests + parent_kind, or parent_pos (positions of the parent values in the pre-images)");
+    const bool from_pos = !(parents && kind);
     AHV_TRY(arena_extent(offsets, n, fixed_len, &ab));
     AHV_REQUIRE(arena || ab == 0, "arena is null");
     if (n == 0) {   // only empty sessions
@@ -251,9 +253,10 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         if (out_match) memset(out_match, 0, S);
         return AHV_OK;
     }
-    AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(8 * (S + 1)) + 2 * p256(32 * n) + p256(n) +
+    AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(8 * (S + 1)) + 2 * p256(32 * n) + p256(n) + p256(4 * n) +
                                 2 * p256(32 * S) + 3 * p256(S) + p256(8 * S)));
     uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);
+    uint32_t *d_pos = from_pos ? (uint32_t *)io_take(ctx, 4 * n) : nullptr;
     uint64_t *d_off = offsets ? (uint64_t *)io_take(ctx, 8 * (n + 1)) : nullptr;
     uint64_t *d_rp = uniform ? nullptr : (uint64_t *)io_take(ctx, 8 * (S + 1));
     uint8_t *d_par = (uint8_t *)io_take(ctx, 32 * n);
@@ -265,7 +268,7 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
     uint8_t *d_verdict = (uint8_t *)io_take(ctx, S);
     uint8_t *d_match = (uint8_t *)io_take(ctx, S);
     int64_t *d_fb = (int64_t *)io_take(ctx, 8 * S);
-    if (!d_arena || (offsets && !d_off) || (!uniform && !d_rp) || !d_par || !d_kind || !d_dig || !d_roots ||
+    if (!d_arena || (from_pos && !d_pos) || (offsets && !d_off) || (!uniform && !d_rp) || !d_par || !d_kind || !d_dig || !d_roots ||
         !d_roots_v || !d_empty || !d_verdict || !d_match || !d_fb) {
         set_error("internal: staging slab too small");
         return AHV_E_NOMEM;
@@ -277,8 +280,13 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         AHV_CUDA(cudaMemcpyAsync(d_arena, arena, ab, cudaMemcpyHostToDevice, st));
         if (offsets) AHV_CUDA(cudaMemcpyAsync(d_off, offsets, 8 * (n + 1), cudaMemcpyHostToDevice, st));
         if (!uniform) AHV_CUDA(cudaMemcpyAsync(d_rp, rowptr, 8 * (S + 1), cudaMemcpyHostToDevice, st));
-        AHV_CUDA(cudaMemcpyAsync(d_par, parents, 32 * n, cudaMemcpyHostToDevice, st));
-        AHV_CUDA(cudaMemcpyAsync(d_kind, kind, n, cudaMemcpyHostToDevice, st));
+        if (from_pos) {
+            AHV_CUDA(cudaMemcpyAsync(d_pos, parent_pos, 4 * n, cudaMemcpyHostToDevice, st));
+            AHV_TRY(ahv_extract_parents_dev(ctx, d_arena, ab, d_off, fixed_len, d_pos, n, d_par, d_kind));
+        } else {
+            AHV_CUDA(cudaMemcpyAsync(d_par, parents, 32 * n, cudaMemcpyHostToDevice, st));
+            AHV_CUDA(cudaMemcpyAsync(d_kind, kind, n, cudaMemcpyHostToDevice, st));
+        }
         AHV_TRY(ahv_commit_dev(ctx, d_arena, ab, d_off, fixed_len, d_rp, S, n, uniform, maxl, d_dig, d_roots, d_empty));
         AHV_TRY(ahv_verify_chains_dev(ctx, d_arena, ab, d_off, fixed_len, d_par, d_kind, d_rp, S, n, uniform, maxl,
                                       d_roots, d_verdict, d_fb, nullptr, d_roots_v, d_match));
@@ -328,10 +336,17 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         const uint64_t Sc = s1 - s0, l0 = s0 * uniform, nc = Sc * uniform, b0 = l0 * fixed_len, bc = nc * fixed_len;
         cudaStream_t hs = ctx->copy_stream;
         AHV_CUDA(cudaMemcpyAsync(d_arena + b0, arena + b0, bc, cudaMemcpyHostToDevice, hs));
-        AHV_CUDA(cudaMemcpyAsync(d_par + 32 * l0, parents + 32 * l0, 32 * nc, cudaMemcpyHostToDevice, hs));
-        AHV_CUDA(cudaMemcpyAsync(d_kind + l0, kind + l0, nc, cudaMemcpyHostToDevice, hs));
+        if (from_pos) {
+            AHV_CUDA(cudaMemcpyAsync(d_pos + l0, parent_pos + l0, 4 * nc, cudaMemcpyHostToDevice, hs));
+        } else {
+            AHV_CUDA(cudaMemcpyAsync(d_par + 32 * l0, parents + 32 * l0, 32 * nc, cudaMemcpyHostToDevice, hs));
+            AHV_CUDA(cudaMemcpyAsync(d_kind + l0, kind + l0, nc, cudaMemcpyHostToDevice, hs));
+        }
         AHV_CUDA(cudaEventRecord(ev_in[k], hs));
         AHV_CUDA(cudaStreamWaitEvent(ctx->stream, ev_in[k], 0));
+        if (from_pos)
+            rc = ahv_extract_parents_dev(ctx, d_arena + b0, bc, nullptr, fixed_len, d_pos + l0, nc, d_par + 32 * l0, d_kind + l0);
+        if (rc != AHV_OK) break;
         rc = ahv_commit_dev(ctx, d_arena + b0, bc, nullptr, fixed_len, nullptr, Sc, nc, uniform, maxl, d_dig + 32 * l0,
                             d_roots + 32 * s0, d_empty + s0);
         if (rc == AHV_OK)

@@ -179,8 +179,10 @@ struct Cols {
     StrCol ch_path, ch_op, ch_content, ch_prev;
 };
 
+// Returns the position, inside the pre-image, of the first character of the parent_hash value
+// (past the opening quote when it is a string): what ahv_audit_sessions takes as parent_pos.
 template <class Sink>
-void emit_delta(Sink &o, const Cols &c, uint64_t i)
+uint64_t emit_delta(Sink &o, const Cols &c, uint64_t i)
 {
     LIT(o, "{\"agent_did\": ");
     c.agent_did.emit(o, i);
@@ -201,6 +203,7 @@ void emit_delta(Sink &o, const Cols &c, uint64_t i)
     c.delta_id.emit(o, i);
     LIT(o, ", \"parent_hash\": ");
     const uint8_t pk = c.parent_kind[i];
+    const uint64_t ppos = (pk == AHV_PARENT_NONE) ? UINT32_MAX : o.n + 1;
     if (pk == AHV_PARENT_NONE) LIT(o, "null");
     else if (pk == AHV_PARENT_HEX) {
         o.put('"');
@@ -217,6 +220,7 @@ void emit_delta(Sink &o, const Cols &c, uint64_t i)
     LIT(o, "\", \"turn_id\": ");
     put_int(o, c.turn_id[i]);
     o.put('}');
+    return ppos;
 }
 
 template <class F>
@@ -239,7 +243,7 @@ void parallel_for(uint64_t n, F f)
 }  // namespace
 
 extern "C" int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets, uint8_t *out_arena,
-                               uint64_t arena_capacity, uint64_t *out_bytes)
+                               uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos)
 {
     if (!cols || !out_offsets || !out_bytes) {
         ahv::set_error("invalid argument: cols / out_offsets / out_bytes is null");
@@ -267,8 +271,10 @@ extern "C" int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offs
     parallel_for(n, [&](uint64_t lo, uint64_t hi) {
         for (uint64_t i = lo; i < hi; ++i) {
             SinkT<false> s(nullptr);
-            emit_delta(s, c, i);
+            const uint64_t pp = emit_delta(s, c, i);
             out_offsets[i + 1] = s.n;
+            // a position past 4 GiB cannot be stored: UINT32_MAX - 1 is never a valid one, so it reads as "other"
+            if (out_parent_pos) out_parent_pos[i] = pp == UINT32_MAX ? UINT32_MAX : (uint32_t)std::min<uint64_t>(pp, UINT32_MAX - 1);
         }
     });
     for (uint64_t i = 0; i < n; ++i) out_offsets[i + 1] += out_offsets[i];

@@ -324,9 +324,13 @@ def run_cuda(args):
     h_roots_e = ctx.host_alloc(32 * S); h_empty_e = ctx.host_alloc(S)
     h_verdict_e = ctx.host_alloc(S); h_fb_e = ctx.host_alloc(8 * S, np.int64); h_match_e = ctx.host_alloc(S)
 
+    h_pos = ctx.host_alloc(4 * n, np.uint32)
+    h_pos[:] = hexpos                            # where each pre-image holds its parent_hash value
+
     def e2e_step():
-        # one upload of the batch, then the commit pass and the verify pass on the device, results back
-        rc = lib.ahv_audit_sessions(H, vp(h_arena.ctypes.data), None, FL, vp(h_par.ctypes.data), vp(h_kind.ctypes.data),
+        # one upload of the batch (pre-images + 4-byte parent positions), then the commit pass and the
+        # verify pass on the device, results back
+        rc = lib.ahv_audit_sessions(H, vp(h_arena.ctypes.data), None, FL, None, None, vp(h_pos.ctypes.data),
                                     None, S, L, vp(h_digs.ctypes.data), vp(h_roots_e.ctypes.data),
                                     vp(h_empty_e.ctypes.data), vp(h_verdict_e.ctypes.data), vp(h_fb_e.ctypes.data),
                                     vp(h_match_e.ctypes.data))
@@ -344,7 +348,7 @@ def run_cuda(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     verified = verified and bool(h_verdict_e.all() and h_match_e.all()) and np.array_equal(h_roots_e, h_roots)
-    h2d = arena_bytes + 32 * n + n                       # arena + parent digests + parent kinds, once per step
+    h2d = arena_bytes + 4 * n                            # arena + parent positions, once per step
     d2h = 32 * n + 32 * S + S + S + 8 * S + S            # digests, roots, empty, verdict, first_bad, match
 
     if rank != 0:

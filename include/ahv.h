@@ -183,12 +183,25 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
  * audit/commitment.py:59-64).  Both device passes run in full (the verify pass re-hashes).  Fixed-size
  * deltas in uniform sessions are pipelined in session chunks (copy-in / hash / copy-out overlap); pass
  * pinned host buffers (ahv_host_alloc) for that overlap to happen.  Host pointers only.
+ * The claimed parents come either as the side arrays (parent_digests + parent_kind) or, with both NULL,
+ * as parent_pos[n]: the byte position, inside each pre-image, of the parent_hash value's first character
+ * (UINT32_MAX where the value is null); the library then reads the parents out of the pre-images on the
+ * device (ahv_extract_parents_dev), which cuts the upload from 33 to 4 bytes per delta.
  */
 int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
-                       const uint8_t *parent_digests, const uint8_t *parent_kind,
+                       const uint8_t *parent_digests, const uint8_t *parent_kind, const uint32_t *parent_pos,
                        const uint64_t *session_rowptr, uint64_t n_sessions, uint64_t uniform_leaves,
                        uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty, uint8_t *out_verdict,
                        int64_t *out_first_bad, uint8_t *out_root_match);
+
+/*
+ * ahv_extract_parents_dev: fills parent_digests / parent_kind from the pre-images themselves: the value
+ * of "parent_hash" as serialised at audit/delta.py:61 (exactly 64 lowercase hex characters between quotes
+ * -> AHV_PARENT_HEX; position UINT32_MAX, i.e. null -> AHV_PARENT_NONE; anything else -> AHV_PARENT_OTHER).
+ */
+int ahv_extract_parents_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes, const uint64_t *d_offsets,
+                            uint64_t fixed_len, const uint32_t *d_parent_pos, uint64_t n,
+                            uint8_t *d_out_parent_digests, uint8_t *d_out_parent_kind);
 
 /*
  * ahv_chain_capture: session-parallel replay of DeltaEngine.capture's chaining,
@@ -211,7 +224,8 @@ int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, 
  * SemanticDelta.compute_hash serialises (audit/delta.py:43-62: json.dumps({...}, sort_keys=True).encode(),
  * CPython's default separators and ensure_ascii escaping, timestamp.isoformat()) into a packed arena,
  * multi-threaded on the host.  Strings are UTF-8 blobs with offsets[count+1].  Call with out_arena = NULL to
- * get sizes: out_offsets[n+1] and *out_bytes are filled either way.  Runs on the CPU by design (the host
+ * get sizes: out_offsets[n+1] and *out_bytes are filled either way; out_parent_pos, when given, receives
+ * the parent_pos array ahv_audit_sessions accepts in place of the parent side arrays.  Runs on the CPU by design (the host
  * packs, the GPU hashes); it needs no ahv_ctx.
  */
 typedef struct ahv_delta_columns {
@@ -233,7 +247,7 @@ typedef struct ahv_delta_columns {
 } ahv_delta_columns;
 
 int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets /* n+1 */, uint8_t *out_arena,
-                    uint64_t arena_capacity, uint64_t *out_bytes);
+                    uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos /* n, or NULL */);
 
 /* ------------------------------------------------------------------ liability / rings
  *

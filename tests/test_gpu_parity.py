@@ -13,6 +13,7 @@ from helpers import chain_preimages, config2_session, hexes, pack_sessions
 from oracle import audit_oracle as ao
 from oracle import coracle as co
 from oracle import liability_oracle as lo
+from agent_hypervisor_b200 import _native as nat
 
 pytestmark = pytest.mark.gpu
 
@@ -315,6 +316,58 @@ def test_audit_sessions_pipelined_and_ragged(ctx, audit_golden):
         if r["n"]:
             assert o["roots"][s].tobytes().hex() == r["root"] and o["root_match"][s] == 1
         assert o["verdict"][s] == 1 and o["first_bad"][s] == -1
+
+
+def test_parents_read_from_preimages(ctx):
+    """ahv_extract_parents_dev and the parent_pos form of ahv_audit_sessions: same side arrays / same
+    results as the host-built parent_digests + parent_kind, for None, digest, non-digest and odd parents."""
+    from datetime import datetime, timezone
+    from agent_hypervisor_b200.audit.packing import ArenaBuilder, PARENT_POS_NONE
+    from agent_hypervisor_b200.audit.delta import SemanticDelta
+    t0 = datetime(2026, 1, 1, tzinfo=timezone.utc)
+    h = "ab" * 32
+    odd_parents = [None, h, h.upper(), h[:-1], h + "0", h[:-1] + "g", "", "x", h[:-1] + '"', "\u00e9" * 8,
+                   "0" * 63 + "\u00e9", '", "parent_hash": "' + h]
+    b = ArenaBuilder()
+    rng = np.random.default_rng(5)
+    for s in range(40):
+        for i in range(int(rng.integers(0, 9))):
+            ph = odd_parents[int(rng.integers(0, len(odd_parents)))]
+            # ids that look like the parent field must not confuse anything: positions come from the emitter
+            b.add_delta(SemanticDelta(delta_id='d", "parent_hash": "%s' % h if i % 3 == 0 else f"d{i}", turn_id=i,
+                                      session_id=f"s{s}", agent_did="did:a", timestamp=t0, changes=[], parent_hash=ph))
+        b.end_session()
+    p = b.finish()
+    assert p.parent_pos is not None and set(p.parent_kind) == {nat.PARENT_NONE, nat.PARENT_HEX, nat.PARENT_OTHER}
+    assert np.array_equal(p.parent_pos == PARENT_POS_NONE, p.parent_kind == nat.PARENT_NONE)
+    par, kind = ctx.extract_parents(p.arena, p.offsets, p.parent_pos)
+    assert np.array_equal(kind, p.parent_kind) and np.array_equal(par, p.parents)
+    # positions that point nowhere sensible are "other", never a read outside the pre-image
+    wild = p.parent_pos.copy()
+    wild[::2] = 0; wild[1::4] = 0xFFFFFFFE; wild[3::4] = (np.diff(p.offsets.astype(np.int64))[3::4] - 3).astype(np.uint32)
+    _, k2 = ctx.extract_parents(p.arena, p.offsets, wild)
+    assert set(k2) <= {nat.PARENT_OTHER}
+    a = ctx.audit_sessions(p.arena, p.offsets, p.parents, p.parent_kind, p.session_rowptr)
+    bpos = ctx.audit_sessions(p.arena, p.offsets, None, None, p.session_rowptr, parent_pos=p.parent_pos)
+    v, fb, _ = co.verify_chains(p.arena, p.offsets, p.parents, p.parent_kind, p.session_rowptr)
+    assert np.array_equal(bpos["verdict"], v) and np.array_equal(bpos["first_bad"], fb)
+    for k in ("digests", "roots", "empty", "verdict", "first_bad", "root_match"):
+        assert np.array_equal(a[k], bpos[k]), k
+    # pipelined uniform path: positions instead of 33 bytes per delta, a broken link in session 900
+    S, L = 1500, 64
+    arena = ctx.host_alloc(S * L * 256)
+    offs, hexpos, rp = workloads.config2_fill(arena, 3, S, L)
+    _, par, kind = ctx.chain_capture(arena, offs, hexpos, rp)
+    arena[(900 * L + 20) * 256 + 30] ^= 1
+    want = ctx.audit_sessions(arena, None, par, kind, None, fixed_len=256, uniform_leaves=L, n_sessions=S)
+    got = ctx.audit_sessions(arena, None, None, None, None, fixed_len=256, uniform_leaves=L, n_sessions=S,
+                             parent_pos=hexpos)
+    for k in ("digests", "roots", "empty", "verdict", "first_bad", "root_match"):
+        assert np.array_equal(want[k], got[k]), k
+    assert list(np.nonzero(got["verdict"] == 0)[0]) == [900] and got["first_bad"][900] == 21
+    ctx.host_free(arena)
+    with pytest.raises(nat.NativeError):
+        ctx.audit_sessions(p.arena, p.offsets, None, None, p.session_rowptr)
 
 
 def test_chain_capture_vs_python_chain(ctx):

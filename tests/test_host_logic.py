@@ -192,6 +192,26 @@ def test_cpp_packer_matches_reference_preimages(audit_golden):
         pos += r["n"]
     a0, o0 = pack_columns(columns_from_deltas([]))
     assert len(o0) == 1 and o0[0] == 0
+    # parent positions: the C++ packer and the Python emitter agree, and the position is where the
+    # parent_hash value starts (what ahv_audit_sessions reads the claimed parent from)
+    from agent_hypervisor_b200.audit.packing import PARENT_POS_NONE, canonical_preimage_pos, classify_parent
+    deltas[3].delta_id = 'x", "parent_hash": "' + "0" * 64 + '"'       # a decoy in an earlier field
+    _, offs2, ppos = pack_columns(columns_from_deltas(deltas), want_parent_pos=True)
+    kinds = set()
+    for i, d in enumerate(deltas):
+        pre, pos = canonical_preimage_pos(d)
+        assert int(ppos[i]) == pos, i
+        k, raw = classify_parent(d.parent_hash)
+        kinds.add(k)
+        if d.parent_hash is None:
+            assert pos == PARENT_POS_NONE and b'"parent_hash": null' in pre
+        else:
+            assert pre[pos - 16:pos] == b'"parent_hash": "'
+            is_hex = pre[pos + 64:pos + 65] == b'"' and all(c in b"0123456789abcdef" for c in pre[pos:pos + 64])
+            assert is_hex == (k == nat.PARENT_HEX)
+            if is_hex:
+                assert bytes.fromhex(pre[pos:pos + 64].decode()) == raw
+    assert kinds == {nat.PARENT_NONE, nat.PARENT_HEX, nat.PARENT_OTHER}
 
 
 def test_install_rebinds_reference_modules():
