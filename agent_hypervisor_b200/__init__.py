@@ -9,7 +9,8 @@ Importing this package loads nothing native; the first call that needs the GPU l
 from ._native import Context, NativeError, NativeUnavailable, get_context, load_library
 from .audit import (ArenaBuilder, BatchAuditor, CommitmentEngine, CommitmentRecord, DeltaEngine, PackedSessions,
                     SemanticDelta, VFSChange)
-from .liability import LiabilityEdge, LiabilityMatrix, VouchGraphCSR, VouchingEngine, VouchingError, VouchRecord
+from .liability import (LiabilityEdge, LiabilityMatrix, SlashingEngine, SlashRequest, SlashResult, VoucherClip, VouchGraphCSR,
+                        VouchingEngine, VouchingError, VouchRecord)
 from .models import ActionDescriptor, ExecutionRing, ReversibilityLevel
 from .rings import RingCheckResult, RingEnforcer
 from .vfs import content_hashes
@@ -21,5 +22,6 @@ __all__ = [
     "Context", "NativeError", "NativeUnavailable", "get_context", "load_library",
     "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions",
     "SemanticDelta", "VFSChange", "LiabilityEdge", "LiabilityMatrix", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
+    "SlashingEngine", "SlashRequest", "SlashResult", "VoucherClip",
     "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer", "content_hashes", "install", "uninstall",
 ]

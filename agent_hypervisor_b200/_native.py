@@ -23,6 +23,24 @@ REASON_NEEDS_CONSENSUS, REASON_RING2_SIGMA, REASON_RING_INSUFFICIENT = 3, 4, 5
 EXPIRY_NONE = np.iinfo(np.int64).max
 
 
+# ahv_slash_record / ahv_clip_record (include/ahv.h)
+SLASH_DT = np.dtype([("agent", "<u4"), ("parent", "<i4"), ("event", "<u4"), ("depth", "<u4"),
+                     ("clip_begin", "<u4"), ("clip_count", "<u4"), ("sigma_before", "<f8")])
+CLIP_DT = np.dtype([("edge", "<u4"), ("slash", "<u4"), ("sigma_before", "<f8"), ("sigma_after", "<f8")])
+SLASH_BAD_EVENT, SLASH_BAD_VOUCHER = 1, 2
+
+
+class SlashBatch(C.Structure):
+    """ahv_slash_batch (include/ahv.h)."""
+    _fields_ = [("n_agents", C.c_uint64), ("rowptr", C.c_void_p), ("voucher", C.c_void_p), ("active", C.c_void_p),
+                ("expiry", C.c_void_p), ("now", C.c_int64), ("n_sessions", C.c_uint64),
+                ("session_agent_rowptr", C.c_void_p), ("event_rowptr", C.c_void_p), ("event_agent", C.c_void_p),
+                ("event_sigma", C.c_void_p), ("event_omega", C.c_void_p), ("event_depth", C.c_void_p),
+                ("scores", C.c_void_p),
+                ("touched", C.c_void_p), ("slash_log", C.c_void_p), ("clip_log", C.c_void_p),
+                ("slash_count", C.c_void_p), ("clip_count", C.c_void_p), ("status", C.c_void_p)]
+
+
 class NativeUnavailable(RuntimeError):
     """libahv_b200.so could not be loaded or no CUDA device is usable."""
 
@@ -70,6 +88,8 @@ SIGNATURES = {
     "ahv_verify_chains_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _u64, _u64, _vp,
                                         _vp, _vp, _vp, _vp, _vp]),
     "ahv_audit_sessions": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahv_slash_cascade": (C.c_int, [_vp, _vp]),
+    "ahv_slash_cascade_dev": (C.c_int, [_vp, _vp]),
     "ahv_extract_parents_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _vp]),
     "ahv_chain_capture": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_chain_capture_dev": (C.c_int, [_vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp]),
@@ -395,6 +415,44 @@ class Context:
         self._check(self.lib.ahv_chain_capture_dev(self.h, _vp(d_arena), arena_bytes, _vp(d_offsets), _vp(d_hexpos),
                                                    _vp(d_rowptr), S, n, _vp(d_digests), _vp(d_par), _vp(d_kind)),
                     "ahv_chain_capture_dev")
+
+    def slash_cascade(self, rowptr, voucher, active, expiry, now: int, session_agent_rowptr, event_rowptr, event_agent,
+                      event_sigma, event_omega, scores, event_depth=None):
+        """ahv_slash_cascade.  Inputs are copied; returns dict(scores, touched, active, slash_log, clip_log,
+        slash_count, clip_count, status) - session s's slash records start at
+        ``event_rowptr[s] + rowptr[a_lo]`` and its clip records at ``rowptr[a_lo]``."""
+        rp = _arr(rowptr, np.uint32)
+        A = len(rp) - 1
+        E = int(rp[-1])
+        vo = _arr(voucher, np.uint32)
+        ac = np.array(active, dtype=np.uint8, copy=True)
+        ex = _arr(expiry, np.int64)
+        srp = _arr(session_agent_rowptr, np.uint64); erp = _arr(event_rowptr, np.uint64)
+        S = len(srp) - 1
+        NE = int(erp[-1])
+        ea = _arr(event_agent, np.uint32); es = _arr(event_sigma, np.float64); eo = _arr(event_omega, np.float64)
+        ed = _arr(event_depth, np.uint8)
+        sc = np.array(scores, dtype=np.float64, copy=True)
+        assert ed is None or len(ed) == NE
+        assert len(vo) == E and len(ac) == E and len(ex) == E and len(sc) == A and len(ea) == NE
+        o = dict(scores=sc, touched=np.zeros(A, np.uint8), active=ac, slash_log=np.zeros(NE + E, dtype=SLASH_DT),
+                 clip_log=np.zeros(E, dtype=CLIP_DT), slash_count=np.zeros(S, np.uint32),
+                 clip_count=np.zeros(S, np.uint32), status=np.zeros(S, np.uint8))
+        b = SlashBatch()
+        b.n_agents, b.now, b.n_sessions = A, int(now), S
+        for name, arr in (("rowptr", rp), ("voucher", vo), ("active", ac), ("expiry", ex), ("session_agent_rowptr", srp),
+                          ("event_rowptr", erp), ("event_agent", ea), ("event_sigma", es), ("event_omega", eo),
+                          ("scores", sc), ("touched", o["touched"]), ("slash_log", o["slash_log"]),
+                          ("clip_log", o["clip_log"]), ("slash_count", o["slash_count"]),
+                          ("clip_count", o["clip_count"]), ("status", o["status"])):
+            setattr(b, name, arr.ctypes.data if arr.size else None)
+        b.event_depth = ed.ctypes.data if ed is not None and ed.size else None
+        with self._lock:
+            self._check(self.lib.ahv_slash_cascade(self.h, C.byref(b)), "ahv_slash_cascade")
+        return o
+
+    def slash_cascade_dev(self, batch: "SlashBatch"):
+        self._check(self.lib.ahv_slash_cascade_dev(self.h, C.byref(batch)), "ahv_slash_cascade_dev")
 
     def extract_parents_dev(self, d_arena, arena_bytes, d_offsets, fixed_len, d_parent_pos, n, d_par, d_kind):
         self._check(self.lib.ahv_extract_parents_dev(self.h, _vp(d_arena), arena_bytes, _vp(d_offsets), int(fixed_len),

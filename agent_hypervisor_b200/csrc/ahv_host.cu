@@ -462,6 +462,60 @@ int ahv_exposure_sums(ahv_ctx *ctx, const uint32_t *rowptr, const double *bonded
     return st.finish();
 }
 
+int ahv_slash_cascade(ahv_ctx *ctx, const ahv_slash_batch *b)
+{
+    AHV_TRY(use_device(ctx));
+    AHV_REQUIRE(b, "batch is null");
+    const uint64_t S = b->n_sessions, A = b->n_agents;
+    if (S == 0) return AHV_OK;
+    AHV_REQUIRE(b->rowptr && b->session_agent_rowptr && b->event_rowptr, "rowptr / session_agent_rowptr / event_rowptr is null");
+    AHV_REQUIRE(b->session_agent_rowptr[S] == A, "session_agent_rowptr[n_sessions] != n_agents");
+    AHV_REQUIRE(A < 0xffffffffull, "more than 2^32 - 2 agent rows");
+    const uint64_t E = b->rowptr[A], NE = b->event_rowptr[S];
+    AHV_REQUIRE(E == 0 || (b->voucher && b->active && b->expiry && b->clip_log), "voucher / active / expiry / clip_log is null");
+    AHV_REQUIRE(NE == 0 || (b->event_agent && b->event_sigma && b->event_omega), "event arrays are null");
+    AHV_REQUIRE(A == 0 || (b->scores && b->touched), "scores / touched is null");
+    AHV_REQUIRE((NE + E == 0 || b->slash_log) && b->slash_count && b->clip_count && b->status,
+                "slash_log / slash_count / clip_count / status is null");
+    for (uint64_t s = 0; s < S; ++s)
+        AHV_REQUIRE(b->session_agent_rowptr[s] <= b->session_agent_rowptr[s + 1] && b->event_rowptr[s] <= b->event_rowptr[s + 1],
+                    "session_agent_rowptr / event_rowptr must not decrease");
+    AHV_TRY(io_reserve(ctx, p256(4 * (A + 1)) + p256(4 * E) + p256(E) + p256(8 * E) + 2 * p256(8 * (S + 1)) + p256(4 * NE) +
+                                2 * p256(8 * NE) + p256(NE) + p256(8 * A) + p256(A) + p256(sizeof(ahv_slash_record) * (NE + E)) +
+                                p256(sizeof(ahv_clip_record) * E) + 2 * p256(4 * S) + p256(S) + 4096));
+    Stager st(ctx);
+    ahv_slash_batch d = *b;
+    d.rowptr = st.in(b->rowptr, A + 1);
+    d.voucher = st.in(b->voucher, E);
+    d.active = st.in(b->active, E);
+    d.expiry = st.in(b->expiry, E);
+    d.session_agent_rowptr = st.in(b->session_agent_rowptr, S + 1);
+    d.event_rowptr = st.in(b->event_rowptr, S + 1);
+    d.event_agent = st.in(b->event_agent, NE);
+    d.event_sigma = st.in(b->event_sigma, NE);
+    d.event_omega = st.in(b->event_omega, NE);
+    d.event_depth = st.in(b->event_depth, NE);
+    d.scores = st.in(b->scores, A);
+    d.touched = st.out(b->touched, A);
+    d.slash_log = st.out(b->slash_log, NE + E);
+    d.clip_log = st.out(b->clip_log, E);
+    d.slash_count = st.out(b->slash_count, S);
+    d.clip_count = st.out(b->clip_count, S);
+    d.status = st.out(b->status, S);
+    if (st.rc != AHV_OK) return st.rc;
+    if (A) AHV_CUDA(cudaMemsetAsync(d.touched, 0, A, ctx->stream));
+    AHV_TRY(ahv_slash_cascade_dev(ctx, &d));
+    st.back(b->active, d.active, E);
+    st.back(b->scores, d.scores, A);
+    st.back(b->touched, d.touched, A);
+    st.back(b->slash_log, d.slash_log, NE + E);
+    st.back(b->clip_log, d.clip_log, E);
+    st.back(b->slash_count, d.slash_count, S);
+    st.back(b->clip_count, d.clip_count, S);
+    st.back(b->status, d.status, S);
+    return st.finish();
+}
+
 int ahv_ring_check(ahv_ctx *ctx, const uint8_t *agent_ring, const uint8_t *flags, const double *sigma,
                    const uint8_t *consensus, const uint8_t *witness, uint64_t n, uint8_t *out_allowed,
                    uint8_t *out_reason, uint8_t *out_required)

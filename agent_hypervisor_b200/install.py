@@ -4,7 +4,8 @@ The reference binds the hot-path classes by name at import time (``core.py:16-29
 ``__init__.py:56-82``, ``api/server.py``), so swapping them means rebinding those names in every
 module that imported them.  ``install()`` does exactly that for ``DeltaEngine``, ``SemanticDelta``,
 ``VFSChange``, ``CommitmentEngine``, ``VouchingEngine``, ``VouchRecord``, ``VouchingError``,
-``LiabilityMatrix``, ``LiabilityEdge``, ``RingEnforcer`` and ``RingCheckResult``; the model enums
+``LiabilityMatrix``, ``LiabilityEdge``, ``SlashingEngine``, ``SlashResult``, ``VoucherClip``,
+``RingEnforcer`` and ``RingCheckResult``; the model enums
 (``ExecutionRing``, ``ActionDescriptor``, ...) stay the reference's own - the GPU classes accept
 them as they are.  ``uninstall()`` restores the originals.
 """
@@ -19,6 +20,7 @@ _REPLACEMENTS = {
     "hypervisor.audit.commitment": ("CommitmentEngine", "CommitmentRecord"),
     "hypervisor.liability.vouching": ("VouchingEngine", "VouchRecord", "VouchingError"),
     "hypervisor.liability": ("LiabilityMatrix", "LiabilityEdge"),
+    "hypervisor.liability.slashing": ("SlashingEngine", "SlashResult", "VoucherClip"),
     "hypervisor.rings.enforcer": ("RingEnforcer", "RingCheckResult"),
 }
 _saved: dict = {}

@@ -298,6 +298,71 @@ int ahv_ring_check_dev(ahv_ctx *ctx, const uint8_t *d_agent_ring, const uint8_t 
                        const double *d_sigma_eff, const uint8_t *d_consensus, const uint8_t *d_witness,
                        uint64_t n, uint8_t *d_out_allowed, uint8_t *d_out_reason, uint8_t *d_out_required);
 
+/*
+ * ahv_slash_cascade: SlashingEngine.slash (liability/slashing.py:62-141) for many sessions in one launch:
+ * the vouchee's score goes to 0.0 (:88); every live vouch record of its row, in insertion order
+ * (get_vouchers_for, vouching.py:153-155), clips its voucher to max(score * (1.0 - risk_weight), 0.05)
+ * (:94-96, SIGMA_FLOOR :54; Python max(): a NaN stays) and is released (:108, active[e] = 0); then, while
+ * depth < MAX_CASCADE_DEPTH = 2 (:53,:122), each of those clips with sigma_after < 0.05 + 0.01 whose
+ * voucher still has a live record is slashed one level deeper, depth first, same risk_weight (:123-138).
+ *
+ * Graph: the CSR the sigma_eff pass uses (rows = agents, records grouped by vouchee in insertion
+ * order, live = active && !(expiry != AHV_EXPIRY_NONE && now > expiry)) plus voucher[e] = the ROW INDEX of
+ * record e's voucher.  Session s owns the agent rows session_agent_rowptr[s] .. [s+1] (an agent present in
+ * two sessions has two rows) and the events event_rowptr[s] .. [s+1], applied in order to the same state;
+ * sessions are independent (one warp each).  scores is the dense agent_scores dict (a missing key is
+ * 0.0, :94), updated in place; touched[a] = 1 where the reference would have written the key.
+ *
+ * Logs, in the order the reference appends to _slash_history (:119, parent before its cascades):
+ * session s's slash records start at slash_log[event_rowptr[s] + rowptr[a_lo]] (slash_count[s] of them;
+ * capacity n_events + E in total) and its clip records at clip_log[rowptr[a_lo]] (clip_count[s]; capacity
+ * E: a record is clipped at most once because the clip releases it).  status[s]: bit 0 = an event named an
+ * agent outside the session, bit 1 = a record's voucher lies outside the session (both skipped).
+ * The reason strings, slash ids and timestamps of SlashResult are made on the host from these records.
+ */
+typedef struct ahv_slash_record {   /* one SlashingEngine.slash call (SlashResult, slashing.py:18-31) */
+    uint32_t agent;                 /* row of the vouchee */
+    int32_t parent;                 /* index, within the session's records, of the slash this cascaded from; -1 = an event */
+    uint32_t event;                 /* index into event_agent[] of the event it belongs to */
+    uint32_t depth;                 /* cascade_depth */
+    uint32_t clip_begin;            /* its clips: clip records clip_begin .. +clip_count of the session */
+    uint32_t clip_count;
+    double sigma_before;            /* vouchee_sigma_before: the event's value, or the clip's sigma_after */
+} ahv_slash_record;                 /* 32 bytes */
+
+typedef struct ahv_clip_record {    /* VoucherClip, slashing.py:34-42 */
+    uint32_t edge;                  /* index of the vouch record (gives vouch_id and voucher) */
+    uint32_t slash;                 /* index, within the session's slash records, of the slash that made it */
+    double sigma_before;
+    double sigma_after;
+} ahv_clip_record;                  /* 24 bytes */
+
+typedef struct ahv_slash_batch {
+    uint64_t n_agents;
+    const uint32_t *rowptr;                 /* n_agents + 1 */
+    const uint32_t *voucher;                /* E */
+    uint8_t *active;                        /* E, in/out */
+    const int64_t *expiry;                  /* E */
+    int64_t now;
+    uint64_t n_sessions;
+    const uint64_t *session_agent_rowptr;   /* n_sessions + 1, last = n_agents */
+    const uint64_t *event_rowptr;           /* n_sessions + 1 */
+    const uint32_t *event_agent;            /* n_events: row of the violating agent */
+    const double *event_sigma;              /* n_events: vouchee_sigma (recorded only) */
+    const double *event_omega;              /* n_events: risk_weight */
+    const uint8_t *event_depth;             /* n_events or NULL (= 0): the cascade_depth argument of slash(), :70 */
+    double *scores;                         /* n_agents, in/out */
+    uint8_t *touched;                       /* n_agents, out */
+    ahv_slash_record *slash_log;            /* n_events + E, out */
+    ahv_clip_record *clip_log;              /* E, out */
+    uint32_t *slash_count;                  /* n_sessions, out */
+    uint32_t *clip_count;                   /* n_sessions, out */
+    uint8_t *status;                        /* n_sessions, out */
+} ahv_slash_batch;
+
+int ahv_slash_cascade(ahv_ctx *ctx, const ahv_slash_batch *batch);       /* every pointer in *batch is a host pointer */
+int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *batch);   /* ... a device pointer (the struct itself on the host) */
+
 /* ------------------------------------------------------------------ measurement
  * ahv_int_peak: register-only kernel issuing the SHA-256 instruction mix
  * (funnel shifts : 3-input logic : 3-input adds = 6:4:4 per round) on every SM;

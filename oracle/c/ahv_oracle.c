@@ -13,6 +13,7 @@
  *   orc_sigma_eff_rings  liability/vouching.py:34-38,128-151,186-197,
  *                        models.py:34-42, rings/enforcer.py:134-137
  *   orc_ring_check       models.py:122-132, rings/enforcer.py:44-128
+ *   orc_slash_cascade    liability/slashing.py:53-141 (+ vouching.py:153-155,168-174)
  *
  * Parity is pinned: tests/test_oracle_golden.py checks every function against
  * vectors generated from the imported reference (tests/golden/make_golden.py)
@@ -252,6 +253,77 @@ void orc_exposure_sums(const uint32_t *rowptr, const double *bonded, const uint8
         }
         if (compensated && c != 0.0 && isfinite(c)) f = f + c;
         out_sum[r] = f;
+    }
+}
+
+/* ---- SlashingEngine.slash (liability/slashing.py:62-141) over the CSR of vouch records by vouchee ----
+ * Log layouts are the ones include/ahv.h declares (ahv_slash_record 32 B, ahv_clip_record 24 B). */
+typedef struct { uint32_t agent; int32_t parent; uint32_t event; uint32_t depth; uint32_t clip_begin; uint32_t clip_count;
+                 double sigma_before; } orc_slash_rec;
+typedef struct { uint32_t edge; uint32_t slash; double before; double after; } orc_clip_rec;
+
+typedef struct {
+    const uint32_t *rowptr, *voucher; uint8_t *active; const int64_t *expiry; int64_t now;
+    double *scores; uint8_t *touched; orc_slash_rec *sl; orc_clip_rec *cl; uint32_t n_slash, n_clip;
+} slash_state;
+
+static int slash_live(const slash_state *st, uint32_t e)       /* vouching.py:34-38,191-196 */
+{
+    return st->active[e] && !(st->expiry[e] != INT64_MAX && st->now > st->expiry[e]);
+}
+
+static void slash_one(slash_state *st, uint32_t v, double sigma_before, double omega, uint32_t depth, int32_t parent,
+                      uint32_t ev)
+{
+    st->scores[v] = 0.0;                                        /* :88 */
+    st->touched[v] = 1;
+    const uint32_t me = st->n_slash++, c0 = st->n_clip;
+    for (uint32_t e = st->rowptr[v]; e < st->rowptr[v + 1]; ++e) {   /* :92 */
+        if (!slash_live(st, e)) continue;
+        const uint32_t u = st->voucher[e];
+        const double before = st->scores[u];                    /* :94 */
+        volatile double keep = 1.0 - omega;
+        volatile double nw = before * keep;                     /* :95 */
+        double after = (0.05 > nw) ? 0.05 : nw;                 /* :96 Python max(new, FLOOR): NaN stays */
+        st->scores[u] = after;                                  /* :97 */
+        st->touched[u] = 1;
+        orc_clip_rec *q = &st->cl[st->n_clip++];
+        q->edge = e; q->slash = me; q->before = before; q->after = after;
+        st->active[e] = 0;                                      /* :108 release_bond */
+    }
+    const uint32_t c1 = st->n_clip;
+    orc_slash_rec *r = &st->sl[me];
+    r->agent = v; r->parent = parent; r->event = ev; r->depth = depth; r->clip_begin = c0; r->clip_count = c1 - c0;
+    r->sigma_before = sigma_before;
+    if (depth < 2) {                                            /* :122 MAX_CASCADE_DEPTH */
+        volatile double th = 0.05 + 0.01;                       /* :124 */
+        for (uint32_t c = c0; c < c1; ++c) {
+            const double after = st->cl[c].after;
+            if (!(after < th)) continue;
+            const uint32_t u = st->voucher[st->cl[c].edge];
+            int any = 0;
+            for (uint32_t e = st->rowptr[u]; e < st->rowptr[u + 1] && !any; ++e) any = slash_live(st, e);
+            if (any) slash_one(st, u, after, omega, depth + 1, (int32_t)me, ev);   /* :126-138 */
+        }
+    }
+}
+
+void orc_slash_cascade(const uint32_t *rowptr, const uint32_t *voucher, uint8_t *active, const int64_t *expiry, int64_t now,
+                       const uint64_t *session_agent_rowptr, const uint64_t *event_rowptr, const uint32_t *event_agent,
+                       const double *event_sigma, const double *event_omega, const uint8_t *event_depth, uint64_t n_sessions,
+                       double *scores,
+                       uint8_t *touched, void *slash_log, void *clip_log, uint32_t *out_n_slash, uint32_t *out_n_clip)
+{
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t s = 0; s < (int64_t)n_sessions; ++s) {
+        const uint64_t a_lo = session_agent_rowptr[s];
+        const uint64_t e_base = rowptr[a_lo];
+        slash_state st = {rowptr, voucher, active, expiry, now, scores, touched,
+                          (orc_slash_rec *)slash_log + event_rowptr[s] + e_base, (orc_clip_rec *)clip_log + e_base, 0, 0};
+        for (uint64_t ev = event_rowptr[s]; ev < event_rowptr[s + 1]; ++ev)
+            slash_one(&st, event_agent[ev], event_sigma[ev], event_omega[ev], event_depth ? event_depth[ev] : 0, -1, (uint32_t)ev);
+        out_n_slash[s] = st.n_slash;
+        out_n_clip[s] = st.n_clip;
     }
 }
 

@@ -47,6 +47,8 @@ def lib():
         ]
         L.orc_exposure_sums.argtypes = [_u32p, _f64p, _u8p, _i64p, C.c_int64, C.c_uint64, C.c_int, _f64p]
         L.orc_ring_check.argtypes = [_u8p, _u8p, _f64p, _u8p, _u8p, C.c_uint64, _u8p, _u8p, _u8p]
+        L.orc_slash_cascade.argtypes = [_u32p, _u32p, _u8p, _i64p, C.c_int64, _u64p, _u64p, _u32p, _f64p, _f64p, _u8p, C.c_uint64,
+                                        _f64p, _u8p, C.c_void_p, C.c_void_p, _u32p, _u32p]
         L.orc_num_threads.restype = C.c_int
         L.orc_set_threads.argtypes = [C.c_int]
         _lib = L
@@ -171,3 +173,29 @@ def exposure_sums(rowptr, bonded, active, expiry, now, compensated):
     lib().orc_exposure_sums(_p(rowptr, _u32p), _p(bonded, _f64p), _p(active, _u8p), _p(expiry, _i64p), int(now), R,
                             1 if compensated else 0, _p(out, _f64p))
     return out
+
+
+def slash_cascade(rowptr, voucher, active, expiry, now, session_agent_rowptr, event_rowptr, event_agent, event_sigma,
+                  event_omega, scores, event_depth=None):
+    """Same contract as liability_oracle.slash_cascade (copies in, copies out)."""
+    from .liability_oracle import CLIP_DT, SLASH_DT
+    rowptr = _c(rowptr, np.uint32); voucher = _c(voucher, np.uint32)
+    active = np.array(active, dtype=np.uint8, copy=True); expiry = _c(expiry, np.int64)
+    srp = _c(session_agent_rowptr, np.uint64); erp = _c(event_rowptr, np.uint64)
+    ea = _c(event_agent, np.uint32); es = _c(event_sigma, np.float64); eo = _c(event_omega, np.float64)
+    scores = np.array(scores, dtype=np.float64, copy=True)
+    S = len(srp) - 1
+    E = int(rowptr[-1])
+    touched = np.zeros(max(len(scores), 1), np.uint8)
+    sl = np.zeros(len(ea) + E + 1, dtype=SLASH_DT); cl = np.zeros(E + 1, dtype=CLIP_DT)
+    ns = np.zeros(max(S, 1), np.uint32); nc = np.zeros(max(S, 1), np.uint32)
+    if voucher.size == 0:
+        voucher = np.zeros(1, np.uint32); active = np.zeros(1, np.uint8); expiry = np.zeros(1, np.int64)
+    if ea.size == 0:
+        ea = np.zeros(1, np.uint32); es = np.zeros(1); eo = np.zeros(1)
+    sc = scores if scores.size else np.zeros(1)
+    lib().orc_slash_cascade(_p(rowptr, _u32p), _p(voucher, _u32p), _p(active, _u8p), _p(expiry, _i64p), int(now),
+                            _p(srp, _u64p), _p(erp, _u64p), _p(ea, _u32p), _p(es, _f64p), _p(eo, _f64p),
+                            None if event_depth is None else _p(_c(event_depth, np.uint8), _u8p), S,
+                            _p(sc, _f64p), _p(touched, _u8p), sl.ctypes.data, cl.ctypes.data, _p(ns, _u32p), _p(nc, _u32p))
+    return scores, touched[: len(scores)], active[:E], sl[: len(event_agent) + E], cl[:E], ns[:S], nc[:S]

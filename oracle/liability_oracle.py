@@ -3,10 +3,10 @@
 
 Reference lines followed (paths under ``/root/reference/src/hypervisor``):
 ``liability/vouching.py:34-38,128-151,186-197``, ``models.py:34-42,122-132``,
-``rings/enforcer.py:44-137``.
+``rings/enforcer.py:44-137``, ``liability/slashing.py:53-141``.
 
 Parity: pinned by ``tests/test_oracle_golden.py`` against the real
-``VouchingEngine`` / ``RingEnforcer`` (``tests/golden/make_golden.py``).
+``VouchingEngine`` / ``RingEnforcer`` / ``SlashingEngine`` (``tests/golden/make_golden.py``).
 """
 
 from __future__ import annotations
@@ -144,3 +144,77 @@ def exposure_sums(rowptr, bonded, active, expiry, now, compensated):
             f += c
         out[r] = f
     return out
+
+
+# ---- collateral slashing (liability/slashing.py) -----------------------------------------------
+SIGMA_FLOOR = 0.05            # slashing.py:54
+MAX_CASCADE_DEPTH = 2         # slashing.py:53
+
+SLASH_DT = np.dtype([("agent", "<u4"), ("parent", "<i4"), ("event", "<u4"), ("depth", "<u4"),
+                     ("clip_begin", "<u4"), ("clip_count", "<u4"), ("sigma_before", "<f8")])
+CLIP_DT = np.dtype([("edge", "<u4"), ("slash", "<u4"), ("sigma_before", "<f8"), ("sigma_after", "<f8")])
+
+
+def slash_cascade(rowptr, voucher, active, expiry, now, session_agent_rowptr, event_rowptr, event_agent,
+                  event_sigma, event_omega, scores, event_depth=None):
+    """CSR restatement of SlashingEngine.slash (slashing.py:62-141) for many sessions.
+
+    Rows = vouch records by vouchee in insertion order (get_vouchers_for -> vouching.py:153-155,186-197);
+    ``voucher[e]`` = row index of record e's voucher; session s owns agent rows
+    ``session_agent_rowptr[s]:[s+1]`` and the events ``event_rowptr[s]:[s+1]``, applied in order.
+    ``scores`` is the dense ``agent_scores`` (missing key = 0.0, slashing.py:94).  Returns copies:
+    (scores, touched, active, slash_log, clip_log, slash_count[S], clip_count[S]); session s's slash
+    records start at ``event_rowptr[s] + rowptr[a_lo]`` and its clip records at ``rowptr[a_lo]``.
+    """
+    rowptr = np.asarray(rowptr); voucher = np.asarray(voucher)
+    active = np.array(active, dtype=np.uint8, copy=True)
+    scores = np.array(scores, dtype=np.float64, copy=True)
+    touched = np.zeros(len(scores), dtype=np.uint8)
+    S = len(session_agent_rowptr) - 1
+    E = int(rowptr[-1])
+    n_ev = int(event_rowptr[-1])
+    slash_log = np.zeros(n_ev + E, dtype=SLASH_DT)
+    clip_log = np.zeros(E, dtype=CLIP_DT)
+    n_slash = np.zeros(S, dtype=np.uint32)
+    n_clip = np.zeros(S, dtype=np.uint32)
+
+    def live(e):      # vouching.py:34-38,191-196
+        return bool(active[e]) and not (expiry[e] != EXPIRY_NONE and now > expiry[e])
+
+    for s in range(S):
+        a_lo = int(session_agent_rowptr[s])
+        e_base = int(rowptr[a_lo])
+        sl = slash_log[int(event_rowptr[s]) + e_base:]
+        cl = clip_log[e_base:]
+        cnt = [0, 0]
+
+        def slash(v, sigma_before, omega, depth, parent, ev):
+            scores[v] = 0.0                                          # :88
+            touched[v] = 1
+            me = cnt[0]; cnt[0] += 1
+            c0 = cnt[1]
+            for e in range(int(rowptr[v]), int(rowptr[v + 1])):     # :92
+                if not live(e):
+                    continue
+                u = int(voucher[e])
+                before = float(scores[u])                            # :94 (.get(..., 0.0): dense zeros)
+                new = before * (1.0 - omega)                         # :95
+                new = max(new, SIGMA_FLOOR)                          # :96 (Python max keeps a NaN first arg)
+                scores[u] = new; touched[u] = 1                      # :97
+                cl[cnt[1]] = (e, me, before, new); cnt[1] += 1       # :99-105
+                active[e] = 0                                        # :108 release_bond
+            c1 = cnt[1]
+            sl[me] = (v, parent, ev, depth, c0, c1 - c0, sigma_before)   # :110-119
+            if depth < MAX_CASCADE_DEPTH:                            # :122
+                for c in range(c0, c1):
+                    after = float(cl[c]["sigma_after"])
+                    if after < SIGMA_FLOOR + 0.01:                   # :124
+                        u = int(voucher[int(cl[c]["edge"])])
+                        if any(live(e) for e in range(int(rowptr[u]), int(rowptr[u + 1]))):   # :126-129
+                            slash(u, after, omega, depth + 1, me, ev)
+
+        for ev in range(int(event_rowptr[s]), int(event_rowptr[s + 1])):
+            slash(int(event_agent[ev]), float(event_sigma[ev]), float(event_omega[ev]),
+                  0 if event_depth is None else int(event_depth[ev]), -1, ev)      # cascade_depth argument, :70
+        n_slash[s], n_clip[s] = cnt
+    return scores, touched, active, slash_log, clip_log, n_slash, n_clip

@@ -25,3 +25,10 @@ def liability_golden():
     import json
     with open(os.path.join(ROOT, "tests", "golden", "liability_golden.json")) as f:
         return json.load(f)
+
+
+@pytest.fixture(scope="session")
+def slashing_golden():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "slashing_golden.json")) as f:
+        return json.load(f)

@@ -6,7 +6,8 @@ Run in the build container only (the GPU box has no /root/reference):
 
     python tests/golden/make_golden.py
 
-Writes tests/golden/audit_golden.json and tests/golden/liability_golden.json.
+Writes tests/golden/audit_golden.json, tests/golden/liability_golden.json and
+tests/golden/slashing_golden.json (``--slashing-only`` rewrites just the last).
 The reference's own tests hold no digest constants (timestamps come from
 datetime.now()), so these fixtures - the reference's outputs on fixed inputs -
 are what pins the oracle and the CUDA path.
@@ -270,7 +271,81 @@ def liability_golden() -> dict:
     return out
 
 
+def fhex(x: float) -> str:
+    return "nan" if x != x else float(x).hex()
+
+
+N_SLASH_CASES = 400
+
+
+def slashing_golden() -> dict:
+    """The real SlashingEngine (liability/slashing.py:62-141) over the real VouchingEngine on the
+    deterministic cases of recipes.random_slash_case: history (pre-order, as appended at :119), clips,
+    final agent_scores in dict order, and which bonds ended up released."""
+    from hypervisor.liability.slashing import SlashingEngine
+    now = datetime.now(timezone.utc)
+    cases = []
+    for seed in range(N_SLASH_CASES):
+        c = recipes.random_slash_case(seed)
+        ve = VouchingEngine()
+        for k, (a, b, active, ek) in enumerate(c["edges"]):
+            exp = None if ek == 0 else (now + timedelta(days=3650) if ek == 1 else now - timedelta(days=3650))
+            ve._vouches[f"vouch:{k}"] = VouchRecord(
+                vouch_id=f"vouch:{k}", voucher_did=f"did:{a}", vouchee_did=f"did:{b}", session_id="s",
+                bonded_sigma_pct=0.2, bonded_amount=0.1, expiry=exp, is_active=active)
+            if k % 5 == 0:      # same edge in another session: must be left alone
+                ve._vouches[f"decoy:{k}"] = VouchRecord(
+                    vouch_id=f"decoy:{k}", voucher_did=f"did:{a}", vouchee_did=f"did:{b}", session_id="other",
+                    bonded_sigma_pct=0.2, bonded_amount=0.1)
+        se = SlashingEngine(ve)
+        scores = {f"did:{a}": v for a, v in c["scores"]}
+        top = []
+        for (v, sig, om, dep) in c["events"]:
+            r = se.slash(vouchee_did=f"did:{v}", session_id="s", vouchee_sigma=sig, risk_weight=om,
+                         reason="golden", agent_scores=scores, cascade_depth=dep)
+            top.append(se.history.index(r))
+        hist = []
+        for r in se.history:
+            hist.append({
+                "vouchee": int(r.vouchee_did[4:]), "depth": r.cascade_depth, "sigma_before": fhex(r.vouchee_sigma_before),
+                "sigma_after": fhex(r.vouchee_sigma_after), "reason": r.reason,
+                "clips": [[int(cl.voucher_did[4:]), fhex(cl.sigma_before), fhex(cl.sigma_after), fhex(cl.risk_weight),
+                           int(cl.vouch_id[6:])] for cl in r.voucher_clips]})
+        assert all(v.is_active for k, v in ve._vouches.items() if k.startswith("decoy:"))
+        cases.append({"seed": seed, "history": hist, "top_level": top,
+                      "scores": [[int(k[4:]), fhex(v)] for k, v in scores.items()],
+                      "active": [int(ve._vouches[f"vouch:{k}"].is_active) for k in range(len(c["edges"]))]})
+    # the four cases the reference's own tests pin (tests/unit/test_slashing.py:14-89)
+    pinned = []
+    for (edges, sc, ev) in [
+        ([("good", "bad", 0.9)], {"bad": 0.7, "good": 0.9}, ("bad", 0.7, 0.5)),
+        ([("voucher", "bad", 0.9)], {"bad": 0.5, "voucher": 0.9}, ("bad", 0.5, 0.5)),
+        ([("voucher", "bad", 0.8)], {"bad": 0.1, "voucher": 0.06}, ("bad", 0.1, 0.95)),
+        ([("v1", "bad", 0.8), ("v2", "bad", 0.7)], {"bad": 0.4, "v1": 0.8, "v2": 0.7}, ("bad", 0.4, 0.3)),
+    ]:
+        ve = VouchingEngine()
+        se = SlashingEngine(ve)
+        for (a, b, s) in edges:
+            ve.vouch(f"did:mesh:{a}", f"did:mesh:{b}", "session:test-slash", s)
+        scores = {f"did:mesh:{k}": v for k, v in sc.items()}
+        r = se.slash(vouchee_did=f"did:mesh:{ev[0]}", session_id="session:test-slash", vouchee_sigma=ev[1],
+                     risk_weight=ev[2], reason="r", agent_scores=scores)
+        pinned.append({"edges": [list(e) for e in edges], "scores_in": sc, "event": list(ev),
+                       "scores_out": {k[9:]: fhex(v) for k, v in scores.items()},
+                       "clips": [[cl.voucher_did[9:], fhex(cl.sigma_before), fhex(cl.sigma_after)] for cl in r.voucher_clips]})
+    return {"cases": cases, "pinned": pinned, "sigma_floor": fhex(SlashingEngine.SIGMA_FLOOR),
+            "max_cascade_depth": SlashingEngine.MAX_CASCADE_DEPTH}
+
+
 if __name__ == "__main__":
+    sg = slashing_golden()
+    with open(os.path.join(HERE, "slashing_golden.json"), "w") as f:
+        json.dump(sg, f, separators=(",", ":"), sort_keys=True)
+    print("slashing cases:", len(sg["cases"]), "with cascades:",
+          sum(1 for c in sg["cases"] if any(h["depth"] > 0 for h in c["history"])),
+          "depth 2:", sum(1 for c in sg["cases"] if any(h["depth"] > 1 for h in c["history"])))
+    if "--slashing-only" in sys.argv:
+        sys.exit(0)
     a = audit_golden()
     with open(os.path.join(HERE, "audit_golden.json"), "w") as f:
         json.dump(a, f, indent=0, sort_keys=True)

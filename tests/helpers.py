@@ -62,3 +62,102 @@ def config2_session(s: int, L: int = 1000):
 
 def hexes(digests: np.ndarray):
     return [bytes(d).hex() for d in np.asarray(digests, dtype=np.uint8).reshape(-1, 32)]
+
+
+# ---- slashing cases (recipes.random_slash_case) as the CSR batch the C ABI takes ------------------
+NOW_US = 1_800_000_000_000_000                   # any instant: expiries are +-10 years around it
+EXPIRY_NONE = np.iinfo(np.int64).max
+
+
+def fromhex(s: str) -> float:
+    return float("nan") if s == "nan" else float.fromhex(s)
+
+
+def same_f64(a, b) -> bool:
+    """Bit-equal except that any NaN equals any NaN."""
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    return a.shape == b.shape and bool(np.all((a.view(np.uint64) == b.view(np.uint64)) | (np.isnan(a) & np.isnan(b))))
+
+
+def slash_batch(cases):
+    """Concatenate slash cases, one session each.  Returns dict of arrays + ``edge_of`` (CSR position ->
+    (case, original edge index)) + ``present`` (agents that had a key in the initial agent_scores)."""
+    rowptr = [0]; voucher = []; active = []; expiry = []; sess_rp = [0]; ev_rp = [0]
+    ev_agent = []; ev_sigma = []; ev_omega = []; ev_depth = []; scores = []; present = []; edge_of = []
+    for ci, c in enumerate(cases):
+        base = sess_rp[-1]
+        A = c["n_agents"]
+        rows = [[] for _ in range(A)]
+        for k, (a, b, act, ek) in enumerate(c["edges"]):
+            rows[b].append((k, a, act, ek))
+        for r in rows:
+            for (k, a, act, ek) in r:
+                voucher.append(base + a); active.append(1 if act else 0)
+                expiry.append(EXPIRY_NONE if ek == 0 else (NOW_US + 315_360_000_000_000 if ek == 1 else NOW_US - 315_360_000_000_000))
+                edge_of.append((ci, k))
+            rowptr.append(len(voucher))
+        sc = np.zeros(A); pr = np.zeros(A, np.uint8)
+        for a, v in c["scores"]:
+            sc[a] = v; pr[a] = 1
+        scores.append(sc); present.append(pr)
+        for (v, sig, om, dep) in c["events"]:
+            ev_agent.append(base + v); ev_sigma.append(sig); ev_omega.append(om); ev_depth.append(dep)
+        ev_rp.append(len(ev_agent))
+        sess_rp.append(base + A)
+    return dict(
+        rowptr=np.array(rowptr, np.uint32), voucher=np.array(voucher, np.uint32), active=np.array(active, np.uint8),
+        expiry=np.array(expiry, np.int64), now=NOW_US, session_agent_rowptr=np.array(sess_rp, np.uint64),
+        event_rowptr=np.array(ev_rp, np.uint64), event_agent=np.array(ev_agent, np.uint32),
+        event_sigma=np.array(ev_sigma, np.float64), event_omega=np.array(ev_omega, np.float64),
+        event_depth=np.array(ev_depth, np.uint8),
+        scores=np.concatenate(scores) if scores else np.zeros(0), present=np.concatenate(present) if present else np.zeros(0, np.uint8),
+        edge_of=edge_of)
+
+
+def check_slash_against_golden(cases, golden_cases, b, out):
+    """out = (scores, touched, active, slash_log, clip_log, n_slash, n_clip) for batch b; golden_cases the
+    reference's records for the same cases (tests/golden/slashing_golden.json)."""
+    scores, touched, active, slash_log, clip_log, n_slash, n_clip = out
+    for s, (c, g) in enumerate(zip(cases, golden_cases)):
+        a_lo = int(b["session_agent_rowptr"][s])
+        e_base = int(b["rowptr"][a_lo])
+        sl = slash_log[int(b["event_rowptr"][s]) + e_base:][: int(n_slash[s])]
+        cl = clip_log[e_base:][: int(n_clip[s])]
+        hist = g["history"]
+        assert len(sl) == len(hist), (s, len(sl), len(hist))
+        tops = [j for j in range(len(sl)) if sl[j]["parent"] < 0]
+        assert tops == g["top_level"]
+        assert [int(sl[j]["depth"]) for j in tops] == [e[3] for e in c["events"]]
+        for j, h in enumerate(hist):
+            r = sl[j]
+            assert int(r["agent"]) - a_lo == h["vouchee"] and int(r["depth"]) == h["depth"]
+            assert same_f64(r["sigma_before"], fromhex(h["sigma_before"]))
+            if h["reason"] != "golden":      # reason: f"Cascade from {parent vouchee}: {parent reason}" (slashing.py:135)
+                ph = hist[int(r["parent"])]
+                assert h["reason"] == f"Cascade from did:{ph['vouchee']}: {ph['reason']}"
+                assert ph["depth"] == h["depth"] - 1
+            else:
+                assert int(r["parent"]) == -1
+            mine = cl[int(r["clip_begin"]): int(r["clip_begin"]) + int(r["clip_count"])]
+            assert len(mine) == len(h["clips"])
+            ev = int(r["event"]) - int(b["event_rowptr"][s])
+            for q, hc in zip(mine, h["clips"]):
+                assert int(q["slash"]) == j
+                ci, k = b["edge_of"][int(q["edge"])]
+                assert ci == s and k == hc[4] and int(b["voucher"][int(q["edge"])]) - a_lo == hc[0]
+                assert same_f64(q["sigma_before"], fromhex(hc[1])) and same_f64(q["sigma_after"], fromhex(hc[2]))
+                assert same_f64(c["events"][ev][2], fromhex(hc[3]))
+        assert sum(int(r["clip_count"]) for r in sl) == len(cl)
+        # final agent_scores: the keys the reference's dict ends with, and their values
+        A = c["n_agents"]
+        keys = {a for a, _ in g["scores"]}
+        for a, v in g["scores"]:
+            assert same_f64(scores[a_lo + a], fromhex(v)), (s, a)
+        for a in range(A):
+            assert (a in keys) == bool(b["present"][a_lo + a] or touched[a_lo + a]), (s, a)
+            if a not in keys:
+                assert scores[a_lo + a] == 0.0
+        # released bonds
+        for pos in range(e_base, int(b["rowptr"][a_lo + A])):
+            ci, k = b["edge_of"][pos]
+            assert int(active[pos]) == g["active"][k], (s, k)

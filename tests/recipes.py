@@ -125,3 +125,44 @@ def random_vouch_graph(seed: int, n_agents: int, n_edges: int):
     consensus = [rng.random() < 0.3 for _ in range(n_agents)]
     current_ring = [rng.choice([1, 2, 3]) for _ in range(n_agents)]
     return dict(edges=edges, sigma=sigma, omega=omega, consensus=consensus, current_ring=current_ring)
+
+
+# ---- slashing cases --------------------------------------------------------------
+SLASH_OMEGAS = [0.95, 0.95, 0.95, 0.5, 0.3, 0.65, 0.2, 0.99, 1.0, 0.0]
+
+
+def random_slash_case(seed: int) -> dict:
+    """One session's vouch records, a score table and a few slash events (all deterministic per seed).
+
+    edges  = [(voucher_idx, vouchee_idx, active, expiry_kind)] in insertion order; duplicates, self-edges
+             and cycles are allowed (the records are placed into ``_vouches`` directly, as the reference's
+             own tests do); expiry_kind in {0: none, 1: far future, 2: far past}
+    scores = [(agent_idx, value)] initial ``agent_scores`` dict in insertion order (some agents missing)
+    events = [(vouchee_idx, vouchee_sigma, risk_weight, cascade_depth)] applied in order to the same state
+             (cascade_depth is slash()'s last argument: 0 for a normal call)
+    """
+    rng = random.Random(0x51A5 + seed)
+    n_agents = rng.choice([1, 2, 3, 5, 8, 13, 40])
+    dense = rng.choice([0.5, 1.5, 4.0])
+    n_edges = 0 if seed % 11 == 0 else int(n_agents * dense) + rng.randrange(3)
+    hubs = [rng.randrange(n_agents) for _ in range(2)]
+    edges = []
+    for _ in range(n_edges):
+        b = rng.choice(hubs) if rng.random() < 0.4 else rng.randrange(n_agents)
+        a = rng.randrange(n_agents)
+        if a == b and rng.random() < 0.8:
+            a = (a + 1) % n_agents
+        edges.append((a, b, rng.random() < 0.9, rng.choices([0, 1, 2], weights=[0.7, 0.2, 0.1])[0]))
+    special = [0.05, 0.06, 0.060000000000000005, 0.0600000001, 0.0, 1.0, 1.2, 1.1999999, 0.059999, -0.3,
+               float("nan"), 1e-300, 5e-324]
+    scores = []
+    order = list(range(n_agents))
+    rng.shuffle(order)
+    for a in order:
+        if rng.random() < 0.8:
+            scores.append((a, rng.choice(special) if rng.random() < 0.25 else rng.random()))
+    events = []
+    for _ in range(rng.choice([1, 1, 2, 3])):
+        v = rng.choice(hubs) if rng.random() < 0.7 else rng.randrange(n_agents)
+        events.append((v, rng.random(), rng.choice(SLASH_OMEGAS), rng.choice([0, 0, 0, 0, 0, 0, 1, 2, 3])))
+    return dict(n_agents=n_agents, edges=edges, scores=scores, events=events)

@@ -282,3 +282,49 @@ def test_exposure_sums_match_python_sum_and_reference(liability_golden):
     assert np.array_equal(a, b) and a[0] == 2.0
     assert lo.exposure_sums(rp, vals, o, nn, 0, False)[0] == 1.0          # plain summation loses the first 1.0
     assert np.array_equal(lo.exposure_sums(rp, vals, o, nn, 0, False), co.exposure_sums(rp, vals, o, nn, 0, False))
+
+
+def test_slashing_cases_match_reference(slashing_golden):
+    """Python restatement of SlashingEngine.slash vs the real engine's history, clips, final scores and
+    released bonds on 400 random sessions - each alone, and all of them as one batch."""
+    from helpers import check_slash_against_golden, slash_batch
+    gold = slashing_golden["cases"]
+    cases = [recipes.random_slash_case(g["seed"]) for g in gold]
+    assert float.fromhex(slashing_golden["sigma_floor"]) == lo.SIGMA_FLOOR
+    assert slashing_golden["max_cascade_depth"] == lo.MAX_CASCADE_DEPTH
+    assert sum(1 for g in gold if any(h["depth"] == 2 for h in g["history"])) > 50
+    for c, g in list(zip(cases, gold))[:60]:
+        b = slash_batch([c])
+        out = lo.slash_cascade(b["rowptr"], b["voucher"], b["active"], b["expiry"], b["now"], b["session_agent_rowptr"],
+                               b["event_rowptr"], b["event_agent"], b["event_sigma"], b["event_omega"], b["scores"], b["event_depth"])
+        check_slash_against_golden([c], [g], b, out)
+    b = slash_batch(cases)
+    out = lo.slash_cascade(b["rowptr"], b["voucher"], b["active"], b["expiry"], b["now"], b["session_agent_rowptr"],
+                           b["event_rowptr"], b["event_agent"], b["event_sigma"], b["event_omega"], b["scores"], b["event_depth"])
+    check_slash_against_golden(cases, gold, b, out)
+    out_c = co.slash_cascade(b["rowptr"], b["voucher"], b["active"], b["expiry"], b["now"], b["session_agent_rowptr"],
+                             b["event_rowptr"], b["event_agent"], b["event_sigma"], b["event_omega"], b["scores"], b["event_depth"])
+    check_slash_against_golden(cases, gold, b, out_c)       # the plain-C restatement, same records
+
+
+def test_slashing_pinned_by_reference_tests(slashing_golden):
+    """The four cases of the reference's tests/unit/test_slashing.py:14-89, through the restatement."""
+    for p in slashing_golden["pinned"]:
+        names = list(p["scores_in"])
+        idx = {n: i for i, n in enumerate(names)}
+        c = dict(n_agents=len(names), edges=[(idx[a], idx[b], True, 0) for a, b, _ in p["edges"]],
+                 scores=[(idx[n], v) for n, v in p["scores_in"].items()],
+                 events=[(idx[p["event"][0]], p["event"][1], p["event"][2], 0)])
+        from helpers import fromhex, slash_batch
+        b = slash_batch([c])
+        sc, *_rest, cl, ns, nc = lo.slash_cascade(
+            b["rowptr"], b["voucher"], b["active"], b["expiry"], b["now"], b["session_agent_rowptr"], b["event_rowptr"],
+            b["event_agent"], b["event_sigma"], b["event_omega"], b["scores"])
+        for n, v in p["scores_out"].items():
+            assert sc[idx[n]] == fromhex(v)
+        assert [[names[int(b["voucher"][int(q["edge"])])], float(q["sigma_before"]), float(q["sigma_after"])] for q in cl[: int(nc[0])]] \
+            == [[n, fromhex(x), fromhex(y)] for n, x, y in p["clips"]]
+    # and the literal numbers those tests assert
+    assert abs(fromhex(slashing_golden["pinned"][1]["scores_out"]["voucher"]) - 0.45) < 1e-9
+    assert abs(fromhex(slashing_golden["pinned"][3]["scores_out"]["v1"]) - 0.56) < 1e-9
+    assert fromhex(slashing_golden["pinned"][2]["scores_out"]["voucher"]) >= 0.05
