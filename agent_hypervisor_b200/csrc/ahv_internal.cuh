@@ -32,6 +32,7 @@ struct ahv_ctx {
     int64_t opt_sort;          // 1: length-sort variable-length batches (default 1)
     int64_t opt_block;         // threads per block for SHA kernels (default 128)
     int64_t opt_fixed_variant; // 0: direct LDG.128, 1: smem-staged (cp.async)
+    int64_t opt_slash_variant; // 0: sessions that fit are staged in shared memory (default), 1: always global memory
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)

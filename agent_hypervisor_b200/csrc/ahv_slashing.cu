@@ -14,6 +14,19 @@
 // and the last lane of the group stores the score.  Chunks run in order, so later chunks read what
 // earlier ones wrote.  The cascade is the reference's depth-first order with an explicit two-entry
 // stack over the clip log, which doubles as the output.
+//
+// The cascade is a chain of dependent look-ups (row bounds -> records -> scores -> next row ...), a DRAM
+// round trip each when done in global memory.  A session whose state fits the warp's slice of shared
+// memory (13 B per agent + 17 B per record) is therefore STAGED first: one coalesced read of its rows,
+// records and scores, the whole cascade out of shared memory, one write-back of what changed.  Larger
+// sessions run the same code on global memory (GlobalView), where rows are long enough to keep the lanes
+// busy.  Both views produce the same records.
+//
+// Small sessions (a handful of records per row) would leave most of a warp's lanes idle, so where 32
+// consecutive sessions together fit one warp's slice (11 B per agent + 3 B per record) they are run by
+// k_slash_lanes instead: the warp stages the 32 sessions' contiguous rows, records and scores with
+// coalesced reads, then every lane walks ITS session serially out of shared memory - the reference's loop
+// as written - and the warp writes back what changed.  k_slash_cascade skips those groups.
 #include "ahv_internal.cuh"
 
 namespace ahv {
@@ -23,6 +36,17 @@ constexpr unsigned FULL = 0xffffffffu;
 constexpr double SIGMA_FLOOR = 0.05;              // slashing.py:54
 constexpr int MAX_CASCADE_DEPTH = 2;              // slashing.py:53
 constexpr int SLASH_WARPS = 4;
+constexpr uint32_t SLASH_SMEM_PER_WARP = 6144;    // bytes of staged session state per warp
+constexpr int LANE_WARPS = 4;                     // k_slash_lanes: warps per CTA
+constexpr uint32_t LANE_SMEM_PER_WARP = 10752;    // bytes of staged state for a group of 32 sessions (5 CTAs per SM)
+constexpr int LANE_CLIP_CACHE = 12;
+
+__host__ __device__ __forceinline__ uint64_t lane_group_bytes(uint64_t agents, uint64_t records)
+{
+    return 11 * agents + 3 * records + 16;      // < 65536 agents and records: 16-bit indices inside a group
+}
+
+constexpr uint8_t F_LIVE = 1, F_WAS_LIVE = 2, F_BAD_VOUCHER = 4;
 
 struct SlashArgs {
     const uint32_t *rowptr;
@@ -44,6 +68,7 @@ struct SlashArgs {
     uint32_t *slash_count;
     uint32_t *clip_count;
     uint8_t *status;
+    uint32_t *big_groups;         // scratch: [0] = count, [1..] = groups of 32 sessions k_slash_lanes left to k_slash_cascade
 };
 
 __device__ __forceinline__ double clip_once(double x, double keep)
@@ -52,75 +77,148 @@ __device__ __forceinline__ double clip_once(double x, double keep)
     return (SIGMA_FLOOR > n) ? SIGMA_FLOOR : n;   // :96  Python max(n, FLOOR): a NaN n stays
 }
 
-__device__ __forceinline__ bool edge_live(const SlashArgs &k, uint64_t e)
+// vouching.py:34-38,191-196 on values already loaded (bitwise on purpose: both loads are always issued,
+// neither waits for the other)
+__device__ __forceinline__ uint32_t live_flag(uint8_t active, int64_t expiry, int64_t now)
 {
-    const int64_t x = k.expiry[e];                // vouching.py:34-38
-    return k.active[e] != 0 && !(x != AHV_EXPIRY_NONE && k.now > x);
+    const uint32_t expired = (uint32_t)(expiry != AHV_EXPIRY_NONE) & (uint32_t)(now > expiry);
+    return (uint32_t)(active != 0) & (expired ^ 1u);
 }
 
+// Session state in global memory.  Agents and records are addressed by their index inside the session.
+struct GlobalView {
+    const uint32_t *rowptr;       // + a_lo
+    const uint32_t *voucher;      // + e_base
+    uint8_t *active;              // + e_base
+    const int64_t *expiry;        // + e_base
+    double *scores;               // + a_lo
+    uint8_t *touched;             // + a_lo
+    const ahv_clip_record *cl;    // the session's clip records
+    int64_t now;
+    uint32_t a_lo, n_agents, e_base;
+
+    __device__ __forceinline__ uint32_t row_begin(uint32_t v) const { return rowptr[v] - e_base; }
+    __device__ __forceinline__ uint32_t row_end(uint32_t v) const { return rowptr[v + 1] - e_base; }
+    // F_LIVE / F_BAD_VOUCHER of record e and its voucher (vouching.py:34-38,191-196)
+    __device__ __forceinline__ uint32_t flags(uint32_t e, uint32_t &u) const
+    {
+        const int64_t x = expiry[e];
+        if (active[e] == 0 || (x != AHV_EXPIRY_NONE && now > x)) return 0;
+        u = voucher[e] - a_lo;                    // wraps far out of range for a voucher below a_lo
+        return u < n_agents ? F_LIVE : F_BAD_VOUCHER;
+    }
+    __device__ __forceinline__ void release(uint32_t e) { active[e] = 0; }
+    __device__ __forceinline__ double score(uint32_t u) const { return scores[u]; }
+    __device__ __forceinline__ void set_score(uint32_t u, double x)
+    {
+        scores[u] = x;
+        touched[u] = 1;
+    }
+    __device__ __forceinline__ void note_clip(uint32_t, uint32_t, double) {}
+    __device__ __forceinline__ double clip_after(uint32_t c) const { return cl[c].sigma_after; }
+    __device__ __forceinline__ uint32_t clip_voucher(uint32_t c) const { return voucher[cl[c].edge - e_base] - a_lo; }
+};
+
+// Session state staged in the warp's slice of shared memory.
+struct SharedView {
+    double *s_score;              // [A]
+    double *s_after;              // [E]  sigma_after of clip c
+    uint32_t *s_rowptr;           // [A+1] record indices inside the session
+    uint32_t *s_voucher;          // [E]  agent index inside the session
+    uint32_t *s_clip_voucher;     // [E]  voucher of clip c
+    uint8_t *s_flags;             // [E]
+    uint8_t *s_touched;           // [A]
+
+    static __device__ __forceinline__ uint64_t bytes(uint32_t A, uint32_t E) { return 13ull * A + 17ull * E + 4u; }
+    __device__ __forceinline__ void carve(uint8_t *base, uint32_t A, uint32_t E)
+    {
+        s_score = reinterpret_cast<double *>(base);
+        s_after = s_score + A;
+        s_rowptr = reinterpret_cast<uint32_t *>(s_after + E);
+        s_voucher = s_rowptr + (A + 1);
+        s_clip_voucher = s_voucher + E;
+        s_flags = reinterpret_cast<uint8_t *>(s_clip_voucher + E);
+        s_touched = s_flags + E;
+    }
+    __device__ __forceinline__ uint32_t row_begin(uint32_t v) const { return s_rowptr[v]; }
+    __device__ __forceinline__ uint32_t row_end(uint32_t v) const { return s_rowptr[v + 1]; }
+    __device__ __forceinline__ uint32_t flags(uint32_t e, uint32_t &u) const
+    {
+        u = s_voucher[e];
+        return s_flags[e] & (F_LIVE | F_BAD_VOUCHER);
+    }
+    __device__ __forceinline__ void release(uint32_t e) { s_flags[e] = F_WAS_LIVE; }
+    __device__ __forceinline__ double score(uint32_t u) const { return s_score[u]; }
+    __device__ __forceinline__ void set_score(uint32_t u, double x)
+    {
+        s_score[u] = x;
+        s_touched[u] = 1;
+    }
+    __device__ __forceinline__ void note_clip(uint32_t c, uint32_t u, double after)
+    {
+        s_clip_voucher[c] = u;
+        s_after[c] = after;
+    }
+    __device__ __forceinline__ double clip_after(uint32_t c) const { return s_after[c]; }
+    __device__ __forceinline__ uint32_t clip_voucher(uint32_t c) const { return s_clip_voucher[c]; }
+};
+
+struct SessionLog {
+    ahv_slash_record *sl;
+    ahv_clip_record *cl;
+    uint32_t n_slash, n_clip;
+    uint32_t a_lo, e_base;
+    uint32_t status;
+};
+
 // get_vouchers_for(u) non-empty?  (slashing.py:126-129)
-__device__ bool row_any_live(const SlashArgs &k, uint32_t u, int lane)
+template <class View>
+__device__ bool row_any_live(const View &m, uint32_t u, int lane)
 {
-    const uint64_t end = k.rowptr[u + 1];
-    for (uint64_t base = k.rowptr[u]; base < end; base += 32) {
-        const uint64_t e = base + lane;
-        const bool l = e < end && edge_live(k, e);
+    const uint32_t end = m.row_end(u);
+    for (uint32_t base = m.row_begin(u); base < end; base += 32) {
+        const uint32_t e = base + lane;
+        uint32_t w;
+        const bool l = e < end && (m.flags(e, w) & F_LIVE);
         if (__any_sync(FULL, l)) return true;
     }
     return false;
 }
 
-struct SessionLog {
-    ahv_slash_record *sl;
-    ahv_clip_record *cl;
-    uint64_t e_base;          // first vouch record of the session (clip records hold global record indices)
-    uint32_t n_slash, n_clip;
-    uint32_t a_lo, a_hi;
-    uint32_t status;
-};
-
 // One SlashingEngine.slash call without its cascade; returns the index of its record.
-__device__ uint32_t slash_once(const SlashArgs &k, SessionLog &g, int lane, uint32_t v, double sigma_before, double keep,
-                               uint32_t depth, int32_t parent, uint32_t ev)
+template <class View>
+__device__ uint32_t slash_once(View &m, SessionLog &g, int lane, uint32_t v, double sigma_before, double keep, uint32_t depth,
+                               int32_t parent, uint32_t ev)
 {
-    if (lane == 0) {
-        k.scores[v] = 0.0;                        // :88
-        k.touched[v] = 1;
-    }
+    if (lane == 0) m.set_score(v, 0.0);           // :88
     __syncwarp();
     const uint32_t me = g.n_slash++;
     const uint32_t c0 = g.n_clip;
-    const uint64_t end = k.rowptr[v + 1];
-    for (uint64_t base = k.rowptr[v]; base < end; base += 32) {
-        const uint64_t e = base + lane;
-        bool live = e < end && edge_live(k, e);
+    const uint32_t end = m.row_end(v);
+    for (uint32_t base = m.row_begin(v); base < end; base += 32) {
+        const uint32_t e = base + lane;
         uint32_t u = 0;
-        if (live) {
-            u = k.voucher[e];
-            if (u < g.a_lo || u >= g.a_hi) {      // a voucher outside the session: refuse the record
-                live = false;
-                g.status |= 2;
-            }
-        }
+        const uint32_t fl = e < end ? m.flags(e, u) : 0u;
+        if (fl & F_BAD_VOUCHER) g.status |= 2;    // a live record whose voucher is outside the session: left alone
+        const bool live = (fl & F_LIVE) != 0;
         const unsigned mask = __ballot_sync(FULL, live);
         // lanes naming the same voucher form a group; idle lanes get a key no live lane can have
         const unsigned peers = __match_any_sync(FULL, live ? (unsigned long long)u : ((1ull << 32) | (unsigned)lane));
         double before = 0.0, after = 0.0;
         if (live) {
             const int rank = __popc(peers & ((1u << lane) - 1u));
-            before = k.scores[u];                 // :94 (a missing key is a dense 0.0)
+            before = m.score(u);                  // :94 (a missing key is a dense 0.0)
             for (int r = 0; r < rank; ++r) before = clip_once(before, keep);
             after = clip_once(before, keep);
         }
         __syncwarp();                             // every lane has read its score before any lane writes
         if (live) {
-            if ((peers >> lane) == 1u) {          // last lane of its group
-                k.scores[u] = after;              // :97
-                k.touched[u] = 1;
-            }
-            k.active[e] = 0;                      // :108 release_bond
-            ahv_clip_record *q = g.cl + (g.n_clip + __popc(mask & ((1u << lane) - 1u)));
-            q->edge = (uint32_t)e;
+            if ((peers >> lane) == 1u) m.set_score(u, after);       // last lane of its group, :97
+            m.release(e);                         // :108 release_bond
+            const uint32_t c = g.n_clip + __popc(mask & ((1u << lane) - 1u));
+            m.note_clip(c, u, after);
+            ahv_clip_record *q = g.cl + c;        // :99-105
+            q->edge = g.e_base + e;
             q->slash = me;
             q->sigma_before = before;
             q->sigma_after = after;
@@ -128,10 +226,9 @@ __device__ uint32_t slash_once(const SlashArgs &k, SessionLog &g, int lane, uint
         g.n_clip += __popc(mask);
         __syncwarp();
     }
-    g.status |= __reduce_or_sync(FULL, g.status);
     if (lane == 0) {
         ahv_slash_record *r = g.sl + me;          // :110-119
-        r->agent = v;
+        r->agent = g.a_lo + v;
         r->parent = parent;
         r->event = ev;
         r->depth = depth;
@@ -142,55 +239,311 @@ __device__ uint32_t slash_once(const SlashArgs &k, SessionLog &g, int lane, uint
     return me;
 }
 
-__global__ void __launch_bounds__(32 * SLASH_WARPS)
-k_slash_cascade(const SlashArgs k)
+// Every event of one session, in order, with the reference's depth-first cascade.
+template <class View>
+__device__ void run_events(const SlashArgs &k, View &m, SessionLog &g, int lane, uint64_t s, uint32_t n_agents)
 {
-    const int lane = threadIdx.x & 31;
-    const uint64_t warp = (uint64_t)blockIdx.x * SLASH_WARPS + (threadIdx.x >> 5);
-    const uint64_t n_warps = (uint64_t)gridDim.x * SLASH_WARPS;
-    const double thresh = __dadd_rn(SIGMA_FLOOR, 0.01);                  // :124
-    for (uint64_t s = warp; s < k.n_sessions; s += n_warps) {
-        SessionLog g;
-        g.a_lo = (uint32_t)k.sess_rp[s];
-        g.a_hi = (uint32_t)k.sess_rp[s + 1];
-        g.e_base = k.rowptr[g.a_lo];
-        g.sl = k.slash_log + (k.ev_rp[s] + g.e_base);
-        g.cl = k.clip_log + g.e_base;
-        g.n_slash = g.n_clip = 0;
-        g.status = 0;
-        for (uint64_t ev = k.ev_rp[s]; ev < k.ev_rp[s + 1]; ++ev) {
-            const uint32_t v0 = k.ev_agent[ev];
-            if (v0 < g.a_lo || v0 >= g.a_hi) {    // an event naming an agent of another session
-                g.status |= 1;
+    const double thresh = __dadd_rn(SIGMA_FLOOR, 0.01);                   // :124
+    for (uint64_t ev = k.ev_rp[s]; ev < k.ev_rp[s + 1]; ++ev) {
+        const uint32_t v0 = k.ev_agent[ev] - g.a_lo;
+        if (v0 >= n_agents) {                     // an event naming an agent of another session
+            g.status |= 1;
+            continue;
+        }
+        const double keep = __dsub_rn(1.0, k.ev_omega[ev]);              // (1.0 - risk_weight), :95
+        const uint32_t depth0 = k.ev_depth ? k.ev_depth[ev] : 0u;         // the caller's cascade_depth argument (:70)
+        uint32_t f_cur[MAX_CASCADE_DEPTH], f_end[MAX_CASCADE_DEPTH], f_id[MAX_CASCADE_DEPTH];
+        f_cur[0] = g.n_clip;
+        f_id[0] = slash_once(m, g, lane, v0, k.ev_sigma[ev], keep, depth0, -1, (uint32_t)ev);
+        f_end[0] = g.n_clip;
+        int d = depth0 < (uint32_t)MAX_CASCADE_DEPTH ? 0 : -1;
+        while (d >= 0) {                          // :122-138, depth first, clips in order
+            if (f_cur[d] == f_end[d]) {
+                --d;
                 continue;
             }
-            const double keep = __dsub_rn(1.0, k.ev_omega[ev]);          // (1.0 - risk_weight), :95
-            uint32_t f_cur[MAX_CASCADE_DEPTH], f_end[MAX_CASCADE_DEPTH], f_id[MAX_CASCADE_DEPTH];
-            const uint32_t depth0 = k.ev_depth ? k.ev_depth[ev] : 0u;     // the caller's cascade_depth argument (:70)
-            f_cur[0] = g.n_clip;
-            f_id[0] = slash_once(k, g, lane, v0, k.ev_sigma[ev], keep, depth0, -1, (uint32_t)ev);
-            f_end[0] = g.n_clip;
+            const uint32_t c = f_cur[d]++;
+            const double after = m.clip_after(c);
+            if (!(after < thresh)) continue;
+            const uint32_t u = m.clip_voucher(c);
+            if (!row_any_live(m, u, lane)) continue;
+            const uint32_t c0 = g.n_clip;
+            const uint32_t id = slash_once(m, g, lane, u, after, keep, depth0 + d + 1, (int32_t)f_id[d], (uint32_t)ev);
+            if (depth0 + d + 1 < (uint32_t)MAX_CASCADE_DEPTH) {
+                ++d;
+                f_cur[d] = c0;
+                f_end[d] = g.n_clip;
+                f_id[d] = id;
+            }
+        }
+    }
+}
+
+// Do sessions s0 .. s0+n-1 (a group of up to 32 consecutive sessions) fit one warp's slice?
+__device__ __forceinline__ bool group_fits(const SlashArgs &k, uint64_t s0, uint32_t n, uint32_t &a_lo, uint32_t &A, uint32_t &e_lo,
+                                           uint32_t &E)
+{
+    a_lo = (uint32_t)k.sess_rp[s0];
+    A = (uint32_t)k.sess_rp[s0 + n] - a_lo;
+    e_lo = k.rowptr[a_lo];
+    E = k.rowptr[a_lo + A] - e_lo;
+    return lane_group_bytes(A, E) <= LANE_SMEM_PER_WARP;
+}
+
+// One lane = one session, serial, on the group's staged state.  Indices: agents and records are
+// group-local in shared memory; `la` is the first agent of this lane's session, `ln` their number.
+struct LaneRun {
+    double *s_score;
+    uint16_t *s_rowptr;           // group-local record index
+    uint16_t *s_voucher;          // group-local agent index
+    uint8_t *s_flags;
+    uint8_t *s_touched;
+    ahv_slash_record *sl;
+    ahv_clip_record *cl;
+    uint32_t la, ln;              // this session's agents inside the group
+    uint32_t ga_lo, ge_lo;        // the group's first agent row / first record (global indices)
+    uint32_t n_slash, n_clip, status;
+    // (sigma_after, voucher) of the first LANE_CLIP_CACHE clips of the slash at cascade depth 0 / 1: what the
+    // cascade loop needs, kept in (L1-resident) local memory instead of reading the clip records back
+    double c_after[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
+    uint32_t c_voucher[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
+
+    __device__ __forceinline__ bool live(uint32_t e, uint32_t &u) const
+    {
+        u = (uint32_t)s_voucher[e] - la;
+        return (s_flags[e] & F_LIVE) && u < ln;
+    }
+    __device__ bool any_live(uint32_t v) const      // slashing.py:126-129
+    {
+        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {
+            uint32_t u;
+            if (live(e, u)) return true;
+        }
+        return false;
+    }
+    // frame: the cascade-stack slot (0 / 1) whose clips this slash produces, or -1 when it will not cascade
+    __device__ uint32_t slash(uint32_t v, double sigma_before, double keep, uint32_t depth, int32_t parent, uint32_t ev,
+                              int frame)
+    {
+        s_score[la + v] = 0.0;                    // :88
+        s_touched[la + v] = 1;
+        const uint32_t me = n_slash++, c0 = n_clip;
+        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {     // :92
+            uint32_t u;
+            if (!live(e, u)) {
+                if ((s_flags[e] & F_LIVE) && u >= ln) status |= 2;              // voucher outside the session
+                continue;
+            }
+            const double before = s_score[la + u];                              // :94
+            const double after = clip_once(before, keep);                       // :95-96
+            s_score[la + u] = after;                                            // :97
+            s_touched[la + u] = 1;
+            s_flags[e] = F_WAS_LIVE;                                            // :108 release_bond
+            if (frame >= 0 && n_clip - c0 < (uint32_t)LANE_CLIP_CACHE) {
+                c_after[frame][n_clip - c0] = after;
+                c_voucher[frame][n_clip - c0] = u;
+            }
+            ahv_clip_record *q = cl + n_clip++;                                 // :99-105
+            q->edge = ge_lo + e;
+            q->slash = me;
+            q->sigma_before = before;
+            q->sigma_after = after;
+        }
+        ahv_slash_record *r = sl + me;            // :110-119
+        r->agent = ga_lo + la + v;
+        r->parent = parent;
+        r->event = ev;
+        r->depth = depth;
+        r->clip_begin = c0;
+        r->clip_count = n_clip - c0;
+        r->sigma_before = sigma_before;
+        return me;
+    }
+    __device__ void events(const SlashArgs &k, uint64_t ev_lo, uint64_t ev_hi)
+    {
+        const double thresh = __dadd_rn(SIGMA_FLOOR, 0.01);                     // :124
+        for (uint64_t ev = ev_lo; ev < ev_hi; ++ev) {
+            const uint32_t v0 = k.ev_agent[ev] - (ga_lo + la);
+            if (v0 >= ln) {
+                status |= 1;
+                continue;
+            }
+            const double keep = __dsub_rn(1.0, k.ev_omega[ev]);
+            const uint32_t depth0 = k.ev_depth ? k.ev_depth[ev] : 0u;
+            uint32_t f_c0[MAX_CASCADE_DEPTH], f_cur[MAX_CASCADE_DEPTH], f_end[MAX_CASCADE_DEPTH], f_id[MAX_CASCADE_DEPTH];
             int d = depth0 < (uint32_t)MAX_CASCADE_DEPTH ? 0 : -1;
-            while (d >= 0) {                      // :122-138, depth first, clips in order
+            f_c0[0] = f_cur[0] = n_clip;
+            f_id[0] = slash(v0, k.ev_sigma[ev], keep, depth0, -1, (uint32_t)ev, d);
+            f_end[0] = n_clip;
+            while (d >= 0) {                      // :122-138
                 if (f_cur[d] == f_end[d]) {
                     --d;
                     continue;
                 }
-                const ahv_clip_record *q = g.cl + f_cur[d]++;
-                const double after = q->sigma_after;
+                const uint32_t c = f_cur[d]++;
+                double after;
+                uint32_t u;
+                if (c - f_c0[d] < (uint32_t)LANE_CLIP_CACHE) {
+                    after = c_after[d][c - f_c0[d]];
+                    u = c_voucher[d][c - f_c0[d]];
+                } else {                          // a long row: this lane's own earlier stores
+                    after = cl[c].sigma_after;
+                    u = (uint32_t)s_voucher[cl[c].edge - ge_lo] - la;
+                }
                 if (!(after < thresh)) continue;
-                const uint32_t u = k.voucher[q->edge];
-                if (!row_any_live(k, u, lane)) continue;
-                const uint32_t c0 = g.n_clip;
-                const uint32_t id = slash_once(k, g, lane, u, after, keep, depth0 + d + 1, (int32_t)f_id[d], (uint32_t)ev);
-                if (depth0 + d + 1 < (uint32_t)MAX_CASCADE_DEPTH) {
+                if (!any_live(u)) continue;
+                const uint32_t c0 = n_clip;
+                const bool deeper = depth0 + d + 1 < (uint32_t)MAX_CASCADE_DEPTH;
+                const uint32_t id = slash(u, after, keep, depth0 + d + 1, (int32_t)f_id[d], (uint32_t)ev, deeper ? d + 1 : -1);
+                if (deeper) {
                     ++d;
-                    f_cur[d] = c0;
-                    f_end[d] = g.n_clip;
+                    f_c0[d] = f_cur[d] = c0;
+                    f_end[d] = n_clip;
                     f_id[d] = id;
                 }
             }
         }
+    }
+};
+
+__global__ void __launch_bounds__(32 * LANE_WARPS)
+k_slash_lanes(const SlashArgs k)
+{
+    extern __shared__ __align__(16) uint8_t slash_smem[];
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const uint64_t n_groups = (k.n_sessions + 31) / 32;
+    const uint64_t n_warps = (uint64_t)gridDim.x * LANE_WARPS;
+    for (uint64_t grp = (uint64_t)blockIdx.x * LANE_WARPS + wib; grp < n_groups; grp += n_warps) {
+        const uint64_t s0 = grp * 32;
+        const uint32_t n = (uint32_t)(k.n_sessions - s0 < 32 ? k.n_sessions - s0 : 32);
+        uint32_t a_lo, A, e_lo, E;
+        if (!group_fits(k, s0, n, a_lo, A, e_lo, E)) {              // k_slash_cascade takes this group
+            if (lane == 0) k.big_groups[1 + atomicAdd(k.big_groups, 1u)] = (uint32_t)grp;
+            continue;
+        }
+        // this lane's session: bounds and events (loads that overlap the staging below)
+        const uint64_t s = s0 + ((uint32_t)lane < n ? lane : 0);
+        const uint32_t my_a0 = (uint32_t)k.sess_rp[s], my_a1 = (uint32_t)k.sess_rp[s + 1];
+        const uint64_t ev_lo = k.ev_rp[s], ev_hi = k.ev_rp[s + 1];
+        LaneRun r;
+        uint8_t *base = slash_smem + (size_t)wib * LANE_SMEM_PER_WARP;
+        r.s_score = reinterpret_cast<double *>(base);
+        r.s_rowptr = reinterpret_cast<uint16_t *>(r.s_score + A);
+        r.s_voucher = r.s_rowptr + (A + 1);
+        r.s_flags = reinterpret_cast<uint8_t *>(r.s_voucher + E);
+        r.s_touched = r.s_flags + E;
+#pragma unroll 8
+        for (uint32_t a = lane; a <= A; a += 32) r.s_rowptr[a] = (uint16_t)(k.rowptr[a_lo + a] - e_lo);
+#pragma unroll 8
+        for (uint32_t a = lane; a < A; a += 32) {
+            r.s_score[a] = k.scores[a_lo + a];
+            r.s_touched[a] = 0;
+        }
+#pragma unroll 8
+        for (uint32_t e = lane; e < E; e += 32) {
+            // a voucher outside the group becomes 0xffff: outside every session of the group as well
+            const uint32_t u = k.voucher[e_lo + e] - a_lo;
+            r.s_voucher[e] = (uint16_t)(u < A ? u : 0xffffu);
+            r.s_flags[e] = live_flag(k.active[e_lo + e], k.expiry[e_lo + e], k.now) ? (F_LIVE | F_WAS_LIVE) : 0;
+        }
+        __syncwarp();
+        if ((uint32_t)lane < n) {
+            r.la = my_a0 - a_lo;
+            r.ln = my_a1 - my_a0;
+            r.ga_lo = a_lo;
+            r.ge_lo = e_lo;
+            const uint32_t e_base = e_lo + r.s_rowptr[r.la];
+            r.sl = k.slash_log + (ev_lo + e_base);
+            r.cl = k.clip_log + e_base;
+            r.n_slash = r.n_clip = r.status = 0;
+            r.events(k, ev_lo, ev_hi);
+            k.slash_count[s] = r.n_slash;
+            k.clip_count[s] = r.n_clip;
+            k.status[s] = (uint8_t)r.status;
+        }
+        __syncwarp();
+        for (uint32_t a = lane; a < A; a += 32)
+            if (r.s_touched[a]) {
+                k.scores[a_lo + a] = r.s_score[a];
+                k.touched[a_lo + a] = 1;
+            }
+        for (uint32_t e = lane; e < E; e += 32)
+            if (r.s_flags[e] == F_WAS_LIVE) k.active[e_lo + e] = 0;
+        __syncwarp();
+    }
+}
+
+template <bool STAGE>
+__global__ void __launch_bounds__(32 * SLASH_WARPS)
+k_slash_cascade(const SlashArgs k, const int from_list)
+{
+    extern __shared__ __align__(16) uint8_t slash_smem[];
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const uint64_t warp = (uint64_t)blockIdx.x * SLASH_WARPS + wib;
+    const uint64_t n_warps = (uint64_t)gridDim.x * SLASH_WARPS;
+    // with the lane kernel in front, only the sessions of the groups it listed are left
+    const uint64_t n_items = from_list ? (uint64_t)k.big_groups[0] * 32 : k.n_sessions;
+    for (uint64_t w = warp; w < n_items; w += n_warps) {
+        const uint64_t s = from_list ? (uint64_t)k.big_groups[1 + (w >> 5)] * 32 + (w & 31) : w;
+        if (s >= k.n_sessions) continue;
+        const uint32_t a_lo = (uint32_t)k.sess_rp[s];
+        const uint32_t A = (uint32_t)k.sess_rp[s + 1] - a_lo;
+        const uint32_t e_base = k.rowptr[a_lo];
+        const uint32_t E = k.rowptr[a_lo + A] - e_base;
+        SessionLog g;
+        g.a_lo = a_lo;
+        g.e_base = e_base;
+        g.sl = k.slash_log + (k.ev_rp[s] + e_base);
+        g.cl = k.clip_log + e_base;
+        g.n_slash = g.n_clip = 0;
+        g.status = 0;
+        if (k.ev_rp[s] == k.ev_rp[s + 1]) {       // nothing to do for this session
+        } else if (STAGE && SharedView::bytes(A, E) <= SLASH_SMEM_PER_WARP) {
+            SharedView m;
+            m.carve(slash_smem + (size_t)wib * SLASH_SMEM_PER_WARP, A, E);
+#pragma unroll 4
+            for (uint32_t a = lane; a <= A; a += 32) m.s_rowptr[a] = k.rowptr[a_lo + a] - e_base;
+#pragma unroll 4
+            for (uint32_t a = lane; a < A; a += 32) {
+                m.s_score[a] = k.scores[a_lo + a];
+                m.s_touched[a] = 0;
+            }
+#pragma unroll 8
+            for (uint32_t e = lane; e < E; e += 32) {
+                const uint32_t u = k.voucher[e_base + e] - a_lo;
+                const uint32_t live = live_flag(k.active[e_base + e], k.expiry[e_base + e], k.now);
+                m.s_voucher[e] = u;
+                m.s_flags[e] = !live ? 0 : (u < A ? (F_LIVE | F_WAS_LIVE) : F_BAD_VOUCHER);
+            }
+            __syncwarp();
+            run_events(k, m, g, lane, s, A);
+            __syncwarp();
+            for (uint32_t a = lane; a < A; a += 32)
+                if (m.s_touched[a]) {
+                    k.scores[a_lo + a] = m.s_score[a];
+                    k.touched[a_lo + a] = 1;
+                }
+            for (uint32_t e = lane; e < E; e += 32)
+                if (m.s_flags[e] == F_WAS_LIVE) k.active[e_base + e] = 0;
+            __syncwarp();                         // the slice is reused by this warp's next session
+        } else {
+            GlobalView m;
+            m.rowptr = k.rowptr + a_lo;
+            m.voucher = k.voucher + e_base;
+            m.active = k.active + e_base;
+            m.expiry = k.expiry + e_base;
+            m.scores = k.scores + a_lo;
+            m.touched = k.touched + a_lo;
+            m.cl = g.cl;
+            m.now = k.now;
+            m.a_lo = a_lo;
+            m.n_agents = A;
+            m.e_base = e_base;
+            run_events(k, m, g, lane, s, A);
+        }
+        g.status |= __reduce_or_sync(FULL, g.status);
         if (lane == 0) {
             k.slash_count[s] = g.n_slash;
             k.clip_count[s] = g.n_clip;
@@ -219,9 +572,34 @@ extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
     k.ev_sigma = b->event_sigma; k.ev_omega = b->event_omega; k.ev_depth = b->event_depth; k.n_sessions = b->n_sessions;
     k.scores = b->scores; k.touched = b->touched; k.slash_log = b->slash_log; k.clip_log = b->clip_log;
     k.slash_count = b->slash_count; k.clip_count = b->clip_count; k.status = b->status;
+    k.big_groups = nullptr;
     const uint64_t want = (b->n_sessions + SLASH_WARPS - 1) / SLASH_WARPS;
     const uint64_t cap = (uint64_t)ctx->sm_count * 16;
-    k_slash_cascade<<<(unsigned)(want < cap ? want : cap), 32 * SLASH_WARPS, 0, ctx->stream>>>(k);
+    const unsigned grid = (unsigned)(want < cap ? want : cap);
+    if (ctx->opt_slash_variant == 1) {            // everything on global memory, warp per session (kept for A/B runs)
+        k_slash_cascade<false><<<grid, 32 * SLASH_WARPS, 0, ctx->stream>>>(k, 0);
+        AHV_CHECK_LAUNCH(ctx);
+        return AHV_OK;
+    }
+    const int lanes = ctx->opt_slash_variant == 0;                       // 2: warp per session only, staged where it fits
+    if (lanes) {
+        const uint64_t n_groups = (b->n_sessions + 31) / 32;
+        AHV_TRY(scratch_reserve(ctx, 4 * (n_groups + 1) + 256));
+        k.big_groups = (uint32_t *)scratch_take(ctx, 4 * (n_groups + 1));
+        AHV_REQUIRE(k.big_groups, "internal: scratch too small for the group list");
+        AHV_CUDA(cudaMemsetAsync(k.big_groups, 0, 4, ctx->stream));
+        static bool attr_set[64] = {};
+        if (ctx->device >= 0 && ctx->device < 64 && !attr_set[ctx->device]) {
+            AHV_CUDA(cudaFuncSetAttribute(k_slash_lanes, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          LANE_WARPS * LANE_SMEM_PER_WARP));
+            attr_set[ctx->device] = true;
+        }
+        const uint64_t groups = (b->n_sessions + 31) / 32;
+        const uint64_t gwant = (groups + LANE_WARPS - 1) / LANE_WARPS;
+        k_slash_lanes<<<(unsigned)(gwant < cap ? gwant : cap), 32 * LANE_WARPS, LANE_WARPS * LANE_SMEM_PER_WARP, ctx->stream>>>(k);
+        AHV_CHECK_LAUNCH(ctx);
+    }
+    k_slash_cascade<true><<<grid, 32 * SLASH_WARPS, SLASH_WARPS * SLASH_SMEM_PER_WARP, ctx->stream>>>(k, lanes);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

@@ -378,6 +378,7 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "fixed_variant" 0/1/2 fixed-size leaf kernel: direct 16-byte loads (default) / cp.async staged / TMA bulk-copy staged
  *   "compress" 0/1      plain additions / scaled-sum compression with additions on the FMA pipe (default 1)
  *   "top_max" 0,2..256  level width at which a session's tree is finished in one warp/CTA (0 = auto)
+ *   "slash_variant" 0/1 slashing: sessions that fit are staged in shared memory (default 0) / always global memory
  *   "sigma_variant" 0/1 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);

@@ -207,3 +207,79 @@ class TestRingEnforcer:
         assert ReversibilityLevel.FULL.default_risk_weight == pytest.approx(0.2)
         assert ReversibilityLevel.PARTIAL.default_risk_weight == pytest.approx(0.65)
         assert ReversibilityLevel.NONE.default_risk_weight == pytest.approx(0.95)
+
+
+# ------------------------------------------------------------------ slashing (test_slashing.py, test_scenarios.py:471-545)
+class TestSlashingEngine:
+    def setup_method(self):
+        from agent_hypervisor_b200 import SlashingEngine, VouchingEngine
+        self.vouching = VouchingEngine()
+        self.slashing = SlashingEngine(self.vouching)
+        self.session = "session:test-slash"
+
+    def _slash(self, scores, sigma, omega, reason="violation"):
+        return self.slashing.slash(vouchee_did="did:mesh:bad", session_id=self.session, vouchee_sigma=sigma,
+                                   risk_weight=omega, reason=reason, agent_scores=scores)
+
+    def test_vouchee_goes_to_zero(self):
+        scores = {"did:mesh:bad": 0.7, "did:mesh:good": 0.9}
+        self.vouching.vouch("did:mesh:good", "did:mesh:bad", self.session, 0.9)
+        r = self._slash(scores, 0.7, 0.5)
+        assert scores["did:mesh:bad"] == 0.0 and r.vouchee_sigma_after == 0.0 and r.vouchee_sigma_before == 0.7
+        assert r.session_id == self.session and r.reason == "violation" and r.cascade_depth == 0
+
+    def test_voucher_clip_and_bond_release(self):
+        scores = {"did:mesh:bad": 0.5, "did:mesh:voucher": 0.9}
+        rec = self.vouching.vouch("did:mesh:voucher", "did:mesh:bad", self.session, 0.9)
+        r = self._slash(scores, 0.5, 0.5, "Hallucination")
+        assert len(r.voucher_clips) == 1
+        clip = r.voucher_clips[0]
+        assert clip.voucher_did == "did:mesh:voucher" and clip.vouch_id == rec.vouch_id and clip.risk_weight == 0.5
+        assert abs(clip.sigma_before - 0.9) < 1e-9 and abs(clip.sigma_after - 0.45) < 1e-9
+        assert abs(scores["did:mesh:voucher"] - 0.45) < 1e-9
+        assert rec.is_active is False and rec.released_at is not None
+        assert self.vouching.get_vouchers_for("did:mesh:bad", self.session) == []
+
+    def test_floor(self):
+        from agent_hypervisor_b200 import SlashingEngine
+        scores = {"did:mesh:bad": 0.1, "did:mesh:voucher": 0.06}
+        self.vouching.vouch("did:mesh:voucher", "did:mesh:bad", self.session, 0.8)
+        self._slash(scores, 0.1, 0.95, "Fraud")
+        assert scores["did:mesh:voucher"] == SlashingEngine.SIGMA_FLOOR
+
+    def test_all_vouchers_clipped_and_history(self):
+        scores = {"did:mesh:bad": 0.4, "did:mesh:v1": 0.8, "did:mesh:v2": 0.7}
+        self.vouching.vouch("did:mesh:v1", "did:mesh:bad", self.session, 0.8)
+        self.vouching.vouch("did:mesh:v2", "did:mesh:bad", self.session, 0.7)
+        r = self._slash(scores, 0.4, 0.3, "Mute triggered")
+        assert [c.voucher_did for c in r.voucher_clips] == ["did:mesh:v1", "did:mesh:v2"]
+        assert abs(scores["did:mesh:v1"] - 0.56) < 1e-9 and abs(scores["did:mesh:v2"] - 0.49) < 1e-9
+        assert self.slashing.history == [r] and self.slashing.history is not self.slashing._slash_history
+
+    def test_cascade_two_levels_and_unknown_voucher(self):
+        """a <- b <- c <- d: slashing a at omega 0.95 wipes b (cascade), then c (depth 2), and clips d without
+        going further; an agent missing from agent_scores is read as 0.0 and gets the floor."""
+        s = self.session
+        for voucher, vouchee in (("b", "a"), ("c", "b"), ("d", "c"), ("e", "d")):
+            self.vouching.vouch(f"did:{voucher}", f"did:{vouchee}", s, 0.9)
+        scores = {"did:a": 0.4, "did:b": 0.9, "did:c": 0.9, "did:e": 0.9}          # did:d missing
+        r = self.slashing.slash("did:a", s, 0.4, 0.95, "drift", scores)
+        h = self.slashing.history
+        assert [(x.vouchee_did, x.cascade_depth) for x in h] == [("did:a", 0), ("did:b", 1), ("did:c", 2)]
+        assert h[0] is r and h[1].reason == "Cascade from did:a: drift"
+        assert h[2].reason == "Cascade from did:b: Cascade from did:a: drift"
+        assert scores == {"did:a": 0.0, "did:b": 0.0, "did:c": 0.0, "did:e": 0.9, "did:d": 0.05}
+        assert list(scores) == ["did:a", "did:b", "did:c", "did:e", "did:d"]
+        assert len(self.vouching.get_vouchers_for("did:d", s)) == 1           # the e -> d bond was never reached
+
+    def test_works_over_the_reference_style_engine_surface(self):
+        """Only `_vouches` and `release_bond` of the vouching engine are used; release_bond errors propagate."""
+        from agent_hypervisor_b200 import VouchingError
+        self.vouching.vouch("did:v", "did:mesh:bad", self.session, 0.9)
+        calls = []
+        orig = self.vouching.release_bond
+        self.vouching.release_bond = lambda vid: (calls.append(vid), orig(vid))[1]
+        self._slash({"did:v": 0.8}, 0.5, 0.5)
+        assert len(calls) == 1
+        with pytest.raises(VouchingError):
+            self.vouching.release_bond("vouch:none")

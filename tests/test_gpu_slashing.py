@@ -22,6 +22,15 @@ def ctx():
     return nat.get_context()
 
 
+@pytest.fixture(params=[0, 2, 1], ids=["lanes+staged", "staged", "global-only"])
+def variant(request, ctx):
+    """Every kernel form: lane per session for groups of small sessions + warp per session staged in shared
+    memory where it fits (default); warp per session only; everything on global memory."""
+    ctx.set_option("slash_variant", request.param)
+    yield request.param
+    ctx.set_option("slash_variant", 0)
+
+
 def run_gpu(ctx, b):
     o = ctx.slash_cascade(b["rowptr"], b["voucher"], b["active"], b["expiry"], b["now"], b["session_agent_rowptr"],
                           b["event_rowptr"], b["event_agent"], b["event_sigma"], b["event_omega"], b["scores"],
@@ -47,7 +56,7 @@ def assert_same_outputs(got, want, b):
         assert same_f64(a["sigma_before"], w["sigma_before"]) and same_f64(a["sigma_after"], w["sigma_after"])
 
 
-def test_golden_cases_one_launch(ctx, slashing_golden):
+def test_golden_cases_one_launch(ctx, slashing_golden, variant):
     gold = slashing_golden["cases"]
     cases = [recipes.random_slash_case(g["seed"]) for g in gold]
     b = slash_batch(cases)
@@ -119,11 +128,15 @@ def run_c(b):
                             b["event_depth"])
 
 
-def test_large_batch_and_giant_session_vs_c_restatement(ctx):
+def test_large_batch_and_giant_session_vs_c_restatement(ctx, variant):
     b = big_batch(11, 30000, giant=(5000, 200000))
     got, want = run_gpu(ctx, b), run_c(b)
     assert int(want[6].sum()) > 100000 and int(want[5].max()) > 50          # real work, real cascades
     assert_same_outputs(got, want, b)
+    # sessions around the staging limit (6 KB of state per warp): both sides of it in one batch
+    for A, E in ((40, 330), (41, 330), (8, 354), (8, 355), (300, 100), (1, 361)):
+        eb = big_batch(100 + A + E, 9, giant=(A, E))
+        assert_same_outputs(run_gpu(ctx, eb), run_c(eb), eb)
     small = big_batch(12, 257)
     py = lo.slash_cascade(small["rowptr"], small["voucher"], small["active"], small["expiry"], small["now"],
                           small["session_agent_rowptr"], small["event_rowptr"], small["event_agent"], small["event_sigma"],

@@ -122,3 +122,37 @@ def count_compressions_fixed(n: int, msg_len: int, leaves_per_session: int) -> t
         c = (c + 1) // 2
         nodes += c
     return leaf, 3 * nodes * (n // leaves_per_session)
+
+
+def slash_sessions(S: int, agents: int = 16, records: int = 48, seed: int = 0x51A5, now_us: int = 1_800_000_000_000_000,
+                   omega: float = 0.95):
+    """S independent sessions for the slashing pass: ``agents`` participants and ``records``
+    vouch records each (uniform voucher / vouchee, 90 % active, 5 % expired), one violation per session at the
+    risk weight core.py:271 uses.  Returns the arrays of ``ahv_slash_batch`` (host side)."""
+    rng = np.random.Generator(np.random.Philox(key=seed))
+    A, E = S * agents, S * records
+    base = np.repeat(np.arange(S, dtype=np.int64) * agents, records)
+    vouchee = base + rng.integers(0, agents, E)
+    voucher = base + rng.integers(0, agents, E)
+    order = np.argsort(vouchee, kind="stable")
+    vouchee, voucher = vouchee[order], voucher[order]
+    rowptr = np.zeros(A + 1, dtype=np.int64)
+    np.add.at(rowptr, vouchee + 1, 1)
+    rowptr = np.cumsum(rowptr).astype(np.uint32)
+    expiry = np.full(E, np.iinfo(np.int64).max, dtype=np.int64)
+    expiry[rng.random(E) < 0.05] = now_us - 1_000_000
+    return dict(
+        rowptr=rowptr, voucher=voucher.astype(np.uint32), active=(rng.random(E) < 0.9).astype(np.uint8), expiry=expiry,
+        now=now_us, session_agent_rowptr=np.arange(S + 1, dtype=np.uint64) * np.uint64(agents),
+        event_rowptr=np.arange(S + 1, dtype=np.uint64),
+        event_agent=(np.arange(S, dtype=np.int64) * agents + rng.integers(0, agents, S)).astype(np.uint32),
+        event_sigma=rng.random(S), event_omega=np.full(S, omega), scores=rng.random(A))
+
+
+def slash_bytes(b: dict, n_slash: int, n_clip: int) -> int:
+    """Algorithmic bytes of one slashing pass: per slash call its row bounds, the vouchee's score and its
+    record (8 + 8 + 32); per record looked at (every record of a slashed row) voucher + active + expiry
+    (13); per clip the score read and written, the released flag and the clip record (16 + 1 + 24);
+    per session its bounds, event and counters (8 + 8 + 4 + 8 + 8 + 9)."""
+    S = len(b["session_agent_rowptr"]) - 1
+    return n_slash * 48 + n_clip * (13 + 41) + S * 45
