@@ -29,6 +29,29 @@ class BatchAuditor:
             fixed_len=fixed if fixed else 0, uniform_leaves=uni, n_sessions=packed.n_sessions)
         return digs, [None if empty[s] else roots[s].tobytes().hex() for s in range(packed.n_sessions)]
 
+    def roots_of_engines(self, engines: Sequence) -> list:
+        """``[e.compute_merkle_root() for e in engines]`` (audit/delta.py:117-134: trees over the STORED
+        ``delta_hash`` strings, nothing re-hashed) with one tree launch for all engines whose hashes are
+        well-formed digests; an engine holding any other string goes through its own method."""
+        from .delta import _LOWER_HEX
+        roots: list = [None] * len(engines)
+        blobs, rowptr, where = [], [0], []
+        for i, e in enumerate(engines):
+            hs = [d.delta_hash for d in getattr(e, "_deltas", e)]
+            joined = "".join(hs) if all(type(h) is str and len(h) == 64 for h in hs) else None
+            if joined is not None and (not hs or _LOWER_HEX.fullmatch(joined)):
+                blobs.append(joined)
+                rowptr.append(rowptr[-1] + len(hs))
+                where.append(i)
+            else:
+                roots[i] = e.compute_merkle_root()
+        if where:
+            digs = np.frombuffer(bytes.fromhex("".join(blobs)), dtype=np.uint8)
+            r, empty = self.ctx.merkle_roots(digs, np.array(rowptr, dtype=np.uint64))
+            for k, i in enumerate(where):
+                roots[i] = None if empty[k] else r[k].tobytes().hex()
+        return roots
+
     def commit_engines(self, engines: Sequence, commitment_engine=None, participants=None) -> list:
         """Roots for many DeltaEngines at once; also refreshes nothing (pure read), like
         compute_merkle_root.  Optionally records them in a CommitmentEngine."""

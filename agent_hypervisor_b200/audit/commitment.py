@@ -48,5 +48,15 @@ class CommitmentEngine:
         self._batch_queue.clear()
         return out
 
+    def verify_batch(self, session_ids, engines, auditor=None) -> list[bool]:
+        """``[self.verify(sid, engine.compute_merkle_root()) for ...]`` (audit/commitment.py:59-64 over
+        audit/delta.py:117-134) for many sessions with ONE commit pass on the device: the roots are rebuilt from
+        the engines' current ``delta_hash`` leaves, exactly as ``compute_merkle_root`` would, and compared with
+        the stored records.  An unknown session, or an empty engine (root ``None``), is ``False``."""
+        from .batch import BatchAuditor
+        auditor = auditor or BatchAuditor()
+        roots = auditor.roots_of_engines(engines)
+        return [self.verify(sid, r) for sid, r in zip(session_ids, roots)]
+
     def get_commitment(self, session_id: str) -> Optional[CommitmentRecord]:
         return self._commitments.get(session_id)

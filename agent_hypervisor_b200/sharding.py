@@ -133,3 +133,51 @@ def gather_session_results(local_roots: np.ndarray, local_verdicts: np.ndarray, 
                              np.ascontiguousarray(local_verdicts, dtype=np.uint8).reshape(-1, 1)], axis=1)
     allp = all_gather_bytes(packed, counts, device=device, group=group)
     return allp[:, :32].copy(), allp[:, 32].copy()
+
+
+# ---------------------------------------------------------------------------- liability batches
+def shard_slash_batch(b: dict, rank: int, world: int) -> tuple[dict, dict]:
+    """This rank's part of a slashing batch (the arrays of ``ahv_slash_batch``; SURVEY.md 8e: shard by
+    session, no data-path collective).  Sessions own contiguous agent rows, records and events, so a
+    contiguous session range is a contiguous slice of every array; indices are rebased to the slice.
+    Returns (local batch, placement) where placement says where the rank's results sit in the whole."""
+    S = len(b["session_agent_rowptr"]) - 1
+    s0, s1 = shard_range(S, world, rank)
+    srp = np.asarray(b["session_agent_rowptr"], dtype=np.uint64)
+    erp = np.asarray(b["event_rowptr"], dtype=np.uint64)
+    rp = np.asarray(b["rowptr"], dtype=np.uint32)
+    a0, a1 = int(srp[s0]), int(srp[s1])
+    e0, e1 = int(rp[a0]), int(rp[a1])
+    v0, v1 = int(erp[s0]), int(erp[s1])
+    local = dict(
+        rowptr=(rp[a0:a1 + 1] - np.uint32(e0)).astype(np.uint32),
+        voucher=(np.asarray(b["voucher"], dtype=np.uint32)[e0:e1] - np.uint32(a0)).astype(np.uint32),
+        active=np.asarray(b["active"], dtype=np.uint8)[e0:e1], expiry=np.asarray(b["expiry"], dtype=np.int64)[e0:e1],
+        now=b["now"], session_agent_rowptr=srp[s0:s1 + 1] - np.uint64(a0), event_rowptr=erp[s0:s1 + 1] - np.uint64(v0),
+        event_agent=(np.asarray(b["event_agent"], dtype=np.uint32)[v0:v1] - np.uint32(a0)).astype(np.uint32),
+        event_sigma=np.asarray(b["event_sigma"], dtype=np.float64)[v0:v1],
+        event_omega=np.asarray(b["event_omega"], dtype=np.float64)[v0:v1],
+        scores=np.asarray(b["scores"], dtype=np.float64)[a0:a1])
+    if b.get("event_depth") is not None:
+        local["event_depth"] = np.asarray(b["event_depth"], dtype=np.uint8)[v0:v1]
+    return local, dict(sessions=(s0, s1), agents=(a0, a1), records=(e0, e1), events=(v0, v1))
+
+
+def place_slash_results(whole: dict, out: dict, placement: dict) -> None:
+    """Write one rank's outputs (dict as returned by ``Context.slash_cascade``) into whole-batch arrays
+    (same keys), turning the rank-local indices of the records back into whole-batch ones."""
+    (s0, s1), (a0, a1), (e0, e1), (v0, v1) = (placement[k] for k in ("sessions", "agents", "records", "events"))
+    whole["scores"][a0:a1] = out["scores"]
+    whole["touched"][a0:a1] = out["touched"]
+    whole["active"][e0:e1] = out["active"]
+    whole["slash_count"][s0:s1] = out["slash_count"]
+    whole["clip_count"][s0:s1] = out["clip_count"]
+    whole["status"][s0:s1] = out["status"]
+    sl = np.array(out["slash_log"], copy=True)
+    sl["agent"] += np.uint32(a0)
+    sl["event"] += np.uint32(v0)
+    cl = np.array(out["clip_log"], copy=True)
+    cl["edge"] += np.uint32(e0)
+    # a session's slash records start at event_rowptr[s] + rowptr[a_lo]: the rank's block moves by v0 + e0
+    whole["slash_log"][v0 + e0: v0 + e0 + len(sl)] = sl
+    whole["clip_log"][e0: e0 + len(cl)] = cl

@@ -283,3 +283,27 @@ class TestSlashingEngine:
         assert len(calls) == 1
         with pytest.raises(VouchingError):
             self.vouching.release_bond("vouch:none")
+
+
+def test_commitment_verify_batch_matches_per_session_verify():
+    """CommitmentEngine.verify_batch == [verify(sid, engine.compute_merkle_root())] (commitment.py:59-64 over
+    delta.py:117-134): clean sessions, a tampered stored hash, an overwritten non-digest hash, an empty engine,
+    an unknown session."""
+    from agent_hypervisor_b200 import CommitmentEngine, DeltaEngine, VFSChange
+    engines = []
+    for s in range(12):
+        e = DeltaEngine(f"s{s}")
+        for i in range(s):                               # 0 .. 11 deltas
+            e.capture("did:a", [VFSChange(path=f"/f{i}", operation="add", content_hash=f"h{s}{i}")])
+        engines.append(e)
+    ce = CommitmentEngine()
+    for e in engines[:-1]:                               # the last session is never committed
+        root = e.compute_merkle_root()
+        if root is not None:
+            ce.commit(e.session_id, root, ["did:a"], e.turn_count)
+    engines[5]._deltas[2].delta_hash = "0" * 64          # stored leaf changed after the commit
+    engines[7]._deltas[0].delta_hash = "not-a-digest"    # the reference would hash the string as it is
+    want = [ce.verify(e.session_id, e.compute_merkle_root()) for e in engines]
+    got = ce.verify_batch([e.session_id for e in engines], engines)
+    assert got == want
+    assert got == [False, True, True, True, True, False, True, False, True, True, True, False]

@@ -83,3 +83,42 @@ def test_gloo_sharded_tree_and_session_gather(world):
     want, _ = co.merkle_roots(digs, np.array([0, n], np.uint64))
     for rank, root, ok in res:
         assert root == bytes(want[0]) and ok
+
+
+def test_slash_batch_shards_reassemble_to_the_whole():
+    """Slashing shards by session with no exchange: every rank's slice run on its own (here by the C
+    restatement) and placed back gives exactly the whole batch's scores, flags and records."""
+    import recipes
+    from helpers import same_f64, slash_batch
+    from oracle.liability_oracle import CLIP_DT, SLASH_DT
+    cases = [recipes.random_slash_case(seed) for seed in range(97)]
+    b = slash_batch(cases)
+    args = ("rowptr", "voucher", "active", "expiry", "now", "session_agent_rowptr", "event_rowptr", "event_agent",
+            "event_sigma", "event_omega", "scores", "event_depth")
+    want = co.slash_cascade(*[b[k] for k in args])
+    keys = ("scores", "touched", "active", "slash_log", "clip_log", "slash_count", "clip_count")
+    for world in (1, 2, 3, 8):
+        A, E, S, NE = len(b["scores"]), len(b["voucher"]), len(cases), len(b["event_agent"])
+        whole = dict(scores=np.zeros(A), touched=np.zeros(A, np.uint8), active=np.zeros(E, np.uint8),
+                     slash_log=np.zeros(NE + E, SLASH_DT), clip_log=np.zeros(E, CLIP_DT), slash_count=np.zeros(S, np.uint32),
+                     clip_count=np.zeros(S, np.uint32), status=np.ones(S, np.uint8))
+        covered = 0
+        for rank in range(world):
+            local, place = sharding.shard_slash_batch(b, rank, world)
+            out = dict(zip(keys, co.slash_cascade(*[local[k] for k in args])))
+            out["status"] = np.zeros(len(out["slash_count"]), np.uint8)
+            sharding.place_slash_results(whole, out, place)
+            covered += place["sessions"][1] - place["sessions"][0]
+        assert covered == S and not whole["status"].any()
+        srp, erp, rp = b["session_agent_rowptr"], b["event_rowptr"], b["rowptr"]
+        assert np.array_equal(np.nan_to_num(whole["scores"], nan=-1.0), np.nan_to_num(want[0], nan=-1.0))
+        for k, w in zip(keys[1:3] + keys[5:], (want[1], want[2], want[5], want[6])):
+            assert np.array_equal(whole[k], w), k
+        for s in range(S):
+            e0 = int(rp[int(srp[s])])
+            for log, cnt, off in (("slash_log", want[5], int(erp[s]) + e0), ("clip_log", want[6], e0)):
+                got = whole[log][off: off + int(cnt[s])]
+                ref = want[3 if log == "slash_log" else 4][off: off + int(cnt[s])]
+                for f in got.dtype.names:
+                    same = same_f64(got[f], ref[f]) if got.dtype[f].kind == "f" else np.array_equal(got[f], ref[f])
+                    assert same, (world, s, log, f)
