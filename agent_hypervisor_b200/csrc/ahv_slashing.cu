@@ -22,11 +22,12 @@
 // sessions run the same code on global memory (GlobalView), where rows are long enough to keep the lanes
 // busy.  Both views produce the same records.
 //
-// Small sessions (a handful of records per row) would leave most of a warp's lanes idle, so where 32
-// consecutive sessions together fit one warp's slice (11 B per agent + 3 B per record) they are run by
-// k_slash_lanes instead: the warp stages the 32 sessions' contiguous rows, records and scores with
-// coalesced reads, then every lane walks ITS session serially out of shared memory - the reference's loop
-// as written - and the warp writes back what changed.  k_slash_cascade skips those groups.
+// Small sessions (a handful of records per row) would leave most of a warp's lanes idle, so k_slash_lanes
+// runs first: a warp takes 32 consecutive sessions, cuts them into runs that fit its slice of shared memory
+// (11 B per agent + 3 B per record), stages a run's contiguous rows, records and scores with coalesced
+// reads, then every lane walks ITS session serially out of shared memory - the reference's loop as
+// written - and the warp writes back what changed.  Sessions so large that fewer than four fit a slice
+// are listed for k_slash_cascade, which then only visits that list.
 #include "ahv_internal.cuh"
 
 namespace ahv {
@@ -40,6 +41,7 @@ constexpr uint32_t SLASH_SMEM_PER_WARP = 6144;    // bytes of staged session sta
 constexpr int LANE_WARPS = 4;                     // k_slash_lanes: warps per CTA
 constexpr uint32_t LANE_SMEM_PER_WARP = 10752;    // bytes of staged state for a group of 32 sessions (5 CTAs per SM)
 constexpr int LANE_CLIP_CACHE = 12;
+constexpr int LANE_MIN_SESSIONS = 4;              // fewer sessions than this in a run: a warp per session instead
 
 __host__ __device__ __forceinline__ uint64_t lane_group_bytes(uint64_t agents, uint64_t records)
 {
@@ -68,7 +70,7 @@ struct SlashArgs {
     uint32_t *slash_count;
     uint32_t *clip_count;
     uint8_t *status;
-    uint32_t *big_groups;         // scratch: [0] = count, [1..] = groups of 32 sessions k_slash_lanes left to k_slash_cascade
+    uint32_t *big_sessions;       // scratch: [0] = count, [1..] = sessions k_slash_lanes left to k_slash_cascade
 };
 
 __device__ __forceinline__ double clip_once(double x, double keep)
@@ -279,17 +281,6 @@ __device__ void run_events(const SlashArgs &k, View &m, SessionLog &g, int lane,
     }
 }
 
-// Do sessions s0 .. s0+n-1 (a group of up to 32 consecutive sessions) fit one warp's slice?
-__device__ __forceinline__ bool group_fits(const SlashArgs &k, uint64_t s0, uint32_t n, uint32_t &a_lo, uint32_t &A, uint32_t &e_lo,
-                                           uint32_t &E)
-{
-    a_lo = (uint32_t)k.sess_rp[s0];
-    A = (uint32_t)k.sess_rp[s0 + n] - a_lo;
-    e_lo = k.rowptr[a_lo];
-    E = k.rowptr[a_lo + A] - e_lo;
-    return lane_group_bytes(A, E) <= LANE_SMEM_PER_WARP;
-}
-
 // One lane = one session, serial, on the group's staged state.  Indices: agents and records are
 // group-local in shared memory; `la` is the first agent of this lane's session, `ln` their number.
 struct LaneRun {
@@ -417,60 +408,72 @@ k_slash_lanes(const SlashArgs k)
     for (uint64_t grp = (uint64_t)blockIdx.x * LANE_WARPS + wib; grp < n_groups; grp += n_warps) {
         const uint64_t s0 = grp * 32;
         const uint32_t n = (uint32_t)(k.n_sessions - s0 < 32 ? k.n_sessions - s0 : 32);
-        uint32_t a_lo, A, e_lo, E;
-        if (!group_fits(k, s0, n, a_lo, A, e_lo, E)) {              // k_slash_cascade takes this group
-            if (lane == 0) k.big_groups[1 + atomicAdd(k.big_groups, 1u)] = (uint32_t)grp;
-            continue;
-        }
-        // this lane's session: bounds and events (loads that overlap the staging below)
-        const uint64_t s = s0 + ((uint32_t)lane < n ? lane : 0);
+        // lane i looks after session s0 + i: its first agent row / record / event, and the ones after it
+        const uint64_t s = s0 + ((uint32_t)lane < n ? lane : n - 1);
         const uint32_t my_a0 = (uint32_t)k.sess_rp[s], my_a1 = (uint32_t)k.sess_rp[s + 1];
         const uint64_t ev_lo = k.ev_rp[s], ev_hi = k.ev_rp[s + 1];
-        LaneRun r;
-        uint8_t *base = slash_smem + (size_t)wib * LANE_SMEM_PER_WARP;
-        r.s_score = reinterpret_cast<double *>(base);
-        r.s_rowptr = reinterpret_cast<uint16_t *>(r.s_score + A);
-        r.s_voucher = r.s_rowptr + (A + 1);
-        r.s_flags = reinterpret_cast<uint8_t *>(r.s_voucher + E);
-        r.s_touched = r.s_flags + E;
-#pragma unroll 8
-        for (uint32_t a = lane; a <= A; a += 32) r.s_rowptr[a] = (uint16_t)(k.rowptr[a_lo + a] - e_lo);
-#pragma unroll 8
-        for (uint32_t a = lane; a < A; a += 32) {
-            r.s_score[a] = k.scores[a_lo + a];
-            r.s_touched[a] = 0;
-        }
-#pragma unroll 8
-        for (uint32_t e = lane; e < E; e += 32) {
-            // a voucher outside the group becomes 0xffff: outside every session of the group as well
-            const uint32_t u = k.voucher[e_lo + e] - a_lo;
-            r.s_voucher[e] = (uint16_t)(u < A ? u : 0xffffu);
-            r.s_flags[e] = live_flag(k.active[e_lo + e], k.expiry[e_lo + e], k.now) ? (F_LIVE | F_WAS_LIVE) : 0;
-        }
-        __syncwarp();
-        if ((uint32_t)lane < n) {
-            r.la = my_a0 - a_lo;
-            r.ln = my_a1 - my_a0;
-            r.ga_lo = a_lo;
-            r.ge_lo = e_lo;
-            const uint32_t e_base = e_lo + r.s_rowptr[r.la];
-            r.sl = k.slash_log + (ev_lo + e_base);
-            r.cl = k.clip_log + e_base;
-            r.n_slash = r.n_clip = r.status = 0;
-            r.events(k, ev_lo, ev_hi);
-            k.slash_count[s] = r.n_slash;
-            k.clip_count[s] = r.n_clip;
-            k.status[s] = (uint8_t)r.status;
-        }
-        __syncwarp();
-        for (uint32_t a = lane; a < A; a += 32)
-            if (r.s_touched[a]) {
-                k.scores[a_lo + a] = r.s_score[a];
-                k.touched[a_lo + a] = 1;
+        const uint32_t my_e0 = k.rowptr[my_a0], my_e1 = k.rowptr[my_a1];
+        uint32_t p = 0;
+        while (p < n) {
+            // the longest run of sessions p .. q-1 whose state fits the slice (sizes grow with q: a prefix)
+            const uint32_t a_lo = __shfl_sync(FULL, my_a0, p), e_lo = __shfl_sync(FULL, my_e0, p);
+            const bool fit = (uint32_t)lane >= p && (uint32_t)lane < n &&
+                             lane_group_bytes(my_a1 - a_lo, my_e1 - e_lo) <= LANE_SMEM_PER_WARP;
+            const uint32_t cnt = __popc(__ballot_sync(FULL, fit));
+            if (cnt < (n - p < (uint32_t)LANE_MIN_SESSIONS ? n - p : (uint32_t)LANE_MIN_SESSIONS)) {
+                // too few lanes would work: session p is k_slash_cascade's (a whole warp for it)
+                if (lane == 0) k.big_sessions[1 + atomicAdd(k.big_sessions, 1u)] = (uint32_t)(s0 + p);
+                ++p;
+                continue;
             }
-        for (uint32_t e = lane; e < E; e += 32)
-            if (r.s_flags[e] == F_WAS_LIVE) k.active[e_lo + e] = 0;
-        __syncwarp();
+            const uint32_t q = p + cnt;
+            const uint32_t A = __shfl_sync(FULL, my_a1, q - 1) - a_lo, E = __shfl_sync(FULL, my_e1, q - 1) - e_lo;
+            LaneRun r;
+            uint8_t *base = slash_smem + (size_t)wib * LANE_SMEM_PER_WARP;
+            r.s_score = reinterpret_cast<double *>(base);
+            r.s_rowptr = reinterpret_cast<uint16_t *>(r.s_score + A);
+            r.s_voucher = r.s_rowptr + (A + 1);
+            r.s_flags = reinterpret_cast<uint8_t *>(r.s_voucher + E);
+            r.s_touched = r.s_flags + E;
+#pragma unroll 8
+            for (uint32_t a = lane; a <= A; a += 32) r.s_rowptr[a] = (uint16_t)(k.rowptr[a_lo + a] - e_lo);
+#pragma unroll 8
+            for (uint32_t a = lane; a < A; a += 32) {
+                r.s_score[a] = k.scores[a_lo + a];
+                r.s_touched[a] = 0;
+            }
+#pragma unroll 8
+            for (uint32_t e = lane; e < E; e += 32) {
+                // a voucher outside the run becomes 0xffff: outside every session of the run as well
+                const uint32_t u = k.voucher[e_lo + e] - a_lo;
+                r.s_voucher[e] = (uint16_t)(u < A ? u : 0xffffu);
+                r.s_flags[e] = live_flag(k.active[e_lo + e], k.expiry[e_lo + e], k.now) ? (F_LIVE | F_WAS_LIVE) : 0;
+            }
+            __syncwarp();
+            if ((uint32_t)lane >= p && (uint32_t)lane < q) {
+                r.la = my_a0 - a_lo;
+                r.ln = my_a1 - my_a0;
+                r.ga_lo = a_lo;
+                r.ge_lo = e_lo;
+                r.sl = k.slash_log + (ev_lo + my_e0);
+                r.cl = k.clip_log + my_e0;
+                r.n_slash = r.n_clip = r.status = 0;
+                r.events(k, ev_lo, ev_hi);
+                k.slash_count[s] = r.n_slash;
+                k.clip_count[s] = r.n_clip;
+                k.status[s] = (uint8_t)r.status;
+            }
+            __syncwarp();
+            for (uint32_t a = lane; a < A; a += 32)
+                if (r.s_touched[a]) {
+                    k.scores[a_lo + a] = r.s_score[a];
+                    k.touched[a_lo + a] = 1;
+                }
+            for (uint32_t e = lane; e < E; e += 32)
+                if (r.s_flags[e] == F_WAS_LIVE) k.active[e_lo + e] = 0;
+            __syncwarp();                         // the slice is reused by the next run
+            p = q;
+        }
     }
 }
 
@@ -484,10 +487,9 @@ k_slash_cascade(const SlashArgs k, const int from_list)
     const uint64_t warp = (uint64_t)blockIdx.x * SLASH_WARPS + wib;
     const uint64_t n_warps = (uint64_t)gridDim.x * SLASH_WARPS;
     // with the lane kernel in front, only the sessions of the groups it listed are left
-    const uint64_t n_items = from_list ? (uint64_t)k.big_groups[0] * 32 : k.n_sessions;
+    const uint64_t n_items = from_list ? (uint64_t)k.big_sessions[0] : k.n_sessions;
     for (uint64_t w = warp; w < n_items; w += n_warps) {
-        const uint64_t s = from_list ? (uint64_t)k.big_groups[1 + (w >> 5)] * 32 + (w & 31) : w;
-        if (s >= k.n_sessions) continue;
+        const uint64_t s = from_list ? (uint64_t)k.big_sessions[1 + w] : w;
         const uint32_t a_lo = (uint32_t)k.sess_rp[s];
         const uint32_t A = (uint32_t)k.sess_rp[s + 1] - a_lo;
         const uint32_t e_base = k.rowptr[a_lo];
@@ -572,7 +574,7 @@ extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
     k.ev_sigma = b->event_sigma; k.ev_omega = b->event_omega; k.ev_depth = b->event_depth; k.n_sessions = b->n_sessions;
     k.scores = b->scores; k.touched = b->touched; k.slash_log = b->slash_log; k.clip_log = b->clip_log;
     k.slash_count = b->slash_count; k.clip_count = b->clip_count; k.status = b->status;
-    k.big_groups = nullptr;
+    k.big_sessions = nullptr;
     const uint64_t want = (b->n_sessions + SLASH_WARPS - 1) / SLASH_WARPS;
     const uint64_t cap = (uint64_t)ctx->sm_count * 16;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
@@ -583,11 +585,11 @@ extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
     }
     const int lanes = ctx->opt_slash_variant == 0;                       // 2: warp per session only, staged where it fits
     if (lanes) {
-        const uint64_t n_groups = (b->n_sessions + 31) / 32;
-        AHV_TRY(scratch_reserve(ctx, 4 * (n_groups + 1) + 256));
-        k.big_groups = (uint32_t *)scratch_take(ctx, 4 * (n_groups + 1));
-        AHV_REQUIRE(k.big_groups, "internal: scratch too small for the group list");
-        AHV_CUDA(cudaMemsetAsync(k.big_groups, 0, 4, ctx->stream));
+        AHV_REQUIRE(b->n_sessions < 0xffffffffull, "more than 2^32 - 2 sessions");
+        AHV_TRY(scratch_reserve(ctx, 4 * (b->n_sessions + 1) + 256));
+        k.big_sessions = (uint32_t *)scratch_take(ctx, 4 * (b->n_sessions + 1));
+        AHV_REQUIRE(k.big_sessions, "internal: scratch too small for the session list");
+        AHV_CUDA(cudaMemsetAsync(k.big_sessions, 0, 4, ctx->stream));
         static bool attr_set[64] = {};
         if (ctx->device >= 0 && ctx->device < 64 && !attr_set[ctx->device]) {
             AHV_CUDA(cudaFuncSetAttribute(k_slash_lanes, cudaFuncAttributeMaxDynamicSharedMemorySize,
