@@ -93,7 +93,7 @@ SIGNATURES = {
     "ahv_extract_parents_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _vp]),
     "ahv_chain_capture": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_chain_capture_dev": (C.c_int, [_vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp]),
-    "ahv_pack_deltas": (C.c_int, [_vp, _vp, _vp, _u64, _u64p, _vp]),
+    "ahv_pack_deltas": (C.c_int, [_vp, _vp, _vp, _u64, _u64p, _vp, C.c_uint32]),
     "ahv_sigma_eff_rings": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,
                                       _vp, _vp, _vp, _vp]),
     "ahv_sigma_eff_rings_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,

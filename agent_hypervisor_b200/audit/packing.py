@@ -247,12 +247,13 @@ def pack_columns(cols: dict, arena: Optional[np.ndarray] = None, want_parent_pos
     nbytes = _C.c_uint64()
     ppos = np.zeros(max(n, 1), dtype=np.uint32) if want_parent_pos else None
     rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, None, 0, _C.byref(nbytes),
-                             ppos.ctypes.data if want_parent_pos else None)
+                             ppos.ctypes.data if want_parent_pos else None, 0)
     if rc:
         raise nat.NativeError(lib.ahv_last_error().decode())
     if arena is None:
         arena = np.empty(max(int(nbytes.value), 1), dtype=np.uint8)
-    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, arena.ctypes.data, arena.nbytes, _C.byref(nbytes), None)
+    rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, arena.ctypes.data, arena.nbytes, _C.byref(nbytes), None,
+                             1)      # AHV_PACK_OFFSETS_VALID: the size query above filled offsets
     if rc:
         raise nat.NativeError(lib.ahv_last_error().decode())
     if want_parent_pos:

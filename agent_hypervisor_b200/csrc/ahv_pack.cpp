@@ -25,17 +25,22 @@ void set_error(const char *fmt, ...);
 
 namespace {
 
+// Everything below is force-inlined into the two per-delta loops: the sink is then a local object whose
+// address never escapes, so its cursor lives in a register (a byte store through `p` could otherwise alias
+// the sink's own members and force a reload per character).
+#define AHV_INLINE inline __attribute__((always_inline))
+
 template <bool WRITE>
 struct SinkT {           // WRITE = false only counts bytes
     uint8_t *p;
     uint64_t n = 0;
     explicit SinkT(uint8_t *dst) : p(dst) {}
-    inline void put(uint8_t c)
+    AHV_INLINE void put(uint8_t c)
     {
         if (WRITE) p[n] = c;
         ++n;
     }
-    inline void lit(const void *s, size_t len)
+    AHV_INLINE void lit(const void *s, size_t len)
     {
         if (WRITE) memcpy(p + n, s, len);
         n += len;
@@ -46,7 +51,7 @@ struct SinkT {           // WRITE = false only counts bytes
 const char HEXD[] = "0123456789abcdef";
 
 template <class Sink>
-inline void put_u4(Sink &o, uint32_t cu)   // \uXXXX
+AHV_INLINE void put_u4(Sink &o, uint32_t cu)   // \uXXXX
 {
     o.put('\\'); o.put('u');
     o.put(HEXD[(cu >> 12) & 15]); o.put(HEXD[(cu >> 8) & 15]); o.put(HEXD[(cu >> 4) & 15]); o.put(HEXD[cu & 15]);
@@ -55,7 +60,7 @@ inline void put_u4(Sink &o, uint32_t cu)   // \uXXXX
 // JSON string (with quotes) from UTF-8 bytes, ensure_ascii semantics.  Invalid UTF-8 cannot occur:
 // the columns are produced by str.encode().
 template <class Sink>
-void put_json_string(Sink &o, const uint8_t *s, uint64_t len)
+AHV_INLINE void put_json_string(Sink &o, const uint8_t *s, uint64_t len)
 {
     o.put('"');
     for (uint64_t i = 0; i < len;) {
@@ -103,7 +108,7 @@ void put_json_string(Sink &o, const uint8_t *s, uint64_t len)
 }
 
 template <class Sink>
-void put_int(Sink &o, int64_t v)
+AHV_INLINE void put_int(Sink &o, int64_t v)
 {
     char buf[24];
     int k = 0;
@@ -114,11 +119,11 @@ void put_int(Sink &o, int64_t v)
 }
 
 template <class Sink>
-inline void put_2(Sink &o, uint32_t v) { o.put((uint8_t)('0' + v / 10)); o.put((uint8_t)('0' + v % 10)); }
+AHV_INLINE void put_2(Sink &o, uint32_t v) { o.put((uint8_t)('0' + v / 10)); o.put((uint8_t)('0' + v % 10)); }
 
 // datetime.isoformat() of (microseconds since the epoch in UTC, utc offset in seconds or INT32_MIN for naive)
 template <class Sink>
-void put_iso(Sink &o, int64_t epoch_us, int32_t off_s)
+AHV_INLINE void put_iso(Sink &o, int64_t epoch_us, int32_t off_s)
 {
     const bool aware = off_s != INT32_MIN;
     int64_t local = epoch_us + (aware ? (int64_t)off_s * 1000000 : 0);
@@ -161,7 +166,7 @@ struct StrCol {
     const uint64_t *off;     // count+1
     const uint8_t *is_null;  // optional
     template <class Sink>
-    inline void emit(Sink &o, uint64_t i) const
+    AHV_INLINE void emit(Sink &o, uint64_t i) const
     {
         if (is_null && is_null[i]) LIT(o, "null");
         else put_json_string(o, blob + off[i], off[i + 1] - off[i]);
@@ -182,7 +187,7 @@ struct Cols {
 // Returns the position, inside the pre-image, of the first character of the parent_hash value
 // (past the opening quote when it is a string): what ahv_audit_sessions takes as parent_pos.
 template <class Sink>
-uint64_t emit_delta(Sink &o, const Cols &c, uint64_t i)
+AHV_INLINE uint64_t emit_delta(Sink &o, const Cols &c, uint64_t i)
 {
     LIT(o, "{\"agent_did\": ");
     c.agent_did.emit(o, i);
@@ -243,7 +248,7 @@ void parallel_for(uint64_t n, F f)
 }  // namespace
 
 extern "C" int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets, uint8_t *out_arena,
-                               uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos)
+                               uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos, uint32_t flags)
 {
     if (!cols || !out_offsets || !out_bytes) {
         ahv::set_error("invalid argument: cols / out_offsets / out_bytes is null");
@@ -266,18 +271,22 @@ extern "C" int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offs
     c.ch_content = {cols->change_content_blob, cols->change_content_off, cols->change_content_null};
     c.ch_prev = {cols->change_prev_blob, cols->change_prev_off, cols->change_prev_null};
     const uint64_t n = c.n;
-    // pass 1: sizes (out_offsets[i+1] = length of delta i), then an exclusive scan
-    out_offsets[0] = 0;
-    parallel_for(n, [&](uint64_t lo, uint64_t hi) {
-        for (uint64_t i = lo; i < hi; ++i) {
-            SinkT<false> s(nullptr);
-            const uint64_t pp = emit_delta(s, c, i);
-            out_offsets[i + 1] = s.n;
-            // a position past 4 GiB cannot be stored: UINT32_MAX - 1 is never a valid one, so it reads as "other"
-            if (out_parent_pos) out_parent_pos[i] = pp == UINT32_MAX ? UINT32_MAX : (uint32_t)std::min<uint64_t>(pp, UINT32_MAX - 1);
-        }
-    });
-    for (uint64_t i = 0; i < n; ++i) out_offsets[i + 1] += out_offsets[i];
+    // pass 1: sizes (out_offsets[i+1] = length of delta i), then an exclusive scan; skipped when the caller
+    // says out_offsets still holds the result of its size query for these columns
+    const bool have_offsets = (flags & AHV_PACK_OFFSETS_VALID) && out_arena && out_offsets[0] == 0;
+    if (!have_offsets) {
+        out_offsets[0] = 0;
+        parallel_for(n, [&](uint64_t lo, uint64_t hi) {
+            for (uint64_t i = lo; i < hi; ++i) {
+                SinkT<false> s(nullptr);
+                const uint64_t pp = emit_delta(s, c, i);
+                out_offsets[i + 1] = s.n;
+                // a position past 4 GiB cannot be stored: UINT32_MAX - 1 is never a valid one, so it reads as "other"
+                if (out_parent_pos) out_parent_pos[i] = pp == UINT32_MAX ? UINT32_MAX : (uint32_t)std::min<uint64_t>(pp, UINT32_MAX - 1);
+            }
+        });
+        for (uint64_t i = 0; i < n; ++i) out_offsets[i + 1] += out_offsets[i];
+    }
     *out_bytes = out_offsets[n];
     if (!out_arena) return AHV_OK;                       // size query
     if (arena_capacity < out_offsets[n]) {

@@ -246,8 +246,10 @@ typedef struct ahv_delta_columns {
     const uint8_t *change_prev_blob;    const uint64_t *change_prev_off;    const uint8_t *change_prev_null;
 } ahv_delta_columns;
 
+#define AHV_PACK_OFFSETS_VALID 1u   /* out_offsets (and out_parent_pos) already hold this batch's size query: only write */
 int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets /* n+1 */, uint8_t *out_arena,
-                    uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos /* n, or NULL */);
+                    uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos /* n, or NULL */,
+                    uint32_t flags);
 
 /* ------------------------------------------------------------------ liability / rings
  *
