@@ -2,6 +2,7 @@ from .delta import DeltaEngine, SemanticDelta, VFSChange
 from .commitment import CommitmentEngine, CommitmentRecord
 from .packing import ArenaBuilder, PackedSessions, canonical_preimage, classify_parent
 from .batch import BatchAuditor
+from .replay import ReplayPipeline
 
 __all__ = ["DeltaEngine", "SemanticDelta", "VFSChange", "CommitmentEngine", "CommitmentRecord",
-           "ArenaBuilder", "PackedSessions", "canonical_preimage", "classify_parent", "BatchAuditor"]
+           "ArenaBuilder", "PackedSessions", "canonical_preimage", "classify_parent", "BatchAuditor", "ReplayPipeline"]

@@ -218,9 +218,11 @@ def columns_from_deltas(deltas) -> dict:
     }
 
 
-def pack_columns(cols: dict, arena: Optional[np.ndarray] = None, want_parent_pos: bool = False):
+def pack_columns(cols: dict, arena: Optional[np.ndarray] = None, want_parent_pos: bool = False,
+                 offsets: Optional[np.ndarray] = None, parent_pos: Optional[np.ndarray] = None):
     """Canonical pre-images of ``cols['n']`` deltas via the C++ packer -> (arena u8[], offsets u64[n+1])
-    and, with ``want_parent_pos``, the uint32[n] positions of the parent values as a third element."""
+    and, with ``want_parent_pos``, the uint32[n] positions of the parent values as a third element.
+    ``arena`` / ``offsets`` / ``parent_pos`` may be caller-owned (e.g. pinned) arrays to write into."""
     lib = nat.load_library()
     keep = []
 
@@ -243,9 +245,16 @@ def pack_columns(cols: dict, arena: Optional[np.ndarray] = None, want_parent_pos
         blob, off, null = cols[nm]
         setattr(st, nm + "_blob", ptr(blob)); setattr(st, nm + "_off", ptr(off)); setattr(st, nm + "_null", ptr(null))
     n = cols["n"]
-    offsets = np.zeros(n + 1, dtype=np.uint64)
+    if offsets is None:
+        offsets = np.zeros(n + 1, dtype=np.uint64)
+    else:
+        assert offsets.dtype == np.uint64 and offsets.flags.c_contiguous and len(offsets) >= n + 1
+        offsets = offsets[: n + 1]
     nbytes = _C.c_uint64()
-    ppos = np.zeros(max(n, 1), dtype=np.uint32) if want_parent_pos else None
+    if parent_pos is not None:
+        assert parent_pos.dtype == np.uint32 and parent_pos.flags.c_contiguous and len(parent_pos) >= n
+        want_parent_pos = True
+    ppos = (parent_pos if parent_pos is not None else np.zeros(max(n, 1), dtype=np.uint32)) if want_parent_pos else None
     rc = lib.ahv_pack_deltas(_C.byref(st), offsets.ctypes.data, None, 0, _C.byref(nbytes),
                              ppos.ctypes.data if want_parent_pos else None, 0)
     if rc:
