@@ -29,63 +29,12 @@
 // written - and the warp writes back what changed.  Sessions so large that fewer than four fit a slice
 // are listed for k_slash_cascade, which then only visits that list.
 #include "ahv_internal.cuh"
+#include "slashing_core.cuh"
 
 namespace ahv {
 namespace {
 
-constexpr unsigned FULL = 0xffffffffu;
-constexpr double SIGMA_FLOOR = 0.05;              // slashing.py:54
-constexpr int MAX_CASCADE_DEPTH = 2;              // slashing.py:53
-constexpr int SLASH_WARPS = 4;
-constexpr uint32_t SLASH_SMEM_PER_WARP = 6144;    // bytes of staged session state per warp
-constexpr int LANE_WARPS = 4;                     // k_slash_lanes: warps per CTA
-constexpr uint32_t LANE_SMEM_PER_WARP = 10752;    // bytes of staged state for a group of 32 sessions (5 CTAs per SM)
-constexpr int LANE_CLIP_CACHE = 12;
-constexpr int LANE_MIN_SESSIONS = 4;              // fewer sessions than this in a run: a warp per session instead
-
-__host__ __device__ __forceinline__ uint64_t lane_group_bytes(uint64_t agents, uint64_t records)
-{
-    return 11 * agents + 3 * records + 16;      // < 65536 agents and records: 16-bit indices inside a group
-}
-
-constexpr uint8_t F_LIVE = 1, F_WAS_LIVE = 2, F_BAD_VOUCHER = 4;
-
-struct SlashArgs {
-    const uint32_t *rowptr;
-    const uint32_t *voucher;
-    uint8_t *active;
-    const int64_t *expiry;
-    int64_t now;
-    const uint64_t *sess_rp;
-    const uint64_t *ev_rp;
-    const uint32_t *ev_agent;
-    const double *ev_sigma;
-    const double *ev_omega;
-    const uint8_t *ev_depth;
-    uint64_t n_sessions;
-    double *scores;
-    uint8_t *touched;
-    ahv_slash_record *slash_log;
-    ahv_clip_record *clip_log;
-    uint32_t *slash_count;
-    uint32_t *clip_count;
-    uint8_t *status;
-    uint32_t *big_sessions;       // scratch: [0] = count, [1..] = sessions k_slash_lanes left to k_slash_cascade
-};
-
-__device__ __forceinline__ double clip_once(double x, double keep)
-{
-    const double n = __dmul_rn(x, keep);          // :95
-    return (SIGMA_FLOOR > n) ? SIGMA_FLOOR : n;   // :96  Python max(n, FLOOR): a NaN n stays
-}
-
-// vouching.py:34-38,191-196 on values already loaded (bitwise on purpose: both loads are always issued,
-// neither waits for the other)
-__device__ __forceinline__ uint32_t live_flag(uint8_t active, int64_t expiry, int64_t now)
-{
-    const uint32_t expired = (uint32_t)(expiry != AHV_EXPIRY_NONE) & (uint32_t)(now > expiry);
-    return (uint32_t)(active != 0) & (expired ^ 1u);
-}
+using namespace ahv::slashing;
 
 // Session state in global memory.  Agents and records are addressed by their index inside the session.
 struct GlobalView {
@@ -245,14 +194,14 @@ __device__ uint32_t slash_once(View &m, SessionLog &g, int lane, uint32_t v, dou
 template <class View>
 __device__ void run_events(const SlashArgs &k, View &m, SessionLog &g, int lane, uint64_t s, uint32_t n_agents)
 {
-    const double thresh = __dadd_rn(SIGMA_FLOOR, 0.01);                   // :124
+    const double thresh = add_rn(SIGMA_FLOOR, 0.01);                      // :124
     for (uint64_t ev = k.ev_rp[s]; ev < k.ev_rp[s + 1]; ++ev) {
         const uint32_t v0 = k.ev_agent[ev] - g.a_lo;
         if (v0 >= n_agents) {                     // an event naming an agent of another session
             g.status |= 1;
             continue;
         }
-        const double keep = __dsub_rn(1.0, k.ev_omega[ev]);              // (1.0 - risk_weight), :95
+        const double keep = add_rn(1.0, -k.ev_omega[ev]);                // (1.0 - risk_weight), :95
         const uint32_t depth0 = k.ev_depth ? k.ev_depth[ev] : 0u;         // the caller's cascade_depth argument (:70)
         uint32_t f_cur[MAX_CASCADE_DEPTH], f_end[MAX_CASCADE_DEPTH], f_id[MAX_CASCADE_DEPTH];
         f_cur[0] = g.n_clip;
@@ -281,122 +230,6 @@ __device__ void run_events(const SlashArgs &k, View &m, SessionLog &g, int lane,
     }
 }
 
-// One lane = one session, serial, on the group's staged state.  Indices: agents and records are
-// group-local in shared memory; `la` is the first agent of this lane's session, `ln` their number.
-struct LaneRun {
-    double *s_score;
-    uint16_t *s_rowptr;           // group-local record index
-    uint16_t *s_voucher;          // group-local agent index
-    uint8_t *s_flags;
-    uint8_t *s_touched;
-    ahv_slash_record *sl;
-    ahv_clip_record *cl;
-    uint32_t la, ln;              // this session's agents inside the group
-    uint32_t ga_lo, ge_lo;        // the group's first agent row / first record (global indices)
-    uint32_t n_slash, n_clip, status;
-    // (sigma_after, voucher) of the first LANE_CLIP_CACHE clips of the slash at cascade depth 0 / 1: what the
-    // cascade loop needs, kept in (L1-resident) local memory instead of reading the clip records back
-    double c_after[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
-    uint32_t c_voucher[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
-
-    __device__ __forceinline__ bool live(uint32_t e, uint32_t &u) const
-    {
-        u = (uint32_t)s_voucher[e] - la;
-        return (s_flags[e] & F_LIVE) && u < ln;
-    }
-    __device__ bool any_live(uint32_t v) const      // slashing.py:126-129
-    {
-        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {
-            uint32_t u;
-            if (live(e, u)) return true;
-        }
-        return false;
-    }
-    // frame: the cascade-stack slot (0 / 1) whose clips this slash produces, or -1 when it will not cascade
-    __device__ uint32_t slash(uint32_t v, double sigma_before, double keep, uint32_t depth, int32_t parent, uint32_t ev,
-                              int frame)
-    {
-        s_score[la + v] = 0.0;                    // :88
-        s_touched[la + v] = 1;
-        const uint32_t me = n_slash++, c0 = n_clip;
-        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {     // :92
-            uint32_t u;
-            if (!live(e, u)) {
-                if ((s_flags[e] & F_LIVE) && u >= ln) status |= 2;              // voucher outside the session
-                continue;
-            }
-            const double before = s_score[la + u];                              // :94
-            const double after = clip_once(before, keep);                       // :95-96
-            s_score[la + u] = after;                                            // :97
-            s_touched[la + u] = 1;
-            s_flags[e] = F_WAS_LIVE;                                            // :108 release_bond
-            if (frame >= 0 && n_clip - c0 < (uint32_t)LANE_CLIP_CACHE) {
-                c_after[frame][n_clip - c0] = after;
-                c_voucher[frame][n_clip - c0] = u;
-            }
-            ahv_clip_record *q = cl + n_clip++;                                 // :99-105
-            q->edge = ge_lo + e;
-            q->slash = me;
-            q->sigma_before = before;
-            q->sigma_after = after;
-        }
-        ahv_slash_record *r = sl + me;            // :110-119
-        r->agent = ga_lo + la + v;
-        r->parent = parent;
-        r->event = ev;
-        r->depth = depth;
-        r->clip_begin = c0;
-        r->clip_count = n_clip - c0;
-        r->sigma_before = sigma_before;
-        return me;
-    }
-    __device__ void events(const SlashArgs &k, uint64_t ev_lo, uint64_t ev_hi)
-    {
-        const double thresh = __dadd_rn(SIGMA_FLOOR, 0.01);                     // :124
-        for (uint64_t ev = ev_lo; ev < ev_hi; ++ev) {
-            const uint32_t v0 = k.ev_agent[ev] - (ga_lo + la);
-            if (v0 >= ln) {
-                status |= 1;
-                continue;
-            }
-            const double keep = __dsub_rn(1.0, k.ev_omega[ev]);
-            const uint32_t depth0 = k.ev_depth ? k.ev_depth[ev] : 0u;
-            uint32_t f_c0[MAX_CASCADE_DEPTH], f_cur[MAX_CASCADE_DEPTH], f_end[MAX_CASCADE_DEPTH], f_id[MAX_CASCADE_DEPTH];
-            int d = depth0 < (uint32_t)MAX_CASCADE_DEPTH ? 0 : -1;
-            f_c0[0] = f_cur[0] = n_clip;
-            f_id[0] = slash(v0, k.ev_sigma[ev], keep, depth0, -1, (uint32_t)ev, d);
-            f_end[0] = n_clip;
-            while (d >= 0) {                      // :122-138
-                if (f_cur[d] == f_end[d]) {
-                    --d;
-                    continue;
-                }
-                const uint32_t c = f_cur[d]++;
-                double after;
-                uint32_t u;
-                if (c - f_c0[d] < (uint32_t)LANE_CLIP_CACHE) {
-                    after = c_after[d][c - f_c0[d]];
-                    u = c_voucher[d][c - f_c0[d]];
-                } else {                          // a long row: this lane's own earlier stores
-                    after = cl[c].sigma_after;
-                    u = (uint32_t)s_voucher[cl[c].edge - ge_lo] - la;
-                }
-                if (!(after < thresh)) continue;
-                if (!any_live(u)) continue;
-                const uint32_t c0 = n_clip;
-                const bool deeper = depth0 + d + 1 < (uint32_t)MAX_CASCADE_DEPTH;
-                const uint32_t id = slash(u, after, keep, depth0 + d + 1, (int32_t)f_id[d], (uint32_t)ev, deeper ? d + 1 : -1);
-                if (deeper) {
-                    ++d;
-                    f_c0[d] = f_cur[d] = c0;
-                    f_end[d] = n_clip;
-                    f_id[d] = id;
-                }
-            }
-        }
-    }
-};
-
 __global__ void __launch_bounds__(32 * LANE_WARPS)
 k_slash_lanes(const SlashArgs k)
 {
@@ -415,62 +248,27 @@ k_slash_lanes(const SlashArgs k)
         const uint32_t my_e0 = k.rowptr[my_a0], my_e1 = k.rowptr[my_a1];
         uint32_t p = 0;
         while (p < n) {
-            // the longest run of sessions p .. q-1 whose state fits the slice (sizes grow with q: a prefix)
             const uint32_t a_lo = __shfl_sync(FULL, my_a0, p), e_lo = __shfl_sync(FULL, my_e0, p);
-            const bool fit = (uint32_t)lane >= p && (uint32_t)lane < n &&
-                             lane_group_bytes(my_a1 - a_lo, my_e1 - e_lo) <= LANE_SMEM_PER_WARP;
-            const uint32_t cnt = __popc(__ballot_sync(FULL, fit));
-            if (cnt < (n - p < (uint32_t)LANE_MIN_SESSIONS ? n - p : (uint32_t)LANE_MIN_SESSIONS)) {
-                // too few lanes would work: session p is k_slash_cascade's (a whole warp for it)
+            // a session of which fewer than LANE_MIN_SESSIONS would fit a slice is k_slash_cascade's (a whole
+            // warp for it)
+            if (lane_group_bytes(__shfl_sync(FULL, my_a1, p) - a_lo, __shfl_sync(FULL, my_e1, p) - e_lo) >
+                LANE_SMEM_PER_WARP / LANE_MIN_SESSIONS) {
                 if (lane == 0) k.big_sessions[1 + atomicAdd(k.big_sessions, 1u)] = (uint32_t)(s0 + p);
                 ++p;
                 continue;
             }
+            // the longest run of sessions p .. q-1 whose state fits the slice (sizes grow with q: a prefix)
+            const bool fit = (uint32_t)lane >= p && (uint32_t)lane < n &&
+                             lane_group_bytes(my_a1 - a_lo, my_e1 - e_lo) <= LANE_SMEM_PER_WARP;
+            const uint32_t cnt = __popc(__ballot_sync(FULL, fit));
             const uint32_t q = p + cnt;
             const uint32_t A = __shfl_sync(FULL, my_a1, q - 1) - a_lo, E = __shfl_sync(FULL, my_e1, q - 1) - e_lo;
             LaneRun r;
-            uint8_t *base = slash_smem + (size_t)wib * LANE_SMEM_PER_WARP;
-            r.s_score = reinterpret_cast<double *>(base);
-            r.s_rowptr = reinterpret_cast<uint16_t *>(r.s_score + A);
-            r.s_voucher = r.s_rowptr + (A + 1);
-            r.s_flags = reinterpret_cast<uint8_t *>(r.s_voucher + E);
-            r.s_touched = r.s_flags + E;
-#pragma unroll 8
-            for (uint32_t a = lane; a <= A; a += 32) r.s_rowptr[a] = (uint16_t)(k.rowptr[a_lo + a] - e_lo);
-#pragma unroll 8
-            for (uint32_t a = lane; a < A; a += 32) {
-                r.s_score[a] = k.scores[a_lo + a];
-                r.s_touched[a] = 0;
-            }
-#pragma unroll 8
-            for (uint32_t e = lane; e < E; e += 32) {
-                // a voucher outside the run becomes 0xffff: outside every session of the run as well
-                const uint32_t u = k.voucher[e_lo + e] - a_lo;
-                r.s_voucher[e] = (uint16_t)(u < A ? u : 0xffffu);
-                r.s_flags[e] = live_flag(k.active[e_lo + e], k.expiry[e_lo + e], k.now) ? (F_LIVE | F_WAS_LIVE) : 0;
-            }
+            stage_run(r, slash_smem + (size_t)wib * LANE_SMEM_PER_WARP, k, a_lo, A, e_lo, E, (uint32_t)lane, 32u);
             __syncwarp();
-            if ((uint32_t)lane >= p && (uint32_t)lane < q) {
-                r.la = my_a0 - a_lo;
-                r.ln = my_a1 - my_a0;
-                r.ga_lo = a_lo;
-                r.ge_lo = e_lo;
-                r.sl = k.slash_log + (ev_lo + my_e0);
-                r.cl = k.clip_log + my_e0;
-                r.n_slash = r.n_clip = r.status = 0;
-                r.events(k, ev_lo, ev_hi);
-                k.slash_count[s] = r.n_slash;
-                k.clip_count[s] = r.n_clip;
-                k.status[s] = (uint8_t)r.status;
-            }
+            if ((uint32_t)lane >= p && (uint32_t)lane < q) run_session(r, k, s, a_lo, e_lo, my_a0, my_a1, my_e0, ev_lo, ev_hi);
             __syncwarp();
-            for (uint32_t a = lane; a < A; a += 32)
-                if (r.s_touched[a]) {
-                    k.scores[a_lo + a] = r.s_score[a];
-                    k.touched[a_lo + a] = 1;
-                }
-            for (uint32_t e = lane; e < E; e += 32)
-                if (r.s_flags[e] == F_WAS_LIVE) k.active[e_lo + e] = 0;
+            write_back_run(r, k, a_lo, A, e_lo, E, (uint32_t)lane, 32u);
             __syncwarp();                         // the slice is reused by the next run
             p = q;
         }
@@ -590,12 +388,6 @@ extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
         k.big_sessions = (uint32_t *)scratch_take(ctx, 4 * (b->n_sessions + 1));
         AHV_REQUIRE(k.big_sessions, "internal: scratch too small for the session list");
         AHV_CUDA(cudaMemsetAsync(k.big_sessions, 0, 4, ctx->stream));
-        static bool attr_set[64] = {};
-        if (ctx->device >= 0 && ctx->device < 64 && !attr_set[ctx->device]) {
-            AHV_CUDA(cudaFuncSetAttribute(k_slash_lanes, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          LANE_WARPS * LANE_SMEM_PER_WARP));
-            attr_set[ctx->device] = true;
-        }
         const uint64_t groups = (b->n_sessions + 31) / 32;
         const uint64_t gwant = (groups + LANE_WARPS - 1) / LANE_WARPS;
         k_slash_lanes<<<(unsigned)(gwant < cap ? gwant : cap), 32 * LANE_WARPS, LANE_WARPS * LANE_SMEM_PER_WARP, ctx->stream>>>(k);

@@ -1,0 +1,264 @@
+// slashing_core.cuh - the per-session arithmetic and the serial (lane-per-session) walker of the
+// slashing pass, host+device so the CPU-only test harness can run the same code (tests/hostemu); the
+// product has no CPU path.  Reference: liability/slashing.py:53-141.
+#pragma once
+#include <stdint.h>
+
+#include "../../include/ahv.h"
+
+#if defined(__CUDACC__)
+#define AHV_SL_HD __host__ __device__
+#define AHV_SL_HDI __host__ __device__ __forceinline__
+#else
+#define AHV_SL_HD
+#define AHV_SL_HDI inline
+#endif
+
+namespace ahv {
+namespace slashing {
+
+constexpr unsigned FULL = 0xffffffffu;
+constexpr double SIGMA_FLOOR = 0.05;              // slashing.py:54
+constexpr int MAX_CASCADE_DEPTH = 2;              // slashing.py:53
+constexpr int SLASH_WARPS = 4;
+constexpr uint32_t SLASH_SMEM_PER_WARP = 6144;    // bytes of staged session state per warp
+constexpr int LANE_WARPS = 4;                     // k_slash_lanes: warps per CTA
+constexpr uint32_t LANE_SMEM_PER_WARP = 10752;    // bytes of staged state for a run of sessions (5 CTAs per SM)
+static_assert(LANE_WARPS * LANE_SMEM_PER_WARP <= 48 * 1024, "k_slash_lanes must fit the default dynamic shared-memory limit");
+constexpr int LANE_CLIP_CACHE = 12;
+constexpr int LANE_MIN_SESSIONS = 4;              // fewer sessions than this in a run: a warp per session instead
+
+AHV_SL_HDI uint64_t lane_group_bytes(uint64_t agents, uint64_t records)
+{
+    return 11 * agents + 3 * records + 16;      // < 65536 agents and records: 16-bit indices inside a group
+}
+
+constexpr uint8_t F_LIVE = 1, F_WAS_LIVE = 2, F_BAD_VOUCHER = 4;
+
+struct SlashArgs {
+    const uint32_t *rowptr;
+    const uint32_t *voucher;
+    uint8_t *active;
+    const int64_t *expiry;
+    int64_t now;
+    const uint64_t *sess_rp;
+    const uint64_t *ev_rp;
+    const uint32_t *ev_agent;
+    const double *ev_sigma;
+    const double *ev_omega;
+    const uint8_t *ev_depth;
+    uint64_t n_sessions;
+    double *scores;
+    uint8_t *touched;
+    ahv_slash_record *slash_log;
+    ahv_clip_record *clip_log;
+    uint32_t *slash_count;
+    uint32_t *clip_count;
+    uint8_t *status;
+    uint32_t *big_sessions;       // scratch: [0] = count, [1..] = sessions k_slash_lanes left to k_slash_cascade
+};
+
+AHV_SL_HDI double clip_once(double x, double keep)
+{
+#if defined(__CUDA_ARCH__)
+    const double n = __dmul_rn(x, keep);          // :95
+#else
+    const volatile double n0 = x * keep;
+    const double n = n0;
+#endif
+    return (SIGMA_FLOOR > n) ? SIGMA_FLOOR : n;   // :96  Python max(n, FLOOR): a NaN n stays
+}
+
+AHV_SL_HDI double add_rn(double a, double b)
+{
+#if defined(__CUDA_ARCH__)
+    return __dadd_rn(a, b);
+#else
+    const volatile double s = a + b;
+    return s;
+#endif
+}
+
+// vouching.py:34-38,191-196 on values already loaded (bitwise on purpose: both loads are always issued,
+// neither waits for the other)
+AHV_SL_HDI uint32_t live_flag(uint8_t active, int64_t expiry, int64_t now)
+{
+    const uint32_t expired = (uint32_t)(expiry != AHV_EXPIRY_NONE) & (uint32_t)(now > expiry);
+    return (uint32_t)(active != 0) & (expired ^ 1u);
+}
+
+// One lane = one session, serial, on the group's staged state.  Indices: agents and records are
+// group-local in shared memory; `la` is the first agent of this lane's session, `ln` their number.
+struct LaneRun {
+    double *s_score;
+    uint16_t *s_rowptr;           // group-local record index
+    uint16_t *s_voucher;          // group-local agent index
+    uint8_t *s_flags;
+    uint8_t *s_touched;
+    ahv_slash_record *sl;
+    ahv_clip_record *cl;
+    uint32_t la, ln;              // this session's agents inside the group
+    uint32_t ga_lo, ge_lo;        // the group's first agent row / first record (global indices)
+    uint32_t n_slash, n_clip, status;
+    // (sigma_after, voucher) of the first LANE_CLIP_CACHE clips of the slash at cascade depth 0 / 1: what the
+    // cascade loop needs, kept in (L1-resident) local memory instead of reading the clip records back
+    double c_after[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
+    uint32_t c_voucher[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
+
+    AHV_SL_HDI bool live(uint32_t e, uint32_t &u) const
+    {
+        u = (uint32_t)s_voucher[e] - la;
+        return (s_flags[e] & F_LIVE) && u < ln;
+    }
+    AHV_SL_HD bool any_live(uint32_t v) const      // slashing.py:126-129
+    {
+        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {
+            uint32_t u;
+            if (live(e, u)) return true;
+        }
+        return false;
+    }
+    // frame: the cascade-stack slot (0 / 1) whose clips this slash produces, or -1 when it will not cascade
+    AHV_SL_HD uint32_t slash(uint32_t v, double sigma_before, double keep, uint32_t depth, int32_t parent, uint32_t ev,
+                              int frame)
+    {
+        s_score[la + v] = 0.0;                    // :88
+        s_touched[la + v] = 1;
+        const uint32_t me = n_slash++, c0 = n_clip;
+        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {     // :92
+            uint32_t u;
+            if (!live(e, u)) {
+                if ((s_flags[e] & F_LIVE) && u >= ln) status |= 2;              // voucher outside the session
+                continue;
+            }
+            const double before = s_score[la + u];                              // :94
+            const double after = clip_once(before, keep);                       // :95-96
+            s_score[la + u] = after;                                            // :97
+            s_touched[la + u] = 1;
+            s_flags[e] = F_WAS_LIVE;                                            // :108 release_bond
+            if (frame >= 0 && n_clip - c0 < (uint32_t)LANE_CLIP_CACHE) {
+                c_after[frame][n_clip - c0] = after;
+                c_voucher[frame][n_clip - c0] = u;
+            }
+            ahv_clip_record *q = cl + n_clip++;                                 // :99-105
+            q->edge = ge_lo + e;
+            q->slash = me;
+            q->sigma_before = before;
+            q->sigma_after = after;
+        }
+        ahv_slash_record *r = sl + me;            // :110-119
+        r->agent = ga_lo + la + v;
+        r->parent = parent;
+        r->event = ev;
+        r->depth = depth;
+        r->clip_begin = c0;
+        r->clip_count = n_clip - c0;
+        r->sigma_before = sigma_before;
+        return me;
+    }
+    AHV_SL_HD void events(const SlashArgs &k, uint64_t ev_lo, uint64_t ev_hi)
+    {
+        const double thresh = add_rn(SIGMA_FLOOR, 0.01);                        // :124
+        for (uint64_t ev = ev_lo; ev < ev_hi; ++ev) {
+            const uint32_t v0 = k.ev_agent[ev] - (ga_lo + la);
+            if (v0 >= ln) {
+                status |= 1;
+                continue;
+            }
+            const double keep = add_rn(1.0, -k.ev_omega[ev]);                   // (1.0 - risk_weight), :95
+            const uint32_t depth0 = k.ev_depth ? k.ev_depth[ev] : 0u;
+            uint32_t f_c0[MAX_CASCADE_DEPTH], f_cur[MAX_CASCADE_DEPTH], f_end[MAX_CASCADE_DEPTH], f_id[MAX_CASCADE_DEPTH];
+            int d = depth0 < (uint32_t)MAX_CASCADE_DEPTH ? 0 : -1;
+            f_c0[0] = f_cur[0] = n_clip;
+            f_id[0] = slash(v0, k.ev_sigma[ev], keep, depth0, -1, (uint32_t)ev, d);
+            f_end[0] = n_clip;
+            while (d >= 0) {                      // :122-138
+                if (f_cur[d] == f_end[d]) {
+                    --d;
+                    continue;
+                }
+                const uint32_t c = f_cur[d]++;
+                double after;
+                uint32_t u;
+                if (c - f_c0[d] < (uint32_t)LANE_CLIP_CACHE) {
+                    after = c_after[d][c - f_c0[d]];
+                    u = c_voucher[d][c - f_c0[d]];
+                } else {                          // a long row: this lane's own earlier stores
+                    after = cl[c].sigma_after;
+                    u = (uint32_t)s_voucher[cl[c].edge - ge_lo] - la;
+                }
+                if (!(after < thresh)) continue;
+                if (!any_live(u)) continue;
+                const uint32_t c0 = n_clip;
+                const bool deeper = depth0 + d + 1 < (uint32_t)MAX_CASCADE_DEPTH;
+                const uint32_t id = slash(u, after, keep, depth0 + d + 1, (int32_t)f_id[d], (uint32_t)ev, deeper ? d + 1 : -1);
+                if (deeper) {
+                    ++d;
+                    f_c0[d] = f_cur[d] = c0;
+                    f_end[d] = n_clip;
+                    f_id[d] = id;
+                }
+            }
+        }
+    }
+};
+
+// Carve a slice for a run of A agents / E records (all sessions p .. q-1 of a group) and fill it from the
+// batch: row pointers and voucher indices become 16-bit run-local ones, live = active and not expired.
+// `lane` / `stride`: 0..31 / 32 for a warp, 0 / 1 for one host thread.
+AHV_SL_HDI void stage_run(LaneRun &r, uint8_t *base, const SlashArgs &k, uint32_t a_lo, uint32_t A, uint32_t e_lo, uint32_t E,
+                          uint32_t lane, uint32_t stride)
+{
+    r.s_score = reinterpret_cast<double *>(base);
+    r.s_rowptr = reinterpret_cast<uint16_t *>(r.s_score + A);
+    r.s_voucher = r.s_rowptr + (A + 1);
+    r.s_flags = reinterpret_cast<uint8_t *>(r.s_voucher + E);
+    r.s_touched = r.s_flags + E;
+#pragma unroll 8
+    for (uint32_t a = lane; a <= A; a += stride) r.s_rowptr[a] = (uint16_t)(k.rowptr[a_lo + a] - e_lo);
+#pragma unroll 8
+    for (uint32_t a = lane; a < A; a += stride) {
+        r.s_score[a] = k.scores[a_lo + a];
+        r.s_touched[a] = 0;
+    }
+#pragma unroll 8
+    for (uint32_t e = lane; e < E; e += stride) {
+        // a voucher outside the run becomes 0xffff: outside every session of the run as well
+        const uint32_t u = k.voucher[e_lo + e] - a_lo;
+        r.s_voucher[e] = (uint16_t)(u < A ? u : 0xffffu);
+        r.s_flags[e] = live_flag(k.active[e_lo + e], k.expiry[e_lo + e], k.now) ? (F_LIVE | F_WAS_LIVE) : 0;
+    }
+}
+
+// What changed goes back: touched scores, released bonds.
+AHV_SL_HDI void write_back_run(const LaneRun &r, const SlashArgs &k, uint32_t a_lo, uint32_t A, uint32_t e_lo, uint32_t E,
+                               uint32_t lane, uint32_t stride)
+{
+    for (uint32_t a = lane; a < A; a += stride)
+        if (r.s_touched[a]) {
+            k.scores[a_lo + a] = r.s_score[a];
+            k.touched[a_lo + a] = 1;
+        }
+    for (uint32_t e = lane; e < E; e += stride)
+        if (r.s_flags[e] == F_WAS_LIVE) k.active[e_lo + e] = 0;
+}
+
+// One session of a staged run (agents my_a0 .. my_a1, first record my_e0, events ev_lo .. ev_hi).
+AHV_SL_HDI void run_session(LaneRun &r, const SlashArgs &k, uint64_t s, uint32_t a_lo, uint32_t e_lo, uint32_t my_a0,
+                            uint32_t my_a1, uint32_t my_e0, uint64_t ev_lo, uint64_t ev_hi)
+{
+    r.la = my_a0 - a_lo;
+    r.ln = my_a1 - my_a0;
+    r.ga_lo = a_lo;
+    r.ge_lo = e_lo;
+    r.sl = k.slash_log + (ev_lo + my_e0);
+    r.cl = k.clip_log + my_e0;
+    r.n_slash = r.n_clip = r.status = 0;
+    r.events(k, ev_lo, ev_hi);
+    k.slash_count[s] = r.n_slash;
+    k.clip_count[s] = r.n_clip;
+    k.status[s] = (uint8_t)r.status;
+}
+
+}  // namespace slashing
+}  // namespace ahv

@@ -137,3 +137,53 @@ extern "C" void emu_compress_search(const uint32_t *block16, uint32_t *out16)
         for (int i = 0; i < 8; ++i) out16[8 * v + i] = st[i];
     }
 }
+
+// ---- slashing: the lane-per-session form (k_slash_lanes) run by one host thread -------------------
+// Same staging (16-bit run-local indices), same LaneRun walker, same run-cutting policy as the kernel;
+// sessions the kernel would hand to k_slash_cascade are reported in out_big (count returned).
+#include <vector>
+#include "../../agent_hypervisor_b200/csrc/slashing_core.cuh"
+extern "C" uint64_t emu_slash_lanes(const ahv_slash_batch *b, uint32_t *out_big)
+{
+    using namespace ahv::slashing;
+    SlashArgs k;
+    k.rowptr = b->rowptr; k.voucher = b->voucher; k.active = b->active; k.expiry = b->expiry; k.now = b->now;
+    k.sess_rp = b->session_agent_rowptr; k.ev_rp = b->event_rowptr; k.ev_agent = b->event_agent;
+    k.ev_sigma = b->event_sigma; k.ev_omega = b->event_omega; k.ev_depth = b->event_depth; k.n_sessions = b->n_sessions;
+    k.scores = b->scores; k.touched = b->touched; k.slash_log = b->slash_log; k.clip_log = b->clip_log;
+    k.slash_count = b->slash_count; k.clip_count = b->clip_count; k.status = b->status; k.big_sessions = nullptr;
+    std::vector<double> slice(LANE_SMEM_PER_WARP / 8 + 2);
+    uint64_t n_big = 0;
+    for (uint64_t s0 = 0; s0 < k.n_sessions; s0 += 32) {
+        const uint32_t n = (uint32_t)(k.n_sessions - s0 < 32 ? k.n_sessions - s0 : 32);
+        uint32_t p = 0;
+        while (p < n) {
+            const uint32_t a_lo = (uint32_t)k.sess_rp[s0 + p], e_lo = k.rowptr[a_lo];
+            const uint32_t a_p1 = (uint32_t)k.sess_rp[s0 + p + 1];
+            if (lane_group_bytes(a_p1 - a_lo, k.rowptr[a_p1] - e_lo) > LANE_SMEM_PER_WARP / LANE_MIN_SESSIONS) {
+                out_big[n_big++] = (uint32_t)(s0 + p);
+                ++p;
+                continue;
+            }
+            uint32_t cnt = 0;
+            while (p + cnt < n) {
+                const uint32_t a1 = (uint32_t)k.sess_rp[s0 + p + cnt + 1];
+                if (lane_group_bytes(a1 - a_lo, k.rowptr[a1] - e_lo) > LANE_SMEM_PER_WARP) break;
+                ++cnt;
+            }
+            const uint32_t q = p + cnt;
+            const uint32_t a_hi = (uint32_t)k.sess_rp[s0 + q];
+            const uint32_t A = a_hi - a_lo, E = k.rowptr[a_hi] - e_lo;
+            LaneRun r;
+            stage_run(r, reinterpret_cast<uint8_t *>(slice.data()), k, a_lo, A, e_lo, E, 0u, 1u);
+            for (uint32_t i = p; i < q; ++i) {
+                const uint64_t s = s0 + i;
+                const uint32_t my_a0 = (uint32_t)k.sess_rp[s], my_a1 = (uint32_t)k.sess_rp[s + 1];
+                run_session(r, k, s, a_lo, e_lo, my_a0, my_a1, k.rowptr[my_a0], k.ev_rp[s], k.ev_rp[s + 1]);
+            }
+            write_back_run(r, k, a_lo, A, e_lo, E, 0u, 1u);
+            p = q;
+        }
+    }
+    return n_big;
+}

@@ -133,3 +133,66 @@ def test_search_formulation_is_the_same_function(emu):
         out = np.zeros(16, np.uint32)
         emu.emu_compress_search(blk.ctypes.data_as(C.POINTER(C.c_uint32)), out.ctypes.data_as(C.POINTER(C.c_uint32)))
         assert np.array_equal(out[:8], out[8:])
+
+
+def test_slash_lane_walker_matches_reference_records(emu, slashing_golden):
+    """The code k_slash_lanes runs per lane (slashing_core.cuh: 16-bit staged runs, serial cascade with the
+    clip cache, write-back), by one host thread, against the real SlashingEngine's recorded history; sessions
+    too large for a slice are the ones the warp kernel would take."""
+    from helpers import check_slash_against_golden, slash_batch
+    from agent_hypervisor_b200 import _native as nat
+    gold = slashing_golden["cases"]
+    cases = [recipes.random_slash_case(g["seed"]) for g in gold]
+    b = slash_batch(cases)
+    A, E, S, NE = len(b["scores"]), len(b["voucher"]), len(cases), len(b["event_agent"])
+    o = dict(scores=np.array(b["scores"], copy=True), touched=np.zeros(A, np.uint8), active=np.array(b["active"], copy=True),
+             slash_log=np.zeros(NE + E, nat.SLASH_DT), clip_log=np.zeros(E, nat.CLIP_DT), slash_count=np.zeros(S, np.uint32),
+             clip_count=np.zeros(S, np.uint32), status=np.zeros(S, np.uint8))
+    sb = nat.SlashBatch()
+    sb.n_agents, sb.now, sb.n_sessions = A, int(b["now"]), S
+    keep = {k: np.ascontiguousarray(b[k]) for k in ("rowptr", "voucher", "expiry", "session_agent_rowptr", "event_rowptr",
+                                                    "event_agent", "event_sigma", "event_omega", "event_depth")}
+    for name, arr in list(keep.items()) + list(o.items()):
+        setattr(sb, name, arr.ctypes.data)
+    big = np.zeros(S, np.uint32)
+    emu.emu_slash_lanes.restype = C.c_uint64
+    n_big = emu.emu_slash_lanes(C.byref(sb), big.ctypes.data_as(C.POINTER(C.c_uint32)))
+    assert n_big == 0 and not o["status"].any()            # every golden session is small enough for a lane
+    check_slash_against_golden(cases, gold, b, (o["scores"], o["touched"], o["active"], o["slash_log"], o["clip_log"],
+                                                o["slash_count"], o["clip_count"]))
+    # long rows overflow the 12-entry clip cache and read the clip records back; big sessions are listed
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import coracle as co
+    rng = np.random.default_rng(3)
+    A2 = [3, 40, 2, 700, 5]; E2 = [60, 300, 0, 3000, 200]                    # the 700 x 3000 session cannot fit
+    srp = np.concatenate([[0], np.cumsum(A2)]).astype(np.uint64)
+    vouchee = np.concatenate([np.sort(rng.integers(0, a, e)) + int(srp[i]) for i, (a, e) in enumerate(zip(A2, E2))])
+    voucher = np.concatenate([rng.integers(0, a, e) + int(srp[i]) for i, (a, e) in enumerate(zip(A2, E2))]).astype(np.uint32)
+    rowptr = np.zeros(int(srp[-1]) + 1, np.uint32); np.add.at(rowptr, vouchee + 1, 1); rowptr = np.cumsum(rowptr).astype(np.uint32)
+    Et = int(rowptr[-1])
+    b2 = dict(rowptr=rowptr, voucher=voucher, active=np.ones(Et, np.uint8), expiry=np.full(Et, np.iinfo(np.int64).max),
+              now=0, session_agent_rowptr=srp, event_rowptr=np.arange(6, dtype=np.uint64), event_agent=srp[:-1].astype(np.uint32),
+              event_sigma=np.full(5, 0.5), event_omega=np.full(5, 0.95), scores=rng.random(int(srp[-1])))
+    want = co.slash_cascade(*[b2[k] for k in ("rowptr", "voucher", "active", "expiry", "now", "session_agent_rowptr",
+                                              "event_rowptr", "event_agent", "event_sigma", "event_omega", "scores")])
+    o2 = dict(scores=np.array(b2["scores"], copy=True), touched=np.zeros(len(b2["scores"]), np.uint8), active=np.array(b2["active"], copy=True),
+              slash_log=np.zeros(5 + Et, nat.SLASH_DT), clip_log=np.zeros(Et, nat.CLIP_DT), slash_count=np.zeros(5, np.uint32),
+              clip_count=np.zeros(5, np.uint32), status=np.zeros(5, np.uint8))
+    sb2 = nat.SlashBatch()
+    sb2.n_agents, sb2.now, sb2.n_sessions = len(b2["scores"]), 0, 5
+    keep2 = {k: np.ascontiguousarray(b2[k]) for k in ("rowptr", "voucher", "expiry", "session_agent_rowptr", "event_rowptr",
+                                                      "event_agent", "event_sigma", "event_omega")}
+    for name, arr in list(keep2.items()) + list(o2.items()):
+        setattr(sb2, name, arr.ctypes.data)
+    sb2.event_depth = None
+    n_big = emu.emu_slash_lanes(C.byref(sb2), big.ctypes.data_as(C.POINTER(C.c_uint32)))
+    assert n_big == 1 and big[0] == 3
+    for s in (0, 1, 2, 4):
+        assert o2["slash_count"][s] == want[5][s] and o2["clip_count"][s] == want[6][s]
+        a0, a1 = int(srp[s]), int(srp[s + 1])
+        assert np.array_equal(o2["scores"][a0:a1], want[0][a0:a1]) and np.array_equal(o2["touched"][a0:a1], want[1][a0:a1])
+        e0, e1 = int(rowptr[a0]), int(rowptr[a1])
+        assert np.array_equal(o2["active"][e0:e1], want[2][e0:e1])
+        assert o2["clip_log"][e0:e0 + int(want[6][s])].tobytes() == want[4][e0:e0 + int(want[6][s])].tobytes()
+    assert int(want[6][0]) > 12                                              # the cache did overflow
