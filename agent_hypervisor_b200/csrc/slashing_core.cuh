@@ -110,7 +110,7 @@ struct LaneRun {
         u = (uint32_t)s_voucher[e] - la;
         return (s_flags[e] & F_LIVE) && u < ln;
     }
-    AHV_SL_HD bool any_live(uint32_t v) const      // slashing.py:126-129
+    AHV_SL_HDI bool any_live(uint32_t v) const      // slashing.py:126-129
     {
         for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {
             uint32_t u;
@@ -119,7 +119,7 @@ struct LaneRun {
         return false;
     }
     // frame: the cascade-stack slot (0 / 1) whose clips this slash produces, or -1 when it will not cascade
-    AHV_SL_HD uint32_t slash(uint32_t v, double sigma_before, double keep, uint32_t depth, int32_t parent, uint32_t ev,
+    AHV_SL_HDI uint32_t slash(uint32_t v, double sigma_before, double keep, uint32_t depth, int32_t parent, uint32_t ev,
                               int frame)
     {
         s_score[la + v] = 0.0;                    // :88
@@ -156,7 +156,7 @@ struct LaneRun {
         r->sigma_before = sigma_before;
         return me;
     }
-    AHV_SL_HD void events(const SlashArgs &k, uint64_t ev_lo, uint64_t ev_hi)
+    AHV_SL_HDI void events(const SlashArgs &k, uint64_t ev_lo, uint64_t ev_hi)
     {
         const double thresh = add_rn(SIGMA_FLOOR, 0.01);                        // :124
         for (uint64_t ev = ev_lo; ev < ev_hi; ++ev) {
