@@ -197,7 +197,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "verified": bool(ok),
     }
-    print(json.dumps(line))
+    emit_line(line)
     return 0
 
 
@@ -439,13 +439,33 @@ def run_cuda(args):
                 "api": "ahv_audit_sessions (host-pointer C ABI, pinned host buffers; commit pass + verify pass on one upload, pipelined in session chunks)"},
         "verified": verified, "device": info,
     }
-    print(json.dumps(line))
+    emit_line(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
     return 0 if verified else 1
 
 
+_RESULT_OUT = None
+
+
+def claim_stdout() -> None:
+    """Keep the real stdout for the one JSON line; anything a library prints to fd 1 from here on (NCCL's
+    version banner at NCCL_DEBUG=VERSION, for one) lands on stderr instead."""
+    global _RESULT_OUT
+    if _RESULT_OUT is None:
+        sys.stdout.flush()
+        _RESULT_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit_line(line: dict) -> None:
+    out = _RESULT_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
