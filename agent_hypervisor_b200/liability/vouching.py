@@ -216,3 +216,31 @@ class VouchingEngine:
                                                      np.asarray(risk_weights, dtype=np.float64), cons, ring_in)
         return {"sigma_eff": se, "ring": ring, "demote": demote,
                 "near_threshold": [agents[i] for i in np.nonzero(near)[0]]}
+
+    def compute_sigma_eff_many(self, requests: Sequence[tuple], now: Optional[datetime] = None,
+                               ctx: Optional[nat.Context] = None) -> np.ndarray:
+        """``[compute_sigma_eff(vouchee, session, sigma, omega) for ...]`` (vouching.py:128-151) for requests
+        that may name different sessions, in one launch: row r of the CSR holds the records whose
+        (vouchee, session) is request r's, in insertion order.  requests: (vouchee_did, session_id,
+        vouchee_sigma, risk_weight)."""
+        ctx = ctx or nat.get_context()
+        index: dict = {}
+        for r, (did, sid, _, _) in enumerate(requests):
+            index.setdefault((did, sid), []).append(r)
+        rows: list[list] = [[] for _ in requests]
+        for v in self._vouches.values():                  # dict order == insertion order
+            for r in index.get((v.vouchee_did, v.session_id), ()):
+                rows[r].append(v)
+        rowptr = np.zeros(len(requests) + 1, dtype=np.uint32)
+        if requests:
+            np.cumsum([len(r) for r in rows], out=rowptr[1:])
+        flat = [v for r in rows for v in r]
+        bonded = np.array([v.bonded_amount for v in flat], dtype=np.float64)
+        active = np.array([1 if v.is_active else 0 for v in flat], dtype=np.uint8)
+        expiry = np.array([nat.EXPIRY_NONE if v.expiry is None else _to_us(v.expiry) for v in flat], dtype=np.int64)
+        A = len(requests)
+        se, _, _, _ = ctx.sigma_eff_rings(rowptr, bonded, active, expiry, _to_us(now or datetime.now(timezone.utc)),
+                                          np.array([q[2] for q in requests], dtype=np.float64),
+                                          np.array([q[3] for q in requests], dtype=np.float64),
+                                          np.zeros(A, np.uint8), np.full(A, 3, np.uint8))
+        return se

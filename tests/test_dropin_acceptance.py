@@ -307,3 +307,29 @@ def test_commitment_verify_batch_matches_per_session_verify():
     got = ce.verify_batch([e.session_id for e in engines], engines)
     assert got == want
     assert got == [False, True, True, True, True, False, True, False, True, True, True, False]
+
+
+def test_sigma_eff_many_sessions_one_launch(liability_golden):
+    """compute_sigma_eff_many over requests from different sessions == the single calls, and == the real
+    engine's recorded values for the golden graphs (tests/golden/liability_golden.json)."""
+    from datetime import datetime, timedelta, timezone
+    import recipes
+    from agent_hypervisor_b200 import VouchingEngine, VouchRecord
+    now = datetime.now(timezone.utc)
+    ve = VouchingEngine()
+    reqs, want = [], []
+    for gi, g in enumerate(liability_golden["graphs"][:4]):
+        rg = recipes.random_vouch_graph(g["seed"], g["A"], g["E"])
+        for k, (a, b, vs, pct, active, ek) in enumerate(rg["edges"]):
+            exp = None if ek == 0 else (now + timedelta(days=3650) if ek == 1 else now - timedelta(days=3650))
+            vid = f"vouch:{gi}:{k}"
+            ve._vouches[vid] = VouchRecord(vouch_id=vid, voucher_did=f"did:{a}", vouchee_did=f"did:{b}", session_id=f"s{gi}",
+                                           bonded_sigma_pct=pct, bonded_amount=vs * pct, expiry=exp, is_active=active)
+        for i in range(g["A"]):
+            reqs.append((f"did:{i}", f"s{gi}", rg["sigma"][i], rg["omega"][i]))
+            want.append(float.fromhex(g["sigma_eff"][i]))
+    order = list(range(len(reqs)))[::-1][::3] + list(range(len(reqs)))       # interleaved sessions, repeats
+    got = ve.compute_sigma_eff_many([reqs[i] for i in order])
+    assert [float(x) for x in got] == [want[i] for i in order]
+    assert ve.compute_sigma_eff(*reqs[7]) == want[7]
+    assert len(ve.compute_sigma_eff_many([])) == 0
