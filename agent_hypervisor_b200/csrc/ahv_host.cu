@@ -2,6 +2,8 @@
 // device-pointer entry point, copy results back, synchronise.  These are what the Python
 // shim (agent_hypervisor_b200/_native.py) binds; the reference-side call each replaces is
 // cited in include/ahv.h.
+#include <vector>
+
 #include "ahv_internal.cuh"
 
 using namespace ahv;
@@ -226,9 +228,10 @@ int ahv_verify_chains(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offset
 
 // Commit + verify of one batch on ONE upload: leaf digests and Merkle roots (audit/delta.py:63,
 // 117-134), then a full verify pass (re-hash, parent links, root rebuild and compare against the
-// roots just committed; audit/delta.py:136-152, audit/commitment.py:59-64).  For fixed-size deltas
-// in uniform sessions the batch is cut into session chunks and pipelined: chunk k+1 is copied in
-// while chunk k is hashed and chunk k-1's results are copied out (three streams, PCIe full duplex).
+// roots just committed; audit/delta.py:136-152, audit/commitment.py:59-64).  A batch of at least 64
+// sessions and 8 MB is cut into session chunks and pipelined: chunk k+1 is copied in while chunk k is
+// hashed and chunk k-1's results are copied out (three streams, PCIe full duplex); ragged sessions get
+// per-chunk row pointers relative to the chunk's first leaf.
 int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
                        const uint8_t *parents, const uint8_t *kind, const uint32_t *parent_pos,
                        const uint64_t *rowptr, uint64_t S, uint64_t uniform, uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty,
@@ -254,7 +257,7 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         return AHV_OK;
     }
     AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(8 * (S + 1)) + 2 * p256(32 * n) + p256(n) + p256(4 * n) +
-                                2 * p256(32 * S) + 3 * p256(S) + p256(8 * S)));
+                                2 * p256(32 * S) + 3 * p256(S) + p256(8 * S) + p256(8 * (S + 64))));
     uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);
     uint32_t *d_pos = from_pos ? (uint32_t *)io_take(ctx, 4 * n) : nullptr;
     uint64_t *d_off = offsets ? (uint64_t *)io_take(ctx, 8 * (n + 1)) : nullptr;
@@ -274,7 +277,7 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         return AHV_E_NOMEM;
     }
 
-    const bool pipelined = uniform && !offsets && fixed_len > 0 && S >= 64;
+    const bool pipelined = S >= 64 && ab >= (8ull << 20);      // worth overlapping: many sessions, megabytes to move
     if (!pipelined) {
         cudaStream_t st = ctx->stream;
         AHV_CUDA(cudaMemcpyAsync(d_arena, arena, ab, cudaMemcpyHostToDevice, st));
@@ -328,36 +331,67 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         AHV_CUDA(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
         ev.n = k + 1;
     }
+    // Ragged sessions: chunk k's tree works on ITS digests, so it needs row pointers relative to its first
+    // leaf; they are laid out chunk after chunk (each with its own end entry) and uploaded with the chunk.
+    std::vector<uint64_t> rel;
+    uint64_t *d_rel = nullptr;
+    if (!uniform) {
+        rel.resize(S + (size_t)nchunk);
+        d_rel = (uint64_t *)io_take(ctx, 8 * (S + (size_t)nchunk));
+        if (!d_rel) {
+            set_error("internal: staging slab too small");
+            return AHV_E_NOMEM;
+        }
+    }
     // (the first chunk may grow the scratch slab, which synchronises once; later chunks reuse it)
     int rc = AHV_OK;
     for (int k = 0; k < nchunk && rc == AHV_OK; ++k) {
         const uint64_t s0 = (uint64_t)k * per, s1 = (s0 + per < S) ? s0 + per : S;
         if (s0 >= s1) { nchunk = k; break; }
-        const uint64_t Sc = s1 - s0, l0 = s0 * uniform, nc = Sc * uniform, b0 = l0 * fixed_len, bc = nc * fixed_len;
+        const uint64_t Sc = s1 - s0;
+        const uint64_t l0 = uniform ? s0 * uniform : rowptr[s0], l1 = uniform ? s1 * uniform : rowptr[s1], nc = l1 - l0;
+        const uint64_t b0 = offsets ? offsets[l0] : l0 * fixed_len, b1 = offsets ? offsets[l1] : l1 * fixed_len, bc = b1 - b0;
         cudaStream_t hs = ctx->copy_stream;
-        AHV_CUDA(cudaMemcpyAsync(d_arena + b0, arena + b0, bc, cudaMemcpyHostToDevice, hs));
-        if (from_pos) {
-            AHV_CUDA(cudaMemcpyAsync(d_pos + l0, parent_pos + l0, 4 * nc, cudaMemcpyHostToDevice, hs));
-        } else {
-            AHV_CUDA(cudaMemcpyAsync(d_par + 32 * l0, parents + 32 * l0, 32 * nc, cudaMemcpyHostToDevice, hs));
-            AHV_CUDA(cudaMemcpyAsync(d_kind + l0, kind + l0, nc, cudaMemcpyHostToDevice, hs));
+        if (bc) AHV_CUDA(cudaMemcpyAsync(d_arena + b0, arena + b0, bc, cudaMemcpyHostToDevice, hs));
+        if (offsets) {
+            // entry l0 is already there (it is the previous chunk's last entry), except for the first chunk
+            const uint64_t f = k == 0 ? l0 : l0 + 1;
+            if (l1 + 1 > f) AHV_CUDA(cudaMemcpyAsync(d_off + f, offsets + f, 8 * (l1 + 1 - f), cudaMemcpyHostToDevice, hs));
+        }
+        uint64_t *d_rp_k = nullptr;
+        if (!uniform) {
+            uint64_t *h = rel.data() + s0 + k;
+            for (uint64_t s = 0; s <= Sc; ++s) h[s] = rowptr[s0 + s] - l0;
+            d_rp_k = d_rel + s0 + k;
+            AHV_CUDA(cudaMemcpyAsync(d_rp_k, h, 8 * (Sc + 1), cudaMemcpyHostToDevice, hs));
+        }
+        if (nc) {
+            if (from_pos) {
+                AHV_CUDA(cudaMemcpyAsync(d_pos + l0, parent_pos + l0, 4 * nc, cudaMemcpyHostToDevice, hs));
+            } else {
+                AHV_CUDA(cudaMemcpyAsync(d_par + 32 * l0, parents + 32 * l0, 32 * nc, cudaMemcpyHostToDevice, hs));
+                AHV_CUDA(cudaMemcpyAsync(d_kind + l0, kind + l0, nc, cudaMemcpyHostToDevice, hs));
+            }
         }
         AHV_CUDA(cudaEventRecord(ev_in[k], hs));
         AHV_CUDA(cudaStreamWaitEvent(ctx->stream, ev_in[k], 0));
-        if (from_pos)
-            rc = ahv_extract_parents_dev(ctx, d_arena + b0, bc, nullptr, fixed_len, d_pos + l0, nc, d_par + 32 * l0, d_kind + l0);
+        // byte offsets stay absolute (base d_arena); with fixed-size deltas the chunk's own base is passed
+        const uint8_t *a_k = offsets ? d_arena : d_arena + b0;
+        const uint64_t *off_k = offsets ? d_off + l0 : nullptr;
+        if (from_pos && nc)
+            rc = ahv_extract_parents_dev(ctx, a_k, ab, off_k, fixed_len, d_pos + l0, nc, d_par + 32 * l0, d_kind + l0);
         if (rc != AHV_OK) break;
-        rc = ahv_commit_dev(ctx, d_arena + b0, bc, nullptr, fixed_len, nullptr, Sc, nc, uniform, maxl, d_dig + 32 * l0,
+        rc = ahv_commit_dev(ctx, a_k, ab, off_k, fixed_len, d_rp_k, Sc, nc, uniform, maxl, d_dig + 32 * l0,
                             d_roots + 32 * s0, d_empty + s0);
         if (rc == AHV_OK)
-            rc = ahv_verify_chains_dev(ctx, d_arena + b0, bc, nullptr, fixed_len, d_par + 32 * l0, d_kind + l0, nullptr, Sc,
-                                       nc, uniform, maxl, d_roots + 32 * s0, d_verdict + s0, d_fb + s0, nullptr,
-                                       d_roots_v + 32 * s0, d_match + s0);
+            rc = ahv_verify_chains_dev(ctx, a_k, ab, off_k, fixed_len, d_par + 32 * l0, d_kind + l0, d_rp_k, Sc, nc, uniform,
+                                       maxl, d_roots + 32 * s0, d_verdict + s0, d_fb + s0, nullptr, d_roots_v + 32 * s0,
+                                       d_match + s0);
         if (rc != AHV_OK) break;
         AHV_CUDA(cudaEventRecord(ev_done[k], ctx->stream));
         cudaStream_t ds = ctx->d2h_stream;
         AHV_CUDA(cudaStreamWaitEvent(ds, ev_done[k], 0));
-        if (out_digests) AHV_CUDA(cudaMemcpyAsync(out_digests + 32 * l0, d_dig + 32 * l0, 32 * nc, cudaMemcpyDeviceToHost, ds));
+        if (out_digests && nc) AHV_CUDA(cudaMemcpyAsync(out_digests + 32 * l0, d_dig + 32 * l0, 32 * nc, cudaMemcpyDeviceToHost, ds));
         AHV_CUDA(cudaMemcpyAsync(out_roots + 32 * s0, d_roots + 32 * s0, 32 * Sc, cudaMemcpyDeviceToHost, ds));
         if (out_empty) AHV_CUDA(cudaMemcpyAsync(out_empty + s0, d_empty + s0, Sc, cudaMemcpyDeviceToHost, ds));
         AHV_CUDA(cudaMemcpyAsync(out_verdict + s0, d_verdict + s0, Sc, cudaMemcpyDeviceToHost, ds));

@@ -180,9 +180,10 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
  * ahv_audit_sessions: ahv_commit followed by ahv_verify_chains against the roots just committed, on a
  * single upload of the batch (what an auditor does when sessions arrive from the host: terminate_session's
  * root, core.py:204, then verify_chain, audit/delta.py:136-152, then CommitmentEngine.verify,
- * audit/commitment.py:59-64).  Both device passes run in full (the verify pass re-hashes).  Fixed-size
- * deltas in uniform sessions are pipelined in session chunks (copy-in / hash / copy-out overlap); pass
- * pinned host buffers (ahv_host_alloc) for that overlap to happen.  Host pointers only.
+ * audit/commitment.py:59-64).  Both device passes run in full (the verify pass re-hashes).  Batches of
+ * at least 64 sessions and 8 MB are pipelined in session chunks (copy-in / hash / copy-out overlap), for
+ * fixed-size and variable-length deltas, uniform and ragged sessions alike; pass pinned host buffers
+ * (ahv_host_alloc) for that overlap to happen.  Host pointers only.
  * The claimed parents come either as the side arrays (parent_digests + parent_kind) or, with both NULL,
  * as parent_pos[n]: the byte position, inside each pre-image, of the parent_hash value's first character
  * (UINT32_MAX where the value is null); the library then reads the parents out of the pre-images on the

@@ -370,6 +370,50 @@ def test_parents_read_from_preimages(ctx):
         ctx.audit_sessions(p.arena, p.offsets, None, None, p.session_rowptr)
 
 
+def test_audit_sessions_ragged_pipelined(ctx):
+    """ahv_audit_sessions on a batch large enough to be pipelined (>= 64 sessions, >= 8 MB) with variable-length
+    messages and ragged sessions (empty ones included): chunked upload / per-chunk relative row pointers give
+    the same digests, roots, verdicts and first-bad indices as the C restatement; then the same arena through
+    the offsets + parent_pos form against the fixed-size fast path."""
+    rng = np.random.default_rng(77)
+    S = 2500
+    counts = rng.integers(0, 41, S); counts[[0, 17, S - 1]] = 0
+    rp = np.zeros(S + 1, np.uint64); rp[1:] = np.cumsum(counts)
+    n = int(rp[-1])
+    lens = rng.integers(1, 500, n)
+    offs = np.zeros(n + 1, np.uint64); offs[1:] = np.cumsum(lens)
+    arena = rng.integers(0, 256, int(offs[-1]), dtype=np.uint8)
+    assert arena.nbytes >= (8 << 20)
+    digs = co.sha256_batch(arena, offs)
+    par = np.zeros((n, 32), np.uint8); par[1:] = digs[:-1]
+    kind = np.ones(n, np.uint8)
+    first = rp[:-1][counts > 0].astype(np.int64)
+    kind[first] = 0; par[first] = 0                     # first delta of a session: parent None
+    bad_sessions = [5, 1200, S - 2]
+    for s in bad_sessions:                              # break one link in the middle of these sessions
+        if counts[s] >= 3:
+            par[int(rp[s]) + 2, 0] ^= 1
+    o = ctx.audit_sessions(arena, offs, par, kind, rp)
+    want_r, want_e = co.merkle_roots(digs, rp)
+    v, fb, _ = co.verify_chains(arena, offs, par, kind, rp)
+    assert np.array_equal(o["digests"], digs) and np.array_equal(o["roots"], want_r) and np.array_equal(o["empty"], want_e)
+    assert np.array_equal(o["verdict"], v) and np.array_equal(o["first_bad"], fb)
+    assert np.array_equal(o["root_match"], 1 - want_e)
+    assert set(np.nonzero(o["verdict"] == 0)[0]) == {s for s in bad_sessions if counts[s] >= 3}
+    # fixed-size content given as a ragged batch (offsets + row pointers + parent positions)
+    S2, L = 1500, 64
+    a2 = ctx.host_alloc(S2 * L * 256)
+    o2, hexpos, rp2 = workloads.config2_fill(a2, 11, S2, L)
+    ctx.chain_capture(a2, o2, hexpos, rp2)
+    a2[(700 * L + 9) * 256 + 30] ^= 2
+    fast = ctx.audit_sessions(a2, None, None, None, None, fixed_len=256, uniform_leaves=L, n_sessions=S2, parent_pos=hexpos)
+    slow = ctx.audit_sessions(a2, o2, None, None, rp2, parent_pos=hexpos)
+    for k in ("digests", "roots", "empty", "verdict", "first_bad", "root_match"):
+        assert np.array_equal(fast[k], slow[k]), k
+    assert list(np.nonzero(slow["verdict"] == 0)[0]) == [700] and slow["first_bad"][700] == 10
+    ctx.host_free(a2)
+
+
 def test_chain_capture_vs_python_chain(ctx):
     sessions = [recipes.golden_session(n) for n in (0, 1, 2, 5, 33)]
     blobs, offs, hexpos, rp = [], [0], [], [0]
