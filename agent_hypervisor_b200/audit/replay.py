@@ -81,6 +81,14 @@ class ReplayPipeline:
             nxt = next(it)
         except StopIteration:
             return
+        self.ctx.set_option("blocking_sync", 1)     # the host cores belong to the packer while the GPU works
+        try:
+            yield from self._run(it, nxt, copy)
+        finally:
+            self.ctx.set_option("blocking_sync", 0)
+
+    def _run(self, it, nxt, copy: bool) -> Iterator[dict]:
+        k = 0
         fut = self._pool.submit(self._pack, k, *nxt)
         while fut is not None:
             n, S, arena, offsets, ppos = fut.result()

@@ -144,6 +144,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_compress = 1;
     c->opt_sigma_variant = 1;
     c->opt_slash_variant = 0;
+    c->opt_blocking_sync = 0;
     *out_ctx = c;
     return AHV_OK;
 }
@@ -287,6 +288,7 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
         AHV_REQUIRE(value == 64 || value == 128 || value == 256, "block must be 64/128/256");
         ctx->opt_block = value;
     } else if (!strcmp(key, "fixed_variant")) ctx->opt_fixed_variant = value;
+    else if (!strcmp(key, "blocking_sync")) ctx->opt_blocking_sync = value != 0;
     else if (!strcmp(key, "slash_variant")) {
         AHV_REQUIRE(value >= 0 && value <= 2, "slash_variant must be 0, 1 or 2");
         ctx->opt_slash_variant = value;

@@ -398,6 +398,15 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         if (out_first_bad) AHV_CUDA(cudaMemcpyAsync(out_first_bad + s0, d_fb + s0, 8 * Sc, cudaMemcpyDeviceToHost, ds));
         if (out_match) AHV_CUDA(cudaMemcpyAsync(out_match + s0, d_match + s0, Sc, cudaMemcpyDeviceToHost, ds));
     }
+    // Option blocking_sync: wait without spinning when the host cores are busy packing the next batch (the copy-out
+    // stream is the last link of every chunk's chain, so one blocking event on it covers all three streams).
+    if (rc == AHV_OK && ctx->opt_blocking_sync) {
+        cudaEvent_t ev_end;
+        if (cudaEventCreateWithFlags(&ev_end, cudaEventBlockingSync | cudaEventDisableTiming) == cudaSuccess) {
+            if (cudaEventRecord(ev_end, ctx->d2h_stream) == cudaSuccess) cudaEventSynchronize(ev_end);
+            cudaEventDestroy(ev_end);
+        }
+    }
     cudaStreamSynchronize(ctx->copy_stream);
     cudaStreamSynchronize(ctx->stream);
     cudaError_t e = cudaStreamSynchronize(ctx->d2h_stream);

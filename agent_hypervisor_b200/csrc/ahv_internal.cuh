@@ -32,6 +32,7 @@ struct ahv_ctx {
     int64_t opt_sort;          // 1: length-sort variable-length batches (default 1)
     int64_t opt_block;         // threads per block for SHA kernels (default 128)
     int64_t opt_fixed_variant; // 0: direct LDG.128, 1: smem-staged (cp.async)
+    int64_t opt_blocking_sync; // 1: ahv_audit_sessions sleeps on an event instead of spinning while the pipeline drains (default 0)
     int64_t opt_slash_variant; // 0: sessions that fit are staged in shared memory (default), 1: always global memory
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions

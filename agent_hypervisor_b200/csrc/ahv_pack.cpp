@@ -14,8 +14,17 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 #include <vector>
+
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
+#include <unistd.h>
 
 #include "../../include/ahv.h"
 
@@ -66,7 +75,25 @@ AHV_INLINE void put_json_string(Sink &o, const uint8_t *s, uint64_t len)
     for (uint64_t i = 0; i < len;) {
         // run of characters the encoder passes through unchanged
         uint64_t j = i;
+#if defined(__SSE2__)
+        // 16 bytes at a time: a byte is special when < 0x20, >= 0x7f (also every non-ASCII byte), '"' or '\\'
+        while (j + 16 <= len) {
+            const __m128i v = _mm_loadu_si128(reinterpret_cast<const __m128i *>(s + j));
+            const __m128i lo = _mm_cmplt_epi8(_mm_xor_si128(v, _mm_set1_epi8((char)0x80)), _mm_set1_epi8((char)(0x20 ^ 0x80)));
+            const __m128i hi = _mm_cmpgt_epi8(_mm_xor_si128(v, _mm_set1_epi8((char)0x80)), _mm_set1_epi8((char)(0x7e ^ 0x80)));
+            const __m128i q = _mm_or_si128(_mm_cmpeq_epi8(v, _mm_set1_epi8('"')), _mm_cmpeq_epi8(v, _mm_set1_epi8('\\')));
+            const int m = _mm_movemask_epi8(_mm_or_si128(_mm_or_si128(lo, hi), q));
+            if (m) {
+                j += (uint64_t)__builtin_ctz((unsigned)m);
+                goto run_done;
+            }
+            j += 16;
+        }
+#endif
         while (j < len && s[j] >= 0x20 && s[j] < 0x7f && s[j] != '"' && s[j] != '\\') ++j;
+#if defined(__SSE2__)
+    run_done:
+#endif
         if (j > i) {
             o.lit(s + i, j - i);
             i = j;
@@ -228,21 +255,105 @@ AHV_INLINE uint64_t emit_delta(Sink &o, const Cols &c, uint64_t i)
     return ppos;
 }
 
+// Worker threads that stay around between calls (a replay packs chunk after chunk; starting and joining 16
+// threads per pass costs about as much as packing 50 000 deltas).  One job at a time; the pool is rebuilt
+// in a forked child, whose copy has no threads.
+class Pool {
+public:
+    // One pool per process.  A forked child gets a NEW one: the parent's threads do not exist there and the
+    // copied mutexes / condition variables may hold waiter state, so nothing of the old object is touched
+    // again (it is left behind, like the pool itself at exit: the workers just end with the process).
+    static Pool &get()
+    {
+        static std::mutex guard;
+        static Pool *pool = nullptr;
+        static pid_t owner = 0;
+        std::lock_guard<std::mutex> lk(guard);
+        if (!pool || owner != getpid()) {
+            pool = new Pool();
+            owner = getpid();
+        }
+        return *pool;
+    }
+    // f(lo, hi) over [0, n) in blocks handed out on demand (a worker that loses its core to another thread
+    // of the process then only delays one block, not a fixed share); returns when every block is done
+    void run(uint64_t n, const std::function<void(uint64_t, uint64_t)> &f)
+    {
+        std::lock_guard<std::mutex> one_job(job_mutex_);
+        ensure_threads();
+        const unsigned t = (unsigned)workers_.size() + 1;                 // the caller works too
+        if (n < 4096 || t == 1) {
+            f(0, n);
+            return;
+        }
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            f_ = &f;
+            n_ = n;
+            grain_ = std::max<uint64_t>(1024, n / (8ull * t));
+            next_.store(0, std::memory_order_relaxed);
+            pending_ = t - 1;
+            ++generation_;
+        }
+        cv_.notify_all();
+        blocks(n, grain_, f);
+        std::unique_lock<std::mutex> lk(m_);
+        done_.wait(lk, [&] { return pending_ == 0; });
+        f_ = nullptr;
+    }
+
+private:
+    void blocks(uint64_t n, uint64_t grain, const std::function<void(uint64_t, uint64_t)> &f)
+    {
+        for (;;) {
+            const uint64_t lo = next_.fetch_add(grain, std::memory_order_relaxed);
+            if (lo >= n) return;
+            f(lo, std::min<uint64_t>(n, lo + grain));
+        }
+    }
+    void ensure_threads()
+    {
+        if (started_) return;
+        started_ = true;
+        unsigned t = std::thread::hardware_concurrency();
+        if (t == 0) t = 1;
+        t = std::min(t, 64u);
+        const uint64_t gen = generation_;
+        for (unsigned k = 0; k + 1 < t; ++k) workers_.emplace_back([this, k, gen] { loop(k, gen); });
+    }
+    void loop(unsigned /*k*/, uint64_t seen)
+    {
+        for (;;) {
+            const std::function<void(uint64_t, uint64_t)> *f;
+            uint64_t n, grain;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [&] { return stop_ || generation_ != seen; });
+                if (stop_) return;
+                seen = generation_;
+                f = f_;
+                n = n_;
+                grain = grain_;
+            }
+            blocks(n, grain, *f);
+            std::lock_guard<std::mutex> lk(m_);
+            if (--pending_ == 0) done_.notify_one();
+        }
+    }
+    std::mutex job_mutex_, m_;
+    std::condition_variable cv_, done_;
+    std::vector<std::thread> workers_;
+    const std::function<void(uint64_t, uint64_t)> *f_ = nullptr;
+    uint64_t n_ = 0, grain_ = 0, generation_ = 0;
+    std::atomic<uint64_t> next_{0};
+    unsigned pending_ = 0;
+    bool started_ = false, stop_ = false;
+};
+
 template <class F>
 void parallel_for(uint64_t n, F f)
 {
-    unsigned t = std::thread::hardware_concurrency();
-    if (t == 0) t = 1;
-    if (n < 4096 || t == 1) { f(0, n); return; }
-    t = (unsigned)std::min<uint64_t>(t, 64);
-    std::vector<std::thread> th;
-    const uint64_t per = (n + t - 1) / t;
-    for (unsigned k = 0; k < t; ++k) {
-        const uint64_t lo = k * per, hi = std::min<uint64_t>(n, lo + per);
-        if (lo >= hi) break;
-        th.emplace_back([=] { f(lo, hi); });
-    }
-    for (auto &x : th) x.join();
+    Pool::get().run(n, std::function<void(uint64_t, uint64_t)>(f));
 }
 
 }  // namespace

@@ -381,7 +381,10 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "fixed_variant" 0/1/2 fixed-size leaf kernel: direct 16-byte loads (default) / cp.async staged / TMA bulk-copy staged
  *   "compress" 0/1      plain additions / scaled-sum compression with additions on the FMA pipe (default 1)
  *   "top_max" 0,2..256  level width at which a session's tree is finished in one warp/CTA (0 = auto)
- *   "slash_variant" 0/1 slashing: sessions that fit are staged in shared memory (default 0) / always global memory
+ *   "blocking_sync" 0/1 ahv_audit_sessions: spin (default 0, lowest latency) / sleep on an event while its pipeline
+ *                   drains, leaving the host cores to a packer thread (1; what ReplayPipeline sets)
+ *   "slash_variant" 0/1/2 slashing: lane per small session + warp per larger one (default 0) / warp per session on
+ *                   global memory only (1) / warp per session, staged in shared memory where it fits (2)
  *   "sigma_variant" 0/1 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);

@@ -243,3 +243,32 @@ def test_install_rebinds_reference_modules():
         sys.path.remove(ref)
         for k in [k for k in sys.modules if k == "hypervisor" or k.startswith("hypervisor.")]:
             del sys.modules[k]
+
+
+def test_cpp_packer_survives_fork():
+    """The packer keeps worker threads between calls; a forked child (multiprocessing's default start method
+    on Linux) must get its own pool instead of waiting for threads that only exist in the parent."""
+    import subprocess
+    import sys
+    code = r'''
+import os, sys
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import recipes
+from test_host_logic import build_deltas
+from agent_hypervisor_b200.audit.packing import columns_from_deltas, pack_columns
+deltas = []
+for seed in range(400):
+    deltas += build_deltas(recipes.random_session(seed))
+cols = columns_from_deltas(deltas)
+assert cols["n"] >= 4096                      # enough to use the worker threads
+a, o = pack_columns(cols)
+pid = os.fork()
+if pid == 0:
+    b, _ = pack_columns(cols)
+    os._exit(0 if b.tobytes() == a.tobytes() else 3)
+_, st = os.waitpid(pid, 0)
+c, _ = pack_columns(cols)
+sys.exit(0 if st == 0 and c.tobytes() == a.tobytes() else 4)
+''' % (ROOT, os.path.join(ROOT, "tests"))
+    r = subprocess.run([sys.executable, "-W", "ignore", "-c", code], timeout=120, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
