@@ -196,3 +196,14 @@ def test_slash_lane_walker_matches_reference_records(emu, slashing_golden):
         assert np.array_equal(o2["active"][e0:e1], want[2][e0:e1])
         assert o2["clip_log"][e0:e0 + int(want[6][s])].tobytes() == want[4][e0:e0 + int(want[6][s])].tobytes()
     assert int(want[6][0]) > 12                                              # the cache did overflow
+
+
+def test_rolled_node_bodies_match_hashlib(emu):
+    """The code-size-reduced compression bodies of the tree kernels (rounds rolled, constants by index) give
+    the reference's node: sha256((left.hex() + right.hex()).encode()) (audit/delta.py:130)."""
+    rng = np.random.default_rng(21)
+    for _ in range(300):
+        l = rng.integers(0, 256, 32, dtype=np.uint8); r = rng.integers(0, 256, 32, dtype=np.uint8)
+        out = np.zeros(32, np.uint8)
+        emu.emu_node_rolled(l.ctypes.data_as(u8p), r.ctypes.data_as(u8p), out.ctypes.data_as(u8p))
+        assert out.tobytes() == hashlib.sha256((l.tobytes().hex() + r.tobytes().hex()).encode()).digest()
