@@ -341,8 +341,9 @@ struct CompressNative {
 struct CompressScaled {
     uint32_t rc;
     AHV_HD void block(uint32_t st[8], uint32_t w[16]) const { sha256_compress_scaled(st, w, rc); }
-    // a hex block of a Merkle node (rolling THIS body as well shrinks a node to 19 KB of code but measured
-    // slower, 3.72 vs 3.61 ms per tree pass: sha256_lab.cuh keeps that variant)
+    // a hex block of a Merkle node.  Rolling THIS body as well (sha256_lab.cuh: sha256_compress_scaled_rolled)
+    // brings a node to 27 KB / 19 KB of code, inside the instruction cache, but measured slower: 9.34 / 9.36
+    // ms per bench step against 9.27 - the rolled rounds lose their immediate constants.
     AHV_HD void node_block(uint32_t st[8], uint32_t w[16]) const { sha256_compress_scaled(st, w, rc); }
     template <class KWT>
     AHV_HD void pad(uint32_t st[8], const KWT &kwc) const { sha256_compress_kw_scaled(st, kwc, rc); }

@@ -317,48 +317,49 @@ AHV_HD void sha256_compress_imad(uint32_t st[8], uint32_t w[16], const ShaMults 
     st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
 }
 
-// (experiment, not used by the kernels) The same compression with rounds 16..63 rolled into three iterations of 16 (after 16 rounds both the
-// register roles and the 16-word schedule window are back in place); K[16..63] come from a table by
-// index.  ~850 instructions of code instead of ~1500: for the tree kernels, whose node code would
-// otherwise not fit the 32 KB instruction cache.  Same arithmetic, same results.
+// (experiment, not used by the kernels: see CompressScaled::node_block) The same compression with its last
+// rounds rolled: rounds 0 .. STRAIGHT-1 are straight-line code with
+// immediate constants, the rest runs 16 rounds per iteration (after 16 rounds both the register roles and
+// the 16-word schedule window are back in place) with K read from a table by index.  Smaller code for the
+// tree kernels, whose node would otherwise not fit the 32 KB instruction cache.  Same arithmetic.
+template <int STRAIGHT>
 AHV_HD void sha256_compress_scaled_rolled(uint32_t st[8], uint32_t w[16], uint32_t rc_)
 {
+    static_assert(STRAIGHT % 16 == 0 && STRAIGHT >= 16 && STRAIGHT <= 64, "whole 16-round groups");
     static constexpr uint32_t K[64] = {AHV_K256_LIST};
     uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#define AHV_SCHED8(base)                                                           \
+    _Pragma("unroll") for (int j_ = 0; j_ < 8; ++j_) {                             \
+        const int i_ = (base) + j_;                                                \
+        uint32_t z_ = imad_rk(w[(i_ - 7) & 15], rc_, 0u);                          \
+        z_ = imad_c(sig1(w[(i_ - 2) & 15]), z_);                                   \
+        z_ = imad_c(sig0(w[(i_ - 15) & 15]), z_);                                  \
+        w[i_ & 15] = imad_ci(z_, w[i_ & 15]);                                      \
+    }
+#define AHV_ROUNDS8(kp, wb)                                                        \
+    AHV_ROUND_SCP(a, b, c, d, e, f, g, h, (kp)[0], w[((wb) + 0) & 15])             \
+    AHV_ROUND_SCP(h, a, b, c, d, e, f, g, (kp)[1], w[((wb) + 1) & 15])             \
+    AHV_ROUND_SCP(g, h, a, b, c, d, e, f, (kp)[2], w[((wb) + 2) & 15])             \
+    AHV_ROUND_SCP(f, g, h, a, b, c, d, e, (kp)[3], w[((wb) + 3) & 15])             \
+    AHV_ROUND_SCP(e, f, g, h, a, b, c, d, (kp)[4], w[((wb) + 4) & 15])             \
+    AHV_ROUND_SCP(d, e, f, g, h, a, b, c, (kp)[5], w[((wb) + 5) & 15])             \
+    AHV_ROUND_SCP(c, d, e, f, g, h, a, b, (kp)[6], w[((wb) + 6) & 15])             \
+    AHV_ROUND_SCP(b, c, d, e, f, g, h, a, (kp)[7], w[((wb) + 7) & 15])
 #pragma unroll
-    for (int t = 0; t < 16; t += 8) {
-        AHV_ROUND_SCP(a, b, c, d, e, f, g, h, K[t + 0], w[t + 0])
-        AHV_ROUND_SCP(h, a, b, c, d, e, f, g, K[t + 1], w[t + 1])
-        AHV_ROUND_SCP(g, h, a, b, c, d, e, f, K[t + 2], w[t + 2])
-        AHV_ROUND_SCP(f, g, h, a, b, c, d, e, K[t + 3], w[t + 3])
-        AHV_ROUND_SCP(e, f, g, h, a, b, c, d, K[t + 4], w[t + 4])
-        AHV_ROUND_SCP(d, e, f, g, h, a, b, c, K[t + 5], w[t + 5])
-        AHV_ROUND_SCP(c, d, e, f, g, h, a, b, K[t + 6], w[t + 6])
-        AHV_ROUND_SCP(b, c, d, e, f, g, h, a, K[t + 7], w[t + 7])
+    for (int t = 0; t < STRAIGHT; t += 8) {
+        if (t >= 16) { AHV_SCHED8(t) }
+        AHV_ROUNDS8(K + t, t)
     }
 #pragma unroll 1
-    for (int t = 16; t < 64; t += 16) {
+    for (int t = STRAIGHT; t < 64; t += 16) {
         const uint32_t *k = K + t;
-#pragma unroll
-        for (int u = 0; u < 16; u += 8) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int i = u + j;                 // (t + i) & 15 == i
-                uint32_t z = imad_rk(w[(i - 7) & 15], rc_, 0u);
-                z = imad_c(sig1(w[(i - 2) & 15]), z);
-                z = imad_c(sig0(w[(i - 15) & 15]), z);
-                w[i] = imad_ci(z, w[i]);
-            }
-            AHV_ROUND_SCP(a, b, c, d, e, f, g, h, k[u + 0], w[u + 0])
-            AHV_ROUND_SCP(h, a, b, c, d, e, f, g, k[u + 1], w[u + 1])
-            AHV_ROUND_SCP(g, h, a, b, c, d, e, f, k[u + 2], w[u + 2])
-            AHV_ROUND_SCP(f, g, h, a, b, c, d, e, k[u + 3], w[u + 3])
-            AHV_ROUND_SCP(e, f, g, h, a, b, c, d, k[u + 4], w[u + 4])
-            AHV_ROUND_SCP(d, e, f, g, h, a, b, c, k[u + 5], w[u + 5])
-            AHV_ROUND_SCP(c, d, e, f, g, h, a, b, k[u + 6], w[u + 6])
-            AHV_ROUND_SCP(b, c, d, e, f, g, h, a, k[u + 7], w[u + 7])
-        }
+        AHV_SCHED8(0)
+        AHV_ROUNDS8(k, 0)
+        AHV_SCHED8(8)
+        AHV_ROUNDS8(k + 8, 8)
     }
+#undef AHV_SCHED8
+#undef AHV_ROUNDS8
     st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
 }
 

@@ -190,7 +190,7 @@ extern "C" uint64_t emu_slash_lanes(const ahv_slash_batch *b, uint32_t *out_big)
 
 // The rolled compression bodies the tree kernels use (sha256_compress_scaled_rolled for the two hex blocks,
 // sha256_compress_kw_scaled_rolled for the padding block): one Merkle node from two raw digests.
-extern "C" void emu_node_rolled(const uint8_t *l32, const uint8_t *r32, uint8_t *out32)
+extern "C" void emu_node_rolled(const uint8_t *l32, const uint8_t *r32, uint8_t *out32, int variant)
 {
     alignas(16) uint8_t a[32], b[32], o[32];
     memcpy(a, l32, 32);
@@ -201,7 +201,9 @@ extern "C" void emu_node_rolled(const uint8_t *l32, const uint8_t *r32, uint8_t 
     ahv::sha256_init(st);
     for (int half = 0; half < 2; ++half) {
         for (int i = 0; i < 8; ++i) ahv::hex_expand(half ? r[i] : l[i], w[2 * i], w[2 * i + 1]);
-        ahv::sha256_compress_scaled_rolled(st, w, ahv::SHA_SC);
+        if (variant == 16) ahv::sha256_compress_scaled_rolled<16>(st, w, ahv::SHA_SC);
+        else if (variant == 32) ahv::sha256_compress_scaled_rolled<32>(st, w, ahv::SHA_SC);
+        else ahv::sha256_compress_scaled_rolled<48>(st, w, ahv::SHA_SC);
     }
     static constexpr ahv::KW64 kwc = ahv::make_kw_pad_scaled(1024);
     ahv::sha256_compress_kw_scaled_rolled(st, kwc.v, ahv::SHA_SC);

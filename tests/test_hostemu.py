@@ -205,5 +205,6 @@ def test_rolled_node_bodies_match_hashlib(emu):
     for _ in range(300):
         l = rng.integers(0, 256, 32, dtype=np.uint8); r = rng.integers(0, 256, 32, dtype=np.uint8)
         out = np.zeros(32, np.uint8)
-        emu.emu_node_rolled(l.ctypes.data_as(u8p), r.ctypes.data_as(u8p), out.ctypes.data_as(u8p))
-        assert out.tobytes() == hashlib.sha256((l.tobytes().hex() + r.tobytes().hex()).encode()).digest()
+        for variant in (16, 32, 48):              # straight-line rounds before the rolled part
+            emu.emu_node_rolled(l.ctypes.data_as(u8p), r.ctypes.data_as(u8p), out.ctypes.data_as(u8p), variant)
+            assert out.tobytes() == hashlib.sha256((l.tobytes().hex() + r.tobytes().hex()).encode()).digest()
