@@ -78,6 +78,7 @@ SIGNATURES = {
     "ahv_timer_stop": (C.c_int, [_vp, C.c_int]),
     "ahv_timer_elapsed_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
     "ahv_sha256_batch": (C.c_int, [_vp, _vp, _vp, _u64, _u64, _vp]),
+    "ahv_sha256_one": (C.c_int, [_vp, C.c_char_p, _u64, _vp]),
     "ahv_sha256_batch_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _u64, _vp]),
     "ahv_merkle_roots": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp]),
     "ahv_merkle_roots_dev": (C.c_int, [_vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp]),
@@ -252,6 +253,13 @@ class Context:
             self._check(self.lib.ahv_sha256_batch(self.h, _ptr(arena), _ptr(offsets), n, int(fixed_len), _ptr(out)),
                         "ahv_sha256_batch")
         return out
+
+    def sha256_one(self, msg: bytes) -> bytes:
+        """SHA-256 of one message through the lowest-latency entry (ahv_sha256_one)."""
+        out = C.create_string_buffer(32)
+        with self._lock:
+            self._check(self.lib.ahv_sha256_one(self.h, msg, len(msg), out), "ahv_sha256_one")
+        return out.raw
 
     def merkle_roots(self, digests, session_rowptr):
         digests = _arr(digests, np.uint8)

@@ -57,10 +57,7 @@ class SemanticDelta:
         return canonical_preimage(self)
 
     def compute_hash(self) -> str:
-        pre = self.preimage()
-        digest = nat.get_context().sha256_batch(np.frombuffer(pre, dtype=np.uint8),
-                                                np.array([0, len(pre)], dtype=np.uint64))
-        self.delta_hash = digest[0].tobytes().hex()
+        self.delta_hash = nat.get_context().sha256_one(self.preimage()).hex()
         return self.delta_hash
 
 

@@ -646,6 +646,29 @@ k_extract_parents(const uint8_t *__restrict__ arena, const uint64_t *__restrict_
     kind[i] = k;
 }
 
+// ------------------------------------------------------------------ one message, lowest latency
+// A single capture (audit/delta.py:85-115 -> :63) is one short message: two copies and a kernel through the
+// batch entry point cost ~30 us of which the hashing is 2.  Here the message travels INSIDE the launch (a
+// __grid_constant__ kernel parameter, up to AHV_ONE_MAX bytes) and the digest is written straight into
+// mapped pinned host memory, so the whole call is one launch and one stream synchronisation.
+struct OneMsg {
+    uint32_t len;
+    uint32_t pad[3];
+    uint8_t data[AHV_ONE_MAX + 16];               // slack: aligned word reads may touch the word after the last byte
+};
+
+template <bool SC>
+__global__ void __launch_bounds__(32)
+k_sha256_one(const __grid_constant__ OneMsg m, uint8_t *out_mapped, uint32_t rc)
+{
+    if (threadIdx.x != 0) return;
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
+    uint32_t st[8];
+    sha256_message(m.data, m.len, st, cp);
+    store_digest(out_mapped, st);
+    __threadfence_system();
+}
+
 // ------------------------------------------------------------------ chained capture
 // One thread per session walks its chain (audit/delta.py:101-114): hash delta i, write the
 // 64 hex characters into delta i+1's pre-image, continue.  Plain (coherent) loads only:
@@ -1020,6 +1043,34 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
             AHV_CHECK_LAUNCH(ctx);
         }
     }
+    return AHV_OK;
+}
+
+int ahv_sha256_one(ahv_ctx *ctx, const uint8_t *msg, uint64_t len, uint8_t *out_digest)
+{
+    AHV_TRY(use_device(ctx));
+    AHV_REQUIRE(out_digest && (msg || len == 0), "msg / out_digest is null");
+    if (len > AHV_ONE_MAX) {                      // too long to ride in the launch: the batch path
+        const uint64_t offs[2] = {0, len};
+        return ahv_sha256_batch(ctx, msg, offs, 1, 0, out_digest);
+    }
+    if (!ctx->one_out) {
+        void *h = nullptr;
+        AHV_CUDA(cudaHostAlloc(&h, 64, cudaHostAllocMapped));
+        ctx->one_out = (uint8_t *)h;
+    }
+    void *d_out = nullptr;
+    AHV_CUDA(cudaHostGetDevicePointer(&d_out, ctx->one_out, 0));
+    OneMsg m;
+    m.len = (uint32_t)len;
+    if (len) memcpy(m.data, msg, len);
+    if (ctx->opt_compress)
+        k_sha256_one<true><<<1, 32, 0, ctx->stream>>>(m, (uint8_t *)d_out, SHA_SC);
+    else
+        k_sha256_one<false><<<1, 32, 0, ctx->stream>>>(m, (uint8_t *)d_out, SHA_SC);
+    AHV_CHECK_LAUNCH(ctx);
+    AHV_CUDA(cudaStreamSynchronize(ctx->stream));
+    memcpy(out_digest, ctx->one_out, 32);
     return AHV_OK;
 }
 

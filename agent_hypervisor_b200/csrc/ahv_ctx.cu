@@ -158,6 +158,7 @@ void ahv_destroy(ahv_ctx *ctx)
     cudaStreamSynchronize(ctx->d2h_stream);
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->io) cudaFree(ctx->io);
+    if (ctx->one_out) cudaFreeHost(ctx->one_out);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(ctx->ev_copy[i]);
     for (int i = 0; i < AHV_MAX_TIMERS; ++i) {
         cudaEventDestroy(ctx->t_start[i]);

@@ -40,6 +40,7 @@ struct ahv_ctx {
     int64_t opt_peak_ctas;     // CTAs of 256 threads per SM in the ahv_int_peak kernels (default 4)
     int64_t opt_leaf_timer;    // >0: bracket every leaf-hash launch with timer slots base..base+15 (round robin)
     uint64_t leaf_launches;    // leaf-hash kernel launches so far (indexes the round robin)
+    uint8_t *one_out;          // 64 B of mapped pinned host memory: where ahv_sha256_one's kernel writes its digest
 };
 
 namespace ahv {

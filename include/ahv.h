@@ -102,6 +102,14 @@ int ahv_timer_elapsed_ms(ahv_ctx *ctx, int slot, float *out_ms); /* synchronises
  */
 int ahv_sha256_batch(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t n,
                      uint64_t fixed_len, uint8_t *out_digests /* n*32 */);
+/*
+ * ahv_sha256_one: the same for ONE message, for the call-at-a-time users of the reference's API
+ * (DeltaEngine.capture -> compute_hash, audit/delta.py:85-115,63).  A message of up to AHV_ONE_MAX bytes is
+ * passed to the device inside the kernel launch and its digest comes back through mapped host memory: one
+ * launch and one synchronisation, no copies.  Longer messages take the ahv_sha256_batch path.
+ */
+#define AHV_ONE_MAX 3584u
+int ahv_sha256_one(ahv_ctx *ctx, const uint8_t *msg, uint64_t len, uint8_t *out_digest /* 32 */);
 int ahv_sha256_batch_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_bytes,
                          const uint64_t *d_offsets, uint64_t n, uint64_t fixed_len,
                          uint8_t *d_out_digests);

@@ -131,6 +131,18 @@ def test_sha256_empty_batch(ctx):
     assert ctx.sha256_batch(np.zeros(0, np.uint8), np.zeros(1, np.uint64)).shape == (0, 32)
 
 
+def test_sha256_one_matches_hashlib(ctx):
+    """ahv_sha256_one (message inside the launch, digest through mapped host memory) at the padding edges, at
+    its size limit and past it (where it falls back to the batch path)."""
+    rng = np.random.default_rng(9)
+    for n in (0, 1, 3, 55, 56, 57, 63, 64, 65, 119, 120, 127, 128, 255, 256, 330, 1000, 3583, 3584, 3585, 5000, 70000):
+        m = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        assert ctx.sha256_one(m) == hashlib.sha256(m).digest(), n
+    for _ in range(200):                          # back to back: the mapped result slot is reused every call
+        m = rng.integers(0, 256, int(rng.integers(0, 600)), dtype=np.uint8).tobytes()
+        assert ctx.sha256_one(m) == hashlib.sha256(m).digest()
+
+
 def test_vfs_content_hashes(ctx):
     """session/sso.py:214-216 for a batch of file contents (incl. empty, unicode, large)."""
     from agent_hypervisor_b200 import content_hashes

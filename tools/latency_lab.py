@@ -26,3 +26,17 @@ for n in (2, 10, 100, 1000):
     msg = rng.integers(0, 256, 300, dtype=np.uint8); off = np.array([0, 300], np.uint64)
     t_sha = med(lambda: ctx.sha256_batch(msg, off))
     print(f"n={n:5d}: merkle_roots host call {t_all:7.1f} us | device-only (launches+sync) {t_dev:7.1f} us | hex->bytes {t_hex:6.1f} us | one 300-B sha256_batch {t_sha:6.1f} us", flush=True)
+
+# one capture: the batch entry (two copies + kernel) against ahv_sha256_one (message in the launch, digest via
+# mapped host memory), and the whole DeltaEngine.capture call
+from agent_hypervisor_b200 import DeltaEngine, VFSChange
+m300 = bytes(rng.integers(0, 256, 300, dtype=np.uint8))
+a300 = np.frombuffer(m300, np.uint8); o300 = np.array([0, 300], np.uint64)
+t_batch = med(lambda: ctx.sha256_batch(a300, o300), 2000)
+t_one = med(lambda: ctx.sha256_one(m300), 2000)
+eng = DeltaEngine("bench-session")
+ch = [VFSChange(path="/f", operation="add", content_hash="h")]
+t_cap = med(lambda: eng.capture("did:mesh:a", ch), 2000)
+import hashlib
+t_hl = med(lambda: hashlib.sha256(m300).digest(), 2000)
+print(f"one 300-B message: sha256_batch {t_batch:.1f} us | sha256_one {t_one:.1f} us | hashlib {t_hl:.2f} us | DeltaEngine.capture {t_cap:.1f} us", flush=True)
