@@ -40,3 +40,9 @@ t_cap = med(lambda: eng.capture("did:mesh:a", ch), 2000)
 import hashlib
 t_hl = med(lambda: hashlib.sha256(m300).digest(), 2000)
 print(f"one 300-B message: sha256_batch {t_batch:.1f} us | sha256_one {t_one:.1f} us | hashlib {t_hl:.2f} us | DeltaEngine.capture {t_cap:.1f} us", flush=True)
+for comp in (0, 1):
+    ctx.set_option("compress", comp)
+    for ln in (64, 300, 1000, 3000):
+        mm = bytes(rng.integers(0, 256, ln, dtype=np.uint8))
+        print(f"compress={comp} sha256_one {ln:5d} B: {med(lambda: ctx.sha256_one(mm), 1000):.1f} us", flush=True)
+ctx.set_option("compress", 1)
