@@ -103,6 +103,14 @@ SIGNATURES = {
     "ahv_exposure_sums_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _u64, C.c_int, _vp]),
     "ahv_ring_check": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_ring_check_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
+    "ahv_comm_unique_id": (C.c_int, [_vp]),
+    "ahv_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "ahv_comm_destroy": (C.c_int, [_vp]),
+    "ahv_comm_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "ahv_comm_all_gather_dev": (C.c_int, [_vp, _vp, _vp, _u64]),
+    "ahv_comm_all_gather": (C.c_int, [_vp, _vp, _vp, _u64]),
+    "ahv_gather_stride": (_u64, [_u64]),
+    "ahv_gather_results_dev": (C.c_int, [_vp, _vp, _vp, _u64, _vp]),
     "ahv_int_peak": (C.c_int, [_vp, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
     "ahv_set_option": (C.c_int, [_vp, C.c_char_p, C.c_int64]),
 }
@@ -239,6 +247,50 @@ class Context:
         v, ms = C.c_double(), C.c_float()
         self._check(self.lib.ahv_int_peak(self.h, mode, iters, C.byref(v), C.byref(ms)), "ahv_int_peak")
         return float(v.value), float(ms.value)
+
+    # -- multi-GPU: NCCL communicator owned by the context (csrc/ahv_comm.cu) ---
+    def comm_unique_id(self) -> bytes:
+        buf = C.create_string_buffer(128)
+        self._check(self.lib.ahv_comm_unique_id(C.cast(buf, _vp)), "ahv_comm_unique_id")
+        return buf.raw
+
+    def comm_init(self, world: int, rank: int, unique_id: Optional[bytes] = None):
+        buf = C.create_string_buffer(unique_id, 128) if unique_id is not None else None
+        self._check(self.lib.ahv_comm_init(self.h, int(world), int(rank), C.cast(buf, _vp) if buf is not None else None),
+                    "ahv_comm_init")
+
+    def comm_destroy(self):
+        self._check(self.lib.ahv_comm_destroy(self.h), "ahv_comm_destroy")
+
+    def comm_info(self) -> dict:
+        w, r, v = C.c_int(), C.c_int(), C.c_int()
+        self._check(self.lib.ahv_comm_info(self.h, C.byref(w), C.byref(r), C.byref(v)), "ahv_comm_info")
+        return {"world": w.value, "rank": r.value, "nccl_version": v.value}
+
+    def comm_all_gather(self, local: np.ndarray) -> np.ndarray:
+        """All-gather equal-sized host arrays: returns [world, *local.shape] (stages through the device)."""
+        local = np.ascontiguousarray(local)
+        world = self.comm_info()["world"]
+        out = np.empty((world,) + local.shape, dtype=local.dtype)
+        with self._lock:
+            self._check(self.lib.ahv_comm_all_gather(self.h, _ptr(local), _ptr(out), local.nbytes), "ahv_comm_all_gather")
+        return out
+
+    def comm_all_gather_dev(self, d_send: int, d_recv: int, bytes_per_rank: int):
+        self._check(self.lib.ahv_comm_all_gather_dev(self.h, _vp(d_send), _vp(d_recv), int(bytes_per_rank)),
+                    "ahv_comm_all_gather_dev")
+
+    def gather_stride(self, n_sessions: int) -> int:
+        return int(self.lib.ahv_gather_stride(int(n_sessions)))
+
+    def gather_results_dev(self, d_roots: int, d_verdict: int, n_sessions: int, d_all: int):
+        """One all-gather of this rank's roots + verdicts into d_all (world * gather_stride(S) bytes)."""
+        self._check(self.lib.ahv_gather_results_dev(self.h, _vp(d_roots), _vp(d_verdict), int(n_sessions), _vp(d_all)),
+                    "ahv_gather_results_dev")
+
+    def barrier(self):
+        """All ranks of the communicator have reached this point (and this rank's stream has drained)."""
+        self.comm_all_gather(np.zeros(1, np.uint64))
 
     # -- host-buffer entry points (numpy in / numpy out) ---------------------
     def sha256_batch(self, arena, offsets=None, fixed_len: int = 0, n: Optional[int] = None) -> np.ndarray:

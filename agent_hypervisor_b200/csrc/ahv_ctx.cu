@@ -137,12 +137,15 @@ int ahv_create(int device, ahv_ctx **out_ctx)
         AHV_CUDA(cudaEventCreate(&c->t_start[i]));
         AHV_CUDA(cudaEventCreate(&c->t_stop[i]));
     }
+    c->comm_world = 1;
     c->opt_sort = 1;
     c->opt_block = 128;
     c->opt_fixed_variant = 0;
     c->opt_top_max = 0;
     c->opt_compress = 1;
     c->opt_sigma_variant = 1;
+    c->opt_sigma_exact = 0;
+    c->opt_sigma_long_cut = 512;
     c->opt_slash_variant = 0;
     c->opt_blocking_sync = 0;
     *out_ctx = c;
@@ -156,6 +159,7 @@ void ahv_destroy(ahv_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     cudaStreamSynchronize(ctx->copy_stream);
     cudaStreamSynchronize(ctx->d2h_stream);
+    comm_release(ctx);
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->io) cudaFree(ctx->io);
     if (ctx->one_out) cudaFreeHost(ctx->one_out);
@@ -297,6 +301,12 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "sigma_variant")) {
         AHV_REQUIRE(value == 0 || value == 1, "sigma_variant must be 0 or 1");
         ctx->opt_sigma_variant = value;
+    } else if (!strcmp(key, "sigma_exact")) {
+        AHV_REQUIRE(value == 0 || value == 1, "sigma_exact must be 0 or 1");
+        ctx->opt_sigma_exact = value;
+    } else if (!strcmp(key, "sigma_long_cut")) {
+        AHV_REQUIRE(value >= 32 && value <= 0x7fffffff, "sigma_long_cut must be 32..2^31-1");
+        ctx->opt_sigma_long_cut = value;
     } else if (!strcmp(key, "compress")) {
         AHV_REQUIRE(value == 0 || value == 1, "compress must be 0 or 1");
         ctx->opt_compress = value;

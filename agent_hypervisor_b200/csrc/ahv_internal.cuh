@@ -35,11 +35,15 @@ struct ahv_ctx {
     int64_t opt_blocking_sync; // 1: ahv_audit_sessions sleeps on an event instead of spinning while the pipeline drains (default 0)
     int64_t opt_slash_variant; // 0: sessions that fit are staged in shared memory (default), 1: always global memory
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
+    int64_t opt_sigma_exact;   // 1: every row summed in the reference's order (bit-identical); 0 (default): rows longer than opt_sigma_long_cut take the fixed-shape parallel sum
+    int64_t opt_sigma_long_cut;// row length (edges) above which the parallel sum is used (default 512)
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)
     int64_t opt_peak_ctas;     // CTAs of 256 threads per SM in the ahv_int_peak kernels (default 4)
     int64_t opt_leaf_timer;    // >0: bracket every leaf-hash launch with timer slots base..base+15 (round robin)
     uint64_t leaf_launches;    // leaf-hash kernel launches so far (indexes the round robin)
+    void *comm;                // ncclComm_t of this rank (ahv_comm_init), NULL in a world of one
+    int comm_world, comm_rank;
     uint8_t *one_out;          // 64 B of mapped pinned host memory: where ahv_sha256_one's kernel writes its digest
 };
 
@@ -88,6 +92,7 @@ void *io_take(ahv_ctx *ctx, uint64_t bytes);
 static inline uint64_t pad256(uint64_t b) { return (b + 255u) & ~(uint64_t)255u; }
 
 int use_device(ahv_ctx *ctx);
+void comm_release(ahv_ctx *ctx);                     // ahv_comm.cu: destroys the communicator, if any
 
 static inline unsigned grid_for(uint64_t threads, unsigned block)
 {

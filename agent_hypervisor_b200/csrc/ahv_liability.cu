@@ -41,10 +41,21 @@ k_sigma_eff_rings(const uint32_t *__restrict__ rowptr, const double *__restrict_
 // up the slice of its own row inside the chunk, in CSR order (phase 2).  Order of additions per
 // row is exactly the reference's, so results stay bit-identical; x + (+0.0) == x for every x the
 // running sum can hold (it starts at +0.0 and can never become -0.0).
-// A row of d edges is d dependent fp64 additions: the longest row bounds the kernel from below
-// (measured ~17 cycles per element), which is what the Zipf-shaped config-4 graph runs into.
+//
+// A row of d edges is d dependent fp64 additions (8.1 cycles each), so one very long row holds its
+// whole tile back: 14 017 edges = 58 us at best, longer than the rest of a 10^7-edge graph takes.
+// With PAR, rows longer than `long_cut` edges are therefore summed by the whole CTA in a FIXED shape
+// that depends on the row alone (not on tiling, chunking or scheduling, so it is the same run to run):
+//     partial[p] = live contributions at row positions p, p+256, p+512, ... added in that order   (p = 0..255)
+//     warp w     = xor-butterfly over partial[32w .. 32w+31] with strides 16, 8, 4, 2, 1
+//     row sum    = ((((((w0 + w1) + w2) + w3) + w4) + w5) + w6) + w7
+// which differs from the reference's left-to-right sum by a few ulp (north_star allows 1e-6
+// relative); agents whose sigma_eff lies within 1e-6 of a ring threshold are flagged in out_near
+// either way.  Rows up to `long_cut` keep the reference's order and stay bit-identical; option
+// sigma_exact=1 keeps it for every row.
 constexpr int SIG_ROWS = 256;
 constexpr int SIG_CHUNK = 2048;
+constexpr int SIG_WARPS = SIG_ROWS / 32;
 
 // Running sum of one row.  Plain: left-to-right fp64 additions (the explicit += loop of
 // vouching.py:146-148, and Python's sum() up to CPython 3.11).  Compensated: CPython >= 3.12's
@@ -72,17 +83,22 @@ template <> struct RowSum<true> {
 };
 
 // MODE 0: sigma_eff + rings.  MODE 1: plain live sum of each row.  MODE 2: compensated live sum.
-template <int MODE>
+// PAR (MODE 0 only): rows of more than long_cut edges take the fixed-shape parallel sum.
+template <int MODE, bool PAR>
 __global__ void __launch_bounds__(SIG_ROWS)
 k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
                   const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
                   const double *__restrict__ sigma, const double *__restrict__ omega,
                   const uint8_t *__restrict__ consensus, const uint8_t *__restrict__ current_ring, uint64_t A,
                   double *__restrict__ out_sigma, uint8_t *__restrict__ out_ring, uint8_t *__restrict__ out_demote,
-                  uint8_t *__restrict__ out_near)
+                  uint8_t *__restrict__ out_near, uint32_t long_cut)
 {
     __shared__ double v[SIG_CHUNK];
-    const uint32_t tid = threadIdx.x;
+    __shared__ double wsum[SIG_WARPS];
+    __shared__ uint32_t wcount[SIG_WARPS];
+    __shared__ uint32_t long_r0[SIG_ROWS], long_r1[SIG_ROWS];
+    __shared__ uint16_t long_owner[SIG_ROWS];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
     const uint64_t a0 = (uint64_t)blockIdx.x * SIG_ROWS;
     const uint64_t a = a0 + tid;
     const bool valid = a < A;
@@ -90,6 +106,32 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
     const uint32_t e_begin = rowptr[a0], e_end = rowptr[a_last];
     const uint32_t my0 = valid ? rowptr[a] : e_end, my1 = valid ? rowptr[a + 1] : e_end;
     RowSum<MODE == 2> acc;
+
+    // list of this tile's long rows, in row order (usually empty)
+    const bool is_long = PAR && (my1 - my0 > long_cut);
+    uint32_t n_long = 0;
+    if (PAR) {
+        const uint32_t b = __ballot_sync(0xffffffffu, is_long);
+        if (lane == 0) wcount[wid] = __popc(b);
+        __syncthreads();
+        uint32_t before = 0;
+#pragma unroll
+        for (int w = 0; w < SIG_WARPS; ++w) {
+            const uint32_t c = wcount[w];
+            if (w < (int)wid) before += c;
+            n_long += c;
+        }
+        if (is_long) {
+            const uint32_t k = before + __popc(b & ((1u << lane) - 1u));
+            long_r0[k] = my0;
+            long_r1[k] = my1;
+            long_owner[k] = (uint16_t)tid;
+        }
+        // (made visible by the barrier after phase 1 of the first chunk: a long row has edges, so there is one)
+    }
+    uint32_t li = 0;          // next long row (uniform over the CTA)
+    double part = 0.0;        // this thread's strided partial of long row li
+
     for (uint32_t c0 = e_begin; c0 < e_end; c0 += SIG_CHUNK) {
         const uint32_t c1 = (e_end - c0 > (uint32_t)SIG_CHUNK) ? c0 + SIG_CHUNK : e_end;
         // phase 1: issue every load of this thread's 8 edges before using any (memory-level parallelism)
@@ -108,8 +150,41 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
         for (int k = 0; k < SIG_CHUNK / SIG_ROWS; ++k)
             v[tid + k * SIG_ROWS] = vouch_accumulate(0.0, b_[k], a_[k], x_[k], now);
         __syncthreads();
-        const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
-        for (uint32_t e = lo; e < hi; ++e) acc.add(v[e - c0]);
+        // phase 2: own row, reference order; values fetched four at a time ahead of the dependent additions
+        if (!is_long) {
+            const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
+            uint32_t e = lo;
+            for (; e + 4 <= hi; e += 4) {
+                const double x0 = v[e - c0], x1 = v[e - c0 + 1], x2 = v[e - c0 + 2], x3 = v[e - c0 + 3];
+                acc.add(x0); acc.add(x1); acc.add(x2); acc.add(x3);
+            }
+            for (; e < hi; ++e) acc.add(v[e - c0]);
+        }
+        if (PAR) {
+            while (li < n_long) {
+                const uint32_t r0 = long_r0[li], r1 = long_r1[li];
+                if (r0 >= c1) break;                                   // starts in a later chunk
+                const uint32_t lo = r0 > c0 ? r0 : c0, hi = r1 < c1 ? r1 : c1;
+                // row positions congruent to tid (mod 256) inside [lo, hi)
+                for (uint32_t e = lo + ((tid - (lo - r0)) & (SIG_ROWS - 1)); e < hi; e += SIG_ROWS)
+                    part = __dadd_rn(part, v[e - c0]);
+                if (r1 > c1) break;                                    // continues in the next chunk
+                double x = part;
+#pragma unroll
+                for (int o = 16; o; o >>= 1) x = __dadd_rn(x, __shfl_xor_sync(0xffffffffu, x, o));
+                if (lane == 0) wsum[wid] = x;
+                __syncthreads();
+                if (tid == long_owner[li]) {
+                    double t = wsum[0];
+#pragma unroll
+                    for (int w = 1; w < SIG_WARPS; ++w) t = __dadd_rn(t, wsum[w]);
+                    acc.f = t;
+                }
+                __syncthreads();
+                part = 0.0;
+                ++li;
+            }
+        }
         __syncthreads();
     }
     if (!valid) return;
@@ -159,11 +234,14 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
         k_sigma_eff_rings<<<grid_for(A, 256), 256, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma,
                                                                      d_omega, d_consensus, d_current_ring, A, d_out_sigma,
                                                                      d_out_ring, d_out_demote, d_out_near);
+    else if (ctx->opt_sigma_exact)
+        k_sigma_eff_tiled<0, false><<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(
+            d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+            d_out_ring, d_out_demote, d_out_near, 0u);
     else
-        k_sigma_eff_tiled<0><<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now,
-                                                                               d_sigma, d_omega, d_consensus, d_current_ring,
-                                                                               A, d_out_sigma, d_out_ring, d_out_demote,
-                                                                               d_out_near);
+        k_sigma_eff_tiled<0, true><<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(
+            d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
@@ -177,13 +255,13 @@ int ahv_exposure_sums_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *
     AHV_REQUIRE(n_rows < 0xffffffffull, "too many rows (limit 2^32-2)");
     const unsigned g = grid_for(n_rows, SIG_ROWS);
     if (compensated)
-        k_sigma_eff_tiled<2><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr, nullptr,
-                                                              nullptr, nullptr, n_rows, d_out_sum, nullptr, nullptr,
-                                                              nullptr);
+        k_sigma_eff_tiled<2, false><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
+                                                                     nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
+                                                                     nullptr, nullptr, 0u);
     else
-        k_sigma_eff_tiled<1><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr, nullptr,
-                                                              nullptr, nullptr, n_rows, d_out_sum, nullptr, nullptr,
-                                                              nullptr);
+        k_sigma_eff_tiled<1, false><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
+                                                                     nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
+                                                                     nullptr, nullptr, 0u);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

@@ -1,5 +1,6 @@
-"""Multi-GPU sharding of the audit path: one process per GPU (torchrun), plumbing over
-``torch.distributed`` (NCCL on GPUs; gloo in the CPU tests).
+"""Multi-GPU sharding of the audit path: one process per GPU (any launcher, e.g. torchrun), the one
+collective - an all-gather of roots / sub-roots - issued by the library's own NCCL communicator
+(``ahv_comm_*`` in the C ABI, ``agent_hypervisor_b200.comm``).
 
 Two schemes:
 
@@ -12,8 +13,10 @@ Two schemes:
   (audit/delta.py:129) duplicates it at every level up to k ("lifting").  The ceil(n/2^k) sub-roots
   are all-gathered and every rank finishes the top of the tree.
 
-torch is imported lazily and only by the collective helpers; hashing is done by the callable
-passed in (default: the GPU context's ``merkle_roots``).
+Hashing is done by the callable passed in (default: the GPU context's ``merkle_roots``) and the exchange
+by ``gather_fn(local[cap, width]) -> [world, cap, width]`` (default: the context's NCCL all-gather), so
+the planning and reassembly logic can be exercised on CPU with any other transport (the tests use a
+world-size-2/3 gloo group).
 """
 
 from __future__ import annotations
@@ -94,45 +97,58 @@ def finish_tree(subroots: np.ndarray, merkle_fn: Optional[Callable] = None) -> O
 
 
 # ---------------------------------------------------------------------------- collectives
-def all_gather_bytes(local: np.ndarray, counts: list[int], device=None, group=None) -> np.ndarray:
+def _default_gather() -> Callable:
+    from ._native import get_context
+    return get_context().comm_all_gather
+
+
+def all_gather_bytes(local: np.ndarray, counts: list[int], gather_fn: Optional[Callable] = None) -> np.ndarray:
     """All-gather rows of a uint8 [rows, width] array whose row counts per rank are ``counts``
     (known to every rank from the plan).  One collective; padded to the largest count."""
-    import torch
-    import torch.distributed as dist
-
-    world = dist.get_world_size(group)
+    gather_fn = gather_fn or _default_gather()
+    world = len(counts)
     width = local.shape[1] if local.ndim == 2 else 1
     cap = max(counts) if counts else 0
-    buf = torch.zeros((cap, width), dtype=torch.uint8, device=device)
+    buf = np.zeros((cap, width), dtype=np.uint8)
     if len(local):
-        buf[: len(local)] = torch.from_numpy(np.ascontiguousarray(local).reshape(len(local), width)).to(buf.device)
-    out = torch.empty((world * cap, width), dtype=torch.uint8, device=buf.device)
-    dist.all_gather_into_tensor(out, buf, group=group)
-    out = out.cpu().numpy().reshape(world, cap, width)
+        buf[: len(local)] = np.ascontiguousarray(local, dtype=np.uint8).reshape(len(local), width)
+    out = np.asarray(gather_fn(buf), dtype=np.uint8).reshape(world, cap, width)
     return np.concatenate([out[r, : counts[r]] for r in range(world)], axis=0)
 
 
 def sharded_tree_root(local_leaf_digests: np.ndarray, n_leaves: int, rank: int, world: int,
-                      k: Optional[int] = None, merkle_fn: Optional[Callable] = None, device=None, group=None):
+                      k: Optional[int] = None, merkle_fn: Optional[Callable] = None, gather_fn: Optional[Callable] = None):
     """Root of one n-leaf tree whose leaves are spread over the ranks by ``plan_tree``."""
     plan = plan_tree(n_leaves, world, k)
     lo, hi = plan["ranges"][rank]
     sub = local_subroots(local_leaf_digests, lo << plan["k"], plan, rank, merkle_fn)
     counts = [h - l for (l, h) in plan["ranges"]]
-    allsub = all_gather_bytes(sub, counts, device=device, group=group) if world > 1 else sub
+    allsub = all_gather_bytes(sub, counts, gather_fn) if world > 1 else sub
     return finish_tree(allsub, merkle_fn), plan
 
 
 def gather_session_results(local_roots: np.ndarray, local_verdicts: np.ndarray, n_sessions: int, rank: int,
-                           world: int, device=None, group=None):
-    """Roots [S,32] and verdicts [S] of all sessions, sessions sharded by ``shard_range``."""
+                           world: int, gather_fn: Optional[Callable] = None):
+    """Roots [S,32] and verdicts [S] of all sessions, sessions sharded by ``shard_range``: ONE all-gather of
+    33 bytes per session (host arrays; the device-resident form is ``Context.gather_results_dev``)."""
     counts = [shard_range(n_sessions, world, r)[1] - shard_range(n_sessions, world, r)[0] for r in range(world)]
     if world == 1:
         return local_roots, local_verdicts
     packed = np.concatenate([np.ascontiguousarray(local_roots, dtype=np.uint8).reshape(-1, 32),
                              np.ascontiguousarray(local_verdicts, dtype=np.uint8).reshape(-1, 1)], axis=1)
-    allp = all_gather_bytes(packed, counts, device=device, group=group)
+    allp = all_gather_bytes(packed, counts, gather_fn)
     return allp[:, :32].copy(), allp[:, 32].copy()
+
+
+def unpack_gathered(all_blocks: np.ndarray, n_sessions_per_rank: int, world: int):
+    """Split the buffer ``ahv_gather_results_dev`` fills (copied to the host) into roots [world*S, 32] and
+    verdicts [world*S]: rank r's block is S*32 root bytes, then S verdict bytes, padded to 16 bytes."""
+    S = n_sessions_per_rank
+    stride = (33 * S + 15) & ~15
+    blocks = np.asarray(all_blocks, dtype=np.uint8).reshape(world, stride)
+    roots = blocks[:, : 32 * S].reshape(world * S, 32).copy()
+    verdicts = blocks[:, 32 * S: 33 * S].reshape(world * S).copy()
+    return roots, verdicts
 
 
 # ---------------------------------------------------------------------------- liability batches

@@ -260,6 +260,34 @@ int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets /* n+1 
                     uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos /* n, or NULL */,
                     uint32_t flags);
 
+/* ------------------------------------------------------------------ multi-GPU (one process per GPU)
+ *
+ * Sessions shard across GPUs with no data-path exchange; the one exchange step collects every
+ * rank's roots and verdicts.  The communicator (NCCL, opened at run time from libnccl.so.2 or the path in
+ * AHV_NCCL_LIB) belongs to the context.  No counterpart in the reference: it is a single-process library;
+ * the call these stand in for is the loop that would visit every session's CommitmentEngine record
+ * (audit/commitment.py:42-64) once sessions live on several devices.
+ *
+ *   ahv_comm_unique_id   rank 0 makes the 128-byte id; the launcher hands it to the other ranks (file, env, ...)
+ *   ahv_comm_init        every rank, same id: collective, returns when all `world` ranks have joined.
+ *                        world == 1 needs no id and no NCCL.
+ *   ahv_comm_all_gather(_dev)  recv[r*bytes .. (r+1)*bytes) = rank r's send buffer; _dev is asynchronous on
+ *                        the ctx stream, the host form stages, gathers, copies back and synchronises.
+ *   ahv_gather_results_dev  ONE all-gather per step: rank r's block of `ahv_gather_stride(S)` bytes in d_all
+ *                        holds its S roots (32*S bytes) followed by its S verdict bytes (zero padded to a
+ *                        multiple of 16); d_all has world * stride bytes.  d_verdict may be NULL (zeros).
+ */
+#define AHV_COMM_ID_BYTES 128
+int ahv_comm_unique_id(uint8_t *out_id /* AHV_COMM_ID_BYTES */);
+int ahv_comm_init(ahv_ctx *ctx, int world, int rank, const uint8_t *id /* AHV_COMM_ID_BYTES */);
+int ahv_comm_destroy(ahv_ctx *ctx);
+int ahv_comm_info(ahv_ctx *ctx, int *world, int *rank, int *nccl_version); /* any pointer may be NULL */
+int ahv_comm_all_gather_dev(ahv_ctx *ctx, const void *d_send, void *d_recv, uint64_t bytes_per_rank);
+int ahv_comm_all_gather(ahv_ctx *ctx, const void *send, void *recv, uint64_t bytes_per_rank);
+uint64_t ahv_gather_stride(uint64_t n_sessions);
+int ahv_gather_results_dev(ahv_ctx *ctx, const uint8_t *d_roots /* S*32 */, const uint8_t *d_verdict /* S or NULL */,
+                           uint64_t n_sessions, uint8_t *d_all /* world * ahv_gather_stride(S) */);
+
 /* ------------------------------------------------------------------ liability / rings
  *
  * ahv_sigma_eff_rings: VouchingEngine.compute_sigma_eff for every agent of one session
@@ -270,7 +298,11 @@ int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets /* n+1 
  *   (vouching.py:34-38; times in microseconds since the epoch).
  *   sum is sequential fp64 from 0.0; sigma_eff = sigma + (omega * sum), two roundings;
  *   result = (1.0 < x) ? 1.0 : x  (Python min(), NaN kept).
- *   out_near[a] = 1 when sigma_eff lies within 1e-6 (relative) of 0.60 or 0.95.
+ *   Rows of more than 512 records (option "sigma_long_cut") are summed in a fixed parallel shape instead
+ *   (256 strided partials, then a fixed tree: deterministic, within a few ulp of the sequential sum; the
+ *   run contract allows 1e-6 relative); option "sigma_exact" = 1 keeps the sequential order for every row.
+ *   out_near[a] = 1 when sigma_eff lies within 1e-6 (relative) of 0.60 or 0.95: the agents whose ring could
+ *   differ from the reference's under that tolerance.
  */
 int ahv_sigma_eff_rings(ahv_ctx *ctx, const uint32_t *rowptr /* A+1 */, const double *bonded,
                         const uint8_t *active, const int64_t *expiry, int64_t now, const double *sigma,
@@ -394,6 +426,10 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "slash_variant" 0/1/2 slashing: lane per small session + warp per larger one (default 0) / warp per session on
  *                   global memory only (1) / warp per session, staged in shared memory where it fits (2)
  *   "sigma_variant" 0/1 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1)
+ *   "sigma_exact" 0/1   sigma_eff: 1 = every row summed left to right like the reference (bit-identical, but one very long
+ *                   row then bounds the pass); 0 (default) = rows longer than "sigma_long_cut" edges are summed by a whole
+ *                   CTA in a fixed, input-independent shape (a few ulp from the reference, same result every run)
+ *   "sigma_long_cut" 32..  that row length (default 512)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);
 

@@ -161,3 +161,49 @@ def check_slash_against_golden(cases, golden_cases, b, out):
         for pos in range(e_base, int(b["rowptr"][a_lo + A])):
             ci, k = b["edge_of"][pos]
             assert int(active[pos]) == g["active"][k], (s, k)
+
+
+# ---- sigma_eff: the fixed-shape sum the CUDA path uses for rows longer than "sigma_long_cut" -------------
+SIGMA_LONG_CUT = 512
+
+
+def fixed_shape_row_sum(vals: np.ndarray) -> float:
+    """csrc/ahv_liability.cu (k_sigma_eff_tiled, PAR): 256 partials over row positions p, p+256, ... added in
+    that order; each warp of 32 partials reduced by an xor butterfly (strides 16, 8, 4, 2, 1); the 8 warp
+    sums added left to right.  ``vals`` = the row's contributions (+0.0 for a record that is not live)."""
+    d = len(vals)
+    pad = (-d) % 256
+    m = np.concatenate([np.asarray(vals, np.float64), np.zeros(pad)]).reshape(-1, 256)
+    part = np.zeros(256)
+    with np.errstate(all="ignore"):
+        for r in m:
+            part = part + r
+        x = part.reshape(8, 32).copy()
+        idx = np.arange(32)
+        for o in (16, 8, 4, 2, 1):
+            x = x + x[:, idx ^ o]
+        t = x[0, 0]
+        for w in range(1, 8):
+            t = t + x[w, 0]
+    return float(t)
+
+
+def sigma_expected_default_path(exact, rowptr, bonded, active, expiry, now, sigma, omega, consensus, current_ring,
+                                cut: int = SIGMA_LONG_CUT):
+    """What the default (non-exact) CUDA path must return, bit for bit: the oracle's result ``exact``
+    (sigma_eff, ring, demote, near) with the rows longer than ``cut`` recomputed in the fixed shape."""
+    se, ring, dem, near = (np.array(x, copy=True) for x in exact)
+    rp = np.asarray(rowptr, np.int64)
+    long_rows = np.nonzero(np.diff(rp) > cut)[0]
+    with np.errstate(all="ignore"):
+        for a in long_rows:
+            sl = slice(rp[a], rp[a + 1])
+            live = (np.asarray(active[sl]) != 0) & ~((np.asarray(expiry[sl]) != EXPIRY_NONE) & (now > np.asarray(expiry[sl])))
+            vals = np.where(live, 0.0 + np.asarray(bonded[sl], np.float64), 0.0)
+            s = np.float64(sigma[a]) + np.float64(omega[a]) * np.float64(fixed_shape_row_sum(vals))
+            s = np.float64(1.0) if 1.0 < s else s
+            se[a] = s
+            ring[a] = 1 if (s > 0.95 and consensus[a]) else (2 if s > 0.60 else 3)
+            dem[a] = 1 if (2 if s > 0.60 else 3) > int(current_ring[a]) else 0
+            near[a] = 1 if (abs(s - 0.60) <= 1e-6 * 0.60 or abs(s - 0.95) <= 1e-6 * 0.95) else 0
+    return se, ring, dem, near, long_rows

@@ -9,7 +9,7 @@ import pytest
 
 import recipes
 import workloads
-from helpers import chain_preimages, config2_session, hexes, pack_sessions
+from helpers import chain_preimages, config2_session, hexes, pack_sessions, sigma_expected_default_path
 from oracle import audit_oracle as ao
 from oracle import coracle as co
 from oracle import liability_oracle as lo
@@ -512,31 +512,56 @@ def test_sigma_eff_golden_graphs(ctx, liability_golden):
         assert list(ring) == gr["ring"] and [bool(x) for x in dem] == gr["demote"]
 
 
-@pytest.mark.parametrize("variant", [1, 0])
-def test_sigma_eff_config4_shape_vs_oracle(ctx, variant):
-    g = workloads.config4_graph(50_000, 500_000)
-    # a few very long rows (beyond one shared-memory chunk) and NaN / inf / -0.0 amounts
-    g["bonded"][:20] = [float("nan"), float("inf"), -0.0, 0.0, 1e308, 1e308, -1e308, 5e-324, 1.0, -1.0] * 2
-    ctx.set_option("sigma_variant", variant)
-    try:
-        got = ctx.sigma_eff_rings(g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"],
-                                  g["consensus"], g["current_ring"])
-    finally:
-        ctx.set_option("sigma_variant", 1)
-    want = co.sigma_eff_rings(g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"],
-                              g["consensus"], g["current_ring"])
+def _check_sigma_default_path(ctx, args, want):
+    """The default sigma_eff path against the oracle: rows up to the cut bit-identical; longer rows within the
+    1e-6 relative tolerance of north_star AND bit-identical to the fixed reduction shape the kernel documents;
+    rings / demotion equal to the reference's wherever the agent is not on the near-threshold list."""
+    got = ctx.sigma_eff_rings(*args)
+    exp = sigma_expected_default_path(want, *args)
+    long_rows = exp[4]
+    short = np.ones(len(want[0]), bool); short[long_rows] = False
+    assert np.array_equal(got[0][short], want[0][short], equal_nan=True)
     fin = np.isfinite(want[0])
     rel = np.abs(got[0][fin] - want[0][fin]) / np.maximum(np.abs(want[0][fin]), 1e-300)
     assert rel.max() <= SIGMA_REL_TOL
+    assert np.array_equal(got[0], exp[0], equal_nan=True)          # the documented shape, bit for bit
+    for g_, e_ in zip(got[1:], exp[1:4]):
+        assert np.array_equal(g_, e_)
+    listed = (got[3] != 0) | (want[3] != 0)
+    assert np.array_equal(got[1][~listed], want[1][~listed]) and np.array_equal(got[2][~listed], want[2][~listed])
+    return got, long_rows, float(rel.max())
+
+
+@pytest.mark.parametrize("mode", ["default", "exact", "row_per_thread"])
+def test_sigma_eff_config4_shape_vs_oracle(ctx, mode):
+    g = workloads.config4_graph(50_000, 500_000)
+    # a few very long rows (beyond one shared-memory chunk) and NaN / inf / -0.0 amounts
+    g["bonded"][:20] = [float("nan"), float("inf"), -0.0, 0.0, 1e308, 1e308, -1e308, 5e-324, 1.0, -1.0] * 2
+    args = (g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"], g["consensus"],
+            g["current_ring"])
+    want = co.sigma_eff_rings(*args)
+    if mode == "default":
+        _, long_rows, _ = _check_sigma_default_path(ctx, args, want)
+        assert len(long_rows) > 10
+        return
+    ctx.set_option("sigma_exact", 1)
+    ctx.set_option("sigma_variant", 0 if mode == "row_per_thread" else 1)
+    try:
+        got = ctx.sigma_eff_rings(*args)
+    finally:
+        ctx.set_option("sigma_variant", 1)
+        ctx.set_option("sigma_exact", 0)
     assert np.array_equal(got[0], want[0], equal_nan=True)  # sequential fp64, no FMA: bit-identical
     for a, b in zip(got[1:], want[1:]):
         assert np.array_equal(a, b)                        # rings, demote flags, near-threshold list
 
 
 def test_sigma_eff_long_and_empty_rows(ctx):
-    """Rows far longer than one shared-memory chunk (2048 edges), empty rows, a partial last CTA."""
+    """Rows far longer than one shared-memory chunk (2048 edges), rows around the parallel-sum cut, several
+    long rows inside one chunk, empty rows, a partial last CTA."""
     rng = np.random.default_rng(4)
-    deg = np.concatenate([[5000, 0, 0, 3000, 1, 2047, 2048, 2049, 0, 9000], rng.integers(0, 30, 700)])
+    deg = np.concatenate([[5000, 0, 0, 3000, 1, 2047, 2048, 2049, 0, 9000, 512, 513, 514, 600, 520, 0, 513, 767, 768, 769],
+                          rng.integers(0, 30, 700), [513, 40000, 513]])
     A = len(deg)
     rowptr = np.concatenate([[0], np.cumsum(deg)]).astype(np.uint32)
     E = int(rowptr[-1])
@@ -546,14 +571,45 @@ def test_sigma_eff_long_and_empty_rows(ctx):
     args = (rowptr, bonded, active, expiry, 1000, rng.random(A), rng.choice([0.2, 0.65, 0.95], A),
             (rng.random(A) < 0.5).astype(np.uint8), rng.integers(1, 4, A).astype(np.uint8))
     want = co.sigma_eff_rings(*args)
-    for variant in (1, 0):
-        ctx.set_option("sigma_variant", variant)
+    _check_sigma_default_path(ctx, args, want)
+    for cut in (32, 100, 4096):                             # other cuts: same contract
+        ctx.set_option("sigma_long_cut", cut)
         try:
             got = ctx.sigma_eff_rings(*args)
         finally:
-            ctx.set_option("sigma_variant", 1)
-        for a, b in zip(got, want):
-            assert np.array_equal(a, b)
+            ctx.set_option("sigma_long_cut", 512)
+        exp = sigma_expected_default_path(want, *args, cut=cut)
+        assert np.array_equal(got[0], exp[0]) and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:4]))
+    ctx.set_option("sigma_exact", 1)
+    try:
+        for variant in (1, 0):
+            ctx.set_option("sigma_variant", variant)
+            got = ctx.sigma_eff_rings(*args)
+            for a, b in zip(got, want):
+                assert np.array_equal(a, b)
+    finally:
+        ctx.set_option("sigma_variant", 1)
+        ctx.set_option("sigma_exact", 0)
+
+
+def test_sigma_eff_config4_full_size(ctx):
+    """BASELINE configs[3] at its stated size: 10^6 agents, 10^7 vouch records (Zipf-like in-degree, longest row
+    14 017), against the C oracle: exact mode bit-identical everywhere; default mode as _check_sigma_default_path."""
+    g = workloads.config4_graph(1_000_000, 10_000_000)
+    args = (g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"], g["consensus"],
+            g["current_ring"])
+    assert len(g["sigma"]) == 1_000_000 and int(g["rowptr"][-1]) == 10_000_000
+    want = co.sigma_eff_rings(*args)
+    _, long_rows, rel = _check_sigma_default_path(ctx, args, want)
+    assert len(long_rows) > 300 and int(np.diff(g["rowptr"].astype(np.int64)).max()) > 10_000
+    ctx.set_option("sigma_exact", 1)
+    try:
+        got = ctx.sigma_eff_rings(*args)
+    finally:
+        ctx.set_option("sigma_exact", 0)
+    assert np.array_equal(got[0], want[0], equal_nan=True)
+    for a, b in zip(got[1:], want[1:]):
+        assert np.array_equal(a, b)
 
 
 def test_liability_matrix_and_exposure(ctx, liability_golden):

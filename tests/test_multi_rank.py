@@ -42,22 +42,38 @@ def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 
 
+def _gloo_gather(world):
+    """The transport of the CPU tests: a gloo all-gather with the signature sharding's gather_fn has
+    (on the GPU box the default is the library's own NCCL all-gather, Context.comm_all_gather)."""
+    import torch
+    import torch.distributed as dist
+
+    def gather(local: np.ndarray) -> np.ndarray:
+        t = torch.from_numpy(np.ascontiguousarray(local))
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return np.stack([o.numpy() for o in out])
+    return gather
+
+
 def _worker(rank, world, port, n, n_sessions, q):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
+    gather = _gloo_gather(world)
     try:
         rng = np.random.default_rng(99)
         digs = rng.integers(0, 256, (n, 32), dtype=np.uint8)            # every rank can regenerate the input
         plan = sharding.plan_tree(n, world)
         lo, hi = plan["ranges"][rank]
         mine = digs[lo << plan["k"]: min(hi << plan["k"], n)]
-        root, _ = sharding.sharded_tree_root(mine, n, rank, world, merkle_fn=co.merkle_roots)
+        root, _ = sharding.sharded_tree_root(mine, n, rank, world, merkle_fn=co.merkle_roots, gather_fn=gather)
         # session sharding: each rank "computes" roots/verdicts of its own sessions, then one gather
         sess_roots = rng.integers(0, 256, (n_sessions, 32), dtype=np.uint8)
         sess_verd = (rng.random(n_sessions) < 0.9).astype(np.uint8)
         s0, s1 = sharding.shard_range(n_sessions, world, rank)
-        all_r, all_v = sharding.gather_session_results(sess_roots[s0:s1], sess_verd[s0:s1], n_sessions, rank, world)
+        all_r, all_v = sharding.gather_session_results(sess_roots[s0:s1], sess_verd[s0:s1], n_sessions, rank, world,
+                                                            gather_fn=gather)
         ok = np.array_equal(all_r, sess_roots) and np.array_equal(all_v, sess_verd)
         q.put((rank, root, ok))
     finally:

@@ -1,0 +1,16 @@
+#!/bin/bash
+# ncu --set full of the kernels VERDICT r01 found unprofiled (run only after the plain run exited 0).
+# usage: tools/prof_kernels.sh <round-tag>   -> gpurun_out/prof_<tag>_<kernel>.ncu-rep
+TAG=${1:-r02}
+mkdir -p gpurun_out
+python tools/prof_kernels.py > gpurun_out/prof_plain_$TAG.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/prof_plain_$TAG.log; exit 1; }
+prof() {   # name, workload, kernel regex, skip, count
+  ncu --set full --clock-control none --import-source on -k regex:"$3" -s $4 -c $5 -f -o gpurun_out/prof_${TAG}_$1 \
+      python tools/prof_kernels.py $2 > gpurun_out/prof_${TAG}_$1.log 2>&1
+  echo "$1 rc=$?"
+}
+prof sigma sigma 'k_sigma_eff_tiled' 1 5          # launches 2,3 = Zipf; 4,5,6 = uniform
+prof var var 'k_sha256_var' 1 1
+prof chain chain 'k_chain_capture' 1 1
+prof tree tree 'k_merkle_level|k_merkle_top' 12 12
+ls -la gpurun_out | head -40
