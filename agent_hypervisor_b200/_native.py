@@ -70,6 +70,7 @@ SIGNATURES = {
     "ahv_dev_alloc": (C.c_int, [_vp, _u64, C.POINTER(_vp)]),
     "ahv_dev_free": (C.c_int, [_vp, _vp]),
     "ahv_host_alloc": (C.c_int, [_vp, _u64, C.POINTER(_vp)]),
+    "ahv_host_alloc_flags": (C.c_int, [_vp, _u64, C.c_uint32, C.POINTER(_vp)]),
     "ahv_host_free": (C.c_int, [_vp, _vp]),
     "ahv_memcpy_h2d": (C.c_int, [_vp, _vp, _vp, _u64]),
     "ahv_memcpy_d2h": (C.c_int, [_vp, _vp, _vp, _u64]),
@@ -88,7 +89,8 @@ SIGNATURES = {
     "ahv_verify_chains": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ahv_verify_chains_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _u64, _u64, _vp,
                                         _vp, _vp, _vp, _vp, _vp]),
-    "ahv_audit_sessions": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ahv_audit_sessions": (C.c_int, [_vp, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _vp,
+                                     _vp]),
     "ahv_slash_cascade": (C.c_int, [_vp, _vp]),
     "ahv_slash_cascade_dev": (C.c_int, [_vp, _vp]),
     "ahv_extract_parents_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp, _vp]),
@@ -206,10 +208,11 @@ class Context:
     def dev_free(self, dptr: int):
         self._check(self.lib.ahv_dev_free(self.h, _vp(dptr)), "ahv_dev_free")
 
-    def host_alloc(self, nbytes: int, dtype=np.uint8) -> np.ndarray:
-        """Pinned host array (freed with host_free(arr))."""
+    def host_alloc(self, nbytes: int, dtype=np.uint8, write_combined: bool = False) -> np.ndarray:
+        """Pinned host array (freed with host_free(arr)).  write_combined: upload-only buffer."""
         p = _vp()
-        self._check(self.lib.ahv_host_alloc(self.h, int(nbytes), C.byref(p)), "ahv_host_alloc")
+        self._check(self.lib.ahv_host_alloc_flags(self.h, int(nbytes), 1 if write_combined else 0, C.byref(p)),
+                    "ahv_host_alloc")
         buf = (C.c_uint8 * int(nbytes)).from_address(p.value)
         a = np.frombuffer(buf, dtype=np.uint8).view(dtype)
         a.flags.writeable = True
@@ -364,17 +367,22 @@ class Context:
 
     def audit_sessions(self, arena, offsets, parent_digests, parent_kind, session_rowptr=None, fixed_len: int = 0,
                        uniform_leaves: int = 0, n_sessions: Optional[int] = None, want_digests: bool = True, out=None,
-                       parent_pos=None):
+                       parent_pos=None, expected_roots=None):
         """Commit + verify on one upload (ahv_audit_sessions).  ``out`` may supply preallocated
-        (e.g. pinned) result arrays: dict with digests/roots/empty/verdict/first_bad/root_match."""
+        (e.g. pinned) result arrays: dict with digests/roots/empty/verdict/first_bad/root_match.
+        ``expected_roots`` [S,32]: the stored commitments ``root_match`` is checked against; without them
+        ``root_match`` only says that the verify pass rebuilt the roots the commit pass of this call produced."""
         arena = _arr(arena, np.uint8)
         offsets = _arr(offsets, np.uint64)
         par = _arr(parent_digests, np.uint8)
         kind = _arr(parent_kind, np.uint8)
         ppos = _arr(parent_pos, np.uint32)
         rp = _arr(session_rowptr, np.uint64)
+        exp = _arr(expected_roots, np.uint8)
         S = (len(rp) - 1) if rp is not None else int(n_sessions)
         n = int(rp[-1]) if rp is not None else S * int(uniform_leaves)
+        if exp is not None and exp.size != 32 * S:
+            raise ValueError(f"expected_roots holds {exp.size} bytes, need {32 * S}")
         o = dict(out or {})
         o.setdefault("digests", np.empty((n, 32), dtype=np.uint8) if want_digests else None)
         o.setdefault("roots", np.zeros((S, 32), dtype=np.uint8))
@@ -385,7 +393,7 @@ class Context:
         with self._lock:
             self._check(self.lib.ahv_audit_sessions(
                 self.h, _ptr(arena), _ptr(offsets), int(fixed_len), _ptr(par), _ptr(kind), _ptr(ppos), _ptr(rp), S,
-                int(uniform_leaves), _ptr(o["digests"]), _ptr(o["roots"]), _ptr(o["empty"]), _ptr(o["verdict"]),
+                int(uniform_leaves), _ptr(exp), _ptr(o["digests"]), _ptr(o["roots"]), _ptr(o["empty"]), _ptr(o["verdict"]),
                 _ptr(o["first_bad"]), _ptr(o["root_match"])), "ahv_audit_sessions")
         return o
 
@@ -404,7 +412,11 @@ class Context:
                                                    _ptr(digs), _ptr(par), _ptr(kind)), "ahv_chain_capture")
         return digs, par, kind
 
-    def sigma_eff_rings(self, rowptr, bonded, active, expiry, now: int, sigma, omega, consensus, current_ring):
+    def sigma_eff_rings(self, rowptr, bonded, active, expiry, now: int, sigma, omega, consensus, current_ring,
+                        exact: Optional[bool] = None):
+        """ahv_sigma_eff_rings.  exact=True: every row summed in the reference's order (bit-identical);
+        exact=False: rows longer than "sigma_long_cut" records take the fixed-shape warp sum (within a few ulp);
+        None: whatever the context's "sigma_exact" option says (default: the fast form)."""
         rp = _arr(rowptr, np.uint32)
         A = len(rp) - 1
         bonded = _arr(bonded, np.float64); active = _arr(active, np.uint8); expiry = _arr(expiry, np.int64)
@@ -413,10 +425,16 @@ class Context:
         o_s = np.empty(A, np.float64); o_r = np.empty(A, np.uint8)
         o_d = np.empty(A, np.uint8); o_n = np.empty(A, np.uint8)
         with self._lock:
-            self._check(self.lib.ahv_sigma_eff_rings(
-                self.h, _ptr(rp), _ptr(bonded), _ptr(active), _ptr(expiry), int(now), _ptr(sigma), _ptr(omega),
-                _ptr(consensus), _ptr(current_ring), A, _ptr(o_s), _ptr(o_r), _ptr(o_d), _ptr(o_n)),
-                "ahv_sigma_eff_rings")
+            if exact is not None:
+                self.set_option("sigma_exact", 1 if exact else 0)
+            try:
+                self._check(self.lib.ahv_sigma_eff_rings(
+                    self.h, _ptr(rp), _ptr(bonded), _ptr(active), _ptr(expiry), int(now), _ptr(sigma), _ptr(omega),
+                    _ptr(consensus), _ptr(current_ring), A, _ptr(o_s), _ptr(o_r), _ptr(o_d), _ptr(o_n)),
+                    "ahv_sigma_eff_rings")
+            finally:
+                if exact is not None:
+                    self.set_option("sigma_exact", 0)
         return o_s, o_r, o_d, o_n
 
     def exposure_sums(self, rowptr, bonded, active, expiry, now: int, compensated: Optional[bool] = None) -> np.ndarray:
@@ -553,11 +571,15 @@ _default_lock = threading.Lock()
 
 
 def get_context(device: Optional[int] = None) -> Context:
-    """Process-wide default context (device from AHV_DEVICE / LOCAL_RANK / 0)."""
+    """Process-wide default context (device from AHV_DEVICE / LOCAL_RANK / 0).  Asking for a different
+    device than the one the default context already lives on is an error: make a ``Context(device)``."""
     global _default_ctx
     with _default_lock:
         if _default_ctx is None:
             if device is None:
                 device = int(os.environ.get("AHV_DEVICE", os.environ.get("LOCAL_RANK", "0")))
             _default_ctx = Context(device)
+        elif device is not None and int(device) != _default_ctx.device:
+            raise ValueError(f"the default context is on device {_default_ctx.device}, not {device}; "
+                             f"create Context({device}) for another GPU")
         return _default_ctx

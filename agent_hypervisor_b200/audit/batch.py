@@ -63,17 +63,28 @@ class BatchAuditor:
                     commitment_engine.commit(e.session_id, r, list(participants or []), len(e._deltas))
         return roots
 
+    @staticmethod
+    def _roots_array(roots_hex: Sequence[Optional[str]], S: int):
+        """hex roots (None / anything that is not a 64-hex digest = no usable commitment) -> ([S,32] bytes, known[S])."""
+        if len(roots_hex) != S:
+            raise ValueError(f"{len(roots_hex)} expected roots for {S} sessions")
+        exp = np.zeros((S, 32), dtype=np.uint8)
+        known = np.zeros(S, dtype=bool)
+        for s, r in enumerate(roots_hex):
+            if isinstance(r, str) and len(r) == 64:
+                try:
+                    exp[s] = np.frombuffer(bytes.fromhex(r), dtype=np.uint8)
+                    known[s] = r == r.lower()            # hexdigest() is lowercase; any other string never matches
+                except ValueError:
+                    pass
+        return exp, known
+
     def verify(self, packed: PackedSessions, expected_roots_hex: Optional[Sequence[Optional[str]]] = None):
         """-> dict(verdict bool[S], first_bad int[S], digests, root_match bool[S] or None)."""
         fixed, uni = packed.uniform_shape()
         exp = None
         if expected_roots_hex is not None:
-            exp = np.zeros((packed.n_sessions, 32), dtype=np.uint8)
-            known = np.zeros(packed.n_sessions, dtype=bool)
-            for s, r in enumerate(expected_roots_hex):
-                if r:
-                    exp[s] = np.frombuffer(bytes.fromhex(r), dtype=np.uint8)
-                    known[s] = True
+            exp, known = self._roots_array(expected_roots_hex, packed.n_sessions)
         res = self.ctx.verify_chains(
             packed.arena, None if fixed else packed.offsets, packed.parents, packed.parent_kind,
             None if uni else packed.session_rowptr, fixed_len=fixed if fixed else 0, uniform_leaves=uni,
@@ -83,20 +94,27 @@ class BatchAuditor:
         res["verdict"] = res["verdict"].astype(bool)
         return res
 
-    def audit(self, packed: PackedSessions):
+    def audit(self, packed: PackedSessions, committed_roots_hex: Optional[Sequence[Optional[str]]] = None):
         """Commit + verify on ONE upload (``ahv_audit_sessions``): what an auditor replaying stored sessions
-        needs - every Merkle root (core.py:204-207) and every verify_chain verdict (audit/delta.py:136-152).
+        needs - every Merkle root (core.py:204-207), every verify_chain verdict (audit/delta.py:136-152) and,
+        when the archive's stored commitments are given (``committed_roots_hex``, one per session, None where
+        there is none), ``CommitmentEngine.verify`` of each rebuilt root against them (audit/commitment.py:59-64).
         The parents are read out of the pre-images on the device when the packer recorded their positions.
-        -> dict(digests, roots hex|None per session, verdict bool[S], first_bad int[S], root_match)."""
+        -> dict(digests, roots hex|None per session, verdict bool[S], first_bad int[S], root_match bool[S] or
+        None when no committed roots were given)."""
         fixed, uni = packed.uniform_shape()
         by_pos = packed.parent_pos is not None
+        exp = known = None
+        if committed_roots_hex is not None:
+            exp, known = self._roots_array(committed_roots_hex, packed.n_sessions)
         o = self.ctx.audit_sessions(
             packed.arena, None if fixed else packed.offsets,
             None if by_pos else packed.parents, None if by_pos else packed.parent_kind,
             None if uni else packed.session_rowptr, fixed_len=fixed if fixed else 0, uniform_leaves=uni,
-            n_sessions=packed.n_sessions, parent_pos=packed.parent_pos if by_pos else None)
+            n_sessions=packed.n_sessions, parent_pos=packed.parent_pos if by_pos else None, expected_roots=exp)
         o["roots"] = [None if o["empty"][s] else o["roots"][s].tobytes().hex() for s in range(packed.n_sessions)]
         o["verdict"] = o["verdict"].astype(bool)
+        o["root_match"] = (o["root_match"].astype(bool) & known) if exp is not None else None
         return o
 
     def verify_engines(self, engines: Sequence) -> list[bool]:

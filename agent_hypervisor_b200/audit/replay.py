@@ -3,7 +3,7 @@
 What an auditor does to check an archive with the reference is, per session, rebuild every
 ``SemanticDelta``, call ``verify_chain`` (audit/delta.py:136-152: one ``json.dumps`` + SHA-256 per
 delta) and compare ``compute_merkle_root`` (:117-134) with the committed root
-(audit/commitment.py:59-64).  Here the archive arrives in chunks of columns; chunk k+1 is serialised
+(audit/commitment.py:59-64; pass the archive's stored roots with each chunk to have that compare done).  Here the archive arrives in chunks of columns; chunk k+1 is serialised
 by the C++ packer (``ahv_pack_deltas``, all host threads) into one pinned buffer set while chunk k,
 in the other set, goes through ``ahv_audit_sessions`` (upload, leaf hashes, trees, link check,
 results back).  Both calls release the GIL, so one helper thread is enough.
@@ -58,7 +58,7 @@ class ReplayPipeline:
     def __exit__(self, *exc):
         self.close()
 
-    def _pack(self, k: int, cols: dict, session_rowptr) -> tuple:
+    def _pack(self, k: int, cols: dict, session_rowptr, committed_roots=None) -> tuple:
         bs = self._sets[k % 2]
         n = int(cols["n"])
         rp = np.asarray(session_rowptr, dtype=np.uint64)
@@ -68,11 +68,16 @@ class ReplayPipeline:
                              f"({self.limits[1]} / {self.limits[2]}), or session_rowptr does not end at n")
         arena, offsets, ppos = pack_columns(cols, arena=bs.arena, offsets=bs.offsets, parent_pos=bs.parent_pos)
         bs.rowptr[: S + 1] = rp
-        return n, S, arena, offsets, ppos
+        exp = None
+        if committed_roots is not None:
+            exp = np.ascontiguousarray(committed_roots, dtype=np.uint8).reshape(S, 32)
+        return n, S, arena, offsets, ppos, exp
 
     def run(self, chunks: Iterable[tuple], copy: bool = True) -> Iterator[dict]:
-        """chunks: iterable of ``(cols, session_rowptr)`` (``cols`` as for ``pack_columns``).  Yields, per
-        chunk, dict(digests [n,32], roots hex|None per session, verdict bool[S], first_bad int64[S]).
+        """chunks: iterable of ``(cols, session_rowptr)`` or ``(cols, session_rowptr, committed_roots)``
+        (``cols`` as for ``pack_columns``; ``committed_roots`` = the archive's stored Merkle roots, uint8 [S,32]).
+        Yields, per chunk, dict(digests [n,32], roots hex|None per session, verdict bool[S], first_bad int64[S],
+        root_match bool[S] against the committed roots, or None when the chunk carried none).
         With ``copy=False`` the arrays are views into the pinned buffers, valid until the chunk after the
         next one is requested."""
         it = iter(chunks)
@@ -91,7 +96,7 @@ class ReplayPipeline:
         k = 0
         fut = self._pool.submit(self._pack, k, *nxt)
         while fut is not None:
-            n, S, arena, offsets, ppos = fut.result()
+            n, S, arena, offsets, ppos, exp = fut.result()
             bs = self._sets[k % 2]
             try:
                 nxt = next(it)
@@ -100,9 +105,11 @@ class ReplayPipeline:
                 fut = None
             out = {key: (v[: 32 * n].reshape(n, 32) if key == "digests" else
                          v[: 32 * S].reshape(S, 32) if key == "roots" else v[:S]) for key, v in bs.out.items()}
-            o = self.ctx.audit_sessions(arena, offsets, None, None, bs.rowptr[: S + 1], parent_pos=ppos, out=out)
+            o = self.ctx.audit_sessions(arena, offsets, None, None, bs.rowptr[: S + 1], parent_pos=ppos, out=out,
+                                        expected_roots=exp)
             res = dict(digests=o["digests"], first_bad=o["first_bad"], verdict=o["verdict"].astype(bool),
-                       roots=[None if o["empty"][s] else o["roots"][s].tobytes().hex() for s in range(S)])
+                       roots=[None if o["empty"][s] else o["roots"][s].tobytes().hex() for s in range(S)],
+                       root_match=(o["root_match"].astype(bool) & ~o["empty"].astype(bool)) if exp is not None else None)
             if copy:
                 res["digests"] = np.array(res["digests"]); res["first_bad"] = np.array(res["first_bad"])
             yield res

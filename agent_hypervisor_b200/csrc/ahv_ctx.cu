@@ -132,7 +132,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     AHV_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     AHV_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     AHV_CUDA(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 4; ++i) AHV_CUDA(cudaEventCreateWithFlags(&c->ev_copy[i], cudaEventDisableTiming));
+    for (int i = 0; i < AHV_PIPE_EVENTS; ++i) AHV_CUDA(cudaEventCreateWithFlags(&c->ev_pipe[i], cudaEventDisableTiming));
     for (int i = 0; i < AHV_MAX_TIMERS; ++i) {
         AHV_CUDA(cudaEventCreate(&c->t_start[i]));
         AHV_CUDA(cudaEventCreate(&c->t_stop[i]));
@@ -145,7 +145,8 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_compress = 1;
     c->opt_sigma_variant = 1;
     c->opt_sigma_exact = 0;
-    c->opt_sigma_long_cut = 512;
+    c->opt_sigma_long_cut = 32;
+    c->opt_sigma_chunk = 2048;
     c->opt_slash_variant = 0;
     c->opt_blocking_sync = 0;
     *out_ctx = c;
@@ -163,7 +164,7 @@ void ahv_destroy(ahv_ctx *ctx)
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->io) cudaFree(ctx->io);
     if (ctx->one_out) cudaFreeHost(ctx->one_out);
-    for (int i = 0; i < 4; ++i) cudaEventDestroy(ctx->ev_copy[i]);
+    for (int i = 0; i < AHV_PIPE_EVENTS; ++i) cudaEventDestroy(ctx->ev_pipe[i]);
     for (int i = 0; i < AHV_MAX_TIMERS; ++i) {
         cudaEventDestroy(ctx->t_start[i]);
         cudaEventDestroy(ctx->t_stop[i]);
@@ -226,6 +227,22 @@ int ahv_host_alloc(ahv_ctx *ctx, uint64_t bytes, void **out_hptr)
     if (e != cudaSuccess) {
         cudaGetLastError();
         set_error("cudaHostAlloc(%llu) failed: %s", (unsigned long long)bytes, cudaGetErrorString(e));
+        return AHV_E_NOMEM;
+    }
+    return AHV_OK;
+}
+
+int ahv_host_alloc_flags(ahv_ctx *ctx, uint64_t bytes, uint32_t flags, void **out_hptr)
+{
+    AHV_TRY(use_device(ctx));
+    AHV_REQUIRE(out_hptr, "out_hptr is null");
+    AHV_REQUIRE((flags & ~(uint32_t)AHV_HOST_WRITE_COMBINED) == 0, "unknown host allocation flag");
+    *out_hptr = nullptr;
+    const unsigned f = (flags & AHV_HOST_WRITE_COMBINED) ? cudaHostAllocWriteCombined : cudaHostAllocDefault;
+    cudaError_t e = cudaHostAlloc(out_hptr, bytes ? bytes : 1, f);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("cudaHostAlloc(%llu, flags %u) failed: %s", (unsigned long long)bytes, flags, cudaGetErrorString(e));
         return AHV_E_NOMEM;
     }
     return AHV_OK;
@@ -305,8 +322,11 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
         AHV_REQUIRE(value == 0 || value == 1, "sigma_exact must be 0 or 1");
         ctx->opt_sigma_exact = value;
     } else if (!strcmp(key, "sigma_long_cut")) {
-        AHV_REQUIRE(value >= 32 && value <= 0x7fffffff, "sigma_long_cut must be 32..2^31-1");
+        AHV_REQUIRE(value >= 4 && value <= 0x7fffffff, "sigma_long_cut must be 4..2^31-1");
         ctx->opt_sigma_long_cut = value;
+    } else if (!strcmp(key, "sigma_chunk")) {
+        AHV_REQUIRE(value == 1024 || value == 2048, "sigma_chunk must be 1024 or 2048");
+        ctx->opt_sigma_chunk = value;
     } else if (!strcmp(key, "compress")) {
         AHV_REQUIRE(value == 0 || value == 1, "compress must be 0 or 1");
         ctx->opt_compress = value;

@@ -234,8 +234,9 @@ int ahv_verify_chains(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offset
 // per-chunk row pointers relative to the chunk's first leaf.
 int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
                        const uint8_t *parents, const uint8_t *kind, const uint32_t *parent_pos,
-                       const uint64_t *rowptr, uint64_t S, uint64_t uniform, uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty,
-                       uint8_t *out_verdict, int64_t *out_first_bad, uint8_t *out_match)
+                       const uint64_t *rowptr, uint64_t S, uint64_t uniform, const uint8_t *expected_roots,
+                       uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty, uint8_t *out_verdict,
+                       int64_t *out_first_bad, uint8_t *out_match)
 {
     AHV_TRY(use_device(ctx));
     if (S == 0) return AHV_OK;
@@ -257,7 +258,7 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
         return AHV_OK;
     }
     AHV_TRY(io_reserve(ctx, p256(ab + 16) + p256(8 * (n + 1)) + p256(8 * (S + 1)) + 2 * p256(32 * n) + p256(n) + p256(4 * n) +
-                                2 * p256(32 * S) + 3 * p256(S) + p256(8 * S) + p256(8 * (S + 64))));
+                                3 * p256(32 * S) + 3 * p256(S) + p256(8 * S) + p256(8 * (S + 64))));
     uint8_t *d_arena = (uint8_t *)io_take(ctx, ab + 16);
     uint32_t *d_pos = from_pos ? (uint32_t *)io_take(ctx, 4 * n) : nullptr;
     uint64_t *d_off = offsets ? (uint64_t *)io_take(ctx, 8 * (n + 1)) : nullptr;
@@ -267,12 +268,13 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
     uint8_t *d_dig = (uint8_t *)io_take(ctx, 32 * n);
     uint8_t *d_roots = (uint8_t *)io_take(ctx, 32 * S);
     uint8_t *d_roots_v = (uint8_t *)io_take(ctx, 32 * S);
+    uint8_t *d_exp = expected_roots ? (uint8_t *)io_take(ctx, 32 * S) : nullptr;   // stored commitments to verify against
     uint8_t *d_empty = (uint8_t *)io_take(ctx, S);
     uint8_t *d_verdict = (uint8_t *)io_take(ctx, S);
     uint8_t *d_match = (uint8_t *)io_take(ctx, S);
     int64_t *d_fb = (int64_t *)io_take(ctx, 8 * S);
     if (!d_arena || (from_pos && !d_pos) || (offsets && !d_off) || (!uniform && !d_rp) || !d_par || !d_kind || !d_dig || !d_roots ||
-        !d_roots_v || !d_empty || !d_verdict || !d_match || !d_fb) {
+        !d_roots_v || (expected_roots && !d_exp) || !d_empty || !d_verdict || !d_match || !d_fb) {
         set_error("internal: staging slab too small");
         return AHV_E_NOMEM;
     }
@@ -290,9 +292,10 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
             AHV_CUDA(cudaMemcpyAsync(d_par, parents, 32 * n, cudaMemcpyHostToDevice, st));
             AHV_CUDA(cudaMemcpyAsync(d_kind, kind, n, cudaMemcpyHostToDevice, st));
         }
+        if (d_exp) AHV_CUDA(cudaMemcpyAsync(d_exp, expected_roots, 32 * S, cudaMemcpyHostToDevice, st));
         AHV_TRY(ahv_commit_dev(ctx, d_arena, ab, d_off, fixed_len, d_rp, S, n, uniform, maxl, d_dig, d_roots, d_empty));
         AHV_TRY(ahv_verify_chains_dev(ctx, d_arena, ab, d_off, fixed_len, d_par, d_kind, d_rp, S, n, uniform, maxl,
-                                      d_roots, d_verdict, d_fb, nullptr, d_roots_v, d_match));
+                                      d_exp ? d_exp : d_roots, d_verdict, d_fb, nullptr, d_roots_v, d_match));
         if (out_digests) AHV_CUDA(cudaMemcpyAsync(out_digests, d_dig, 32 * n, cudaMemcpyDeviceToHost, st));
         AHV_CUDA(cudaMemcpyAsync(out_roots, d_roots, 32 * S, cudaMemcpyDeviceToHost, st));
         if (out_empty) AHV_CUDA(cudaMemcpyAsync(out_empty, d_empty, S, cudaMemcpyDeviceToHost, st));
@@ -309,28 +312,17 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
     if (nchunk < 2) nchunk = 2;
     if (nchunk > MAXC) nchunk = MAXC;
     const uint64_t per = (S + nchunk - 1) / nchunk;
-    struct Events {                       // destroyed on every exit path, after the streams have drained
+    static_assert(2 * MAXC <= AHV_PIPE_EVENTS, "the context's event pool must cover every chunk");
+    struct Drain {                        // on every exit path the three streams have drained before the buffers are reused
         ahv_ctx *ctx;
-        cudaEvent_t in[MAXC], done[MAXC];
-        int n = 0;
-        ~Events()
+        ~Drain()
         {
             cudaStreamSynchronize(ctx->copy_stream);
             cudaStreamSynchronize(ctx->stream);
             cudaStreamSynchronize(ctx->d2h_stream);
-            for (int k = 0; k < n; ++k) {
-                cudaEventDestroy(in[k]);
-                cudaEventDestroy(done[k]);
-            }
         }
-    } ev;
-    ev.ctx = ctx;
-    cudaEvent_t *ev_in = ev.in, *ev_done = ev.done;
-    for (int k = 0; k < nchunk; ++k) {
-        AHV_CUDA(cudaEventCreateWithFlags(&ev_in[k], cudaEventDisableTiming));
-        AHV_CUDA(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
-        ev.n = k + 1;
-    }
+    } drain{ctx};
+    cudaEvent_t *ev_in = ctx->ev_pipe, *ev_done = ctx->ev_pipe + MAXC;     // made once in ahv_create
     // Ragged sessions: chunk k's tree works on ITS digests, so it needs row pointers relative to its first
     // leaf; they are laid out chunk after chunk (each with its own end entry) and uploaded with the chunk.
     std::vector<uint64_t> rel;
@@ -373,6 +365,7 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
                 AHV_CUDA(cudaMemcpyAsync(d_kind + l0, kind + l0, nc, cudaMemcpyHostToDevice, hs));
             }
         }
+        if (d_exp) AHV_CUDA(cudaMemcpyAsync(d_exp + 32 * s0, expected_roots + 32 * s0, 32 * Sc, cudaMemcpyHostToDevice, hs));
         AHV_CUDA(cudaEventRecord(ev_in[k], hs));
         AHV_CUDA(cudaStreamWaitEvent(ctx->stream, ev_in[k], 0));
         // byte offsets stay absolute (base d_arena); with fixed-size deltas the chunk's own base is passed
@@ -385,8 +378,8 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
                             d_roots + 32 * s0, d_empty + s0);
         if (rc == AHV_OK)
             rc = ahv_verify_chains_dev(ctx, a_k, ab, off_k, fixed_len, d_par + 32 * l0, d_kind + l0, d_rp_k, Sc, nc, uniform,
-                                       maxl, d_roots + 32 * s0, d_verdict + s0, d_fb + s0, nullptr, d_roots_v + 32 * s0,
-                                       d_match + s0);
+                                       maxl, (d_exp ? d_exp : d_roots) + 32 * s0, d_verdict + s0, d_fb + s0, nullptr,
+                                       d_roots_v + 32 * s0, d_match + s0);
         if (rc != AHV_OK) break;
         AHV_CUDA(cudaEventRecord(ev_done[k], ctx->stream));
         cudaStream_t ds = ctx->d2h_stream;

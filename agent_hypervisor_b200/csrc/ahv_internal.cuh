@@ -8,13 +8,14 @@
 #include "../../include/ahv.h"
 
 #define AHV_MAX_TIMERS 64
+#define AHV_PIPE_EVENTS 64
 
 struct ahv_ctx {
     int device;
     cudaStream_t stream;
     cudaStream_t copy_stream;     // H2D of the pipelined host entry point
     cudaStream_t d2h_stream;      // D2H of the pipelined host entry point (PCIe is full duplex)
-    cudaEvent_t ev_copy[4];       // chunk hand-off between copy_stream and stream
+    cudaEvent_t ev_pipe[AHV_PIPE_EVENTS];   // chunk hand-off events of the pipelined host entry (copy-in done / hashed)
     int sm_count;
     int clock_khz;
     uint64_t total_mem;
@@ -37,6 +38,7 @@ struct ahv_ctx {
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_sigma_exact;   // 1: every row summed in the reference's order (bit-identical); 0 (default): rows longer than opt_sigma_long_cut take the fixed-shape parallel sum
     int64_t opt_sigma_long_cut;// row length (edges) above which the parallel sum is used (default 512)
+    int64_t opt_sigma_chunk;   // edges per shared-memory chunk of the tiled sigma_eff kernel: 2048 (default) or 1024
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)
     int64_t opt_peak_ctas;     // CTAs of 256 threads per SM in the ahv_int_peak kernels (default 4)

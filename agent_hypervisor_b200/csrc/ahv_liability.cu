@@ -35,26 +35,31 @@ k_sigma_eff_rings(const uint32_t *__restrict__ rowptr, const double *__restrict_
     if (out_near) out_near[a] = (uint8_t)near_threshold(se);
 }
 
-// Tiled form (default): a CTA owns 256 consecutive agent rows.  Their edges are one contiguous
-// CSR range, streamed through shared memory in chunks with fully coalesced loads (phase 1: each
-// edge becomes its contribution, bonded or +0.0 when inactive/expired); then every thread adds
-// up the slice of its own row inside the chunk, in CSR order (phase 2).  Order of additions per
-// row is exactly the reference's, so results stay bit-identical; x + (+0.0) == x for every x the
-// running sum can hold (it starts at +0.0 and can never become -0.0).
+// Tiled form (default): a CTA of 128 threads owns 128 consecutive agent rows.  Their edges are one
+// contiguous CSR range; it arrives in shared memory in chunks of up to 2048 edges by THREE bulk
+// asynchronous copies per chunk (cp.async.bulk, the 1-D TMA path: one thread issues them, the bytes land
+// without passing through registers and complete on an mbarrier), so the copy costs next to no issue
+// slots and six CTAs fit an SM, their copy and sum phases overlapping.  Most tiles fit one chunk: one
+// wait, then every thread adds up its own row in CSR order.  The order of additions per row is exactly
+// the reference's (vouching.py:146-148), so results are bit-identical.  A record that is not live is
+// skipped, which equals adding +0.0: the running sum starts at +0.0 and can never become -0.0.
+// The bulk copies move whole 16-edge groups (16-byte alignment of all three arrays): a chunk grid starts
+// at the 16-edge boundary at or below the tile's first edge (those extra edges lie inside the arrays),
+// and the last, partial group of the tile is fetched with ordinary loads so nothing past the arrays'
+// ends is ever read.
 //
-// A row of d edges is d dependent fp64 additions (8.1 cycles each), so one very long row holds its
-// whole tile back: 14 017 edges = 58 us at best, longer than the rest of a 10^7-edge graph takes.
-// With PAR, rows longer than `long_cut` edges are therefore summed by the whole CTA in a FIXED shape
-// that depends on the row alone (not on tiling, chunking or scheduling, so it is the same run to run):
-//     partial[p] = live contributions at row positions p, p+256, p+512, ... added in that order   (p = 0..255)
-//     warp w     = xor-butterfly over partial[32w .. 32w+31] with strides 16, 8, 4, 2, 1
-//     row sum    = ((((((w0 + w1) + w2) + w3) + w4) + w5) + w6) + w7
-// which differs from the reference's left-to-right sum by a few ulp (north_star allows 1e-6
-// relative); agents whose sigma_eff lies within 1e-6 of a ring threshold are flagged in out_near
-// either way.  Rows up to `long_cut` keep the reference's order and stay bit-identical; option
-// sigma_exact=1 keeps it for every row.
-constexpr int SIG_ROWS = 256;
-constexpr int SIG_CHUNK = 2048;
+// A row of d edges is d dependent fp64 additions, so one long row holds its whole tile back (a row of
+// 14 017 edges alone costs more than the rest of a 10^7-edge graph).  With PAR, rows longer than
+// `long_cut` edges are therefore summed by one WARP each, in a FIXED shape that depends on the row alone
+// (not on tiling, chunking or scheduling, so it is the same run to run):
+//     partial[p] = live amounts at row positions p, p+32, p+64, ... added in that order   (p = 0..31)
+//     row sum    = xor-butterfly over the 32 partials with strides 16, 8, 4, 2, 1
+//                  (every lane ends with the same value; lane 0's is used)
+// which differs from the reference's left-to-right sum by a few ulp (north_star allows 1e-6 relative);
+// agents whose sigma_eff lies within 1e-6 of a ring threshold are flagged in out_near either way.  Rows
+// up to `long_cut` keep the reference's order and stay bit-identical; option sigma_exact=1 keeps it for
+// every row.
+constexpr int SIG_ROWS = 128;
 constexpr int SIG_WARPS = SIG_ROWS / 32;
 
 // Running sum of one row.  Plain: left-to-right fp64 additions (the explicit += loop of
@@ -82,10 +87,30 @@ template <> struct RowSum<true> {
     }
 };
 
+template <int CHUNK>
+struct alignas(128) SigStage {         // one chunk of edges as it lies in global memory
+    double b[CHUNK];                   // after the conversion pass: the amount each record contributes
+    int64_t x[CHUNK];
+    uint8_t a[CHUNK];
+};
+
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint32_t mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes), "r"(mbar) : "memory");
+}
+
+// amount a record contributes: bonded when live (vouching.py:34-38,186-197), else +0.0
+__device__ __forceinline__ double live_amount(double b, uint32_t active, int64_t x, int64_t now)
+{
+    const bool live = active && !((x != AHV_EXPIRY_NONE) && (now > x));
+    return live ? b : 0.0;
+}
+
 // MODE 0: sigma_eff + rings.  MODE 1: plain live sum of each row.  MODE 2: compensated live sum.
-// PAR (MODE 0 only): rows of more than long_cut edges take the fixed-shape parallel sum.
-template <int MODE, bool PAR>
-__global__ void __launch_bounds__(SIG_ROWS)
+// PAR (MODE 0 only): rows of more than long_cut edges take the fixed-shape warp sum.
+template <int MODE, bool PAR, int SIG_CHUNK>
+__global__ void __launch_bounds__(SIG_ROWS, SIG_CHUNK == 2048 ? 6 : 10)
 k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
                   const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
                   const double *__restrict__ sigma, const double *__restrict__ omega,
@@ -93,26 +118,58 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
                   double *__restrict__ out_sigma, uint8_t *__restrict__ out_ring, uint8_t *__restrict__ out_demote,
                   uint8_t *__restrict__ out_near, uint32_t long_cut)
 {
-    __shared__ double v[SIG_CHUNK];
-    __shared__ double wsum[SIG_WARPS];
-    __shared__ uint32_t wcount[SIG_WARPS];
+    extern __shared__ __align__(128) uint8_t sig_smem[];
+    SigStage<SIG_CHUNK> &st = *reinterpret_cast<SigStage<SIG_CHUNK> *>(sig_smem);
+    __shared__ __align__(8) uint64_t mbar_storage;
+    __shared__ double long_sum[SIG_ROWS];
     __shared__ uint32_t long_r0[SIG_ROWS], long_r1[SIG_ROWS];
     __shared__ uint16_t long_owner[SIG_ROWS];
+    __shared__ uint32_t wcount[SIG_WARPS];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_storage);
     const uint64_t a0 = (uint64_t)blockIdx.x * SIG_ROWS;
     const uint64_t a = a0 + tid;
     const bool valid = a < A;
     const uint64_t a_last = (a0 + SIG_ROWS < A) ? a0 + SIG_ROWS : A;
-    const uint32_t e_begin = rowptr[a0], e_end = rowptr[a_last];
-    const uint32_t my0 = valid ? rowptr[a] : e_end, my1 = valid ? rowptr[a + 1] : e_end;
-    RowSum<MODE == 2> acc;
+    const uint32_t e_begin = __ldg(rowptr + a0), e_end = __ldg(rowptr + a_last);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared.b64 [%0], %1;" ::"r"(mbar), "r"(1u) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // chunk grid from the 16-edge boundary at or below the first edge; copies issued by thread 0
+    const uint32_t base = e_begin & ~15u;
+    const uint32_t nchunk = (e_end > base) ? (e_end - base + SIG_CHUNK - 1) / SIG_CHUNK : 0;
+    auto issue = [&](uint32_t k) {                                  // thread 0 only
+        const uint32_t c0 = base + k * SIG_CHUNK;
+        const uint32_t cnt = (e_end - c0 > (uint32_t)SIG_CHUNK) ? (uint32_t)SIG_CHUNK : e_end - c0;
+        const uint32_t cnt16 = cnt & ~15u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(cnt16 * 17u) : "memory");
+        if (cnt16) {
+            bulk_g2s(st.b, bonded + c0, cnt16 * 8u, mbar);
+            bulk_g2s(st.x, expiry + c0, cnt16 * 8u, mbar);
+            bulk_g2s(st.a, active + c0, cnt16, mbar);
+        }
+    };
+    if (tid == 0 && nchunk) issue(0);
 
-    // list of this tile's long rows, in row order (usually empty)
+    const uint32_t my0 = valid ? __ldg(rowptr + a) : e_end, my1 = valid ? __ldg(rowptr + a + 1) : e_end;
+    // per-agent inputs are requested now, long before they are needed
+    double sg = 0.0, om = 0.0;
+    uint8_t cons = 0, ring_in = 0;
+    if (MODE == 0 && valid) {
+        sg = __ldg(sigma + a);
+        om = __ldg(omega + a);
+        if (out_ring) cons = __ldg(consensus + a);
+        if (out_demote) ring_in = __ldg(current_ring + a);
+    }
+
+    RowSum<MODE == 2> acc;
+    // list of this tile's long rows, in row order (usually empty); long row k belongs to warp k % 4
     const bool is_long = PAR && (my1 - my0 > long_cut);
     uint32_t n_long = 0;
     if (PAR) {
-        const uint32_t b = __ballot_sync(0xffffffffu, is_long);
-        if (lane == 0) wcount[wid] = __popc(b);
+        const uint32_t bal = __ballot_sync(0xffffffffu, is_long);
+        if (lane == 0) wcount[wid] = __popc(bal);
         __syncthreads();
         uint32_t before = 0;
 #pragma unroll
@@ -122,83 +179,91 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
             n_long += c;
         }
         if (is_long) {
-            const uint32_t k = before + __popc(b & ((1u << lane) - 1u));
+            const uint32_t k = before + __popc(bal & ((1u << lane) - 1u));
             long_r0[k] = my0;
             long_r1[k] = my1;
             long_owner[k] = (uint16_t)tid;
         }
-        // (made visible by the barrier after phase 1 of the first chunk: a long row has edges, so there is one)
     }
-    uint32_t li = 0;          // next long row (uniform over the CTA)
-    double part = 0.0;        // this thread's strided partial of long row li
+    __syncthreads();          // mbarrier initialised, long-row list complete
+    uint32_t lk = wid;        // this warp's next long row
+    double part = 0.0;        // this lane's strided partial of it
 
-    for (uint32_t c0 = e_begin; c0 < e_end; c0 += SIG_CHUNK) {
+    for (uint32_t k = 0; k < nchunk; ++k) {
+        const uint32_t c0 = base + k * SIG_CHUNK;
         const uint32_t c1 = (e_end - c0 > (uint32_t)SIG_CHUNK) ? c0 + SIG_CHUNK : e_end;
-        // phase 1: issue every load of this thread's 8 edges before using any (memory-level parallelism)
-        double b_[SIG_CHUNK / SIG_ROWS];
-        int64_t x_[SIG_CHUNK / SIG_ROWS];
-        uint8_t a_[SIG_CHUNK / SIG_ROWS];
-#pragma unroll
-        for (int k = 0; k < SIG_CHUNK / SIG_ROWS; ++k) {
-            const uint32_t e = c0 + tid + k * SIG_ROWS;
-            const bool in = e < c1;
-            b_[k] = in ? __ldg(bonded + e) : 0.0;
-            x_[k] = in ? __ldg(expiry + e) : AHV_EXPIRY_NONE;
-            a_[k] = in ? __ldg(active + e) : (uint8_t)0;
+        // the last, partial 16-edge group of the tile: ordinary loads (a bulk copy would read past e_end)
+        const uint32_t cnt16 = (c1 - c0) & ~15u;
+        if (tid < (c1 - c0) - cnt16) {
+            const uint32_t i = cnt16 + tid;
+            st.b[i] = __ldg(bonded + c0 + i);
+            st.x[i] = __ldg(expiry + c0 + i);
+            st.a[i] = __ldg(active + c0 + i);
         }
-#pragma unroll
-        for (int k = 0; k < SIG_CHUNK / SIG_ROWS; ++k)
-            v[tid + k * SIG_ROWS] = vouch_accumulate(0.0, b_[k], a_[k], x_[k], now);
+        {   // wait for this chunk's bytes (phase k of the barrier)
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                             "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(mbar), "r"(k & 1u) : "memory");
+        }
+        if (cnt16 != c1 - c0) __syncthreads();            // the tail elements were written by other threads
+        // conversion pass, all lanes busy: b[i] <- the amount record i contributes (two records per step)
+        for (uint32_t i = 2 * tid; i < c1 - c0; i += 2 * SIG_ROWS) {
+            double2 b2 = *reinterpret_cast<const double2 *>(&st.b[i]);
+            const longlong2 x2 = *reinterpret_cast<const longlong2 *>(&st.x[i]);
+            const uint32_t a2 = *reinterpret_cast<const uint16_t *>(&st.a[i]);
+            b2.x = live_amount(b2.x, a2 & 0xffu, x2.x, now);
+            b2.y = live_amount(b2.y, a2 >> 8, x2.y, now);         // (one slot past an odd count: never read)
+            *reinterpret_cast<double2 *>(&st.b[i]) = b2;
+        }
         __syncthreads();
-        // phase 2: own row, reference order; values fetched four at a time ahead of the dependent additions
-        if (!is_long) {
+        if (!is_long) {                                   // own row, reference order
             const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
             uint32_t e = lo;
-            for (; e + 4 <= hi; e += 4) {
-                const double x0 = v[e - c0], x1 = v[e - c0 + 1], x2 = v[e - c0 + 2], x3 = v[e - c0 + 3];
+            for (; e + 4 <= hi; e += 4) {                 // operands fetched ahead of the dependent additions
+                const double x0 = st.b[e - c0], x1 = st.b[e - c0 + 1], x2 = st.b[e - c0 + 2], x3 = st.b[e - c0 + 3];
                 acc.add(x0); acc.add(x1); acc.add(x2); acc.add(x3);
             }
-            for (; e < hi; ++e) acc.add(v[e - c0]);
+            for (; e < hi; ++e) acc.add(st.b[e - c0]);
         }
         if (PAR) {
-            while (li < n_long) {
-                const uint32_t r0 = long_r0[li], r1 = long_r1[li];
+            while (lk < n_long) {
+                const uint32_t r0 = long_r0[lk], r1 = long_r1[lk];
                 if (r0 >= c1) break;                                   // starts in a later chunk
                 const uint32_t lo = r0 > c0 ? r0 : c0, hi = r1 < c1 ? r1 : c1;
-                // row positions congruent to tid (mod 256) inside [lo, hi)
-                for (uint32_t e = lo + ((tid - (lo - r0)) & (SIG_ROWS - 1)); e < hi; e += SIG_ROWS)
-                    part = __dadd_rn(part, v[e - c0]);
+                // row positions congruent to lane (mod 32) inside [lo, hi)
+                for (uint32_t e = lo + ((lane - (lo - r0)) & 31u); e < hi; e += 32)
+                    part = __dadd_rn(part, st.b[e - c0]);
                 if (r1 > c1) break;                                    // continues in the next chunk
                 double x = part;
 #pragma unroll
                 for (int o = 16; o; o >>= 1) x = __dadd_rn(x, __shfl_xor_sync(0xffffffffu, x, o));
-                if (lane == 0) wsum[wid] = x;
-                __syncthreads();
-                if (tid == long_owner[li]) {
-                    double t = wsum[0];
-#pragma unroll
-                    for (int w = 1; w < SIG_WARPS; ++w) t = __dadd_rn(t, wsum[w]);
-                    acc.f = t;
-                }
-                __syncthreads();
+                if (lane == 0) long_sum[long_owner[lk]] = x;
                 part = 0.0;
-                ++li;
+                lk += SIG_WARPS;
             }
         }
-        __syncthreads();
+        if (k + 1 < nchunk) {
+            __syncthreads();                              // every warp is done with the stage
+            if (tid == 0) issue(k + 1);
+        }
     }
+    if (PAR && n_long) __syncthreads();                   // the warps' row sums are in long_sum
     if (!valid) return;
+    if (is_long) acc.f = long_sum[tid];
     const double contrib = acc.result();
     if (MODE != 0) {
         out_sigma[a] = contrib;
         return;
     }
-    const double se = sigma_eff_of(sigma[a], omega[a], contrib);
+    const double se = sigma_eff_of(sg, om, contrib);
     out_sigma[a] = se;
-    if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, consensus[a] != 0);
-    if (out_demote) out_demote[a] = (uint8_t)(ring_from_sigma(se, false) > (int)current_ring[a]);
+    if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, cons != 0);
+    if (out_demote) out_demote[a] = (uint8_t)(ring_from_sigma(se, false) > (int)ring_in);
     if (out_near) out_near[a] = (uint8_t)near_threshold(se);
 }
+
+
 
 __global__ void __launch_bounds__(256)
 k_ring_check(const uint8_t *__restrict__ agent_ring, const uint8_t *__restrict__ flags,
@@ -230,16 +295,25 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
     AHV_REQUIRE(!d_out_ring || d_consensus, "out_ring needs consensus");
     AHV_REQUIRE(!d_out_demote || d_current_ring, "out_demote needs current_ring");
     AHV_REQUIRE(A < 0xffffffffull, "too many agents (limit 2^32-2)");
-    if (ctx->opt_sigma_variant == 0)
+    // the tiled kernel moves 16-edge groups with bulk copies: all three edge arrays must be 16-byte aligned
+    // (anything from cudaMalloc / ahv_dev_alloc is); otherwise every row is summed by its own thread, in the
+    // reference's order
+    const bool aligned = ((reinterpret_cast<uintptr_t>(d_bonded) | reinterpret_cast<uintptr_t>(d_expiry) |
+                           reinterpret_cast<uintptr_t>(d_active)) & 15u) == 0;
+    if (ctx->opt_sigma_variant == 0 || !aligned)
         k_sigma_eff_rings<<<grid_for(A, 256), 256, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma,
                                                                      d_omega, d_consensus, d_current_ring, A, d_out_sigma,
                                                                      d_out_ring, d_out_demote, d_out_near);
     else if (ctx->opt_sigma_exact)
-        k_sigma_eff_tiled<0, false><<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(
+        k_sigma_eff_tiled<0, false, 2048><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
             d_out_ring, d_out_demote, d_out_near, 0u);
+    else if (ctx->opt_sigma_chunk == 1024)
+        k_sigma_eff_tiled<0, true, 1024><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1024>), ctx->stream>>>(
+            d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut);
     else
-        k_sigma_eff_tiled<0, true><<<grid_for(A, SIG_ROWS), SIG_ROWS, 0, ctx->stream>>>(
+        k_sigma_eff_tiled<0, true, 2048><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
             d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut);
     AHV_CHECK_LAUNCH(ctx);
@@ -253,13 +327,15 @@ int ahv_exposure_sums_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *
     if (n_rows == 0) return AHV_OK;
     AHV_REQUIRE(d_rowptr && d_out_sum, "rowptr / out_sum is null");
     AHV_REQUIRE(n_rows < 0xffffffffull, "too many rows (limit 2^32-2)");
+    AHV_REQUIRE(((reinterpret_cast<uintptr_t>(d_bonded) | reinterpret_cast<uintptr_t>(d_expiry) |
+                  reinterpret_cast<uintptr_t>(d_active)) & 15u) == 0, "bonded / active / expiry must be 16-byte aligned");
     const unsigned g = grid_for(n_rows, SIG_ROWS);
     if (compensated)
-        k_sigma_eff_tiled<2, false><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
+        k_sigma_eff_tiled<2, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
                                                                      nullptr, nullptr, 0u);
     else
-        k_sigma_eff_tiled<1, false><<<g, SIG_ROWS, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
+        k_sigma_eff_tiled<1, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
                                                                      nullptr, nullptr, 0u);
     AHV_CHECK_LAUNCH(ctx);

@@ -64,12 +64,13 @@ class VouchGraphCSR:
 
     @staticmethod
     def from_records(records, session_id: str, agents: Sequence[str]) -> "VouchGraphCSR":
-        index = {a: i for i, a in enumerate(agents)}
+        index: dict = {}
+        for i, a in enumerate(agents):                  # the same DID may be asked for more than once
+            index.setdefault(a, []).append(i)
         rows: list[list] = [[] for _ in agents]
         for v in records:                               # dict order == insertion order (vouching.py:190)
             if v.session_id == session_id:
-                r = index.get(v.vouchee_did)
-                if r is not None:
+                for r in index.get(v.vouchee_did, ()):
                     rows[r].append(v)
         rowptr = np.zeros(len(agents) + 1, dtype=np.uint32)
         np.cumsum([len(r) for r in rows], out=rowptr[1:])
@@ -94,6 +95,11 @@ class VouchingEngine:
     MIN_VOUCHER_SCORE = 0.50
     DEFAULT_BOND_PCT = 0.20
     DEFAULT_MAX_EXPOSURE = 0.80
+
+    # The drop-in class returns the reference's own bits: every row is summed left to right
+    # (vouching.py:146-148).  Set False to let rows of more than 32 records take the faster fixed-shape
+    # warp sum of ahv_sigma_eff_rings (a few ulp away, inside the 1e-6 tolerance; same value every run).
+    exact_order = True
 
     def __init__(self, max_exposure: Optional[float] = None) -> None:
         self._vouches: dict[str, VouchRecord] = {}
@@ -213,7 +219,8 @@ class VouchingEngine:
         now_us = _to_us(now or datetime.now(timezone.utc))
         se, ring, demote, near = ctx.sigma_eff_rings(g.rowptr, g.bonded, g.active, g.expiry, now_us,
                                                      np.asarray(sigmas, dtype=np.float64),
-                                                     np.asarray(risk_weights, dtype=np.float64), cons, ring_in)
+                                                     np.asarray(risk_weights, dtype=np.float64), cons, ring_in,
+                                                     exact=self.exact_order)
         return {"sigma_eff": se, "ring": ring, "demote": demote,
                 "near_threshold": [agents[i] for i in np.nonzero(near)[0]]}
 
@@ -242,5 +249,5 @@ class VouchingEngine:
         se, _, _, _ = ctx.sigma_eff_rings(rowptr, bonded, active, expiry, _to_us(now or datetime.now(timezone.utc)),
                                           np.array([q[2] for q in requests], dtype=np.float64),
                                           np.array([q[3] for q in requests], dtype=np.float64),
-                                          np.zeros(A, np.uint8), np.full(A, 3, np.uint8))
+                                          np.zeros(A, np.uint8), np.full(A, 3, np.uint8), exact=self.exact_order)
         return se

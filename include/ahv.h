@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define AHV_ABI_VERSION 1
+#define AHV_ABI_VERSION 2
 
 #define AHV_OK 0
 #define AHV_E_INVALID (-1)  /* bad argument */
@@ -83,6 +83,9 @@ uint64_t ahv_launch_count(ahv_ctx *ctx);
 int ahv_dev_alloc(ahv_ctx *ctx, uint64_t bytes, void **out_dptr);
 int ahv_dev_free(ahv_ctx *ctx, void *dptr);
 int ahv_host_alloc(ahv_ctx *ctx, uint64_t bytes, void **out_hptr); /* pinned */
+/* flags: AHV_HOST_WRITE_COMBINED = upload-only buffer (fast for the GPU to read, very slow for the CPU to read back) */
+#define AHV_HOST_WRITE_COMBINED 1u
+int ahv_host_alloc_flags(ahv_ctx *ctx, uint64_t bytes, uint32_t flags, void **out_hptr);
 int ahv_host_free(ahv_ctx *ctx, void *hptr);
 int ahv_memcpy_h2d(ahv_ctx *ctx, void *dptr, const void *hptr, uint64_t bytes); /* async on ctx stream */
 int ahv_memcpy_d2h(ahv_ctx *ctx, void *hptr, const void *dptr, uint64_t bytes); /* async on ctx stream */
@@ -185,10 +188,13 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
                           uint8_t *d_out_roots, uint8_t *d_out_root_match);
 
 /*
- * ahv_audit_sessions: ahv_commit followed by ahv_verify_chains against the roots just committed, on a
- * single upload of the batch (what an auditor does when sessions arrive from the host: terminate_session's
- * root, core.py:204, then verify_chain, audit/delta.py:136-152, then CommitmentEngine.verify,
- * audit/commitment.py:59-64).  Both device passes run in full (the verify pass re-hashes).  Batches of
+ * ahv_audit_sessions: ahv_commit followed by ahv_verify_chains, on a single upload of the batch (what an
+ * auditor does when sessions arrive from the host: terminate_session's root, core.py:204, then verify_chain,
+ * audit/delta.py:136-152, then CommitmentEngine.verify, audit/commitment.py:59-64).  Both device passes run
+ * in full (the verify pass re-hashes).  expected_roots (S*32, or NULL): the STORED commitments to compare the
+ * rebuilt roots with (an archive's CommitmentRecord.merkle_root per session); with NULL the rebuilt roots
+ * are compared with the ones this same call has just committed, which checks the two passes against each
+ * other and nothing else.  Batches of
  * at least 64 sessions and 8 MB are pipelined in session chunks (copy-in / hash / copy-out overlap), for
  * fixed-size and variable-length deltas, uniform and ragged sessions alike; pass pinned host buffers
  * (ahv_host_alloc) for that overlap to happen.  Host pointers only.
@@ -200,8 +206,8 @@ int ahv_verify_chains_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_b
 int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offsets, uint64_t fixed_len,
                        const uint8_t *parent_digests, const uint8_t *parent_kind, const uint32_t *parent_pos,
                        const uint64_t *session_rowptr, uint64_t n_sessions, uint64_t uniform_leaves,
-                       uint8_t *out_digests, uint8_t *out_roots, uint8_t *out_empty, uint8_t *out_verdict,
-                       int64_t *out_first_bad, uint8_t *out_root_match);
+                       const uint8_t *expected_roots /* S*32 or NULL */, uint8_t *out_digests, uint8_t *out_roots,
+                       uint8_t *out_empty, uint8_t *out_verdict, int64_t *out_first_bad, uint8_t *out_root_match);
 
 /*
  * ahv_extract_parents_dev: fills parent_digests / parent_kind from the pre-images themselves: the value
@@ -298,9 +304,9 @@ int ahv_gather_results_dev(ahv_ctx *ctx, const uint8_t *d_roots /* S*32 */, cons
  *   (vouching.py:34-38; times in microseconds since the epoch).
  *   sum is sequential fp64 from 0.0; sigma_eff = sigma + (omega * sum), two roundings;
  *   result = (1.0 < x) ? 1.0 : x  (Python min(), NaN kept).
- *   Rows of more than 512 records (option "sigma_long_cut") are summed in a fixed parallel shape instead
- *   (256 strided partials, then a fixed tree: deterministic, within a few ulp of the sequential sum; the
- *   run contract allows 1e-6 relative); option "sigma_exact" = 1 keeps the sequential order for every row.
+ *   Rows of more than 32 records (option "sigma_long_cut") are summed in a fixed parallel shape instead
+ *   (by one warp: 32 strided partials, then a fixed butterfly: deterministic, within a few ulp of the
+ *   sequential sum; the run contract allows 1e-6 relative); option "sigma_exact" = 1 keeps the sequential order for every row.
  *   out_near[a] = 1 when sigma_eff lies within 1e-6 (relative) of 0.60 or 0.95: the agents whose ring could
  *   differ from the reference's under that tolerance.
  */
@@ -427,9 +433,10 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *                   global memory only (1) / warp per session, staged in shared memory where it fits (2)
  *   "sigma_variant" 0/1 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1)
  *   "sigma_exact" 0/1   sigma_eff: 1 = every row summed left to right like the reference (bit-identical, but one very long
- *                   row then bounds the pass); 0 (default) = rows longer than "sigma_long_cut" edges are summed by a whole
- *                   CTA in a fixed, input-independent shape (a few ulp from the reference, same result every run)
- *   "sigma_long_cut" 32..  that row length (default 512)
+ *                   row then bounds the pass); 0 (default) = rows longer than "sigma_long_cut" edges are summed by a
+ *                   warp in a fixed shape that depends on the row alone (a few ulp from the reference, same result every run)
+ *   "sigma_long_cut" 4..  that row length (default 32)
+ *   "sigma_chunk" 1024/2048  records per shared-memory chunk of that kernel (default 2048)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);
 

@@ -164,28 +164,24 @@ def check_slash_against_golden(cases, golden_cases, b, out):
 
 
 # ---- sigma_eff: the fixed-shape sum the CUDA path uses for rows longer than "sigma_long_cut" -------------
-SIGMA_LONG_CUT = 512
+SIGMA_LONG_CUT = 32
 
 
 def fixed_shape_row_sum(vals: np.ndarray) -> float:
-    """csrc/ahv_liability.cu (k_sigma_eff_tiled, PAR): 256 partials over row positions p, p+256, ... added in
-    that order; each warp of 32 partials reduced by an xor butterfly (strides 16, 8, 4, 2, 1); the 8 warp
-    sums added left to right.  ``vals`` = the row's contributions (+0.0 for a record that is not live)."""
+    """csrc/ahv_liability.cu (k_sigma_eff_tiled, PAR): 32 partials over row positions p, p+32, ... added in
+    that order, then an xor butterfly over the 32 lanes (strides 16, 8, 4, 2, 1); lane 0's value.
+    ``vals`` = the row's contributions (+0.0 for a record that is not live)."""
     d = len(vals)
-    pad = (-d) % 256
-    m = np.concatenate([np.asarray(vals, np.float64), np.zeros(pad)]).reshape(-1, 256)
-    part = np.zeros(256)
+    pad = (-d) % 32
+    m = np.concatenate([np.asarray(vals, np.float64), np.zeros(pad)]).reshape(-1, 32)
+    x = np.zeros(32)
     with np.errstate(all="ignore"):
         for r in m:
-            part = part + r
-        x = part.reshape(8, 32).copy()
+            x = x + r
         idx = np.arange(32)
         for o in (16, 8, 4, 2, 1):
-            x = x + x[:, idx ^ o]
-        t = x[0, 0]
-        for w in range(1, 8):
-            t = t + x[w, 0]
-    return float(t)
+            x = x + x[idx ^ o]
+    return float(x[0])
 
 
 def sigma_expected_default_path(exact, rowptr, bonded, active, expiry, now, sigma, omega, consensus, current_ring,
@@ -199,7 +195,7 @@ def sigma_expected_default_path(exact, rowptr, bonded, active, expiry, now, sigm
         for a in long_rows:
             sl = slice(rp[a], rp[a + 1])
             live = (np.asarray(active[sl]) != 0) & ~((np.asarray(expiry[sl]) != EXPIRY_NONE) & (now > np.asarray(expiry[sl])))
-            vals = np.where(live, 0.0 + np.asarray(bonded[sl], np.float64), 0.0)
+            vals = np.where(live, np.asarray(bonded[sl], np.float64), 0.0)
             s = np.float64(sigma[a]) + np.float64(omega[a]) * np.float64(fixed_shape_row_sum(vals))
             s = np.float64(1.0) if 1.0 < s else s
             se[a] = s

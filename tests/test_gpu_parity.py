@@ -9,7 +9,7 @@ import pytest
 
 import recipes
 import workloads
-from helpers import chain_preimages, config2_session, hexes, pack_sessions, sigma_expected_default_path
+from helpers import SIGMA_LONG_CUT, chain_preimages, config2_session, hexes, pack_sessions, sigma_expected_default_path
 from oracle import audit_oracle as ao
 from oracle import coracle as co
 from oracle import liability_oracle as lo
@@ -318,6 +318,13 @@ def test_audit_sessions_pipelined_and_ragged(ctx, audit_golden):
         assert np.array_equal(o["verdict"], v) and np.array_equal(o["first_bad"], fb)
         assert list(np.nonzero(o["verdict"] == 0)[0]) == bad_sessions
         assert o["root_match"].all() and not o["empty"].any()      # compared with the roots of the same upload
+    # against STORED commitments (the clean upload's roots): the tampered archive fails exactly where it differs,
+    # including the last delta of session 1499 that verify_chain cannot see (audit/commitment.py:59-64)
+    clean_r, _ = co.merkle_roots(co.sha256_batch(np.asarray(arena), offs), rp)
+    o = ctx.audit_sessions(bad, None, par, kind, None, fixed_len=256, uniform_leaves=L, n_sessions=S, expected_roots=clean_r)
+    assert list(np.nonzero(o["root_match"] == 0)[0]) == [700, 1499] and list(np.nonzero(o["verdict"] == 0)[0]) == [700]
+    o = ctx.audit_sessions(arena, None, par, kind, None, fixed_len=256, uniform_leaves=L, n_sessions=S, expected_roots=clean_r)
+    assert o["root_match"].all()
     ctx.host_free(arena)
     rs = audit_golden["random_sessions"][:300]
     sessions = [chain_preimages(recipes.random_session(r["seed"])) for r in rs]
@@ -328,6 +335,17 @@ def test_audit_sessions_pipelined_and_ragged(ctx, audit_golden):
         if r["n"]:
             assert o["roots"][s].tobytes().hex() == r["root"] and o["root_match"][s] == 1
         assert o["verdict"][s] == 1 and o["first_bad"][s] == -1
+    # ragged (unpipelined) path with stored commitments: golden roots, one of them wrong; an empty session never matches
+    exp = np.zeros((len(rs), 32), np.uint8)
+    for s, r in enumerate(rs):
+        if r["n"]:
+            exp[s] = np.frombuffer(bytes.fromhex(r["root"]), np.uint8)
+    wrong = next(s for s, r in enumerate(rs) if r["n"] > 1)
+    exp[wrong, 5] ^= 0x10
+    o = ctx.audit_sessions(a2, o2, p2, k2, rp2, expected_roots=exp)
+    assert [int(x) for x in o["root_match"]] == [1 if (r["n"] and s != wrong) else 0 for s, r in enumerate(rs)]
+    with pytest.raises(ValueError):
+        ctx.audit_sessions(a2, o2, p2, k2, rp2, expected_roots=exp[:-1])
 
 
 def test_parents_read_from_preimages(ctx):
@@ -505,10 +523,22 @@ def test_sigma_eff_golden_graphs(ctx, liability_golden):
     for gr in liability_golden["graphs"]:
         g = recipes.random_vouch_graph(gr["seed"], gr["A"], gr["E"])
         rowptr, bonded, act, exp, now = graph_to_csr(g, gr["A"])
+        want = np.array([float.fromhex(x) for x in gr["sigma_eff"]])
+        # default path: rows of up to SIGMA_LONG_CUT records bit-identical to the real engine, longer ones within 1e-6
         se, ring, dem, near = ctx.sigma_eff_rings(rowptr, bonded, act, exp, now, g["sigma"], g["omega"],
                                                   g["consensus"], g["current_ring"])
-        want = np.array([float.fromhex(x) for x in gr["sigma_eff"]])
-        assert np.allclose(se, want, rtol=SIGMA_REL_TOL, atol=0) and np.array_equal(se, want)
+        short = np.diff(rowptr.astype(np.int64)) <= SIGMA_LONG_CUT
+        assert np.allclose(se, want, rtol=SIGMA_REL_TOL, atol=0) and np.array_equal(se[short], want[short])
+        listed = near != 0
+        assert [r for r, n in zip(ring, listed) if not n] == [r for r, n in zip(gr["ring"], listed) if not n]
+        # exact mode: every row in the reference's order
+        ctx.set_option("sigma_exact", 1)
+        try:
+            se, ring, dem, near = ctx.sigma_eff_rings(rowptr, bonded, act, exp, now, g["sigma"], g["omega"],
+                                                      g["consensus"], g["current_ring"])
+        finally:
+            ctx.set_option("sigma_exact", 0)
+        assert np.array_equal(se, want)
         assert list(ring) == gr["ring"] and [bool(x) for x in dem] == gr["demote"]
 
 
@@ -560,7 +590,7 @@ def test_sigma_eff_long_and_empty_rows(ctx):
     """Rows far longer than one shared-memory chunk (2048 edges), rows around the parallel-sum cut, several
     long rows inside one chunk, empty rows, a partial last CTA."""
     rng = np.random.default_rng(4)
-    deg = np.concatenate([[5000, 0, 0, 3000, 1, 2047, 2048, 2049, 0, 9000, 512, 513, 514, 600, 520, 0, 513, 767, 768, 769],
+    deg = np.concatenate([[5000, 0, 0, 3000, 1, 2047, 2048, 2049, 0, 9000, 512, 513, 514, 600, 520, 0, 513, 767, 768, 769, 31, 32, 33, 34, 64, 65, 15, 16, 17],
                           rng.integers(0, 30, 700), [513, 40000, 513]])
     A = len(deg)
     rowptr = np.concatenate([[0], np.cumsum(deg)]).astype(np.uint32)
@@ -572,12 +602,14 @@ def test_sigma_eff_long_and_empty_rows(ctx):
             (rng.random(A) < 0.5).astype(np.uint8), rng.integers(1, 4, A).astype(np.uint8))
     want = co.sigma_eff_rings(*args)
     _check_sigma_default_path(ctx, args, want)
-    for cut in (32, 100, 4096):                             # other cuts: same contract
+    for cut, chunk in ((4, 2048), (100, 1024), (512, 2048), (4096, 1024)):      # other cuts / chunk sizes: same contract
         ctx.set_option("sigma_long_cut", cut)
+        ctx.set_option("sigma_chunk", chunk)
         try:
             got = ctx.sigma_eff_rings(*args)
         finally:
-            ctx.set_option("sigma_long_cut", 512)
+            ctx.set_option("sigma_long_cut", SIGMA_LONG_CUT)
+            ctx.set_option("sigma_chunk", 2048)
         exp = sigma_expected_default_path(want, *args, cut=cut)
         assert np.array_equal(got[0], exp[0]) and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:4]))
     ctx.set_option("sigma_exact", 1)
@@ -685,6 +717,19 @@ def test_ring_check_grid_and_dropin(ctx, liability_golden):
     assert ve.compute_sigma_eff("did:l", "s1", 0.3, 0.5) == pts[2]
     out = ve.compute_sigma_eff_batch("s1", ["did:l", "did:nobody"], [0.3, 0.6], [0.5, 0.5])
     assert out["sigma_eff"][0] == pts[2] and out["sigma_eff"][1] == 0.6 and out["near_threshold"] == ["did:nobody"]
+    # the same DID asked for twice: both entries get its vouch rows (as two calls of the reference would)
+    out = ve.compute_sigma_eff_batch("s1", ["did:l", "did:x", "did:l"], [0.3, 0.1, 0.3], [0.5, 0.5, 0.5])
+    assert out["sigma_eff"][0] == pts[2] and out["sigma_eff"][2] == pts[2] and out["sigma_eff"][1] == 0.1
+    # a drop-in row longer than the fast path's cut stays in the reference's order (VouchingEngine.exact_order)
+    ve = VouchingEngine(max_exposure=1.0)
+    amounts = []
+    for k in range(80):
+        r = ve.vouch(f"did:h{k}", "did:many", "s1", 0.5 + 0.005 * k, bond_pct=0.001 + 0.0001 * k)
+        amounts.append(r.bonded_amount)
+    total = 0.0
+    for x in amounts:
+        total += x                                                        # vouching.py:146-148
+    assert ve.compute_sigma_eff("did:many", "s1", 0.01, 0.9) == min(0.01 + (0.9 * total), 1.0)
 
 
 def test_sharded_single_tree_matches_whole_tree(ctx):

@@ -56,6 +56,20 @@ def test_pipeline_matches_per_chunk_results():
             for i, d in enumerate(deltas):
                 assert got["digests"][i].tobytes().hex() == hashlib.sha256(canonical_preimage(d)).hexdigest()
             assert [bool(v) for v in got["verdict"]] == want_verdict and got["roots"] == want_roots
+            assert got["root_match"] is None and ref["root_match"] is None      # no stored commitments were given
+        # the archive's stored commitments travel with each chunk: session 4 of chunk 1 has a wrong one on file
+        def with_roots(k, c):
+            stored = np.stack([np.frombuffer(bytes.fromhex(r), np.uint8) for r in c[3]]).copy()
+            if k == 1:
+                stored[4, 0] ^= 1
+            return c[0], c[1], stored
+        checked = list(pipe.run(with_roots(k, c) for k, c in enumerate(chunks)))
+        for k, got in enumerate(checked):
+            assert list(got["root_match"]) == [not (k == 1 and s == 4) for s in range(len(got["roots"]))]
+            assert got["roots"] == results[k]["roots"]
+        ref = auditor.audit(pack_sessions([chunks[1][2][int(chunks[1][1][s]):int(chunks[1][1][s + 1])] for s in range(10)]),
+                            committed_roots_hex=[r if s != 4 else "0" * 64 for s, r in enumerate(chunks[1][3])])
+        assert list(ref["root_match"]) == [s != 4 for s in range(10)]
         # views instead of copies, and a chunk too large for the buffers
         views = list(pipe.run([(chunks[0][0], chunks[0][1])], copy=False))
         assert np.array_equal(views[0]["digests"], results[0]["digests"])

@@ -134,7 +134,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), f"{name} declared in ahv.h but not exported"
         assert name in nat.SIGNATURES, f"{name} has no ctypes signature"
     assert set(nat.SIGNATURES) <= declared
-    assert lib.ahv_abi_version() == 1
+    assert lib.ahv_abi_version() == 2
 
 
 def test_no_cpu_fallback_without_gpu():

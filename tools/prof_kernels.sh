@@ -9,8 +9,8 @@ prof() {   # name, workload, kernel regex, skip, count
       python tools/prof_kernels.py $2 > gpurun_out/prof_${TAG}_$1.log 2>&1
   echo "$1 rc=$?"
 }
-prof sigma sigma 'k_sigma_eff_tiled' 1 5          # launches 2,3 = Zipf; 4,5,6 = uniform
+prof sigma sigma 'k_sigma_eff_tiled' 2 2          # launch 3 = Zipf, launch 4 = uniform
 prof var var 'k_sha256_var' 1 1
 prof chain chain 'k_chain_capture' 1 1
-prof tree tree 'k_merkle_level|k_merkle_top' 12 12
-ls -la gpurun_out | head -40
+prof tree tree 'k_merkle_level|k_merkle_top' 20 2   # levels 1 and 2 of a uniform 10^4 x 1000 tree
+du -sh gpurun_out; ls -la gpurun_out | head -40   # gpurun copies back at most 64 MiB
