@@ -147,6 +147,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_sigma_exact = 0;
     c->opt_sigma_long_cut = 32;
     c->opt_sigma_chunk = 2048;
+    c->opt_sigma_share = 1;
     c->opt_slash_variant = 0;
     c->opt_blocking_sync = 0;
     *out_ctx = c;
@@ -163,6 +164,7 @@ void ahv_destroy(ahv_ctx *ctx)
     comm_release(ctx);
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->io) cudaFree(ctx->io);
+    if (ctx->sigma_work) cudaFree(ctx->sigma_work);
     if (ctx->one_out) cudaFreeHost(ctx->one_out);
     for (int i = 0; i < AHV_PIPE_EVENTS; ++i) cudaEventDestroy(ctx->ev_pipe[i]);
     for (int i = 0; i < AHV_MAX_TIMERS; ++i) {
@@ -324,8 +326,11 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     } else if (!strcmp(key, "sigma_long_cut")) {
         AHV_REQUIRE(value >= 4 && value <= 0x7fffffff, "sigma_long_cut must be 4..2^31-1");
         ctx->opt_sigma_long_cut = value;
+    } else if (!strcmp(key, "sigma_share")) {
+        AHV_REQUIRE(value == 0 || value == 1, "sigma_share must be 0 or 1");
+        ctx->opt_sigma_share = value;
     } else if (!strcmp(key, "sigma_chunk")) {
-        AHV_REQUIRE(value == 1024 || value == 2048, "sigma_chunk must be 1024 or 2048");
+        AHV_REQUIRE(value == 1024 || value == 1536 || value == 2048, "sigma_chunk must be 1024, 1536 or 2048");
         ctx->opt_sigma_chunk = value;
     } else if (!strcmp(key, "compress")) {
         AHV_REQUIRE(value == 0 || value == 1, "compress must be 0 or 1");

@@ -38,12 +38,16 @@ struct ahv_ctx {
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_sigma_exact;   // 1: every row summed in the reference's order (bit-identical); 0 (default): rows longer than opt_sigma_long_cut take the fixed-shape parallel sum
     int64_t opt_sigma_long_cut;// row length (edges) above which the parallel sum is used (default 512)
+    int64_t opt_sigma_share;   // 1 (default): heavy tiles of the tiled sigma_eff kernel go through a queue shared by the CTAs
     int64_t opt_sigma_chunk;   // edges per shared-memory chunk of the tiled sigma_eff kernel: 2048 (default) or 1024
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)
     int64_t opt_peak_ctas;     // CTAs of 256 threads per SM in the ahv_int_peak kernels (default 4)
     int64_t opt_leaf_timer;    // >0: bracket every leaf-hash launch with timer slots base..base+15 (round robin)
     uint64_t leaf_launches;    // leaf-hash kernel launches so far (indexes the round robin)
+    uint8_t *sigma_work;       // queue + claim flags of the tiled sigma_eff kernel (ahv_liability.cu)
+    uint64_t sigma_work_tiles;
+    uint32_t sigma_epoch;      // number of the last tiled sigma_eff launch (work-queue generation)
     void *comm;                // ncclComm_t of this rank (ahv_comm_init), NULL in a world of one
     int comm_world, comm_rank;
     uint8_t *one_out;          // 64 B of mapped pinned host memory: where ahv_sha256_one's kernel writes its digest

@@ -107,16 +107,41 @@ __device__ __forceinline__ double live_amount(double b, uint32_t active, int64_t
     return live ? b : 0.0;
 }
 
+// Work sharing between the CTAs of one launch.  A tile whose rows hold far more edges than a chunk (one row of
+// 14 017 records = 7 chunks, one after the other) takes several times longer than an ordinary tile; if its
+// CTA is scheduled late, the whole launch waits for it.  So the CTAs of the first wave look through ALL
+// tiles' edge counts while their own first chunk is in flight (a handful of loads each) and put the heavy
+// ones in a queue; a CTA that has finished its own tile takes heavy tiles from the queue, so they start
+// within the first microseconds.  Every heavy tile is claimed (atomic exchange with this launch's number) by
+// whoever gets to it first - its own CTA or one that took it from the queue - so it is processed exactly
+// once whatever the timing; should a CTA ever read a queue slot before its writer has filled it, it finds an
+// older launch's tile number there, and processing an ordinary tile twice only writes the same values twice.
+// Launches alternate between two queues, each launch zeroing the other one's counters, so nothing needs
+// clearing between launches and a graph without heavy tiles pays one extra load per CTA.  None of this
+// changes any result.
+struct SigWork {
+    uint32_t *counters;        // [2][2]: per queue, tail and head
+    uint32_t *queue;           // [2][cap]; NULL = no work sharing
+    uint32_t *claimed;         // per tile: number of the launch that claimed it last
+    uint32_t cap;
+    uint32_t epoch;            // this launch's number (never 0); its queue is epoch & 1
+};
+constexpr uint32_t SIG_NONE = 0xffffffffu;
+constexpr uint32_t SIG_HEAVY_EDGES = 4096;      // a tile with more edges than this goes through the queue
+constexpr uint32_t SIG_SCAN_CTAS = 512;         // CTAs that share the look-through (all resident in the first wave)
+constexpr uint32_t SIG_QUEUE_CAP = 4096;
+constexpr uint32_t SIG_AHEAD = 1024;            // look-ahead distance of the L2 prefetches, in tiles (about one wave of CTAs)
+
 // MODE 0: sigma_eff + rings.  MODE 1: plain live sum of each row.  MODE 2: compensated live sum.
 // PAR (MODE 0 only): rows of more than long_cut edges take the fixed-shape warp sum.
 template <int MODE, bool PAR, int SIG_CHUNK>
-__global__ void __launch_bounds__(SIG_ROWS, SIG_CHUNK == 2048 ? 6 : 10)
+__global__ void __launch_bounds__(SIG_ROWS, SIG_CHUNK == 2048 ? 6 : (SIG_CHUNK == 1536 ? 8 : 10))
 k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
                   const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
                   const double *__restrict__ sigma, const double *__restrict__ omega,
                   const uint8_t *__restrict__ consensus, const uint8_t *__restrict__ current_ring, uint64_t A,
                   double *__restrict__ out_sigma, uint8_t *__restrict__ out_ring, uint8_t *__restrict__ out_demote,
-                  uint8_t *__restrict__ out_near, uint32_t long_cut)
+                  uint8_t *__restrict__ out_near, uint32_t long_cut, SigWork wk)
 {
     extern __shared__ __align__(128) uint8_t sig_smem[];
     SigStage<SIG_CHUNK> &st = *reinterpret_cast<SigStage<SIG_CHUNK> *>(sig_smem);
@@ -125,145 +150,238 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
     __shared__ uint32_t long_r0[SIG_ROWS], long_r1[SIG_ROWS];
     __shared__ uint16_t long_owner[SIG_ROWS];
     __shared__ uint32_t wcount[SIG_WARPS];
+    __shared__ uint32_t s_word;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_storage);
-    const uint64_t a0 = (uint64_t)blockIdx.x * SIG_ROWS;
-    const uint64_t a = a0 + tid;
-    const bool valid = a < A;
-    const uint64_t a_last = (a0 + SIG_ROWS < A) ? a0 + SIG_ROWS : A;
-    const uint32_t e_begin = __ldg(rowptr + a0), e_end = __ldg(rowptr + a_last);
+    const uint32_t ntiles = gridDim.x;
     if (tid == 0) {
         asm volatile("mbarrier.init.shared.b64 [%0], %1;" ::"r"(mbar), "r"(1u) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    // chunk grid from the 16-edge boundary at or below the first edge; copies issued by thread 0
-    const uint32_t base = e_begin & ~15u;
-    const uint32_t nchunk = (e_end > base) ? (e_end - base + SIG_CHUNK - 1) / SIG_CHUNK : 0;
-    auto issue = [&](uint32_t k) {                                  // thread 0 only
-        const uint32_t c0 = base + k * SIG_CHUNK;
-        const uint32_t cnt = (e_end - c0 > (uint32_t)SIG_CHUNK) ? (uint32_t)SIG_CHUNK : e_end - c0;
-        const uint32_t cnt16 = cnt & ~15u;
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(cnt16 * 17u) : "memory");
-        if (cnt16) {
-            bulk_g2s(st.b, bonded + c0, cnt16 * 8u, mbar);
-            bulk_g2s(st.x, expiry + c0, cnt16 * 8u, mbar);
-            bulk_g2s(st.a, active + c0, cnt16, mbar);
+    uint32_t *const q_cnt = wk.queue ? wk.counters + 2 * (wk.epoch & 1u) : nullptr;
+    uint32_t *const q_ent = wk.queue ? wk.queue + (size_t)wk.cap * (wk.epoch & 1u) : nullptr;
+    if (wk.queue && blockIdx.x == 0 && tid < 2) wk.counters[2 * ((wk.epoch & 1u) ^ 1u) + tid] = 0u;   // the next launch's queue
+    bool first = true;
+    __syncthreads();                                      // mbarrier initialised
+    uint32_t phase = 0;                                   // chunks this CTA has waited for so far (mbarrier parity)
+    uint32_t tile = blockIdx.x;
+    while (tile != SIG_NONE) {
+        const uint64_t a0 = (uint64_t)tile * SIG_ROWS;
+        const uint64_t a = a0 + tid;
+        const bool valid = a < A;
+        const uint64_t a_last = (a0 + SIG_ROWS < A) ? a0 + SIG_ROWS : A;
+        const uint32_t e_begin = __ldg(rowptr + a0), e_end = __ldg(rowptr + a_last);
+        const uint32_t my0 = valid ? __ldg(rowptr + a) : 0u, my1 = valid ? __ldg(rowptr + a + 1) : 0u;
+        // Look-ahead through L2 (first tile of each CTA; CTAs start roughly in tile order): the row pointers of
+        // the tile SIG_AHEAD tiles further on were put into L2 by an earlier CTA, so they arrive quickly; when this
+        // tile is done, that tile's edges and per-agent inputs are sent for (bulk L2 prefetch), and the row pointers
+        // of the tile 2 * SIG_AHEAD further on.  A CTA then finds its inputs in L2 instead of waiting for DRAM
+        // three times in a row.
+        uint32_t f0 = 0, f1 = 0;
+        const uint64_t tile_f = (uint64_t)tile + SIG_AHEAD;
+        if (first && tid == 0 && tile_f < ntiles) {
+            const uint64_t r0 = tile_f * SIG_ROWS, r1 = (r0 + SIG_ROWS < A) ? r0 + SIG_ROWS : A;
+            f0 = __ldg(rowptr + r0);
+            f1 = __ldg(rowptr + r1);
         }
-    };
-    if (tid == 0 && nchunk) issue(0);
-
-    const uint32_t my0 = valid ? __ldg(rowptr + a) : e_end, my1 = valid ? __ldg(rowptr + a + 1) : e_end;
-    // per-agent inputs are requested now, long before they are needed
-    double sg = 0.0, om = 0.0;
-    uint8_t cons = 0, ring_in = 0;
-    if (MODE == 0 && valid) {
-        sg = __ldg(sigma + a);
-        om = __ldg(omega + a);
-        if (out_ring) cons = __ldg(consensus + a);
-        if (out_demote) ring_in = __ldg(current_ring + a);
-    }
-
-    RowSum<MODE == 2> acc;
-    // list of this tile's long rows, in row order (usually empty); long row k belongs to warp k % 4
-    const bool is_long = PAR && (my1 - my0 > long_cut);
-    uint32_t n_long = 0;
-    if (PAR) {
-        const uint32_t bal = __ballot_sync(0xffffffffu, is_long);
-        if (lane == 0) wcount[wid] = __popc(bal);
-        __syncthreads();
-        uint32_t before = 0;
-#pragma unroll
-        for (int w = 0; w < SIG_WARPS; ++w) {
-            const uint32_t c = wcount[w];
-            if (w < (int)wid) before += c;
-            n_long += c;
+        // how many heavy tiles are queued: asked for now, looked at when this tile is done
+        uint32_t q_tail = 0;
+        if (wk.queue && tid == 0) q_tail = *reinterpret_cast<volatile uint32_t *>(&q_cnt[0]);
+        bool take = true;
+        if (wk.queue && e_end - e_begin > SIG_HEAVY_EDGES) {          // heavy: first come, first served
+            if (tid == 0) s_word = atomicExch(&wk.claimed[tile], wk.epoch);
+            __syncthreads();
+            take = (s_word != wk.epoch);
+            __syncthreads();                                          // s_word is reused below
         }
-        if (is_long) {
-            const uint32_t k = before + __popc(bal & ((1u << lane) - 1u));
-            long_r0[k] = my0;
-            long_r1[k] = my1;
-            long_owner[k] = (uint16_t)tid;
-        }
-    }
-    __syncthreads();          // mbarrier initialised, long-row list complete
-    uint32_t lk = wid;        // this warp's next long row
-    double part = 0.0;        // this lane's strided partial of it
-
-    for (uint32_t k = 0; k < nchunk; ++k) {
-        const uint32_t c0 = base + k * SIG_CHUNK;
-        const uint32_t c1 = (e_end - c0 > (uint32_t)SIG_CHUNK) ? c0 + SIG_CHUNK : e_end;
-        // the last, partial 16-edge group of the tile: ordinary loads (a bulk copy would read past e_end)
-        const uint32_t cnt16 = (c1 - c0) & ~15u;
-        if (tid < (c1 - c0) - cnt16) {
-            const uint32_t i = cnt16 + tid;
-            st.b[i] = __ldg(bonded + c0 + i);
-            st.x[i] = __ldg(expiry + c0 + i);
-            st.a[i] = __ldg(active + c0 + i);
-        }
-        {   // wait for this chunk's bytes (phase k of the barrier)
-            uint32_t done = 0;
-            while (!done)
-                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-                             "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(mbar), "r"(k & 1u) : "memory");
-        }
-        if (cnt16 != c1 - c0) __syncthreads();            // the tail elements were written by other threads
-        // conversion pass, all lanes busy: b[i] <- the amount record i contributes (two records per step)
-        for (uint32_t i = 2 * tid; i < c1 - c0; i += 2 * SIG_ROWS) {
-            double2 b2 = *reinterpret_cast<const double2 *>(&st.b[i]);
-            const longlong2 x2 = *reinterpret_cast<const longlong2 *>(&st.x[i]);
-            const uint32_t a2 = *reinterpret_cast<const uint16_t *>(&st.a[i]);
-            b2.x = live_amount(b2.x, a2 & 0xffu, x2.x, now);
-            b2.y = live_amount(b2.y, a2 >> 8, x2.y, now);         // (one slot past an odd count: never read)
-            *reinterpret_cast<double2 *>(&st.b[i]) = b2;
-        }
-        __syncthreads();
-        if (!is_long) {                                   // own row, reference order
-            const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
-            uint32_t e = lo;
-            for (; e + 4 <= hi; e += 4) {                 // operands fetched ahead of the dependent additions
-                const double x0 = st.b[e - c0], x1 = st.b[e - c0 + 1], x2 = st.b[e - c0 + 2], x3 = st.b[e - c0 + 3];
-                acc.add(x0); acc.add(x1); acc.add(x2); acc.add(x3);
+        if (take) {
+            // chunk grid from the 16-edge boundary at or below the first edge; copies issued by thread 0
+            const uint32_t base = e_begin & ~15u;
+            const uint32_t nchunk = (e_end > base) ? (e_end - base + SIG_CHUNK - 1) / SIG_CHUNK : 0;
+            auto issue = [&](uint32_t k) {                            // thread 0 only
+                const uint32_t c0 = base + k * SIG_CHUNK;
+                const uint32_t cnt = (e_end - c0 > (uint32_t)SIG_CHUNK) ? (uint32_t)SIG_CHUNK : e_end - c0;
+                const uint32_t cnt16 = cnt & ~15u;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(cnt16 * 17u) : "memory");
+                if (cnt16) {
+                    bulk_g2s(st.b, bonded + c0, cnt16 * 8u, mbar);
+                    bulk_g2s(st.x, expiry + c0, cnt16 * 8u, mbar);
+                    bulk_g2s(st.a, active + c0, cnt16, mbar);
+                }
+            };
+            if (tid == 0 && nchunk) issue(0);
+            // look-through (first tile of the first SIG_SCAN_CTAS CTAs, while the chunk is in flight):
+            // CTA b checks tiles b + i * SIG_SCAN_CTAS, one per thread
+            if (wk.queue && first && blockIdx.x < SIG_SCAN_CTAS) {
+                for (uint32_t t = blockIdx.x + tid * SIG_SCAN_CTAS; t < ntiles; t += SIG_ROWS * SIG_SCAN_CTAS) {
+                    const uint64_t r0 = (uint64_t)t * SIG_ROWS, r1 = (r0 + SIG_ROWS < A) ? r0 + SIG_ROWS : A;
+                    if (__ldg(rowptr + r1) - __ldg(rowptr + r0) > SIG_HEAVY_EDGES) {
+                        const uint32_t slot = atomicAdd(&q_cnt[0], 1u);
+                        if (slot < wk.cap) q_ent[slot] = t;
+                    }
+                }
             }
-            for (; e < hi; ++e) acc.add(st.b[e - c0]);
-        }
-        if (PAR) {
-            while (lk < n_long) {
-                const uint32_t r0 = long_r0[lk], r1 = long_r1[lk];
-                if (r0 >= c1) break;                                   // starts in a later chunk
-                const uint32_t lo = r0 > c0 ? r0 : c0, hi = r1 < c1 ? r1 : c1;
-                // row positions congruent to lane (mod 32) inside [lo, hi)
-                for (uint32_t e = lo + ((lane - (lo - r0)) & 31u); e < hi; e += 32)
-                    part = __dadd_rn(part, st.b[e - c0]);
-                if (r1 > c1) break;                                    // continues in the next chunk
-                double x = part;
+
+            // per-agent inputs are requested now, long before they are needed
+            double sg = 0.0, om = 0.0;
+            uint8_t cons = 0, ring_in = 0;
+            if (MODE == 0 && valid) {
+                sg = __ldg(sigma + a);
+                om = __ldg(omega + a);
+                if (out_ring) cons = __ldg(consensus + a);
+                if (out_demote) ring_in = __ldg(current_ring + a);
+            }
+
+            RowSum<MODE == 2> acc;
+            // list of this tile's long rows, in row order (often empty); long row k belongs to warp k % 4
+            const bool is_long = PAR && (my1 - my0 > long_cut);
+            uint32_t n_long = 0;
+            if (PAR) {
+                const uint32_t bal = __ballot_sync(0xffffffffu, is_long);
+                if (lane == 0) wcount[wid] = __popc(bal);
+                __syncthreads();
+                uint32_t before = 0;
 #pragma unroll
-                for (int o = 16; o; o >>= 1) x = __dadd_rn(x, __shfl_xor_sync(0xffffffffu, x, o));
-                if (lane == 0) long_sum[long_owner[lk]] = x;
-                part = 0.0;
-                lk += SIG_WARPS;
+                for (int w = 0; w < SIG_WARPS; ++w) {
+                    const uint32_t c = wcount[w];
+                    if (w < (int)wid) before += c;
+                    n_long += c;
+                }
+                if (is_long) {
+                    const uint32_t k = before + __popc(bal & ((1u << lane) - 1u));
+                    long_r0[k] = my0;
+                    long_r1[k] = my1;
+                    long_owner[k] = (uint16_t)tid;
+                }
+                // (the list is read after the first chunk's conversion barrier: a long row has edges, so there is one)
+            }
+            uint32_t lk = wid;        // this warp's next long row
+            double part = 0.0;        // this lane's strided partial of it
+
+            for (uint32_t k = 0; k < nchunk; ++k, ++phase) {
+                const uint32_t c0 = base + k * SIG_CHUNK;
+                const uint32_t c1 = (e_end - c0 > (uint32_t)SIG_CHUNK) ? c0 + SIG_CHUNK : e_end;
+                // the last, partial 16-edge group of the tile: ordinary loads (a bulk copy would read past e_end)
+                const uint32_t cnt16 = (c1 - c0) & ~15u;
+                if (tid < (c1 - c0) - cnt16) {
+                    const uint32_t i = cnt16 + tid;
+                    st.b[i] = __ldg(bonded + c0 + i);
+                    st.x[i] = __ldg(expiry + c0 + i);
+                    st.a[i] = __ldg(active + c0 + i);
+                }
+                {   // wait for this chunk's bytes
+                    uint32_t done = 0;
+                    while (!done)
+                        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(mbar), "r"(phase & 1u) : "memory");
+                }
+                if (cnt16 != c1 - c0) __syncthreads();            // the tail elements were written by other threads
+                // conversion pass, all lanes busy: b[i] <- the amount record i contributes (two records per step)
+                for (uint32_t i = 2 * tid; i < c1 - c0; i += 2 * SIG_ROWS) {
+                    double2 b2 = *reinterpret_cast<const double2 *>(&st.b[i]);
+                    const longlong2 x2 = *reinterpret_cast<const longlong2 *>(&st.x[i]);
+                    const uint32_t a2 = *reinterpret_cast<const uint16_t *>(&st.a[i]);
+                    b2.x = live_amount(b2.x, a2 & 0xffu, x2.x, now);
+                    b2.y = live_amount(b2.y, a2 >> 8, x2.y, now);         // (one slot past an odd count: never read)
+                    *reinterpret_cast<double2 *>(&st.b[i]) = b2;
+                }
+                __syncthreads();
+                if (!is_long) {                                   // own row, reference order
+                    const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
+                    uint32_t e = lo;
+                    for (; e + 4 <= hi; e += 4) {                 // operands fetched ahead of the dependent additions
+                        const double x0 = st.b[e - c0], x1 = st.b[e - c0 + 1], x2 = st.b[e - c0 + 2], x3 = st.b[e - c0 + 3];
+                        acc.add(x0); acc.add(x1); acc.add(x2); acc.add(x3);
+                    }
+                    for (; e < hi; ++e) acc.add(st.b[e - c0]);
+                }
+                if (PAR) {
+                    while (lk < n_long) {
+                        const uint32_t r0 = long_r0[lk], r1 = long_r1[lk];
+                        if (r0 >= c1) break;                                   // starts in a later chunk
+                        const uint32_t lo = r0 > c0 ? r0 : c0, hi = r1 < c1 ? r1 : c1;
+                        // row positions congruent to lane (mod 32) inside [lo, hi)
+                        for (uint32_t e = lo + ((lane - (lo - r0)) & 31u); e < hi; e += 32)
+                            part = __dadd_rn(part, st.b[e - c0]);
+                        if (r1 > c1) break;                                    // continues in the next chunk
+                        double x = part;
+#pragma unroll
+                        for (int o = 16; o; o >>= 1) x = __dadd_rn(x, __shfl_xor_sync(0xffffffffu, x, o));
+                        if (lane == 0) long_sum[long_owner[lk]] = x;
+                        part = 0.0;
+                        lk += SIG_WARPS;
+                    }
+                }
+                if (k + 1 < nchunk) {
+                    __syncthreads();                              // every warp is done with the stage
+                    if (tid == 0) issue(k + 1);
+                }
+            }
+            if (PAR && n_long) __syncthreads();                   // the warps' row sums are in long_sum
+            if (valid) {
+                if (is_long) acc.f = long_sum[tid];
+                const double contrib = acc.result();
+                if (MODE != 0) {
+                    out_sigma[a] = contrib;
+                } else {
+                    const double se = sigma_eff_of(sg, om, contrib);
+                    out_sigma[a] = se;
+                    if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, cons != 0);
+                    if (out_demote) out_demote[a] = (uint8_t)(ring_from_sigma(se, false) > (int)ring_in);
+                    if (out_near) out_near[a] = (uint8_t)near_threshold(se);
+                }
             }
         }
-        if (k + 1 < nchunk) {
-            __syncthreads();                              // every warp is done with the stage
-            if (tid == 0) issue(k + 1);
+        if (first && tid < 8) {
+            const uint64_t tile_ff = (uint64_t)tile + 2 * SIG_AHEAD;
+            if (tid < 4 && tile_ff < ntiles) {                        // 128 row pointers = four 128-byte lines
+                const uint64_t r = tile_ff * SIG_ROWS + 32u * tid;
+                if (r <= A) asm volatile("prefetch.global.L2 [%0];" ::"l"(rowptr + r));
+            }
+            if (tile_f < ntiles) {
+                const uint64_t r0 = tile_f * SIG_ROWS;
+                if (tid == 0 && f1 > f0) {
+                    const uint32_t p0 = f0 & ~15u;
+                    uint32_t cnt = (f1 - p0) & ~15u;
+                    if (cnt > 4096u) cnt = 4096u;                     // a heavy tile's later chunks are left to themselves
+                    if (cnt) {
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(bonded + p0), "r"(cnt * 8u) : "memory");
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(expiry + p0), "r"(cnt * 8u) : "memory");
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(active + p0), "r"(cnt) : "memory");
+                    }
+                }
+                if (MODE == 0 && tid >= 4) {                          // sigma and omega of 128 agents: 8 lines each
+                    const uint64_t r = r0 + 32u * (tid - 4u);         // two lines per thread and array
+                    if (r < A) {
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(sigma + r));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(omega + r));
+                    }
+                    if (r + 16 < A) {
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(sigma + r + 16));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(omega + r + 16));
+                    }
+                }
+            }
         }
+        first = false;
+        if (!wk.queue) break;
+        // next: a heavy tile from the queue, if any is waiting (thread 0 knows; nothing queued = one barrier and out)
+        if (!__syncthreads_or(tid == 0 && q_tail != 0u)) break;      // (also: everyone is done with the stage and the lists)
+        if (tid == 0) {
+            uint32_t next = SIG_NONE;
+            const uint32_t tail = min(q_tail, wk.cap);
+            if (tail && *reinterpret_cast<volatile uint32_t *>(&q_cnt[1]) < tail) {
+                const uint32_t slot = atomicAdd(&q_cnt[1], 1u);
+                if (slot < tail) next = *reinterpret_cast<volatile uint32_t *>(&q_ent[slot]);
+                if (next >= ntiles) next = SIG_NONE;      // a slot nobody has ever written
+            }
+            s_word = next;
+        }
+        __syncthreads();
+        tile = s_word;
+        __syncthreads();
     }
-    if (PAR && n_long) __syncthreads();                   // the warps' row sums are in long_sum
-    if (!valid) return;
-    if (is_long) acc.f = long_sum[tid];
-    const double contrib = acc.result();
-    if (MODE != 0) {
-        out_sigma[a] = contrib;
-        return;
-    }
-    const double se = sigma_eff_of(sg, om, contrib);
-    out_sigma[a] = se;
-    if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, cons != 0);
-    if (out_demote) out_demote[a] = (uint8_t)(ring_from_sigma(se, false) > (int)ring_in);
-    if (out_near) out_near[a] = (uint8_t)near_threshold(se);
 }
-
-
 
 __global__ void __launch_bounds__(256)
 k_ring_check(const uint8_t *__restrict__ agent_ring, const uint8_t *__restrict__ flags,
@@ -278,6 +396,43 @@ k_ring_check(const uint8_t *__restrict__ agent_ring, const uint8_t *__restrict__
     if (allowed) allowed[i] = (uint8_t)(code == AHV_REASON_GRANTED);
     if (reason) reason[i] = (uint8_t)code;
     if (required) required[i] = (uint8_t)req;
+}
+
+}  // namespace
+
+namespace {
+
+// the queue / claim flags of the tiled sigma_eff kernel: allocated once per context (regrown when a larger
+// graph arrives), left in its empty state by every launch
+int sigma_work(ahv_ctx *ctx, uint64_t ntiles, SigWork *out)
+{
+    const uint64_t off_queue = 256, off_claimed = off_queue + pad256(2 * 4ull * SIG_QUEUE_CAP);
+    if (ntiles > ctx->sigma_work_tiles) {
+        AHV_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->sigma_work) AHV_CUDA(cudaFree(ctx->sigma_work));
+        ctx->sigma_work = nullptr;
+        ctx->sigma_work_tiles = 0;
+        const uint64_t tiles = ntiles + ntiles / 4 + 1024;
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, off_claimed + 4ull * tiles);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            set_error("device allocation for the sigma_eff work queue failed: %s", cudaGetErrorString(e));
+            return AHV_E_NOMEM;
+        }
+        ctx->sigma_work = (uint8_t *)p;
+        ctx->sigma_work_tiles = tiles;
+        AHV_CUDA(cudaMemsetAsync(ctx->sigma_work, 0, off_claimed + 4ull * tiles, ctx->stream));
+        AHV_CUDA(cudaMemsetAsync(ctx->sigma_work + off_queue, 0xff, 2 * 4ull * SIG_QUEUE_CAP, ctx->stream));
+        ctx->sigma_epoch = 0;
+    }
+    if (++ctx->sigma_epoch == 0) ctx->sigma_epoch = 1;    // 0 is what a never-claimed tile holds
+    out->counters = reinterpret_cast<uint32_t *>(ctx->sigma_work);
+    out->queue = reinterpret_cast<uint32_t *>(ctx->sigma_work + off_queue);
+    out->claimed = reinterpret_cast<uint32_t *>(ctx->sigma_work + off_claimed);
+    out->cap = SIG_QUEUE_CAP;
+    out->epoch = ctx->sigma_epoch;
+    return AHV_OK;
 }
 
 }  // namespace
@@ -300,6 +455,8 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
     // reference's order
     const bool aligned = ((reinterpret_cast<uintptr_t>(d_bonded) | reinterpret_cast<uintptr_t>(d_expiry) |
                            reinterpret_cast<uintptr_t>(d_active)) & 15u) == 0;
+    SigWork wk = {nullptr, nullptr, nullptr, 0, 0};
+    if (ctx->opt_sigma_variant != 0 && aligned && ctx->opt_sigma_share) AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
     if (ctx->opt_sigma_variant == 0 || !aligned)
         k_sigma_eff_rings<<<grid_for(A, 256), 256, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma,
                                                                      d_omega, d_consensus, d_current_ring, A, d_out_sigma,
@@ -307,15 +464,19 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
     else if (ctx->opt_sigma_exact)
         k_sigma_eff_tiled<0, false, 2048><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, 0u);
+            d_out_ring, d_out_demote, d_out_near, 0u, wk);
     else if (ctx->opt_sigma_chunk == 1024)
         k_sigma_eff_tiled<0, true, 1024><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1024>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut);
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+    else if (ctx->opt_sigma_chunk == 1536)
+        k_sigma_eff_tiled<0, true, 1536><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1536>), ctx->stream>>>(
+            d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
     else
         k_sigma_eff_tiled<0, true, 2048><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut);
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
@@ -333,11 +494,11 @@ int ahv_exposure_sums_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *
     if (compensated)
         k_sigma_eff_tiled<2, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
-                                                                     nullptr, nullptr, 0u);
+                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0});
     else
         k_sigma_eff_tiled<1, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
-                                                                     nullptr, nullptr, 0u);
+                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0});
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

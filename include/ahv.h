@@ -436,6 +436,7 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *                   row then bounds the pass); 0 (default) = rows longer than "sigma_long_cut" edges are summed by a
  *                   warp in a fixed shape that depends on the row alone (a few ulp from the reference, same result every run)
  *   "sigma_long_cut" 4..  that row length (default 32)
+ *   "sigma_share" 0/1   CTAs of that kernel take over tiles with many more edges than a chunk from a shared queue (default 1)
  *   "sigma_chunk" 1024/2048  records per shared-memory chunk of that kernel (default 2048)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);

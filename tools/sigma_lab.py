@@ -68,16 +68,18 @@ def run_config4():
         arrs = {k: gr[k] for k in ("rowptr", "bonded", "active", "expiry", "sigma", "omega", "consensus", "current_ring")}
         d = upload(arrs)
         res = {}
-        for label, opts in (("exact", dict(sigma_exact=1)), ("cut8", dict(sigma_long_cut=8)), ("cut16", dict(sigma_long_cut=16)),
+        for label, opts in (("exact", dict(sigma_exact=1)), ("cut16", dict(sigma_long_cut=16)),
                             ("cut32", dict(sigma_long_cut=32)), ("cut64", dict(sigma_long_cut=64)), ("cut128", dict(sigma_long_cut=128)),
-                            ("cut512", dict(sigma_long_cut=512)),
-                            ("cut16_chunk1024", dict(sigma_long_cut=16, sigma_chunk=1024)),
+                            ("cut32_noshare", dict(sigma_long_cut=32, sigma_share=0)),
                             ("cut32_chunk1024", dict(sigma_long_cut=32, sigma_chunk=1024)),
+                            ("cut32_chunk1536", dict(sigma_long_cut=32, sigma_chunk=1536)),
+                            ("cut64_chunk1536", dict(sigma_long_cut=64, sigma_chunk=1536)),
+                            ("cut32_chunk1536_noshare", dict(sigma_long_cut=32, sigma_chunk=1536, sigma_share=0)),
                             ("row_per_thread_exact", dict(sigma_exact=1, sigma_variant=0))):
             for k, v in opts.items():
                 ctx.set_option(k, v)
             best, med = time_pass(d, A, gr["now"])
-            ctx.set_option("sigma_exact", 0); ctx.set_option("sigma_long_cut", 32); ctx.set_option("sigma_variant", 1); ctx.set_option("sigma_chunk", 2048)
+            ctx.set_option("sigma_exact", 0); ctx.set_option("sigma_long_cut", 32); ctx.set_option("sigma_variant", 1); ctx.set_option("sigma_chunk", 2048); ctx.set_option("sigma_share", 1)
             res[label] = {"best_us": best * 1e3, "median_us": med * 1e3, "GBps_best": nbytes / best / 1e6,
                           "GBps_median": nbytes / med / 1e6}
             print(f"config4 {name:8s} {label:22s} best {best*1e3:7.1f} us  median {med*1e3:7.1f} us  {nbytes/med/1e6:7.0f} GB/s", flush=True)
