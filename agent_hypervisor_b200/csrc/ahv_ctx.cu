@@ -146,7 +146,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_sigma_variant = 1;
     c->opt_sigma_exact = 0;
     c->opt_sigma_long_cut = 32;
-    c->opt_sigma_chunk = 2048;
+    c->opt_sigma_chunk = 1536;
     c->opt_sigma_share = 1;
     c->opt_slash_variant = 0;
     c->opt_blocking_sync = 0;
@@ -318,7 +318,7 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
         ctx->opt_slash_variant = value;
     }
     else if (!strcmp(key, "sigma_variant")) {
-        AHV_REQUIRE(value == 0 || value == 1, "sigma_variant must be 0 or 1");
+        AHV_REQUIRE(value >= 0 && value <= 2, "sigma_variant must be 0, 1 or 2");
         ctx->opt_sigma_variant = value;
     } else if (!strcmp(key, "sigma_exact")) {
         AHV_REQUIRE(value == 0 || value == 1, "sigma_exact must be 0 or 1");

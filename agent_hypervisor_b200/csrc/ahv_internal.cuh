@@ -47,6 +47,7 @@ struct ahv_ctx {
     uint64_t leaf_launches;    // leaf-hash kernel launches so far (indexes the round robin)
     uint8_t *sigma_work;       // queue + claim flags of the tiled sigma_eff kernel (ahv_liability.cu)
     uint64_t sigma_work_tiles;
+    uint32_t sigma_tick_epoch; // number of the last streaming sigma_eff launch (which of its two tile counters is live)
     uint32_t sigma_epoch;      // number of the last tiled sigma_eff launch (work-queue generation)
     void *comm;                // ncclComm_t of this rank (ahv_comm_init), NULL in a world of one
     int comm_world, comm_rank;

@@ -383,6 +383,220 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
     }
 }
 
+// Streaming form (option sigma_variant = 2; an experiment kept for comparison, measured SLOWER than the tiled
+// form: 53 vs 39 us on the uniform config-4 graph, 76 vs 57 us on the Zipf one - with two stages per CTA only
+// four CTAs = 16 warps fit an SM, and the conversion / summing phases, which are chains of dependent
+// shared-memory loads and fp64 additions, then have too few warps to overlap with): the same tiles, sums and
+// results as k_sigma_eff_tiled, but the
+// CTAs are persistent (four per SM) and each runs a two-stage pipeline: while the 128 threads convert and sum
+// the chunk in one shared-memory stage, the bulk copies of the NEXT chunk - the same tile's, or the first one
+// of the CTA's next tile - are already filling the other stage, and the row pointers of the tiles after that
+// are on their way into registers.  Tiles are handed out by an atomic counter (a CTA that meets a heavy tile
+// simply comes back for fewer), fetched three tiles ahead so that no one waits for the counter.  A CTA pays
+// the DRAM latency of row pointers -> edges -> per-agent inputs once, at its start, instead of once per tile.
+constexpr int SIG_SCH = 1536;                    // edges per stage
+constexpr uint32_t SIG_STREAM_CTAS_PER_SM = 4;
+
+template <bool PAR>
+__global__ void __launch_bounds__(SIG_ROWS, SIG_STREAM_CTAS_PER_SM)
+k_sigma_eff_stream(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
+                   const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
+                   const double *__restrict__ sigma, const double *__restrict__ omega,
+                   const uint8_t *__restrict__ consensus, const uint8_t *__restrict__ current_ring, uint64_t A,
+                   double *__restrict__ out_sigma, uint8_t *__restrict__ out_ring, uint8_t *__restrict__ out_demote,
+                   uint8_t *__restrict__ out_near, uint32_t long_cut, uint32_t ntiles, uint32_t *tick, uint32_t epoch)
+{
+    extern __shared__ __align__(128) uint8_t sig_smem[];
+    SigStage<SIG_SCH> *stages = reinterpret_cast<SigStage<SIG_SCH> *>(sig_smem);
+    __shared__ __align__(8) uint64_t mbar_storage[2];
+    __shared__ double long_sum[SIG_ROWS];
+    __shared__ uint32_t long_r0[SIG_ROWS], long_r1[SIG_ROWS];
+    __shared__ uint16_t long_owner[SIG_ROWS];
+    __shared__ uint32_t wcount[SIG_WARPS];
+    __shared__ uint32_t s_ids[4];                         // tile numbers of this CTA's tiles j, j+1, j+2, j+3 (ring)
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    const uint32_t mbar0 = (uint32_t)__cvta_generic_to_shared(&mbar_storage[0]);
+    uint32_t *const ctr = tick + (epoch & 1u);            // tiles handed out beyond the first gridDim.x
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared.b64 [%0], %1;" ::"r"(mbar0), "r"(1u) : "memory");
+        asm volatile("mbarrier.init.shared.b64 [%0], %1;" ::"r"(mbar0 + 8u), "r"(1u) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (blockIdx.x == 0) tick[(epoch & 1u) ^ 1u] = 0u;            // the next launch's counter
+        s_ids[0] = blockIdx.x;
+        s_ids[1] = gridDim.x + atomicAdd(ctr, 1u);
+        s_ids[2] = gridDim.x + atomicAdd(ctr, 1u);
+    }
+    __syncthreads();
+
+    auto tile_end_row = [&](uint32_t t) { const uint64_t r = (uint64_t)t * SIG_ROWS + SIG_ROWS; return r < A ? r : A; };
+    // thread 0: the bulk copies of chunk k of a tile whose edges are [e0, e1), into stage s
+    auto issue = [&](uint32_t e0, uint32_t e1, uint32_t k, uint32_t s) {
+        const uint32_t mb = mbar0 + 8u * s;
+        const uint32_t base = e0 & ~15u;
+        uint32_t cnt16 = 0, c0 = base + k * SIG_SCH;
+        if (e1 > c0) {
+            const uint32_t cnt = (e1 - c0 > (uint32_t)SIG_SCH) ? (uint32_t)SIG_SCH : e1 - c0;
+            cnt16 = cnt & ~15u;
+        }
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(cnt16 * 17u) : "memory");
+        if (cnt16) {
+            bulk_g2s(stages[s].b, bonded + c0, cnt16 * 8u, mb);
+            bulk_g2s(stages[s].x, expiry + c0, cnt16 * 8u, mb);
+            bulk_g2s(stages[s].a, active + c0, cnt16, mb);
+        }
+    };
+    auto nchunks = [&](uint32_t e0, uint32_t e1) {        // at least one (an empty tile is one empty chunk)
+        const uint32_t base = e0 & ~15u;
+        const uint32_t c = (e1 > base) ? (e1 - base + SIG_SCH - 1) / SIG_SCH : 0u;
+        return c ? c : 1u;
+    };
+
+    // prologue: tile 0 of this CTA (its bounds are waited for here, once), bounds of tile 1 requested
+    uint32_t id = s_ids[0], id1 = s_ids[1], id2 = s_ids[2];
+    uint32_t cb0 = __ldg(rowptr + (uint64_t)id * SIG_ROWS), cb1 = __ldg(rowptr + tile_end_row(id));
+    uint32_t nb0 = 0, nb1 = 0;
+    if (id1 < ntiles) {
+        nb0 = __ldg(rowptr + (uint64_t)id1 * SIG_ROWS);
+        nb1 = __ldg(rowptr + tile_end_row(id1));
+    }
+    uint32_t my0 = 0, my1 = 0;
+    {
+        const uint64_t a = (uint64_t)id * SIG_ROWS + tid;
+        if (a < A) {
+            my0 = __ldg(rowptr + a);
+            my1 = __ldg(rowptr + a + 1);
+        }
+    }
+    if (tid == 0) issue(cb0, cb1, 0, 0);
+    uint32_t n = 0;                                       // chunks consumed so far: stage n & 1, parity (n >> 1) & 1
+
+    for (uint32_t j = 0;; ++j) {
+        // ---- requests for later tiles (consumed one tile from now)
+        uint32_t n2b0 = 0, n2b1 = 0, nmy0 = 0, nmy1 = 0;
+        if (id2 < ntiles) {
+            n2b0 = __ldg(rowptr + (uint64_t)id2 * SIG_ROWS);
+            n2b1 = __ldg(rowptr + tile_end_row(id2));
+        }
+        if (id1 < ntiles) {
+            const uint64_t a = (uint64_t)id1 * SIG_ROWS + tid;
+            if (a < A) {
+                nmy0 = __ldg(rowptr + a);
+                nmy1 = __ldg(rowptr + a + 1);
+            }
+        }
+        if (tid == 0) s_ids[(j + 3u) & 3u] = (id2 < ntiles) ? gridDim.x + atomicAdd(ctr, 1u) : SIG_NONE;
+        // ---- this tile
+        const uint64_t a = (uint64_t)id * SIG_ROWS + tid;
+        const bool valid = a < A;
+        double sg = 0.0, om = 0.0;
+        uint8_t cons = 0, ring_in = 0;
+        if (valid) {
+            sg = __ldg(sigma + a);
+            om = __ldg(omega + a);
+            if (out_ring) cons = __ldg(consensus + a);
+            if (out_demote) ring_in = __ldg(current_ring + a);
+        }
+        const uint32_t e_end = cb1, base = cb0 & ~15u, nchunk = nchunks(cb0, cb1);
+        RowSum<false> acc;
+        const bool is_long = PAR && (my1 - my0 > long_cut);
+        uint32_t n_long = 0;
+        if (PAR) {
+            const uint32_t bal = __ballot_sync(0xffffffffu, is_long);
+            if (lane == 0) wcount[wid] = __popc(bal);
+            __syncthreads();
+            uint32_t before = 0;
+#pragma unroll
+            for (int w = 0; w < SIG_WARPS; ++w) {
+                const uint32_t c = wcount[w];
+                if (w < (int)wid) before += c;
+                n_long += c;
+            }
+            if (is_long) {
+                const uint32_t k = before + __popc(bal & ((1u << lane) - 1u));
+                long_r0[k] = my0;
+                long_r1[k] = my1;
+                long_owner[k] = (uint16_t)tid;
+            }
+            // (read after the first chunk's conversion barrier)
+        }
+        uint32_t lk = wid;
+        double part = 0.0;
+        for (uint32_t k = 0; k < nchunk; ++k, ++n) {
+            SigStage<SIG_SCH> &st = stages[n & 1u];
+            // the next chunk's copies go out now, into the stage the previous chunk has left
+            if (tid == 0) {
+                if (k + 1 < nchunk) issue(cb0, cb1, k + 1, (n + 1u) & 1u);
+                else if (id1 < ntiles) issue(nb0, nb1, 0, (n + 1u) & 1u);
+            }
+            const uint32_t c0 = base + k * SIG_SCH;
+            const uint32_t c1 = (e_end <= c0) ? c0 : ((e_end - c0 > (uint32_t)SIG_SCH) ? c0 + SIG_SCH : e_end);
+            const uint32_t cnt16 = (c1 - c0) & ~15u;
+            if (tid < (c1 - c0) - cnt16) {                            // last, partial 16-edge group: ordinary loads
+                const uint32_t i = cnt16 + tid;
+                st.b[i] = __ldg(bonded + c0 + i);
+                st.x[i] = __ldg(expiry + c0 + i);
+                st.a[i] = __ldg(active + c0 + i);
+            }
+            {
+                uint32_t done = 0;
+                const uint32_t mb = mbar0 + 8u * (n & 1u);
+                while (!done)
+                    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                                 "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(mb), "r"((n >> 1) & 1u) : "memory");
+            }
+            if (cnt16 != c1 - c0) __syncthreads();
+            for (uint32_t i = 2 * tid; i < c1 - c0; i += 2 * SIG_ROWS) {
+                double2 b2 = *reinterpret_cast<const double2 *>(&st.b[i]);
+                const longlong2 x2 = *reinterpret_cast<const longlong2 *>(&st.x[i]);
+                const uint32_t a2 = *reinterpret_cast<const uint16_t *>(&st.a[i]);
+                b2.x = live_amount(b2.x, a2 & 0xffu, x2.x, now);
+                b2.y = live_amount(b2.y, a2 >> 8, x2.y, now);
+                *reinterpret_cast<double2 *>(&st.b[i]) = b2;
+            }
+            __syncthreads();
+            if (!is_long) {
+                const uint32_t lo = my0 > c0 ? my0 : c0, hi = my1 < c1 ? my1 : c1;
+                uint32_t e = lo;
+                for (; e + 4 <= hi; e += 4) {
+                    const double x0 = st.b[e - c0], x1 = st.b[e - c0 + 1], x2 = st.b[e - c0 + 2], x3 = st.b[e - c0 + 3];
+                    acc.add(x0); acc.add(x1); acc.add(x2); acc.add(x3);
+                }
+                for (; e < hi; ++e) acc.add(st.b[e - c0]);
+            }
+            if (PAR) {
+                while (lk < n_long) {
+                    const uint32_t r0 = long_r0[lk], r1 = long_r1[lk];
+                    if (r0 >= c1) break;
+                    const uint32_t lo = r0 > c0 ? r0 : c0, hi = r1 < c1 ? r1 : c1;
+                    for (uint32_t e = lo + ((lane - (lo - r0)) & 31u); e < hi; e += 32)
+                        part = __dadd_rn(part, st.b[e - c0]);
+                    if (r1 > c1) break;
+                    double x = part;
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) x = __dadd_rn(x, __shfl_xor_sync(0xffffffffu, x, o));
+                    if (lane == 0) long_sum[long_owner[lk]] = x;
+                    part = 0.0;
+                    lk += SIG_WARPS;
+                }
+            }
+            __syncthreads();                              // the stage is free for the chunk after next; long_sum is complete
+        }
+        if (valid) {
+            if (is_long) acc.f = long_sum[tid];
+            const double se = sigma_eff_of(sg, om, acc.result());
+            out_sigma[a] = se;
+            if (out_ring) out_ring[a] = (uint8_t)ring_from_sigma(se, cons != 0);
+            if (out_demote) out_demote[a] = (uint8_t)(ring_from_sigma(se, false) > (int)ring_in);
+            if (out_near) out_near[a] = (uint8_t)near_threshold(se);
+        }
+        if (id1 >= ntiles) break;
+        // ---- on to the CTA's next tile
+        id = id1; id1 = id2; id2 = s_ids[(j + 3u) & 3u];                 // written before this tile's barriers
+        cb0 = nb0; cb1 = nb1; nb0 = n2b0; nb1 = n2b1;
+        my0 = nmy0; my1 = nmy1;
+    }
+}
+
 __global__ void __launch_bounds__(256)
 k_ring_check(const uint8_t *__restrict__ agent_ring, const uint8_t *__restrict__ flags,
              const double *__restrict__ sigma, const uint8_t *__restrict__ consensus,
@@ -425,6 +639,7 @@ int sigma_work(ahv_ctx *ctx, uint64_t ntiles, SigWork *out)
         AHV_CUDA(cudaMemsetAsync(ctx->sigma_work, 0, off_claimed + 4ull * tiles, ctx->stream));
         AHV_CUDA(cudaMemsetAsync(ctx->sigma_work + off_queue, 0xff, 2 * 4ull * SIG_QUEUE_CAP, ctx->stream));
         ctx->sigma_epoch = 0;
+        ctx->sigma_tick_epoch = 0;
     }
     if (++ctx->sigma_epoch == 0) ctx->sigma_epoch = 1;    // 0 is what a never-claimed tile holds
     out->counters = reinterpret_cast<uint32_t *>(ctx->sigma_work);
@@ -456,8 +671,30 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
     const bool aligned = ((reinterpret_cast<uintptr_t>(d_bonded) | reinterpret_cast<uintptr_t>(d_expiry) |
                            reinterpret_cast<uintptr_t>(d_active)) & 15u) == 0;
     SigWork wk = {nullptr, nullptr, nullptr, 0, 0};
-    if (ctx->opt_sigma_variant != 0 && aligned && ctx->opt_sigma_share) AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
-    if (ctx->opt_sigma_variant == 0 || !aligned)
+    if (ctx->opt_sigma_variant == 1 && aligned && ctx->opt_sigma_share) AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
+    if (ctx->opt_sigma_variant == 2 && aligned) {
+        AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
+        const uint32_t ntiles = grid_for(A, SIG_ROWS);
+        const uint32_t resident = (uint32_t)ctx->sm_count * SIG_STREAM_CTAS_PER_SM;
+        const uint32_t g = ntiles < resident ? ntiles : resident;
+        const size_t smem = 2 * sizeof(SigStage<SIG_SCH>);
+        const uint32_t tick_epoch = ++ctx->sigma_tick_epoch;       // streaming launches alternate between two tile counters
+        static bool attr_set[2] = {false, false};
+        const int which = ctx->opt_sigma_exact ? 0 : 1;
+        if (!attr_set[which]) {
+            if (which) AHV_CUDA(cudaFuncSetAttribute(k_sigma_eff_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            else AHV_CUDA(cudaFuncSetAttribute(k_sigma_eff_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set[which] = true;
+        }
+        if (which)
+            k_sigma_eff_stream<true><<<g, SIG_ROWS, smem, ctx->stream>>>(
+                d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+                d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, ntiles, wk.counters + 4, tick_epoch);
+        else
+            k_sigma_eff_stream<false><<<g, SIG_ROWS, smem, ctx->stream>>>(
+                d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+                d_out_ring, d_out_demote, d_out_near, 0u, ntiles, wk.counters + 4, tick_epoch);
+    } else if (ctx->opt_sigma_variant == 0 || !aligned)
         k_sigma_eff_rings<<<grid_for(A, 256), 256, 0, ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma,
                                                                      d_omega, d_consensus, d_current_ring, A, d_out_sigma,
                                                                      d_out_ring, d_out_demote, d_out_near);
@@ -469,7 +706,7 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
         k_sigma_eff_tiled<0, true, 1024><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1024>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
             d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
-    else if (ctx->opt_sigma_chunk == 1536)
+    else if (ctx->opt_sigma_chunk != 2048)
         k_sigma_eff_tiled<0, true, 1536><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1536>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
             d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);

@@ -431,13 +431,14 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *                   drains, leaving the host cores to a packer thread (1; what ReplayPipeline sets)
  *   "slash_variant" 0/1/2 slashing: lane per small session + warp per larger one (default 0) / warp per session on
  *                   global memory only (1) / warp per session, staged in shared memory where it fits (2)
- *   "sigma_variant" 0/1 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1)
+ *   "sigma_variant" 0/1/2 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1) /
+ *                   persistent CTAs with a two-stage pipeline (2; measured slower, kept for comparison)
  *   "sigma_exact" 0/1   sigma_eff: 1 = every row summed left to right like the reference (bit-identical, but one very long
  *                   row then bounds the pass); 0 (default) = rows longer than "sigma_long_cut" edges are summed by a
  *                   warp in a fixed shape that depends on the row alone (a few ulp from the reference, same result every run)
  *   "sigma_long_cut" 4..  that row length (default 32)
  *   "sigma_share" 0/1   CTAs of that kernel take over tiles with many more edges than a chunk from a shared queue (default 1)
- *   "sigma_chunk" 1024/2048  records per shared-memory chunk of that kernel (default 2048)
+ *   "sigma_chunk" 1024/1536/2048  records per shared-memory chunk of that kernel (default 1536)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);
 

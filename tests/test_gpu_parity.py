@@ -562,7 +562,7 @@ def _check_sigma_default_path(ctx, args, want):
     return got, long_rows, float(rel.max())
 
 
-@pytest.mark.parametrize("mode", ["default", "exact", "row_per_thread"])
+@pytest.mark.parametrize("mode", ["default", "stream", "exact", "row_per_thread"])
 def test_sigma_eff_config4_shape_vs_oracle(ctx, mode):
     g = workloads.config4_graph(50_000, 500_000)
     # a few very long rows (beyond one shared-memory chunk) and NaN / inf / -0.0 amounts
@@ -570,8 +570,12 @@ def test_sigma_eff_config4_shape_vs_oracle(ctx, mode):
     args = (g["rowptr"], g["bonded"], g["active"], g["expiry"], g["now"], g["sigma"], g["omega"], g["consensus"],
             g["current_ring"])
     want = co.sigma_eff_rings(*args)
-    if mode == "default":
-        _, long_rows, _ = _check_sigma_default_path(ctx, args, want)
+    if mode in ("default", "stream"):
+        ctx.set_option("sigma_variant", 2 if mode == "stream" else 1)
+        try:
+            _, long_rows, _ = _check_sigma_default_path(ctx, args, want)
+        finally:
+            ctx.set_option("sigma_variant", 1)
         assert len(long_rows) > 10
         return
     ctx.set_option("sigma_exact", 1)
@@ -602,19 +606,19 @@ def test_sigma_eff_long_and_empty_rows(ctx):
             (rng.random(A) < 0.5).astype(np.uint8), rng.integers(1, 4, A).astype(np.uint8))
     want = co.sigma_eff_rings(*args)
     _check_sigma_default_path(ctx, args, want)
-    for cut, chunk in ((4, 2048), (100, 1024), (512, 2048), (4096, 1024)):      # other cuts / chunk sizes: same contract
+    for cut, chunk in ((4, 2048), (100, 1024), (512, 1536), (4096, 1024)):      # other cuts / chunk sizes: same contract
         ctx.set_option("sigma_long_cut", cut)
         ctx.set_option("sigma_chunk", chunk)
         try:
             got = ctx.sigma_eff_rings(*args)
         finally:
             ctx.set_option("sigma_long_cut", SIGMA_LONG_CUT)
-            ctx.set_option("sigma_chunk", 2048)
+            ctx.set_option("sigma_chunk", 1536)
         exp = sigma_expected_default_path(want, *args, cut=cut)
         assert np.array_equal(got[0], exp[0]) and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:4]))
     ctx.set_option("sigma_exact", 1)
     try:
-        for variant in (1, 0):
+        for variant in (1, 0, 2):
             ctx.set_option("sigma_variant", variant)
             got = ctx.sigma_eff_rings(*args)
             for a, b in zip(got, want):
@@ -622,6 +626,15 @@ def test_sigma_eff_long_and_empty_rows(ctx):
     finally:
         ctx.set_option("sigma_variant", 1)
         ctx.set_option("sigma_exact", 0)
+    # the streaming form (persistent CTAs, two-stage pipeline): same sums, same bits as the tiled one
+    ctx.set_option("sigma_variant", 2)
+    try:
+        for _ in range(3):                                   # consecutive launches alternate between two tile counters
+            got = ctx.sigma_eff_rings(*args)
+            exp = sigma_expected_default_path(want, *args)
+            assert np.array_equal(got[0], exp[0]) and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:4]))
+    finally:
+        ctx.set_option("sigma_variant", 1)
 
 
 def test_sigma_eff_config4_full_size(ctx):
