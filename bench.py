@@ -24,6 +24,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+REF_COPY = os.path.join(ROOT, "baseline", "_ref")          # copy of the reference tree made by __graft_entry__.build()
 
 SESSIONS_PER_GPU = 10_000
 LEAVES = 1000
@@ -163,16 +164,98 @@ def cpu_chain_sample(S: int, L: int, flen: int, first_session: int = 0):
     return arena, parents
 
 
+def reference_own(cores: int, budget_s: float = 60.0):
+    """The UNMODIFIED reference, from the copy under baseline/_ref (never from the original tree): its own
+    benchmarks/bench_hypervisor.py run as a subprocess, config 1 (one session, 1000 benchmark-shaped deltas:
+    capture, compute_merkle_root, verify_chain timed separately) and the commit+verify metric of this bench
+    with the real DeltaEngine objects on all host cores.  None if the copy is not there."""
+    src = os.path.join(REF_COPY, "src")
+    if not os.path.isdir(os.path.join(src, "hypervisor")):
+        return None
+    out = {"kind": "reference", "tree": "baseline/_ref (copy of the reference, unmodified)"}
+    # (1) the reference's own benchmark file, as it is
+    script = os.path.join(REF_COPY, "benchmarks", "bench_hypervisor.py")
+    try:
+        t0 = time.perf_counter()
+        r = subprocess.run([sys.executable, script], cwd=os.path.join(REF_COPY, "benchmarks"), capture_output=True,
+                           text=True, timeout=600)
+        own = {"rc": r.returncode, "seconds": time.perf_counter() - t0}
+        res = os.path.join(REF_COPY, "benchmarks", "results", "benchmarks.json")
+        if r.returncode == 0 and os.path.exists(res):
+            data = json.load(open(res))
+            rows = data.get("benchmarks", data if isinstance(data, list) else [])
+            keep = {}
+            for row in rows:
+                if isinstance(row, dict) and "name" in row:
+                    keep[row["name"]] = {k: row[k] for k in ("mean_us", "median_us", "p99_us", "ops_per_sec") if k in row}
+            own["results"] = keep
+        else:
+            own["stdout_tail"] = (r.stdout or "")[-600:]
+            own["stderr_tail"] = (r.stderr or "")[-300:]
+        out["bench_hypervisor_py"] = own
+    except Exception as e:                                   # a reported baseline must not break the bench line
+        out["bench_hypervisor_py"] = {"error": repr(e)}
+    # (2) + (3) with the real classes, in worker processes that import the copy
+    code = r"""
+import json, statistics, sys, time
+sys.path.insert(0, sys.argv[1])
+from hypervisor.audit.delta import DeltaEngine, VFSChange
+mode, n_sessions = sys.argv[2], int(sys.argv[3])
+def build(sid):
+    de = DeltaEngine(sid)
+    for i in range(1000):
+        de.capture("did:mesh:a", [VFSChange(path=f"/f{i}", operation="add", content_hash=f"h{i}")])
+    return de
+if mode == "config1":
+    def med(fn, reps, warm):
+        ts = []
+        for i in range(reps + warm):
+            t0 = time.perf_counter(); r = fn(); dt = time.perf_counter() - t0
+            if i >= warm: ts.append(dt)
+        return statistics.median(ts) * 1e3, r
+    t_cap, de = med(lambda: build("bench-session"), 5, 1)
+    t_root, root = med(de.compute_merkle_root, 20, 2)
+    t_ver, ok = med(de.verify_chain, 20, 2)
+    print(json.dumps({"capture_1000_ms": t_cap, "merkle_root_ms": t_root, "verify_chain_ms": t_ver, "verify": bool(ok), "root": root}))
+else:
+    engines = [build(f"session:{k}") for k in range(n_sessions)]
+    t0 = time.perf_counter()
+    ok = True
+    for de in engines:
+        r = de.compute_merkle_root()          # core.py:204
+        ok = de.verify_chain() and ok         # audit/delta.py:136-152 (re-serialises and re-hashes every delta)
+    print(json.dumps({"seconds": time.perf_counter() - t0, "deltas": 1000 * n_sessions, "verify": bool(ok)}))
+"""
+    try:
+        r = subprocess.run([sys.executable, "-c", code, src, "config1", "1"], capture_output=True, text=True, timeout=300)
+        out["config1"] = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"rc": r.returncode, "stderr_tail": r.stderr[-300:]}
+        per = 4                                                        # sessions per worker: ~0.1 s of timed work each
+        procs = [subprocess.Popen([sys.executable, "-c", code, src, "pipeline", str(per)], stdout=subprocess.PIPE, text=True)
+                 for _ in range(cores)]
+        outs = [json.loads(p.communicate(timeout=budget_s * 5)[0].strip().splitlines()[-1]) for p in procs]
+        worst = max(o["seconds"] for o in outs)
+        n = sum(o["deltas"] for o in outs)
+        out["commit_verify"] = {"value": n / worst, "unit": UNIT, "cores": cores, "verify": all(o["verify"] for o in outs),
+                                "sample": f"{cores} processes x {per} sessions x 1000 benchmark-shaped deltas: compute_merkle_root + "
+                                          f"verify_chain of the real DeltaEngine (json.dumps + hashlib per delta); throughput = all "
+                                          f"deltas / slowest process"}
+    except Exception as e:
+        out["commit_verify"] = {"error": repr(e)}
+    return out
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path = its hashlib pipeline,
-    restated at arena level (oracle port; the Python reference cannot travel to the GPU box), on all
-    host cores.  Each step is a bounded sample of the configs[1] workload."""
+    """--impl reference: the reference's CPU implementation of the path on all host cores.  The line's value is
+    its hashlib pipeline restated at arena level (oracle port: pre-packed pre-images of the configs[1] recipe, so
+    WITHOUT the reference's json.dumps cost - this flatters the reference); the unmodified reference itself,
+    run from the copy under baseline/_ref, is reported beside it under cpu_baseline.reference_own."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
-    S = max(cores, min(64 * cores, 4096))
-    S = min(S, 16 * cores) if cores > 64 else S
+    S = args.ref_sessions or max(cores, min(64 * cores, 4096))
+    if not args.ref_sessions and cores > 64:
+        S = min(S, 16 * cores)
     arena, parents = cpu_chain_sample(S, LEAVES, MSG_LEN)
     with cpu_pool(arena, LEAVES, MSG_LEN, parents, cores) as pool:
         for _ in range(max(args.warmup, 1)):
@@ -186,14 +269,18 @@ def run_reference(args):
     n = S * LEAVES
     value = n * args.steps / total
     sample = f"{S} sessions x {LEAVES} x {MSG_LEN} B per step (config-2 recipe), hashlib arena-level port, {cores} processes"
+    own = None if args.no_reference_own else reference_own(cores)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": "configs[1]: 10k sessions x 1k fixed-size 256 B deltas, commit + verify (bounded sample)",
+        "config": {"workload": f"configs[1] recipe (1k fixed-size 256 B deltas per session, commit + verify), bounded sample of "
+                               f"{S} sessions per step (the CUDA arm runs 10k sessions per GPU per step; throughput is per delta)",
                    "sample_sessions": S, "leaves_per_session": LEAVES, "delta_bytes": MSG_LEN,
-                   "note": "pre-packed arenas: the reference's json.dumps serialisation cost is NOT included"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                   "note": "pre-packed arenas: the reference's json.dumps serialisation cost is NOT included in `value`; "
+                           "cpu_baseline.reference_own has the unmodified reference with it"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "reference_own": own if own is not None else "baseline/_ref not present (built only where /root/reference exists)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "verified": bool(ok),
     }
@@ -202,13 +289,161 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------------- CUDA arm
+def pin_near_gpu(device: int):
+    """Restrict this process to the host cores next to its GPU (NVML's ideal CPU affinity) BEFORE any pinned
+    buffer is allocated, so that first touch places the upload buffers on the GPU's NUMA node."""
+    info = {"applied": False}
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(device)
+        words = (os.cpu_count() + 63) // 64
+        mask = nv.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        info["nvml_cpus"] = len(cpus)
+        try:
+            info["numa_node"] = int(open(f"/sys/bus/pci/devices/{nv.nvmlDeviceGetPciInfo(h).busId.decode().lower()[4:]}/numa_node").read())
+        except Exception:
+            pass
+        if use and use != allowed:
+            os.sched_setaffinity(0, use)
+            info["applied"] = True
+        info["cpus_used"] = len(use or allowed)
+    except Exception as e:
+        info["error"] = repr(e)[:120]
+    return info
+
+
+def timed_ms(ctx, fn, reps=3, warm=1):
+    """CUDA-event time of fn on the context's stream: (best, mean) over reps after warm-up."""
+    for _ in range(warm):
+        fn()
+    ctx.sync()
+    ts = []
+    for _ in range(reps):
+        ctx.timer_start(1); fn(); ctx.timer_stop(1)
+        ts.append(ctx.timer_ms(1))
+    return min(ts), float(np.mean(ts))
+
+
+def extra_configs(ctx, peaks, peak_dual, check: bool):
+    """The other BASELINE.json configs at their stated sizes on one GPU, timed with CUDA events after the headline
+    region (device-resident inputs); with check=True a sample of each is compared with the oracle (checker only)."""
+    import workloads
+    out = {}
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    co = None
+    if check:
+        from oracle import coracle as co
+    # ---- configs[2]: variable-length deltas 64 B..16 KB, 10^7 leaves: hash, hash + 10^4 trees, verify
+    n1, tiles = 1_000_000, 10
+    a1, o1 = workloads.config3_arena(n1)
+    B1 = int(o1[-1])
+    pad = (-B1) % 16
+    if pad:                                                   # keep every tile 16-byte aligned: the last message of a tile grows by the pad
+        a1 = np.concatenate([a1, np.zeros(pad, np.uint8)])
+        o1 = o1.copy(); o1[-1] += np.uint64(pad)
+    B1p = B1 + pad
+    n = n1 * tiles
+    offs = np.concatenate([o1[:-1] + np.uint64(k * B1p) for k in range(tiles)] + [np.array([tiles * B1p], np.uint64)])
+    comp = int(((np.diff(o1.astype(np.int64)) + 9 + 63) // 64).sum()) * tiles
+    S3, L3 = n // 1000, 1000
+    d = {k: ctx.dev_alloc(v) for k, v in dict(arena=B1p * tiles + 64, offs=offs.nbytes, digs=32 * n, par=32 * n, kind=n,
+                                               roots=32 * S3, roots2=32 * S3, empty=S3, verdict=S3, fb=8 * S3, match=S3).items()}
+    for k in range(tiles):
+        ctx.h2d(d["arena"] + k * B1p, a1)
+    ctx.h2d(d["offs"], offs)
+    ctx.sync()
+    hash_ms, _ = timed_ms(ctx, lambda: ctx.sha256_batch_dev(d["arena"], B1p * tiles, d["offs"], n, 0, d["digs"]), reps=2)
+    commit_ms, _ = timed_ms(ctx, lambda: ctx.commit_dev(d["arena"], B1p * tiles, d["offs"], 0, 0, S3, n, L3, L3, d["digs"],
+                                                        d["roots"], d["empty"]), reps=2)
+    # parents = digest of the message before (first of a session: None): built on the host from the digests
+    h_digs = np.empty((n, 32), np.uint8)
+    ctx.d2h(h_digs, d["digs"]); ctx.sync()
+    par = np.zeros((n, 32), np.uint8); par[1:] = h_digs[:-1]
+    kind = np.ones(n, np.uint8); kind[::L3] = 0
+    ctx.h2d(d["par"], par); ctx.h2d(d["kind"], kind); ctx.sync()
+    verify_ms, _ = timed_ms(ctx, lambda: ctx.verify_chains_dev(d["arena"], B1p * tiles, d["offs"], 0, d["par"], d["kind"], 0, S3, n,
+                                                               L3, L3, d["roots"], d["verdict"], d["fb"], 0, d["roots2"], d["match"]),
+                            reps=2)
+    h_verdict = np.empty(S3, np.uint8); h_match = np.empty(S3, np.uint8); h_roots = np.empty((S3, 32), np.uint8)
+    ctx.d2h(h_verdict, d["verdict"]); ctx.d2h(h_match, d["match"]); ctx.d2h(h_roots, d["roots"]); ctx.sync()
+    ok3 = bool(h_verdict.all() and h_match.all()) and all(np.array_equal(h_digs[:n1], h_digs[k * n1:(k + 1) * n1]) for k in (1, tiles - 1))
+    if check:
+        ns = 20_000                                           # first 20 sessions of tile 0 against the C oracle
+        want = co.sha256_batch(a1, o1[: ns + 1])
+        wr, _ = co.merkle_roots(want, np.arange(ns // L3 + 1, dtype=np.uint64) * np.uint64(L3))
+        ok3 = ok3 and np.array_equal(want, h_digs[:ns]) and np.array_equal(wr, h_roots[: ns // L3])
+    for p_ in d.values():
+        ctx.dev_free(p_)
+    msg_bytes = B1 * tiles
+    out["var_len"] = {
+        "workload": "configs[2]: 10^7 messages, lengths log-uniform 64 B..16 KB (a 10^6-message arena tiled 10x on the "
+                    "device), tightly packed (every byte alignment), length-sorted launch order; 10^4 sessions x 1000",
+        "messages": n, "message_bytes": msg_bytes, "compressions": comp,
+        "hash_ms": hash_ms, "compressions_per_s": comp / hash_ms * 1e3, "message_GBps": msg_bytes / hash_ms / 1e6,
+        "frac_of_int_peak": comp * ALGO_INSTR_PER_COMPRESSION / (hash_ms * 1e-3) / peak_dual,
+        "commit_ms": commit_ms, "verify_ms": verify_ms,
+        "deltas_committed_verified_per_s": n / ((commit_ms + verify_ms) * 1e-3), "verified": bool(ok3),
+        "checked_against_oracle": "first 20 000 digests + 20 roots" if check else None}
+    del h_digs, par, kind, a1, offs
+
+    # ---- configs[3]: sigma_eff + ring gating, 10^6 agents, 10^7 vouch records (Zipf-like in-degree, and degree 10)
+    A, E = 1_000_000, 10_000_000
+    g = workloads.config4_graph(A, E)
+    nbytes = workloads.config4_bytes(A, E)
+    keys = ("rowptr", "bonded", "active", "expiry", "sigma", "omega", "consensus", "current_ring")
+    dd = {k: ctx.dev_alloc(g[k].nbytes) for k in keys}
+    for k in keys:
+        ctx.h2d(dd[k], g[k])
+    o = [ctx.dev_alloc(8 * A), ctx.dev_alloc(A), ctx.dev_alloc(A), ctx.dev_alloc(A)]
+    ctx.sync()
+    run = lambda: ctx.sigma_eff_rings_dev(dd["rowptr"], dd["bonded"], dd["active"], dd["expiry"], g["now"], dd["sigma"],
+                                          dd["omega"], dd["consensus"], dd["current_ring"], A, *o)
+    sig = {"workload": "configs[3]: 10^6 agents, 10^7 vouch records, one session; sigma_eff, ring, demotion flag, near-threshold list",
+           "algorithmic_bytes": nbytes, "hbm_peak_gbs": hbm_peak, "longest_row": int(np.diff(g["rowptr"].astype(np.int64)).max()),
+           "sum_order": "rows of up to 32 records in the reference's order (bit-identical), longer rows by one warp in a fixed shape"}
+    for shape in ("zipf", "uniform"):
+        if shape == "uniform":
+            ctx.h2d(dd["rowptr"], (np.arange(A + 1, dtype=np.uint64) * 10).astype(np.uint32)); ctx.sync()
+        best, mean = timed_ms(ctx, run, reps=20, warm=3)
+        sig[shape] = {"ms": mean, "best_ms": best, "GBps": nbytes / mean / 1e6, "frac": nbytes / mean / 1e6 / hbm_peak}
+        if shape == "zipf":
+            ctx.set_option("sigma_exact", 1)
+            b2, m2 = timed_ms(ctx, run, reps=5, warm=1)
+            ctx.set_option("sigma_exact", 0)
+            sig["zipf_exact_order"] = {"ms": m2, "GBps": nbytes / m2 / 1e6, "frac": nbytes / m2 / 1e6 / hbm_peak}
+            if check:
+                run(); got = [np.empty(A, np.float64), np.empty(A, np.uint8), np.empty(A, np.uint8), np.empty(A, np.uint8)]
+                for arr, ptr in zip(got, o):
+                    ctx.d2h(arr, ptr)
+                ctx.sync()
+                want = co.sigma_eff_rings(*[g[k] for k in ("rowptr", "bonded", "active", "expiry", "now", "sigma", "omega",
+                                                           "consensus", "current_ring")])
+                rel = np.abs(got[0] - want[0]) / np.maximum(np.abs(want[0]), 1e-300)
+                listed = (got[3] != 0) | (want[3] != 0)
+                short = np.diff(g["rowptr"].astype(np.int64)) <= 32
+                sig["max_rel_err_vs_oracle"] = float(rel.max())
+                sig["bit_identical_rows"] = int((got[0] == want[0]).sum())
+                sig["near_threshold_agents"] = int(listed.sum())
+                sig["verified"] = bool(rel.max() <= 1e-6 and np.array_equal(got[0][short], want[0][short]) and
+                                       np.array_equal(got[1][~listed], want[1][~listed]) and
+                                       np.array_equal(got[2][~listed], want[2][~listed]))
+    for p_ in list(dd.values()) + o:
+        ctx.dev_free(p_)
+    out["sigma_eff"] = sig
+    return out
+
+
 def run_cuda(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
-            # convenience: re-launch under torchrun
+            # convenience: re-launch under torchrun (used only as the process launcher)
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                    "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000), __file__] + sys.argv[1:]
             return subprocess.call(cmd)
@@ -217,39 +452,34 @@ def run_cuda(args):
     import __graft_entry__ as ge
     if rank == 0:
         ge.build()
-    dist = torch = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        dist.barrier()
+    host = pin_near_gpu(local) if not args.no_affinity else {"applied": False}
 
     import workloads
     from agent_hypervisor_b200 import Context
+    from agent_hypervisor_b200 import comm as ahv_comm
     ctx = Context(local)
+    # the library's own NCCL communicator (one process per GPU; no torch in this process)
+    ahv_comm.init_from_env(ctx, rank, world)
+    ctx.barrier()
     info = ctx.device_info()
     S, L, FL = args.sessions, LEAVES, MSG_LEN
     n = S * L
     arena_bytes = n * FL
 
+    def max_over_ranks(x: float) -> float:
+        return float(ctx.comm_all_gather(np.array([x], np.float64)).max()) if world > 1 else x
+
     # ---- inputs: template arena in pinned host memory -> device -> chained on the device
     h_arena = ctx.host_alloc(arena_bytes)
     offs, hexpos, rp = workloads.config2_fill(h_arena, rank * S, S, L, FL)
+    stride = ctx.gather_stride(S)
     names = dict(arena=arena_bytes, offs=offs.nbytes, hexpos=hexpos.nbytes, rp=rp.nbytes, digs=32 * n, par=32 * n,
-                 kind=n, empty=S, verdict=S, fb=8 * S, match=S, roots_v=32 * S)
+                 kind=n, empty=S, verdict=S, fb=8 * S, match=S, roots_v=32 * S, roots=32 * S, gathered=world * stride)
     d = {k: ctx.dev_alloc(v) for k, v in names.items()}
-    if world > 1:
-        t_roots = torch.empty(32 * S, dtype=torch.uint8, device=f"cuda:{local}")
-        t_all_roots = torch.empty(32 * S * world, dtype=torch.uint8, device=f"cuda:{local}")
-        t_verdict = torch.empty(S, dtype=torch.uint8, device=f"cuda:{local}")
-        t_all_verdict = torch.empty(S * world, dtype=torch.uint8, device=f"cuda:{local}")
-        d_roots, d_verdict = t_roots.data_ptr(), t_verdict.data_ptr()
-        ext_stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local))
-    else:
-        d_roots, d_verdict = ctx.dev_alloc(32 * S), d["verdict"]
+    d_roots, d_verdict = d["roots"], d["verdict"]
     ctx.h2d(d["arena"], h_arena); ctx.h2d(d["offs"], offs); ctx.h2d(d["hexpos"], hexpos); ctx.h2d(d["rp"], rp)
-    ctx.chain_capture_dev(d["arena"], arena_bytes, d["offs"], d["hexpos"], d["rp"], S, n, d["digs"], d["par"], d["kind"])
+    chain_ms, _ = timed_ms(ctx, lambda: ctx.chain_capture_dev(d["arena"], arena_bytes, d["offs"], d["hexpos"], d["rp"], S, n,
+                                                              d["digs"], d["par"], d["kind"]), reps=2, warm=1)
     ctx.d2h(h_arena, d["arena"])          # chained arena back in pinned host memory for the e2e leg
     h_par = ctx.host_alloc(32 * n); h_kind = ctx.host_alloc(n)
     ctx.d2h(h_par, d["par"]); ctx.d2h(h_kind, d["kind"])
@@ -261,11 +491,9 @@ def run_cuda(args):
         ctx.verify_chains_dev(d["arena"], arena_bytes, 0, FL, d["par"], d["kind"], 0, S, n, L, L, d_roots,
                               d_verdict, d["fb"], 0, d["roots_v"], d["match"])
         if world > 1 and not args.no_gather:
-            # the collectives are ordered after the kernels on the library's own stream (wrapped as a
-            # torch ExternalStream): no host synchronisation inside a step
-            with torch.cuda.stream(ext_stream):
-                dist.all_gather_into_tensor(t_all_roots, t_roots)        # 32 B x S sub-roots per rank over NVLink
-                dist.all_gather_into_tensor(t_all_verdict, t_verdict)
+            # ONE all-gather of every rank's roots + verdicts (33 B per session), issued by the library on its own
+            # stream right behind the kernels: no host synchronisation inside a step
+            ctx.gather_results_dev(d_roots, d_verdict, S, d["gathered"])
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -274,30 +502,23 @@ def run_cuda(args):
     if rank == 0 and not args.no_clocks:
         sampler.start()
         time.sleep(0.1)
-    if world > 1:          # every rank enters the timed region together (after rank 0 started its sampler)
-        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    ctx.sync(); ctx.barrier(); ctx.sync()      # every rank enters the timed region together
     ctx.set_option("leaf_timer", 32)
     launches0 = ctx.launch_count()
     t_wall0 = time.perf_counter()
     ctx.timer_start(0)
     for _ in range(args.steps):
         step()
-    if world > 1:
-        torch.cuda.synchronize()
     ctx.timer_stop(0)
     ms_total = ctx.timer_ms(0)
     ctx.sync()
     t_wall1 = time.perf_counter()
     launches = ctx.launch_count() - launches0
     ctx.set_option("leaf_timer", 0)
+    ctx.barrier()
+    ms_total = max_over_ranks(ms_total)
     if world > 1:
-        dist.barrier()
-        t = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
-        lt = torch.tensor([launches], dtype=torch.int64, device=f"cuda:{local}")
-        dist.all_reduce(lt, op=dist.ReduceOp.SUM)
-        launches = int(lt.item())
+        launches = int(ctx.comm_all_gather(np.array([launches], np.int64)).sum())
     clocks = None
     if rank == 0:
         time.sleep(0.15)
@@ -312,8 +533,17 @@ def run_cuda(args):
     # results of the last step
     h_verdict = np.empty(S, np.uint8); h_match = np.empty(S, np.uint8); h_roots = np.empty(32 * S, np.uint8)
     ctx.d2h(h_verdict, d_verdict); ctx.d2h(h_match, d["match"]); ctx.d2h(h_roots, d_roots)
+    h_all = np.empty(world * stride, np.uint8)
+    if world > 1:
+        ctx.d2h(h_all, d["gathered"])
     ctx.sync()
     verified = bool(h_verdict.all() and h_match.all())
+    if world > 1 and not args.no_gather:
+        from agent_hypervisor_b200 import sharding
+        all_roots, all_verdicts = sharding.unpack_gathered(h_all, S, world)
+        verified = verified and np.array_equal(all_roots[rank * S:(rank + 1) * S].reshape(-1), h_roots) and bool(all_verdicts.all())
+        # every rank holds every rank's roots: all sessions distinct, none left unwritten
+        verified = verified and len({r.tobytes() for r in all_roots[::max(1, S // 64)]}) == len(all_roots[::max(1, S // 64)])
 
     # ---- end-to-end through the host-pointer C ABI (pinned host buffers, copies inside the timed region)
     e2e_steps = max(1, min(args.steps, 3))
@@ -327,37 +557,41 @@ def run_cuda(args):
     h_pos = ctx.host_alloc(4 * n, np.uint32)
     h_pos[:] = hexpos                            # where each pre-image holds its parent_hash value
 
-    def e2e_step():
+    def e2e_step(with_digests=True):
         # one upload of the batch (pre-images + 4-byte parent positions), then the commit pass and the
         # verify pass on the device, results back
         rc = lib.ahv_audit_sessions(H, vp(h_arena.ctypes.data), None, FL, None, None, vp(h_pos.ctypes.data),
-                                    None, S, L, vp(h_digs.ctypes.data), vp(h_roots_e.ctypes.data),
-                                    vp(h_empty_e.ctypes.data), vp(h_verdict_e.ctypes.data), vp(h_fb_e.ctypes.data),
-                                    vp(h_match_e.ctypes.data))
+                                    None, S, L, None, vp(h_digs.ctypes.data) if with_digests else None,
+                                    vp(h_roots_e.ctypes.data), vp(h_empty_e.ctypes.data), vp(h_verdict_e.ctypes.data),
+                                    vp(h_fb_e.ctypes.data), vp(h_match_e.ctypes.data))
         assert rc == 0, lib.ahv_last_error()
 
+    def wall(fn, reps):
+        ctx.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        return max_over_ranks(time.perf_counter() - t0)
+
     e2e_step()                                   # warm-up (sizes the staging slab)
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+    e2e_s = wall(e2e_step, e2e_steps)
     verified = verified and bool(h_verdict_e.all() and h_match_e.all()) and np.array_equal(h_roots_e, h_roots)
+    e2e_nodig_s = wall(lambda: e2e_step(False), e2e_steps)
+    # the plain-copy ceiling beside it: the same pinned arena, host -> device, nothing else, all ranks at once
+    def copy_only():
+        ctx.h2d(d["arena"], h_arena); ctx.sync()
+    copy_only()
+    copy_s = wall(copy_only, e2e_steps)
     h2d = arena_bytes + 4 * n                            # arena + parent positions, once per step
     d2h = 32 * n + 32 * S + S + S + 8 * S + S            # digests, roots, empty, verdict, first_bad, match
 
     if rank != 0:
-        if world > 1:
-            dist.barrier(); dist.destroy_process_group()
+        ctx.barrier()
+        ctx.comm_destroy()
         return 0
 
     # ---- roofline of the dominant kernel (leaf SHA-256; 2 launches per step)
-    # integer ceilings measured live by register-only kernels on all SMs (csrc/ahv_peak.cu)
+    # integer rates measured live by register-only kernels on all SMs (csrc/ahv_peak.cu)
     peak_alu, _ = ctx.int_peak(0, 30000)          # SHF+LOP3 only: the ALU pipe alone (64 lanes/clk/SM)
     peak_dual, _ = ctx.int_peak(10, 30000)        # SHF+LOP3 co-issued with IMAD: both integer-capable pipes
     peak_native, _ = ctx.int_peak(2, 3000)        # whole compressions, plain additions (compiler's placement)
@@ -373,9 +607,10 @@ def run_cuda(args):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_bytes = n * FL + 32 * n
-    traffic = None
+    traffic, traffic_src = None, None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "leaf_kernel_traffic.json")))["dram_bytes_per_launch"]
+        tr = json.load(open(os.path.join(ROOT, "profiles", "leaf_kernel_traffic.json")))
+        traffic, traffic_src = tr["dram_bytes_per_launch"], tr.get("source", "ncu --set full, round 1 (profiles/r01/prof_audit_raw.csv)")
     except Exception:
         pass
     # instructions SHA-256 can only issue on the ALU pipe (funnel shifts, 3-input logic, byte swaps):
@@ -385,6 +620,7 @@ def run_cuda(args):
         "kernel": "k_sha256_fixed (leaf SHA-256, one 256 B delta per thread)",
         "bound": "int32-pipe", "achieved": achieved / 1e12, "peak": peak_dual / 1e12, "unit": "Tinstr/s",
         "frac": achieved / peak_dual, "traffic": traffic,
+        "traffic_source": f"not observed by this run: {traffic_src}" if traffic is not None else None,
         "algorithmic": f"{ALGO_INSTR_PER_COMPRESSION} int instr/compression x {comp_per_launch} compressions/launch",
         "launch_ms": leaf_avg_ms, "launches_timed": n_leaf,
         "peak_source": "measured live: ahv_int_peak mode 10 (SHF+LOP3 on the ALU pipe co-issued with IMAD on the FMA "
@@ -395,15 +631,20 @@ def run_cuda(args):
                          "note": "shift/logic instructions that cannot leave the ALU pipe, over its measured peak; "
                                  "additions run as IMAD on the FMA pipe"},
         "alu_pipe_peak_tinstr": peak_alu / 1e12, "frac_of_alu_pipe": achieved / peak_alu,
-        "compress_ceiling_native_tinstr": peak_native / 1e12, "compress_ceiling_scaled_tinstr": peak_scaled / 1e12,
-        "frac_of_compress_ceiling": achieved / peak_scaled,
+        # whole-compression microbenchmarks (register-only, no loads): comparison points, NOT upper bounds - the leaf
+        # kernel's fifth block is a constant-schedule padding block that costs fewer instructions than these loops' blocks
+        "compress_microbench_native_tinstr": peak_native / 1e12, "compress_microbench_scaled_tinstr": peak_scaled / 1e12,
+        "vs_compress_microbench": achieved / peak_scaled,
         "hbm": {"achieved": hbm_bytes / (leaf_avg_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": hbm_bytes / (leaf_avg_ms * 1e-3) / 1e9 / hbm_peak,
                 "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback"},
     }
+    if roofline["frac"] > 1.0 or roofline["binding_pipe"]["frac"] > 1.0:
+        roofline["inconsistent"] = "a fraction above 1: the peak microbenchmark is not an upper bound for this kernel"
 
     # ---- CPU baseline beside it (oracle port on the host cores, bounded sample) + parity check
     cpu = None
+    configs = None
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         Sc = min(S, max(cores, min(16 * cores, 1024)))
@@ -420,9 +661,19 @@ def run_cuda(args):
         cpu = {"value": Sc * L / dt, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"first {Sc} of the GPU run's sessions ({Sc * L} deltas), hashlib arena-level port of "
                          f"delta.py:63,117-152, {cores} processes; roots compared with the GPU's"}
+    if world == 1 and not args.no_configs:
+        for k_ in ("arena", "digs", "par", "kind"):           # make room: config 3 needs 30 GB + digests
+            ctx.dev_free(d.pop(k_))
+        configs = extra_configs(ctx, peaks, peak_dual, check=not args.no_cpu_baseline)
+        configs["chain_capture"] = {
+            "workload": "configs[1] arena: 10^4 sessions x 1000 x 256 B chained on the device (audit/delta.py:101-114), one lane per session",
+            "ms": chain_ms, "deltas_per_s": n / chain_ms * 1e3,
+            "verified": "the chained arena is the input of the headline commit + verify step (all links verify)"}
+        verified = verified and bool(configs["var_len"]["verified"]) and bool(configs["sigma_eff"].get("verified", True))
 
     seconds = ms_total * 1e-3
     value = world * n * args.steps / seconds
+    e2e_value = world * n * e2e_steps / e2e_s
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -430,18 +681,27 @@ def run_cuda(args):
         "config": {"workload": "configs[1]: 10k sessions x 1k fixed-size 256 B deltas per GPU, commit + verify",
                    "sessions_per_gpu": S, "leaves_per_session": L, "delta_bytes": FL,
                    "l2_note": "inputs (2.56 GB arena per GPU) exceed the 126 MB L2; no flush needed",
-                   "sharding": "sessions sharded by rank; roots + verdicts all-gathered over NCCL" if world > 1 else "single GPU"},
+                   "sharding": ("sessions sharded by rank; roots + verdicts collected by ONE ncclAllGather per step, issued "
+                                "inside libahv_b200.so (ahv_gather_results_dev)") if world > 1 else "single GPU"},
         "sha256_message_GBps": world * 2 * n * FL * args.steps / seconds / 1e9,
         "compressions_per_s": world * 2 * (leaf_c + node_c) * args.steps / seconds,
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-        "e2e": {"value": world * n * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                "api": "ahv_audit_sessions (host-pointer C ABI, pinned host buffers; commit pass + verify pass on one upload, pipelined in session chunks)"},
+                "api": "ahv_audit_sessions (host-pointer C ABI, pinned host buffers; commit pass + verify pass on one upload, pipelined in session chunks)",
+                "upload_GBps_all_ranks": world * h2d * e2e_steps / e2e_s / 1e9,
+                "h2d_ceiling_gbs": world * arena_bytes * e2e_steps / copy_s / 1e9,
+                "h2d_ceiling_note": "the same pinned arena copied host -> device with nothing else running, all ranks at once",
+                "frac_of_h2d_ceiling": (h2d / e2e_s) / (arena_bytes / copy_s),
+                "without_digests": {"value": world * n * e2e_steps / e2e_nodig_s, "d2h_bytes_per_step": d2h - 32 * n,
+                                    "note": "out_digests = NULL: roots, verdicts, first-bad indices and root matches only"}},
+        "comm": ctx.comm_info(), "host": host, "configs": configs,
         "verified": verified, "device": info,
     }
     emit_line(line)
     if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+        ctx.barrier()
+        ctx.comm_destroy()
     return 0 if verified else 1
 
 
@@ -473,6 +733,10 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--sessions", type=int, default=SESSIONS_PER_GPU, help="sessions per GPU (default: configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the configs[2]/configs[3] legs (variable-length deltas, sigma_eff)")
+    ap.add_argument("--no-affinity", action="store_true", help="do not pin the process to the cores next to its GPU")
+    ap.add_argument("--ref-sessions", type=int, default=0, help="--impl reference: sessions per step (default: bounded by the core count)")
+    ap.add_argument("--no-reference-own", action="store_true", help="--impl reference: skip the unmodified reference's own runs")
     ap.add_argument("--no-clocks", action="store_true", help="diagnostic: do not poll nvidia-smi during the timed region")
     ap.add_argument("--no-gather", action="store_true", help="diagnostic: skip the per-step all-gather")
     args = ap.parse_args()
