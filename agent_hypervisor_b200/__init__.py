@@ -15,6 +15,7 @@ from .models import ActionDescriptor, ExecutionRing, ReversibilityLevel
 from .rings import RingCheckResult, RingEnforcer
 from .vfs import content_hashes
 from .install import install, uninstall
+from .integration import terminate_sessions, terminate_sessions_sync
 
 __version__ = "0.1.0"
 
@@ -23,5 +24,5 @@ __all__ = [
     "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions", "ReplayPipeline",
     "SemanticDelta", "VFSChange", "LiabilityEdge", "LiabilityMatrix", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
     "SlashingEngine", "SlashRequest", "SlashResult", "VoucherClip",
-    "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer", "content_hashes", "install", "uninstall",
+    "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer", "content_hashes", "install", "uninstall", "terminate_sessions", "terminate_sessions_sync",
 ]

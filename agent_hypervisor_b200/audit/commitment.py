@@ -22,6 +22,15 @@ class CommitmentRecord:
     committed_to: str = "local"
 
 
+class _PendingCommit:
+    """A queued session whose root is still to be computed (CommitmentEngine.queue_engine_for_batch)."""
+
+    __slots__ = ("session_id", "engine", "participant_dids")
+
+    def __init__(self, session_id, engine, participant_dids):
+        self.session_id, self.engine, self.participant_dids = session_id, engine, participant_dids
+
+
 class CommitmentEngine:
     def __init__(self) -> None:
         self._commitments: dict[str, CommitmentRecord] = {}
@@ -43,9 +52,34 @@ class CommitmentEngine:
     def queue_for_batch(self, record: CommitmentRecord) -> None:
         self._batch_queue.append(record)
 
-    def flush_batch(self) -> list[CommitmentRecord]:
-        out = list(self._batch_queue)
+    def queue_engine_for_batch(self, session_id: str, engine, participant_dids: list[str]) -> None:
+        """Queue a session whose Summary Hash has NOT been computed yet: ``flush_batch`` builds the trees of
+        all queued engines in one device launch (what ``core.py:204-211`` does per session: root of the
+        engine's ``delta_hash`` leaves, then ``commit``).  The reference's queue only carries finished records
+        (audit/commitment.py:66-68); this is the natural batching point SURVEY.md 8f names."""
+        self._batch_queue.append(_PendingCommit(session_id, engine, list(participant_dids)))
+
+    def flush_batch(self, auditor=None) -> list[CommitmentRecord]:
+        """audit/commitment.py:70-74: returns the queued records, in queue order, and empties the queue.  Queued
+        engines are committed first - one ``ahv_merkle_roots`` launch for all of them; an engine without deltas
+        has no root and yields no record (core.py:205)."""
+        queue = list(self._batch_queue)
         self._batch_queue.clear()
+        pending = [q for q in queue if isinstance(q, _PendingCommit)]
+        roots = {}
+        if pending:
+            from .batch import BatchAuditor
+            auditor = auditor or BatchAuditor()
+            for q, r in zip(pending, auditor.roots_of_engines([q.engine for q in pending])):
+                roots[id(q)] = r
+        out = []
+        for q in queue:
+            if isinstance(q, _PendingCommit):
+                r = roots[id(q)]
+                if r:
+                    out.append(self.commit(q.session_id, r, q.participant_dids, q.engine.turn_count))
+            else:
+                out.append(q)
         return out
 
     def verify_batch(self, session_ids, engines, auditor=None) -> list[bool]:
