@@ -444,7 +444,7 @@ constexpr uint32_t TOP_MAX = 256;
 template <bool UNIFORM, bool SC>
 __global__ void __launch_bounds__(128)
 k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const uint64_t *__restrict__ rp_in,
-             uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc)
+             uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc, uint32_t *__restrict__ status)
 {
     const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     __shared__ uint32_t buf[2][TOP_MAX][8 + 1];   // +1 word pad against bank conflicts
@@ -459,9 +459,12 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
         in0 = rp_in[s];
         c = (uint32_t)(rp_in[s + 1] - in0);
     }
-    if (c == 0) {
+    if (c == 0 || c > TOP_MAX) {
+        // c > TOP_MAX: the caller of a _dev entry understated max_session_leaves, so fewer level steps ran than this
+        // session needs; it gets a zero root and the context's sticky error flag is raised (reported by ahv_sync)
         if (threadIdx.x < 32) roots[32 * s + threadIdx.x] = 0;
-        if (threadIdx.x == 0 && empty) empty[s] = 1;
+        if (threadIdx.x == 0 && empty) empty[s] = (c == 0) ? 1 : 0;
+        if (threadIdx.x == 0 && c) atomicOr(status, AHV_STATUS_MAX_LEAVES);
         return;
     }
     if (threadIdx.x == 0 && empty) empty[s] = 0;
@@ -511,7 +514,7 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
 template <bool UNIFORM, bool SC>
 __global__ void __launch_bounds__(128)
 k_merkle_top_warp(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const uint64_t *__restrict__ rp_in,
-                  uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc)
+                  uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc, uint32_t *__restrict__ status)
 {
     const typename Pol<SC>::type cp = Pol<SC>::make(rc);
     __shared__ uint32_t buf[4][2][64][8 + 1];
@@ -527,9 +530,10 @@ k_merkle_top_warp(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, c
         in0 = rp_in[s];
         c = (uint32_t)(rp_in[s + 1] - in0);
     }
-    if (c == 0) {
+    if (c == 0 || c > 64u) {                              // c > 64: see k_merkle_top
         roots[32 * s + lane] = 0;
-        if (lane == 0 && empty) empty[s] = 1;
+        if (lane == 0 && empty) empty[s] = (c == 0) ? 1 : 0;
+        if (lane == 0 && c) atomicOr(status, AHV_STATUS_MAX_LEAVES);
         return;
     }
     if (lane == 0 && empty) empty[s] = 0;
@@ -865,17 +869,21 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
         }
     }
     const uint64_t top = tree_top(ctx, S);
+    if (top > 64 && S > 0x7fffffffull) {                  // one CTA per session: gridDim.x is limited to 2^31 - 1
+        set_error("more than 2^31 - 1 sessions with an in-CTA tree finish (top_max > 64); use top_max <= 64 or split the batch");
+        return AHV_E_TOOLARGE;
+    }
     if (top <= 64) {
         const unsigned g4 = (unsigned)((S + 3) / 4);
-        if (uniform && sc) k_merkle_top_warp<true, true><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
-        else if (uniform) k_merkle_top_warp<true, false><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
-        else if (sc) k_merkle_top_warp<false, true><<<g4, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
-        else k_merkle_top_warp<false, false><<<g4, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
+        if (uniform && sc) k_merkle_top_warp<true, true><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);
+        else if (uniform) k_merkle_top_warp<true, false><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);
+        else if (sc) k_merkle_top_warp<false, true><<<g4, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc, ctx->status_d);
+        else k_merkle_top_warp<false, false><<<g4, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc, ctx->status_d);
     } else
-    if (uniform && sc) k_merkle_top<true, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
-    else if (uniform) k_merkle_top<true, false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc);
-    else if (sc) k_merkle_top<false, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
-    else k_merkle_top<false, false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc);
+    if (uniform && sc) k_merkle_top<true, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);
+    else if (uniform) k_merkle_top<true, false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);
+    else if (sc) k_merkle_top<false, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc, ctx->status_d);
+    else k_merkle_top<false, false><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc, ctx->status_d);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
@@ -1205,6 +1213,10 @@ extern "C" int ahv_merkle_roots_noalloc_dev(ahv_ctx *ctx, const uint8_t *d_diges
                   (unsigned long long)S);
         return AHV_E_TOOLARGE;
     }
+    if (S > 0x7fffffffull) {
+        set_error("more than 2^31 - 1 sessions in one allocation-free call");
+        return AHV_E_TOOLARGE;
+    }
     uint8_t *base = nullptr;
     AHV_TRY(noalloc_base(ctx, &base));
 
@@ -1226,7 +1238,7 @@ extern "C" int ahv_merkle_roots_noalloc_dev(ahv_ctx *ctx, const uint8_t *d_diges
             cur = dst;
         }
     }
-    k_merkle_top<false, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, SHA_SC);
+    k_merkle_top<false, true><<<(unsigned)S, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, SHA_SC, ctx->status_d);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

@@ -82,6 +82,18 @@ int io_reserve(ahv_ctx *ctx, uint64_t bytes)
     return AHV_OK;
 }
 
+// Device-side sanity flags raised by kernels since the last check (sticky until reported once).
+int check_status(ahv_ctx *ctx)
+{
+    const uint32_t st = __atomic_exchange_n(ctx->status_h, 0u, __ATOMIC_ACQ_REL);
+    if (st & AHV_STATUS_MAX_LEAVES) {
+        set_error("max_session_leaves was smaller than a session's real leaf count: the affected sessions' roots were "
+                  "written as zeros; pass the true maximum (or 0 to let the library find it)");
+        return AHV_E_INVALID;
+    }
+    return AHV_OK;
+}
+
 void *io_take(ahv_ctx *ctx, uint64_t bytes)
 {
     uint64_t b = pad256(bytes ? bytes : 1);
@@ -137,6 +149,14 @@ int ahv_create(int device, ahv_ctx **out_ctx)
         AHV_CUDA(cudaEventCreate(&c->t_start[i]));
         AHV_CUDA(cudaEventCreate(&c->t_stop[i]));
     }
+    {
+        void *h = nullptr, *dv = nullptr;
+        AHV_CUDA(cudaHostAlloc(&h, 64, cudaHostAllocMapped));
+        memset(h, 0, 64);
+        AHV_CUDA(cudaHostGetDevicePointer(&dv, h, 0));
+        c->status_h = (uint32_t *)h;
+        c->status_d = (uint32_t *)dv;
+    }
     c->comm_world = 1;
     c->opt_sort = 1;
     c->opt_block = 128;
@@ -166,6 +186,7 @@ void ahv_destroy(ahv_ctx *ctx)
     if (ctx->io) cudaFree(ctx->io);
     if (ctx->sigma_work) cudaFree(ctx->sigma_work);
     if (ctx->one_out) cudaFreeHost(ctx->one_out);
+    if (ctx->status_h) cudaFreeHost(ctx->status_h);
     for (int i = 0; i < AHV_PIPE_EVENTS; ++i) cudaEventDestroy(ctx->ev_pipe[i]);
     for (int i = 0; i < AHV_MAX_TIMERS; ++i) {
         cudaEventDestroy(ctx->t_start[i]);
@@ -183,7 +204,7 @@ int ahv_sync(ahv_ctx *ctx)
     AHV_CUDA(cudaStreamSynchronize(ctx->copy_stream));
     AHV_CUDA(cudaStreamSynchronize(ctx->stream));
     AHV_CUDA(cudaStreamSynchronize(ctx->d2h_stream));
-    return AHV_OK;
+    return check_status(ctx);
 }
 
 int ahv_device_info(ahv_ctx *ctx, int *sm_count, int *sm_clock_khz, uint64_t *total_mem)

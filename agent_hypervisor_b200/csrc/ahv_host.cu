@@ -57,7 +57,7 @@ struct Stager {
     {
         if (rc != AHV_OK) return rc;
         AHV_CUDA(cudaStreamSynchronize(ctx->stream));
-        return AHV_OK;
+        return check_status(ctx);
     }
 };
 
@@ -67,7 +67,10 @@ uint64_t p256(uint64_t b) { return pad256(b ? b : 1); }
 int arena_extent(const uint64_t *offsets, uint64_t n, uint64_t fixed_len, uint64_t *bytes)
 {
     if (offsets) {
-        AHV_REQUIRE(offsets[0] <= offsets[n], "offsets must be non-decreasing");
+        // every message length is offsets[i+1] - offsets[i]: one decreasing pair would wrap to ~2^64 bytes
+        uint64_t bad = 0;
+        for (uint64_t i = 0; i < n; ++i) bad |= (uint64_t)(offsets[i + 1] < offsets[i]);
+        AHV_REQUIRE(!bad, "offsets must be non-decreasing");
         *bytes = offsets[n];
     } else {
         *bytes = n * fixed_len;

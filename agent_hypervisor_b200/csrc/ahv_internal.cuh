@@ -9,6 +9,7 @@
 
 #define AHV_MAX_TIMERS 64
 #define AHV_PIPE_EVENTS 64
+#define AHV_STATUS_MAX_LEAVES 1u   // a _dev tree entry was given a max_session_leaves smaller than a session really has
 
 struct ahv_ctx {
     int device;
@@ -51,6 +52,7 @@ struct ahv_ctx {
     uint32_t sigma_epoch;      // number of the last tiled sigma_eff launch (work-queue generation)
     void *comm;                // ncclComm_t of this rank (ahv_comm_init), NULL in a world of one
     int comm_world, comm_rank;
+    uint32_t *status_h, *status_d; // sticky device-side error flags (mapped pinned host word and its device alias); ahv_sync reports them
     uint8_t *one_out;          // 64 B of mapped pinned host memory: where ahv_sha256_one's kernel writes its digest
 };
 
@@ -99,6 +101,7 @@ void *io_take(ahv_ctx *ctx, uint64_t bytes);
 static inline uint64_t pad256(uint64_t b) { return (b + 255u) & ~(uint64_t)255u; }
 
 int use_device(ahv_ctx *ctx);
+int check_status(ahv_ctx *ctx);                       // sticky device-side error flags -> error code (clears them)
 void comm_release(ahv_ctx *ctx);                     // ahv_comm.cu: destroys the communicator, if any
 
 static inline unsigned grid_for(uint64_t threads, unsigned block)

@@ -71,6 +71,9 @@ const char *ahv_last_error(void);
 /* One context per GPU per process.  device = CUDA ordinal. */
 int ahv_create(int device, ahv_ctx **out_ctx);
 void ahv_destroy(ahv_ctx *ctx);
+/* Waits for everything the context has enqueued.  Also reports (once) a sanity flag a kernel of a _dev entry
+ * point raised since the last call, as AHV_E_INVALID: today that is a max_session_leaves smaller than a
+ * session's real size (the affected roots are zeros). */
 int ahv_sync(ahv_ctx *ctx);
 /* sm_count, max SM clock (kHz), total device memory (bytes); any pointer may be NULL */
 int ahv_device_info(ahv_ctx *ctx, int *sm_count, int *sm_clock_khz, uint64_t *total_mem);
@@ -124,7 +127,8 @@ int ahv_sha256_batch_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena_by
  *   duplicates its last node (:129), one leaf -> root is the leaf (:125),
  *   no leaves -> None (:119-120), reported as out_empty[s] = 1 and a zero root.
  *   max_session_leaves: the largest session size (0 = let the library find it;
- *   the _dev variant then synchronises once).
+ *   the _dev variant then synchronises once).  It sizes the in-CTA finish of the tree: if it is given too
+ *   small, the sessions that do not fit get zero roots and the next ahv_sync returns AHV_E_INVALID.
  */
 int ahv_merkle_roots(ahv_ctx *ctx, const uint8_t *digests /* n*32 */, const uint64_t *session_rowptr,
                      uint64_t n_sessions, uint8_t *out_roots /* S*32 */, uint8_t *out_empty /* S */);

@@ -805,3 +805,114 @@ def test_config2_full_size_properties(ctx):
         assert np.array_equal(dg.reshape(-1), h["digs"][int(s) * L * 32:(int(s) + 1) * L * 32])
         r, _ = co.merkle_roots(dg, np.array([0, L], np.uint64))
         assert np.array_equal(r[0], h["roots"][int(s) * 32:(int(s) + 1) * 32])
+
+
+# ------------------------------------------------------------------ guards and end-of-allocation reads
+def test_understated_max_session_leaves_is_reported_not_corrupting(ctx):
+    """A _dev tree entry sizes its in-CTA finish from the caller's max_session_leaves.  Too small a value used to
+    overrun the finish kernels' shared-memory level; now the sessions that do not fit get zero roots, the others
+    stay right, and the next ahv_sync reports it once."""
+    from agent_hypervisor_b200 import NativeError
+    rng = np.random.default_rng(3)
+    for sizes, claimed in (([1000, 3, 70, 500, 64], 64), ([300] * 20000 + [50000], 300), ([100000, 2], 4)):
+        rp = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+        n, S = int(rp[-1]), len(sizes)
+        digs = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        want, _ = co.merkle_roots(digs, rp)
+        d_dig, d_rp, d_roots, d_empty = ctx.dev_alloc(32 * n), ctx.dev_alloc(rp.nbytes), ctx.dev_alloc(32 * S), ctx.dev_alloc(S)
+        try:
+            ctx.h2d(d_dig, digs); ctx.h2d(d_rp, rp)
+            for entry in (ctx.merkle_roots_dev, ctx.merkle_roots_noalloc_dev):
+                if entry == ctx.merkle_roots_noalloc_dev and n > 200_000:
+                    continue
+                ctx.memset(d_roots, 0xA5, 32 * S)
+                entry(d_dig, d_rp, S, n, claimed, d_roots, d_empty)
+                got = np.empty((S, 32), np.uint8)
+                ctx.d2h(got, d_roots)
+                with pytest.raises(NativeError, match="max_session_leaves was smaller"):
+                    ctx.sync()
+                ctx.sync()                                            # reported once
+                bad = [s for s in range(S) if not np.array_equal(got[s], want[s])]
+                assert bad and all(not got[s].any() for s in bad)     # zero roots, never garbage
+                assert all(sizes[s] > claimed for s in bad)           # only sessions larger than what was claimed
+                entry(d_dig, d_rp, S, n, max(sizes), d_roots, d_empty)     # the true maximum: everything right
+                ctx.d2h(got, d_roots); ctx.sync()
+                assert np.array_equal(got, want)
+        finally:
+            for p in (d_dig, d_rp, d_roots, d_empty):
+                ctx.dev_free(p)
+
+
+def test_host_entries_reject_decreasing_offsets(ctx):
+    import ctypes as C
+    vp = C.c_void_p
+    a = np.zeros(4096, np.uint8)
+    out = np.zeros((4, 32), np.uint8)
+    offs = np.array([0, 100, 50, 200, 300], np.uint64)                # one decreasing pair inside
+    assert ctx.lib.ahv_sha256_batch(ctx.h, vp(a.ctypes.data), vp(offs.ctypes.data), 4, 0, vp(out.ctypes.data)) == -1
+    assert b"non-decreasing" in ctx.lib.ahv_last_error()
+    rp = np.array([0, 4], np.uint64)
+    roots = np.zeros((1, 32), np.uint8)
+    assert ctx.lib.ahv_commit(ctx.h, vp(a.ctypes.data), vp(offs.ctypes.data), 0, vp(rp.ctypes.data), 1, 0, None,
+                              vp(roots.ctypes.data), None) == -1
+
+
+def test_reads_stop_at_the_end_of_the_allocation(ctx):
+    """compute-sanitizer is not available on this pool, so out-of-bounds safety of the unaligned tail reads is
+    checked the blunt way: inputs are placed so that their last byte is the LAST byte of a device allocation
+    (a read past it would leave the allocation; with a 2 MiB-granular allocator that is the next, unmapped page)."""
+    rng = np.random.default_rng(12)
+    BLOCK = 2 << 20
+    for trial in range(6):
+        lens = np.concatenate([rng.integers(0, 300, 400), [1, 2, 3, 55, 56, 63, 64, 65, 119, 120, 121 + trial]])
+        offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        total = int(offs[-1])
+        arena = rng.integers(0, 256, total, dtype=np.uint8)
+        blk = ctx.dev_alloc(BLOCK)
+        d_offs, d_out = ctx.dev_alloc(offs.nbytes), ctx.dev_alloc(32 * len(lens))
+        try:
+            base = blk + BLOCK - total                                # the arena ends exactly where the block ends
+            ctx.lib.ahv_memcpy_h2d(ctx.h, base, arena.ctypes.data, total)
+            ctx.h2d(d_offs, offs)
+            for sort in (0, 1):
+                ctx.set_option("sort", sort)
+                ctx.sha256_batch_dev(base, total, d_offs, len(lens), 0, d_out)
+                got = np.empty((len(lens), 32), np.uint8)
+                ctx.d2h(got, d_out); ctx.sync()
+                assert np.array_equal(got, co.sha256_batch(arena, offs))
+        finally:
+            ctx.set_option("sort", 1)
+            for p in (blk, d_offs, d_out):
+                ctx.dev_free(p)
+    # the sigma_eff pass (16-byte bulk copies + ordinary loads for the last partial group): edge arrays that end with
+    # their allocations
+    A = 5000
+    deg = rng.integers(0, 24, A); deg[-1] = 13; deg[100] = 700
+    rowptr = np.concatenate([[0], np.cumsum(deg)]).astype(np.uint32)
+    E = int(rowptr[-1])
+    E += (-E) % 2                                                      # keep the 8-byte arrays 16-byte aligned at their start
+    rowptr[-1] = E
+    g = dict(bonded=rng.random(E), active=(rng.random(E) < 0.9).astype(np.uint8), expiry=np.full(E, lo.EXPIRY_NONE, np.int64))
+    blocks = {k: ctx.dev_alloc(BLOCK) for k in g}
+    starts = {k: blocks[k] + BLOCK - ((g[k].nbytes + 15) // 16) * 16 for k in g}        # 16-byte aligned starts, ...
+    starts["bonded"] = blocks["bonded"] + BLOCK - g["bonded"].nbytes                      # ... these two end exactly with the block
+    starts["expiry"] = blocks["expiry"] + BLOCK - g["expiry"].nbytes
+    sigma, omega = rng.random(A), rng.choice([0.2, 0.65, 0.95], A)
+    cons, ring = np.zeros(A, np.uint8), np.full(A, 3, np.uint8)
+    small = {k: ctx.dev_alloc(max(v.nbytes, 16)) for k, v in dict(rowptr=rowptr, sigma=sigma, omega=omega, cons=cons, ring=ring).items()}
+    outs = [ctx.dev_alloc(8 * A), ctx.dev_alloc(A), ctx.dev_alloc(A), ctx.dev_alloc(A)]
+    try:
+        for k in g:
+            ctx.lib.ahv_memcpy_h2d(ctx.h, starts[k], g[k].ctypes.data, g[k].nbytes)
+        for k, v in dict(rowptr=rowptr, sigma=sigma, omega=omega, cons=cons, ring=ring).items():
+            ctx.h2d(small[k], v)
+        ctx.sigma_eff_rings_dev(small["rowptr"], starts["bonded"], starts["active"], starts["expiry"], 1000, small["sigma"],
+                                small["omega"], small["cons"], small["ring"], A, *outs)
+        got = np.empty(A, np.float64)
+        ctx.d2h(got, outs[0]); ctx.sync()
+        want = co.sigma_eff_rings(rowptr, g["bonded"], g["active"], g["expiry"], 1000, sigma, omega, cons, ring)
+        exp = sigma_expected_default_path(want, rowptr, g["bonded"], g["active"], g["expiry"], 1000, sigma, omega, cons, ring)
+        assert np.array_equal(got, exp[0])
+    finally:
+        for p in list(blocks.values()) + list(small.values()) + outs:
+            ctx.dev_free(p)

@@ -13,6 +13,8 @@ Named test_zz_* so that pytest collects it last: a failure here cannot hide any 
 import numpy as np
 import pytest
 
+from oracle import coracle as co
+
 pytestmark = pytest.mark.gpu
 
 
@@ -51,6 +53,8 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
         got_roots, got_empty = _roots(ctx, digs, rp, noalloc=True)
         assert np.array_equal(got_empty, want_empty)
         assert np.array_equal(got_roots, want_roots)        # bit-exact, like every digest test here
+        oracle_roots, oracle_empty = co.merkle_roots(digs, rp)             # ... and both against the oracle, not only each other
+        assert np.array_equal(got_roots, oracle_roots) and np.array_equal(got_empty, oracle_empty)
         assert list(got_empty) == [1 if s == 0 else 0 for s in sizes]
 
 
