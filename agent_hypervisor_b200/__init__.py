@@ -7,7 +7,7 @@ Importing this package loads nothing native; the first call that needs the GPU l
 """
 
 from ._native import Context, NativeError, NativeUnavailable, get_context, load_library
-from .audit import (ArenaBuilder, BatchAuditor, CommitmentEngine, CommitmentRecord, DeltaEngine, PackedSessions,
+from .audit import (ArenaBuilder, BatchAuditor, CommitmentEngine, CommitmentRecord, DeltaEngine, DeviceReplay, PackedSessions,
                     ReplayPipeline, SemanticDelta, VFSChange)
 from .liability import (LiabilityEdge, LiabilityMatrix, SlashingEngine, SlashRequest, SlashResult, VoucherClip, VouchGraphCSR,
                         VouchingEngine, VouchingError, VouchRecord)
@@ -21,7 +21,7 @@ __version__ = "0.1.0"
 
 __all__ = [
     "Context", "NativeError", "NativeUnavailable", "get_context", "load_library",
-    "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions", "ReplayPipeline",
+    "ArenaBuilder", "BatchAuditor", "CommitmentEngine", "CommitmentRecord", "DeltaEngine", "PackedSessions", "ReplayPipeline", "DeviceReplay",
     "SemanticDelta", "VFSChange", "LiabilityEdge", "LiabilityMatrix", "VouchGraphCSR", "VouchingEngine", "VouchingError", "VouchRecord",
     "SlashingEngine", "SlashRequest", "SlashResult", "VoucherClip",
     "ActionDescriptor", "ExecutionRing", "ReversibilityLevel", "RingCheckResult", "RingEnforcer", "content_hashes", "install", "uninstall", "terminate_sessions", "terminate_sessions_sync",

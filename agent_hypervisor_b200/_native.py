@@ -75,6 +75,8 @@ SIGNATURES = {
     "ahv_memcpy_h2d": (C.c_int, [_vp, _vp, _vp, _u64]),
     "ahv_memcpy_d2h": (C.c_int, [_vp, _vp, _vp, _u64]),
     "ahv_memset_dev": (C.c_int, [_vp, _vp, C.c_int, _u64]),
+    "ahv_upload_async": (C.c_int, [_vp, _vp, _vp, _u64]),
+    "ahv_upload_fence": (C.c_int, [_vp]),
     "ahv_timer_start": (C.c_int, [_vp, C.c_int]),
     "ahv_timer_stop": (C.c_int, [_vp, C.c_int]),
     "ahv_timer_elapsed_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
@@ -97,6 +99,7 @@ SIGNATURES = {
     "ahv_chain_capture": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "ahv_chain_capture_dev": (C.c_int, [_vp, _vp, _u64, _vp, _vp, _vp, _u64, _u64, _vp, _vp, _vp]),
     "ahv_pack_deltas": (C.c_int, [_vp, _vp, _vp, _u64, _u64p, _vp, C.c_uint32]),
+    "ahv_pack_deltas_dev": (C.c_int, [_vp, _vp, _vp, _vp, _u64, _u64p, _vp, C.c_uint32]),
     "ahv_sigma_eff_rings": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,
                                       _vp, _vp, _vp, _vp]),
     "ahv_sigma_eff_rings_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, _u64,
@@ -231,6 +234,21 @@ class Context:
 
     def d2h(self, arr: np.ndarray, dptr: int):
         self._check(self.lib.ahv_memcpy_d2h(self.h, _vp(arr.ctypes.data), _vp(dptr), arr.nbytes), "ahv_memcpy_d2h")
+
+    def upload_async(self, dptr: int, arr: np.ndarray, nbytes: Optional[int] = None):
+        """Host -> device on the context's second stream (overlaps the main stream's kernels); see upload_fence."""
+        self._check(self.lib.ahv_upload_async(self.h, _vp(dptr), _vp(arr.ctypes.data), int(arr.nbytes if nbytes is None else nbytes)),
+                    "ahv_upload_async")
+
+    def upload_fence(self):
+        self._check(self.lib.ahv_upload_fence(self.h), "ahv_upload_fence")
+
+    def pack_deltas_dev(self, cols_struct, d_offsets: int, d_arena: int, capacity: int, d_parent_pos: int, want_bytes: bool = False):
+        """ahv_pack_deltas_dev; ``cols_struct`` is the ctypes struct of audit.packing with DEVICE pointers."""
+        nb = _u64()
+        self._check(self.lib.ahv_pack_deltas_dev(self.h, C.byref(cols_struct), _vp(d_offsets), _vp(d_arena), int(capacity),
+                                                 C.byref(nb) if want_bytes else None, _vp(d_parent_pos), 0), "ahv_pack_deltas_dev")
+        return int(nb.value) if want_bytes else None
 
     def memset(self, dptr: int, value: int, nbytes: int):
         self._check(self.lib.ahv_memset_dev(self.h, _vp(dptr), int(value), int(nbytes)), "ahv_memset_dev")

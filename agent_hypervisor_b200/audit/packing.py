@@ -268,3 +268,52 @@ def pack_columns(cols: dict, arena: Optional[np.ndarray] = None, want_parent_pos
     if want_parent_pos:
         return arena[: int(nbytes.value)], offsets, ppos[:n]
     return arena[: int(nbytes.value)], offsets
+
+
+# ---------------------------------------------------------------------------------------------
+# Columns on the device: one pinned staging buffer holding every column array (16-byte aligned
+# pieces), mirrored by one device buffer, so that a chunk of columns travels in ONE copy and the
+# device packer (ahv_pack_deltas_dev) reads it in place.
+# ---------------------------------------------------------------------------------------------
+_COLUMN_ARRAYS = (
+    ("delta_id_blob", "delta_id", 0), ("delta_id_off", "delta_id", 1), ("session_id_blob", "session_id", 0),
+    ("session_id_off", "session_id", 1), ("agent_did_blob", "agent_did", 0), ("agent_did_off", "agent_did", 1),
+    ("turn_id", "turn_id", None), ("timestamp_us", "timestamp_us", None), ("timestamp_utcoffset_s", "timestamp_utcoffset_s", None),
+    ("parent_kind", "parent_kind", None), ("parent_digest", "parent_digest", None),
+    ("parent_other_blob", "parent_other", 0), ("parent_other_off", "parent_other", 1), ("change_rowptr", "change_rowptr", None),
+    ("change_path_blob", "change_path", 0), ("change_path_off", "change_path", 1), ("change_op_blob", "change_op", 0),
+    ("change_op_off", "change_op", 1), ("change_content_blob", "change_content", 0), ("change_content_off", "change_content", 1),
+    ("change_content_null", "change_content", 2), ("change_prev_blob", "change_prev", 0), ("change_prev_off", "change_prev", 1),
+    ("change_prev_null", "change_prev", 2))
+
+
+def column_bytes(cols: dict) -> int:
+    """Bytes ``stage_columns`` needs for these columns."""
+    total = 0
+    for _, key, part in _COLUMN_ARRAYS:
+        a = cols[key] if part is None else cols[key][part]
+        total += (np.asarray(a).nbytes + 15) & ~15
+    return total + 16
+
+
+def stage_columns(cols: dict, staging: np.ndarray):
+    """Copy every column array into ``staging`` (a pinned uint8 buffer).  Returns (layout, used_bytes) where
+    layout maps struct field -> byte offset inside the buffer; the same offsets hold on the device copy."""
+    layout, pos = {}, 0
+    for field, key, part in _COLUMN_ARRAYS:
+        a = np.ascontiguousarray(cols[key] if part is None else cols[key][part])
+        nb = a.nbytes
+        if pos + nb > staging.nbytes:
+            raise ValueError(f"column staging buffer of {staging.nbytes} bytes is too small")
+        staging[pos: pos + nb] = a.view(np.uint8).reshape(-1)
+        layout[field] = pos
+        pos += (nb + 15) & ~15
+    return layout, pos
+
+
+def device_columns_struct(n: int, layout: dict, d_base: int) -> "_DeltaColumns":
+    st = _DeltaColumns()
+    st.n = n
+    for field, off in layout.items():
+        setattr(st, field, d_base + off)
+    return st

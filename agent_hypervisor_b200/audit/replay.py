@@ -114,3 +114,121 @@ class ReplayPipeline:
                 res["digests"] = np.array(res["digests"]); res["first_bad"] = np.array(res["first_bad"])
             yield res
             k += 1
+
+
+class DeviceReplay:
+    """Replay with the canonical packer ON THE DEVICE (``ahv_pack_deltas_dev``): a chunk's COLUMNS are staged in one
+    pinned buffer, uploaded in one copy on the context's second stream (overlapping the previous chunk's kernels),
+    serialised by one thread per delta straight into the arena the hashing kernels read, then committed and
+    verified (``ahv_extract_parents_dev`` -> ``ahv_commit_dev`` -> ``ahv_verify_chains_dev``), and only digests,
+    roots and verdicts travel back.  No host core serialises anything; the upload is the fields (< 200 bytes per
+    delta) instead of the pre-images (~330 bytes).  Same results as ``ReplayPipeline``.
+
+    Sizes: ``arena_bytes`` of pre-images, ``max_deltas`` deltas, ``max_sessions`` sessions and ``column_bytes``
+    of staged columns (``packing.column_bytes``) for the largest chunk."""
+
+    def __init__(self, arena_bytes: int, max_deltas: int, max_sessions: int, column_bytes: int,
+                 ctx: Optional[nat.Context] = None) -> None:
+        self.ctx = ctx or nat.get_context()
+        c = self.ctx
+        n, S = max(int(max_deltas), 1), max(int(max_sessions), 1)
+        self.limits = (int(arena_bytes), n, S, int(column_bytes))
+        self._stage = [c.host_alloc(int(column_bytes)) for _ in range(2)]
+        self._d_cols = [c.dev_alloc(int(column_bytes)) for _ in range(2)]
+        self._h_rp = [c.host_alloc(8 * (S + 1), np.uint64) for _ in range(2)]
+        self._h_exp = [c.host_alloc(32 * S) for _ in range(2)]
+        self._d_rp = [c.dev_alloc(8 * (S + 1)) for _ in range(2)]
+        self._d_exp = [c.dev_alloc(32 * S) for _ in range(2)]
+        sizes = dict(arena=int(arena_bytes) + 64, offs=8 * (n + 1), ppos=4 * n, par=32 * n, kind=n, digs=32 * n, roots=32 * S,
+                     roots_v=32 * S, empty=S, verdict=S, fb=8 * S, match=S)
+        self._d = {k: c.dev_alloc(v) for k, v in sizes.items()}
+        self._out = [dict(digests=c.host_alloc(32 * n), roots=c.host_alloc(32 * S), empty=c.host_alloc(S), verdict=c.host_alloc(S),
+                          first_bad=c.host_alloc(8 * S, np.int64), root_match=c.host_alloc(S)) for _ in range(2)]
+
+    def close(self) -> None:
+        c = self.ctx
+        c.sync()
+        for a in self._stage + self._h_rp + self._h_exp + [v for o in self._out for v in o.values()]:
+            c.host_free(a)
+        for p in self._d_cols + self._d_rp + self._d_exp + list(self._d.values()):
+            c.dev_free(p)
+        self._stage = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _stage_chunk(self, k: int, cols: dict, session_rowptr, committed_roots=None):
+        """Host side of chunk k: columns into the pinned staging buffer, upload started on the second stream."""
+        from .packing import device_columns_struct, stage_columns
+        c, b = self.ctx, k % 2
+        n = int(cols["n"])
+        rp = np.asarray(session_rowptr, dtype=np.uint64)
+        S = len(rp) - 1
+        if n > self.limits[1] or S > self.limits[2] or int(rp[-1]) != n:
+            raise ValueError(f"chunk {k}: {n} deltas / {S} sessions exceed the pipeline's buffers "
+                             f"({self.limits[1]} / {self.limits[2]}), or session_rowptr does not end at n")
+        layout, used = stage_columns(cols, self._stage[b])
+        self._h_rp[b][: S + 1] = rp
+        c.upload_async(self._d_cols[b], self._stage[b], used)
+        c.upload_async(self._d_rp[b], self._h_rp[b], 8 * (S + 1))
+        has_exp = committed_roots is not None
+        if has_exp:
+            self._h_exp[b][: 32 * S] = np.ascontiguousarray(committed_roots, dtype=np.uint8).reshape(-1)
+            c.upload_async(self._d_exp[b], self._h_exp[b], 32 * S)
+        maxl = int(np.diff(rp.astype(np.int64)).max()) if S else 0
+        return dict(n=n, S=S, b=b, st=device_columns_struct(n, layout, self._d_cols[b]), has_exp=has_exp, maxl=max(maxl, 1))
+
+    def _enqueue(self, ch: dict) -> None:
+        """Device side of a staged chunk: pack, parents, commit, verify, results back - all asynchronous."""
+        c, d, b, n, S = self.ctx, self._d, ch["b"], ch["n"], ch["S"]
+        o = self._out[b]
+        c.upload_fence()                                           # the kernels below wait for this chunk's uploads
+        if n == 0:
+            return
+        cap = self.limits[0]
+        c.pack_deltas_dev(ch["st"], d["offs"], d["arena"], cap, d["ppos"])
+        c.extract_parents_dev(d["arena"], cap, d["offs"], 0, d["ppos"], n, d["par"], d["kind"])
+        c.commit_dev(d["arena"], cap, d["offs"], 0, self._d_rp[b], S, n, 0, ch["maxl"], d["digs"], d["roots"], d["empty"])
+        c.verify_chains_dev(d["arena"], cap, d["offs"], 0, d["par"], d["kind"], self._d_rp[b], S, n, 0, ch["maxl"],
+                            self._d_exp[b] if ch["has_exp"] else d["roots"], d["verdict"], d["fb"], 0, d["roots_v"], d["match"])
+        lib, h, vp = c.lib, c.h, nat._vp
+        for key, ptr, nb in (("digests", d["digs"], 32 * n), ("roots", d["roots"], 32 * S), ("empty", d["empty"], S),
+                             ("verdict", d["verdict"], S), ("first_bad", d["fb"], 8 * S), ("root_match", d["match"], S)):
+            c._check(lib.ahv_memcpy_d2h(h, vp(o[key].ctypes.data), vp(ptr), nb), "ahv_memcpy_d2h")
+
+    def run(self, chunks: Iterable[tuple], copy: bool = True) -> Iterator[dict]:
+        """chunks: iterable of ``(cols, session_rowptr)`` or ``(cols, session_rowptr, committed_roots)`` as for
+        ``ReplayPipeline.run``; yields the same per-chunk dicts.  While the GPU works on chunk k the host stages
+        chunk k+1 and its upload runs on the second stream."""
+        it = iter(chunks)
+        try:
+            cur = self._stage_chunk(0, *next(it))
+        except StopIteration:
+            return
+        k = 0
+        while cur is not None:
+            self._enqueue(cur)
+            try:
+                nxt = self._stage_chunk(k + 1, *next(it))          # overlaps the kernels of chunk k
+            except StopIteration:
+                nxt = None
+            self.ctx.sync()                                        # chunk k's results are in its pinned output set
+            n, S, o = cur["n"], cur["S"], self._out[cur["b"]]
+            if n == 0:
+                res = dict(digests=np.zeros((0, 32), np.uint8), first_bad=np.full(S, -1, np.int64), verdict=np.ones(S, bool),
+                           roots=[None] * S, root_match=np.zeros(S, bool) if cur["has_exp"] else None)
+            else:
+                empty = o["empty"][:S].astype(bool)
+                roots = o["roots"][: 32 * S].reshape(S, 32)
+                res = dict(digests=o["digests"][: 32 * n].reshape(n, 32), first_bad=o["first_bad"][:S],
+                           verdict=o["verdict"][:S].astype(bool),
+                           roots=[None if empty[s] else roots[s].tobytes().hex() for s in range(S)],
+                           root_match=(o["root_match"][:S].astype(bool) & ~empty) if cur["has_exp"] else None)
+                if copy:
+                    res["digests"] = np.array(res["digests"]); res["first_bad"] = np.array(res["first_bad"])
+            yield res
+            cur = nxt
+            k += 1

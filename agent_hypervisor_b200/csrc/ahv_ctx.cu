@@ -91,6 +91,10 @@ int check_status(ahv_ctx *ctx)
                   "written as zeros; pass the true maximum (or 0 to let the library find it)");
         return AHV_E_INVALID;
     }
+    if (st & AHV_STATUS_PACK_OVERFLOW) {
+        set_error("ahv_pack_deltas_dev: the pre-images need more bytes than arena_capacity; nothing was written");
+        return AHV_E_TOOLARGE;
+    }
     return AHV_OK;
 }
 
@@ -282,6 +286,22 @@ int ahv_memcpy_h2d(ahv_ctx *ctx, void *dptr, const void *hptr, uint64_t bytes)
 {
     AHV_TRY(use_device(ctx));
     if (bytes) AHV_CUDA(cudaMemcpyAsync(dptr, hptr, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return AHV_OK;
+}
+
+int ahv_upload_async(ahv_ctx *ctx, void *dptr, const void *hptr, uint64_t bytes)
+{
+    AHV_TRY(use_device(ctx));
+    if (bytes) AHV_CUDA(cudaMemcpyAsync(dptr, hptr, bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    return AHV_OK;
+}
+
+int ahv_upload_fence(ahv_ctx *ctx)
+{
+    AHV_TRY(use_device(ctx));
+    cudaEvent_t ev = ctx->ev_pipe[AHV_PIPE_EVENTS - 1 - (ctx->upload_fences++ & 7u)];     // (ahv_audit_sessions uses the low slots)
+    AHV_CUDA(cudaEventRecord(ev, ctx->copy_stream));
+    AHV_CUDA(cudaStreamWaitEvent(ctx->stream, ev, 0));
     return AHV_OK;
 }
 

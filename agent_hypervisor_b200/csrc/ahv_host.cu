@@ -315,7 +315,7 @@ int ahv_audit_sessions(ahv_ctx *ctx, const uint8_t *arena, const uint64_t *offse
     if (nchunk < 2) nchunk = 2;
     if (nchunk > MAXC) nchunk = MAXC;
     const uint64_t per = (S + nchunk - 1) / nchunk;
-    static_assert(2 * MAXC <= AHV_PIPE_EVENTS, "the context's event pool must cover every chunk");
+    static_assert(2 * MAXC + 8 <= AHV_PIPE_EVENTS, "the context's event pool must cover every chunk");
     struct Drain {                        // on every exit path the three streams have drained before the buffers are reused
         ahv_ctx *ctx;
         ~Drain()

@@ -8,7 +8,8 @@
 #include "../../include/ahv.h"
 
 #define AHV_MAX_TIMERS 64
-#define AHV_PIPE_EVENTS 64
+#define AHV_PIPE_EVENTS 72       // 64 for the chunks of ahv_audit_sessions + 8 for ahv_upload_fence
+#define AHV_STATUS_PACK_OVERFLOW 2u // ahv_pack_deltas_dev: the pre-images need more bytes than the arena the caller gave
 #define AHV_STATUS_MAX_LEAVES 1u   // a _dev tree entry was given a max_session_leaves smaller than a session really has
 
 struct ahv_ctx {
@@ -29,6 +30,7 @@ struct ahv_ctx {
     uint64_t io_cap;
     uint64_t io_used;
     uint64_t launches;
+    uint32_t upload_fences;    // ahv_upload_fence calls so far (picks one of eight events)
     cudaEvent_t t_start[AHV_MAX_TIMERS], t_stop[AHV_MAX_TIMERS];
     // tuning options (ahv_set_option)
     int64_t opt_sort;          // 1: length-sort variable-length batches (default 1)

@@ -1,0 +1,144 @@
+// ahv_pack_dev.cu - the canonical packer on the device (widening of SURVEY.md 8f row 1): the same emitter as
+// the host packer (pack_core.cuh: byte-identical to json.dumps(..., sort_keys=True).encode() of
+// audit/delta.py:43-62), one thread per delta, so that a replay uploads COLUMNS (the fields, < 200 bytes per
+// delta) instead of pre-images (~330 bytes) and no host core serialises anything.
+//   pass 1  k_pack_sizes : every delta's length and the position of its parent_hash value
+//   scan    k_scan_u64   : lengths -> offsets (one CTA walks the array; ~1 ms per 10^7)
+//   pass 2  k_pack_write : the bytes, straight into the arena the hashing kernels read
+// HBM-bound in principle (columns in, pre-images out); in this first form the byte-wise stores of pass 2 are
+// issue-bound (every lane writes its own delta).
+#include "ahv_internal.cuh"
+#include "pack_core.cuh"
+
+using namespace ahv;
+using namespace ahv_pack;
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+k_pack_sizes(const Cols c, uint64_t *__restrict__ offsets, uint32_t *__restrict__ ppos)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c.n) return;
+    SinkT<false> s(nullptr);
+    const uint64_t pp = emit_delta(s, c, i);
+    offsets[i + 1] = s.n;
+    if (i == 0) offsets[0] = 0;
+    // a position past 4 GiB cannot be stored: UINT32_MAX - 1 is never a valid one, so it reads as "other"
+    if (ppos) ppos[i] = pp == 0xffffffffull ? 0xffffffffu : (uint32_t)(pp < 0xfffffffeull ? pp : 0xfffffffeull);
+}
+
+// in place: a[1..n] (lengths) -> inclusive prefix sums, a[0] stays 0; one CTA
+__global__ void __launch_bounds__(1024)
+k_scan_u64(uint64_t *__restrict__ a, uint64_t n)
+{
+    __shared__ uint64_t warp_sum[32];
+    __shared__ uint64_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    constexpr int PER = 4;                                   // consecutive elements per thread
+    for (uint64_t base = 1; base <= n; base += (uint64_t)blockDim.x * PER) {
+        const uint64_t i0 = base + (uint64_t)threadIdx.x * PER;
+        uint64_t v[PER], t = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            v[k] = (i0 + k <= n) ? a[i0 + k] : 0;
+            t += v[k];
+        }
+        uint64_t x = t;                                      // inclusive scan of the threads' totals
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= (uint32_t)o) x += y;
+        }
+        if (lane == 31) warp_sum[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            uint64_t ws = warp_sum[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint64_t y = __shfl_up_sync(0xffffffffu, ws, o);
+                if (lane >= (uint32_t)o) ws += y;
+            }
+            warp_sum[lane] = ws;
+        }
+        __syncthreads();
+        uint64_t run = carry + (wid ? warp_sum[wid - 1] : 0) + (x - t);
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            run += v[k];
+            if (i0 + k <= n) a[i0 + k] = run;
+        }
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = run;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_pack_write(const Cols c, const uint64_t *__restrict__ offsets, uint8_t *__restrict__ arena, uint64_t capacity,
+             uint32_t *__restrict__ status)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c.n) return;
+    if (offsets[c.n] > capacity) {                           // nothing is written past the caller's arena
+        if (i == 0) atomicOr(status, AHV_STATUS_PACK_OVERFLOW);
+        return;
+    }
+    SinkT<true> s(arena + offsets[i]);
+    emit_delta(s, c, i);
+}
+
+}  // namespace
+
+extern "C" int ahv_pack_deltas_dev(ahv_ctx *ctx, const ahv_delta_columns *cols, uint64_t *d_out_offsets,
+                                   uint8_t *d_out_arena, uint64_t arena_capacity, uint64_t *out_bytes,
+                                   uint32_t *d_out_parent_pos, uint32_t flags)
+{
+    AHV_TRY(use_device(ctx));
+    AHV_REQUIRE(cols && d_out_offsets, "cols / out_offsets is null");
+    Cols c;
+    c.n = cols->n;
+    c.delta_id = {cols->delta_id_blob, cols->delta_id_off, nullptr};
+    c.session_id = {cols->session_id_blob, cols->session_id_off, nullptr};
+    c.agent_did = {cols->agent_did_blob, cols->agent_did_off, nullptr};
+    c.turn_id = cols->turn_id;
+    c.ts_us = cols->timestamp_us;
+    c.ts_off = cols->timestamp_utcoffset_s;
+    c.parent_kind = cols->parent_kind;
+    c.parent_digest = cols->parent_digest;
+    c.parent_other = {cols->parent_other_blob, cols->parent_other_off, nullptr};
+    c.change_rowptr = cols->change_rowptr;
+    c.ch_path = {cols->change_path_blob, cols->change_path_off, nullptr};
+    c.ch_op = {cols->change_op_blob, cols->change_op_off, nullptr};
+    c.ch_content = {cols->change_content_blob, cols->change_content_off, cols->change_content_null};
+    c.ch_prev = {cols->change_prev_blob, cols->change_prev_off, cols->change_prev_null};
+    const uint64_t n = c.n;
+    AHV_REQUIRE(n < 0xffffffffull, "too many deltas (limit 2^32-2 per call)");
+    if (n == 0) {
+        AHV_CUDA(cudaMemsetAsync(d_out_offsets, 0, 8, ctx->stream));
+        if (out_bytes) *out_bytes = 0;
+        return AHV_OK;
+    }
+    AHV_REQUIRE(c.turn_id && c.ts_us && c.ts_off && c.parent_kind && c.change_rowptr && c.delta_id.off && c.session_id.off &&
+                c.agent_did.off, "a required column is null");
+    if (!((flags & AHV_PACK_OFFSETS_VALID) && d_out_arena)) {
+        k_pack_sizes<<<grid_for(n, 256), 256, 0, ctx->stream>>>(c, d_out_offsets, d_out_parent_pos);
+        AHV_CHECK_LAUNCH(ctx);
+        k_scan_u64<<<1, 1024, 0, ctx->stream>>>(d_out_offsets, n);
+        AHV_CHECK_LAUNCH(ctx);
+    }
+    if (d_out_arena) {
+        k_pack_write<<<grid_for(n, 256), 256, 0, ctx->stream>>>(c, d_out_offsets, d_out_arena, arena_capacity, ctx->status_d);
+        AHV_CHECK_LAUNCH(ctx);
+    }
+    if (out_bytes) {                                         // the caller wants the size on the host: one synchronisation
+        AHV_CUDA(cudaMemcpyAsync(out_bytes, d_out_offsets + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        AHV_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (d_out_arena && *out_bytes > arena_capacity) {
+            __atomic_and_fetch(ctx->status_h, ~AHV_STATUS_PACK_OVERFLOW, __ATOMIC_ACQ_REL);
+            set_error("arena capacity %llu < %llu bytes needed", (unsigned long long)arena_capacity, (unsigned long long)*out_bytes);
+            return AHV_E_TOOLARGE;
+        }
+    }
+    return AHV_OK;
+}

@@ -93,6 +93,11 @@ int ahv_host_free(ahv_ctx *ctx, void *hptr);
 int ahv_memcpy_h2d(ahv_ctx *ctx, void *dptr, const void *hptr, uint64_t bytes); /* async on ctx stream */
 int ahv_memcpy_d2h(ahv_ctx *ctx, void *hptr, const void *dptr, uint64_t bytes); /* async on ctx stream */
 int ahv_memset_dev(ahv_ctx *ctx, void *dptr, int value, uint64_t bytes);
+/* Upload on the context's SECOND stream, so that it overlaps the kernels already enqueued on the main one
+ * (double-buffered pipelines); ahv_upload_fence makes everything enqueued on the main stream afterwards wait for
+ * the uploads issued so far.  The caller keeps source and destination untouched until then. */
+int ahv_upload_async(ahv_ctx *ctx, void *dptr, const void *hptr, uint64_t bytes);
+int ahv_upload_fence(ahv_ctx *ctx);
 
 /* CUDA-event timers on the ctx stream (slot 0..63): start/stop bracket work, elapsed in ms */
 int ahv_timer_start(ahv_ctx *ctx, int slot);
@@ -269,6 +274,18 @@ typedef struct ahv_delta_columns {
 int ahv_pack_deltas(const ahv_delta_columns *cols, uint64_t *out_offsets /* n+1 */, uint8_t *out_arena,
                     uint64_t arena_capacity, uint64_t *out_bytes, uint32_t *out_parent_pos /* n, or NULL */,
                     uint32_t flags);
+
+/*
+ * ahv_pack_deltas_dev: the same packer on the device (same emitter source, byte-identical output), one thread per
+ * delta: a replay can upload the COLUMNS (the struct stays on the host, every pointer in it is a device pointer)
+ * and never serialise on the host.  Asynchronous on the ctx stream: sizes -> offsets (d_out_offsets[n+1]) -> bytes
+ * into d_out_arena (skip the write with d_out_arena = NULL).  If the pre-images would not fit arena_capacity
+ * nothing is written and the next ahv_sync returns AHV_E_TOOLARGE; with out_bytes (a HOST pointer) the call
+ * synchronises once, returns the byte count there and reports the overflow itself.
+ */
+int ahv_pack_deltas_dev(ahv_ctx *ctx, const ahv_delta_columns *cols, uint64_t *d_out_offsets /* n+1 */,
+                        uint8_t *d_out_arena, uint64_t arena_capacity, uint64_t *out_bytes /* host, or NULL */,
+                        uint32_t *d_out_parent_pos /* n, or NULL */, uint32_t flags);
 
 /* ------------------------------------------------------------------ multi-GPU (one process per GPU)
  *

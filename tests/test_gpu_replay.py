@@ -79,3 +79,85 @@ def test_pipeline_matches_per_chunk_results():
             list(pipe.run([(big[0], big[1])]))
     with ReplayPipeline(64, 1, 1) as empty:
         assert list(empty.run([])) == []
+
+
+def test_device_packer_is_byte_identical_to_the_host_packer(audit_golden):
+    """ahv_pack_deltas_dev (one thread per delta, same emitter source) against ahv_pack_deltas and against the real
+    reference's json.dumps on the golden random sessions (escapes, surrogate pairs, None fields, odd timestamps)."""
+    from agent_hypervisor_b200 import get_context
+    from agent_hypervisor_b200.audit.packing import (canonical_preimage, column_bytes, columns_from_deltas,
+                                                     device_columns_struct, pack_columns, stage_columns)
+    from agent_hypervisor_b200 import SemanticDelta, VFSChange
+    ctx = get_context()
+    rs = audit_golden["random_sessions"]
+    deltas = []
+    for r in rs[:400]:
+        parent = None
+        for f in recipes.random_session(r["seed"]):
+            d = SemanticDelta(delta_id=f["delta_id"], turn_id=f["turn_id"], session_id=f["session_id"], agent_did=f["agent_did"],
+                              timestamp=f["timestamp"], changes=[VFSChange(**c) for c in f["changes"]], parent_hash=parent)
+            parent = hashlib.sha256(canonical_preimage(d)).hexdigest()
+            deltas.append(d)
+    # a few parents that are not digests, and a None in the middle
+    deltas[5].parent_hash = "not-a-digest é\U0001f600"; deltas[9].parent_hash = None; deltas[11].parent_hash = "A" * 64
+    cols = columns_from_deltas(deltas)
+    n = cols["n"]
+    want_arena, want_offs, want_pos = pack_columns(cols, want_parent_pos=True)
+    assert bytes(want_arena) == b"".join(canonical_preimage(d) for d in deltas)
+    stage = ctx.host_alloc(column_bytes(cols))
+    layout, used = stage_columns(cols, stage)
+    d_cols, d_offs, d_pos = ctx.dev_alloc(used), ctx.dev_alloc(8 * (n + 1)), ctx.dev_alloc(4 * n)
+    d_arena = ctx.dev_alloc(len(want_arena) + 64)
+    try:
+        ctx.h2d(d_cols, stage[:used])
+        st = device_columns_struct(n, layout, d_cols)
+        nbytes = ctx.pack_deltas_dev(st, d_offs, 0, 0, d_pos, want_bytes=True)                  # size query
+        assert nbytes == len(want_arena)
+        ctx.pack_deltas_dev(st, d_offs, d_arena, len(want_arena), d_pos)
+        got_arena, got_offs, got_pos = np.empty(len(want_arena), np.uint8), np.empty(n + 1, np.uint64), np.empty(n, np.uint32)
+        ctx.d2h(got_arena, d_arena); ctx.d2h(got_offs, d_offs); ctx.d2h(got_pos, d_pos); ctx.sync()
+        assert np.array_equal(got_offs, want_offs) and np.array_equal(got_pos, want_pos)
+        assert np.array_equal(got_arena, want_arena)
+        # an arena that is too small: nothing written, reported by the next sync
+        from agent_hypervisor_b200 import NativeError
+        ctx.memset(d_arena, 0x5A, len(want_arena))
+        ctx.pack_deltas_dev(st, d_offs, d_arena, len(want_arena) - 1, d_pos)
+        with pytest.raises(NativeError, match="arena_capacity"):
+            ctx.sync()
+        ctx.d2h(got_arena, d_arena); ctx.sync()
+        assert (got_arena == 0x5A).all()
+    finally:
+        ctx.host_free(stage)
+        for p in (d_cols, d_offs, d_pos, d_arena):
+            ctx.dev_free(p)
+
+
+def test_device_replay_matches_the_host_packer_pipeline():
+    from agent_hypervisor_b200 import DeviceReplay, ReplayPipeline
+    from agent_hypervisor_b200.audit.packing import canonical_preimage, column_bytes
+    chunks = [_chunk(range(10 * k, 10 * k + 10), tamper=(3, 1) if k == 2 else None) for k in range(5)]
+    chunks.append(_chunk([7]))
+    n_max = max(int(c[0]["n"]) for c in chunks)
+    bytes_max = max(sum(len(canonical_preimage(d)) for d in c[2]) for c in chunks)
+    col_max = max(column_bytes(c[0]) for c in chunks)
+
+    def with_roots(k, c):
+        stored = np.stack([np.frombuffer(bytes.fromhex(r or "00" * 32), np.uint8) for r in c[3]]).copy()
+        if k == 1:
+            stored[4, 0] ^= 1
+        return c[0], c[1], stored
+    with ReplayPipeline(bytes_max + 64, n_max, 10) as host, DeviceReplay(bytes_max + 64, n_max, 10, col_max) as dev:
+        for feed in (lambda: ((c[0], c[1]) for c in chunks), lambda: (with_roots(k, c) for k, c in enumerate(chunks))):
+            want = list(host.run(feed()))
+            got = list(dev.run(feed()))
+            assert len(got) == len(want) == len(chunks)
+            for w, g, c in zip(want, got, chunks):
+                assert np.array_equal(g["digests"], w["digests"]) and g["roots"] == w["roots"] == c[3]
+                assert list(g["verdict"]) == list(w["verdict"]) == c[4] and np.array_equal(g["first_bad"], w["first_bad"])
+                assert (g["root_match"] is None) == (w["root_match"] is None)
+                if g["root_match"] is not None:
+                    assert list(g["root_match"]) == list(w["root_match"])
+        assert list(dev.run([])) == []
+        big = _chunk(range(100, 112))
+        with pytest.raises(ValueError):
+            list(dev.run([(big[0], big[1])]))
