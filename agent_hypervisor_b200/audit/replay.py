@@ -116,6 +116,36 @@ class ReplayPipeline:
             k += 1
 
 
+class StagedColumns:
+    """One chunk of columns already laid out in pinned host memory (``packing.stage_columns``), ready to be
+    uploaded as it is: what an archive reader that fills pinned buffers directly would hand to ``DeviceReplay``.
+    Made by ``DeviceReplay.prestage``; freed with ``close``."""
+
+    def __init__(self, ctx: nat.Context, cols: dict, session_rowptr, committed_roots=None) -> None:
+        from .packing import column_bytes, stage_columns
+        self.ctx = ctx
+        self.n = int(cols["n"])
+        rp = np.asarray(session_rowptr, dtype=np.uint64)
+        self.S = len(rp) - 1
+        if int(rp[-1]) != self.n:
+            raise ValueError("session_rowptr does not end at n")
+        self.buf = ctx.host_alloc(column_bytes(cols))
+        self.layout, self.used = stage_columns(cols, self.buf)
+        self.rp = ctx.host_alloc(8 * (self.S + 1), np.uint64)
+        self.rp[:] = rp
+        self.maxl = max(int(np.diff(rp.astype(np.int64)).max()) if self.S else 0, 1)
+        self.roots = None
+        if committed_roots is not None:
+            self.roots = ctx.host_alloc(32 * max(self.S, 1))
+            self.roots[: 32 * self.S] = np.ascontiguousarray(committed_roots, dtype=np.uint8).reshape(-1)
+
+    def close(self) -> None:
+        for a in (self.buf, self.rp, self.roots):
+            if a is not None:
+                self.ctx.host_free(a)
+        self.buf = self.rp = self.roots = None
+
+
 class DeviceReplay:
     """Replay with the canonical packer ON THE DEVICE (``ahv_pack_deltas_dev``): a chunk's COLUMNS are staged in one
     pinned buffer, uploaded in one copy on the context's second stream (overlapping the previous chunk's kernels),
@@ -160,10 +190,24 @@ class DeviceReplay:
     def __exit__(self, *exc):
         self.close()
 
-    def _stage_chunk(self, k: int, cols: dict, session_rowptr, committed_roots=None):
-        """Host side of chunk k: columns into the pinned staging buffer, upload started on the second stream."""
+    def prestage(self, cols: dict, session_rowptr, committed_roots=None) -> StagedColumns:
+        return StagedColumns(self.ctx, cols, session_rowptr, committed_roots)
+
+    def _stage_chunk(self, k: int, cols, session_rowptr=None, committed_roots=None):
+        """Host side of chunk k: columns into the pinned staging buffer (unless they already are in one), upload
+        started on the second stream."""
         from .packing import device_columns_struct, stage_columns
         c, b = self.ctx, k % 2
+        if isinstance(cols, StagedColumns):
+            sc = cols
+            if sc.n > self.limits[1] or sc.S > self.limits[2] or sc.used > self.limits[3]:
+                raise ValueError(f"chunk {k} exceeds the pipeline's buffers")
+            c.upload_async(self._d_cols[b], sc.buf, sc.used)
+            c.upload_async(self._d_rp[b], sc.rp, 8 * (sc.S + 1))
+            if sc.roots is not None:
+                c.upload_async(self._d_exp[b], sc.roots, 32 * sc.S)
+            return dict(n=sc.n, S=sc.S, b=b, st=device_columns_struct(sc.n, sc.layout, self._d_cols[b]),
+                        has_exp=sc.roots is not None, maxl=sc.maxl)
         n = int(cols["n"])
         rp = np.asarray(session_rowptr, dtype=np.uint64)
         S = len(rp) - 1
@@ -200,10 +244,11 @@ class DeviceReplay:
             c._check(lib.ahv_memcpy_d2h(h, vp(o[key].ctypes.data), vp(ptr), nb), "ahv_memcpy_d2h")
 
     def run(self, chunks: Iterable[tuple], copy: bool = True) -> Iterator[dict]:
-        """chunks: iterable of ``(cols, session_rowptr)`` or ``(cols, session_rowptr, committed_roots)`` as for
-        ``ReplayPipeline.run``; yields the same per-chunk dicts.  While the GPU works on chunk k the host stages
-        chunk k+1 and its upload runs on the second stream."""
-        it = iter(chunks)
+        """chunks: iterable of ``(cols, session_rowptr)`` / ``(cols, session_rowptr, committed_roots)`` as for
+        ``ReplayPipeline.run``, or of ``StagedColumns`` (columns already in pinned memory: no host copy at all);
+        yields the same per-chunk dicts.  While the GPU works on chunk k the host stages chunk k+1 and its upload
+        runs on the second stream."""
+        it = (ch if isinstance(ch, tuple) else (ch,) for ch in chunks)
         try:
             cur = self._stage_chunk(0, *next(it))
         except StopIteration:

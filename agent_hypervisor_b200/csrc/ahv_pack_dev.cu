@@ -4,9 +4,10 @@
 // delta) instead of pre-images (~330 bytes) and no host core serialises anything.
 //   pass 1  k_pack_sizes : every delta's length and the position of its parent_hash value
 //   scan    k_scan_u64   : lengths -> offsets (one CTA walks the array; ~1 ms per 10^7)
-//   pass 2  k_pack_write : the bytes, straight into the arena the hashing kernels read
-// HBM-bound in principle (columns in, pre-images out); in this first form the byte-wise stores of pass 2 are
-// issue-bound (every lane writes its own delta).
+//   pass 2  k_pack_write : the bytes, into the arena the hashing kernels read (staged per warp in shared memory,
+//                          written out with 16-byte stores)
+// HBM-bound in principle (columns in, pre-images out); in practice bound by the serial, divergent emission of
+// each lane's delta (a few instructions per output byte).
 #include "ahv_internal.cuh"
 #include "pack_core.cuh"
 
@@ -74,18 +75,54 @@ k_scan_u64(uint64_t *__restrict__ a, uint64_t n)
     }
 }
 
-__global__ void __launch_bounds__(256)
+// Pass 2.  The 32 deltas of a warp are neighbours in the arena, so the warp's output is ONE contiguous byte range:
+// every lane serialises its delta into the warp's shared-memory slot (byte stores are cheap there), then the
+// warp copies the range out with 16-byte stores (the slot is offset by the range's misalignment, so 16-byte
+// pieces of shared memory line up with 16-byte pieces of the arena).  A warp whose 32 pre-images exceed the slot
+// (very long strings) writes straight to global memory instead.
+constexpr uint32_t PACK_WARP_SLOT = 12288;      // bytes of shared memory per warp (+16 for the alignment shift)
+constexpr uint32_t PACK_THREADS = 128;
+
+__global__ void __launch_bounds__(PACK_THREADS)
 k_pack_write(const Cols c, const uint64_t *__restrict__ offsets, uint8_t *__restrict__ arena, uint64_t capacity,
              uint32_t *__restrict__ status)
 {
+    extern __shared__ __align__(16) uint8_t pack_smem[];
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= c.n) return;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint64_t i0 = i - lane;
+    if (i0 >= c.n) return;                                   // whole warp out of range
     if (offsets[c.n] > capacity) {                           // nothing is written past the caller's arena
         if (i == 0) atomicOr(status, AHV_STATUS_PACK_OVERFLOW);
         return;
     }
-    SinkT<true> s(arena + offsets[i]);
-    emit_delta(s, c, i);
+    const uint64_t i1 = (i0 + 32 < c.n) ? i0 + 32 : c.n;
+    const uint64_t base = offsets[i0], end = offsets[i1];
+    const uint32_t shift = (uint32_t)((reinterpret_cast<uintptr_t>(arena) + base) & 15u);
+    uint8_t *slot = pack_smem + (size_t)wid * (PACK_WARP_SLOT + 16);
+    if (end - base > PACK_WARP_SLOT) {                       // too long for the slot: direct
+        if (i < c.n) {
+            SinkT<true> s(arena + offsets[i]);
+            emit_delta(s, c, i);
+        }
+        return;
+    }
+    if (i < c.n) {
+        SinkT<true> s(slot + shift + (offsets[i] - base));
+        emit_delta(s, c, i);
+    }
+    __syncwarp();
+    const uint32_t total = (uint32_t)(end - base);
+    uint8_t *g = arena + base - shift;                       // 16-byte aligned; slot[k] <-> g[k]
+    const uint32_t span = shift + total;                     // bytes [shift, span) of the slot are data
+    for (uint32_t k = lane * 16u; k < span; k += 32u * 16u) {
+        if (k >= shift && k + 16u <= span) {
+            *reinterpret_cast<uint4 *>(g + k) = *reinterpret_cast<const uint4 *>(slot + k);
+        } else {                                             // first / last piece: only the bytes that are ours
+            const uint32_t lo = k < shift ? shift : k, hi = (k + 16u < span) ? k + 16u : span;
+            for (uint32_t q = lo; q < hi; ++q) g[q] = slot[q];
+        }
+    }
 }
 
 }  // namespace
@@ -128,7 +165,14 @@ extern "C" int ahv_pack_deltas_dev(ahv_ctx *ctx, const ahv_delta_columns *cols, 
         AHV_CHECK_LAUNCH(ctx);
     }
     if (d_out_arena) {
-        k_pack_write<<<grid_for(n, 256), 256, 0, ctx->stream>>>(c, d_out_offsets, d_out_arena, arena_capacity, ctx->status_d);
+        const size_t smem = (size_t)(PACK_THREADS / 32) * (PACK_WARP_SLOT + 16);
+        static bool attr_set = false;
+        if (!attr_set) {
+            AHV_CUDA(cudaFuncSetAttribute(k_pack_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set = true;
+        }
+        k_pack_write<<<grid_for(n, PACK_THREADS), PACK_THREADS, smem, ctx->stream>>>(c, d_out_offsets, d_out_arena, arena_capacity,
+                                                                                      ctx->status_d);
         AHV_CHECK_LAUNCH(ctx);
     }
     if (out_bytes) {                                         // the caller wants the size on the host: one synchronisation
