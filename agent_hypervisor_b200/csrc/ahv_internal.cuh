@@ -41,6 +41,7 @@ struct ahv_ctx {
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_sigma_exact;   // 1: every row summed in the reference's order (bit-identical); 0 (default): rows longer than opt_sigma_long_cut take the fixed-shape parallel sum
     int64_t opt_sigma_long_cut;// row length (edges) above which the parallel sum is used (default 512)
+    int64_t opt_sigma_heavy;   // tiles with more edges than this go through the shared queue (default 3072)
     int64_t opt_sigma_share;   // 1 (default): heavy tiles of the tiled sigma_eff kernel go through a queue shared by the CTAs
     int64_t opt_sigma_chunk;   // edges per shared-memory chunk of the tiled sigma_eff kernel: 2048 (default) or 1024
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions

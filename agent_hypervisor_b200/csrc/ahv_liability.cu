@@ -125,9 +125,9 @@ struct SigWork {
     uint32_t *claimed;         // per tile: number of the launch that claimed it last
     uint32_t cap;
     uint32_t epoch;            // this launch's number (never 0); its queue is epoch & 1
+    uint32_t heavy;            // a tile with more edges than this goes through the queue
 };
 constexpr uint32_t SIG_NONE = 0xffffffffu;
-constexpr uint32_t SIG_HEAVY_EDGES = 4096;      // a tile with more edges than this goes through the queue
 constexpr uint32_t SIG_SCAN_CTAS = 512;         // CTAs that share the look-through (all resident in the first wave)
 constexpr uint32_t SIG_QUEUE_CAP = 4096;
 constexpr uint32_t SIG_AHEAD = 1024;            // look-ahead distance of the L2 prefetches, in tiles (about one wave of CTAs)
@@ -188,7 +188,7 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
         uint32_t q_tail = 0;
         if (wk.queue && tid == 0) q_tail = *reinterpret_cast<volatile uint32_t *>(&q_cnt[0]);
         bool take = true;
-        if (wk.queue && e_end - e_begin > SIG_HEAVY_EDGES) {          // heavy: first come, first served
+        if (wk.queue && e_end - e_begin > wk.heavy) {          // heavy: first come, first served
             if (tid == 0) s_word = atomicExch(&wk.claimed[tile], wk.epoch);
             __syncthreads();
             take = (s_word != wk.epoch);
@@ -215,7 +215,7 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
             if (wk.queue && first && blockIdx.x < SIG_SCAN_CTAS) {
                 for (uint32_t t = blockIdx.x + tid * SIG_SCAN_CTAS; t < ntiles; t += SIG_ROWS * SIG_SCAN_CTAS) {
                     const uint64_t r0 = (uint64_t)t * SIG_ROWS, r1 = (r0 + SIG_ROWS < A) ? r0 + SIG_ROWS : A;
-                    if (__ldg(rowptr + r1) - __ldg(rowptr + r0) > SIG_HEAVY_EDGES) {
+                    if (__ldg(rowptr + r1) - __ldg(rowptr + r0) > wk.heavy) {
                         const uint32_t slot = atomicAdd(&q_cnt[0], 1u);
                         if (slot < wk.cap) q_ent[slot] = t;
                     }
@@ -647,6 +647,7 @@ int sigma_work(ahv_ctx *ctx, uint64_t ntiles, SigWork *out)
     out->claimed = reinterpret_cast<uint32_t *>(ctx->sigma_work + off_claimed);
     out->cap = SIG_QUEUE_CAP;
     out->epoch = ctx->sigma_epoch;
+    out->heavy = (uint32_t)ctx->opt_sigma_heavy;
     return AHV_OK;
 }
 
@@ -670,7 +671,7 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
     // reference's order
     const bool aligned = ((reinterpret_cast<uintptr_t>(d_bonded) | reinterpret_cast<uintptr_t>(d_expiry) |
                            reinterpret_cast<uintptr_t>(d_active)) & 15u) == 0;
-    SigWork wk = {nullptr, nullptr, nullptr, 0, 0};
+    SigWork wk = {nullptr, nullptr, nullptr, 0, 0, 0};
     if (ctx->opt_sigma_variant == 1 && aligned && ctx->opt_sigma_share) AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
     if (ctx->opt_sigma_variant == 2 && aligned) {
         AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
@@ -731,11 +732,11 @@ int ahv_exposure_sums_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *
     if (compensated)
         k_sigma_eff_tiled<2, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
-                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0});
+                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0, 0});
     else
         k_sigma_eff_tiled<1, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
-                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0});
+                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0, 0});
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

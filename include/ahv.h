@@ -459,6 +459,7 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *                   warp in a fixed shape that depends on the row alone (a few ulp from the reference, same result every run)
  *   "sigma_long_cut" 4..  that row length (default 32)
  *   "sigma_share" 0/1   CTAs of that kernel take over tiles with many more edges than a chunk from a shared queue (default 1)
+ *   "sigma_heavy" 256..  a tile of that kernel with more edges than this is handed out through the shared queue (default 3072)
  *   "sigma_chunk" 1024/1536/2048  records per shared-memory chunk of that kernel (default 1536)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);
