@@ -127,6 +127,43 @@ def test_config3_shape_vs_oracle(ctx):
     assert lens.min() >= 64 and lens.max() <= 16384 and 2000 < lens.mean() < 4000
 
 
+def test_config3_one_million_messages_vs_oracle(ctx):
+    """BASELINE configs[2] shape at 10^6 messages (2.9 GB, log-uniform 64 B..16 KB, tightly packed so every byte
+    alignment occurs), everything against the C oracle: digests with the length-sorted and the unsorted launch
+    order, 10^3 trees x 10^3 leaves and ONE 10^6-leaf tree, verify with two broken links."""
+    n = 1_000_000
+    arena, offs = workloads.config3_arena(n, seed=0xA6E27)
+    want = co.sha256_batch(arena, offs)
+    d_a, d_o, d_d = ctx.dev_alloc(arena.nbytes + 64), ctx.dev_alloc(offs.nbytes), ctx.dev_alloc(32 * n)
+    try:
+        ctx.h2d(d_a, arena); ctx.h2d(d_o, offs)
+        got = np.empty((n, 32), np.uint8)
+        for sort in (1, 0):
+            ctx.set_option("sort", sort)
+            ctx.memset(d_d, 0, 32 * n)
+            ctx.sha256_batch_dev(d_a, arena.nbytes, d_o, n, 0, d_d)
+            ctx.d2h(got, d_d); ctx.sync()
+            assert np.array_equal(got, want), f"sort={sort}"
+    finally:
+        ctx.set_option("sort", 1)
+        for p in (d_a, d_o, d_d):
+            ctx.dev_free(p)
+    rp = np.arange(1001, dtype=np.uint64) * np.uint64(1000)
+    r1, _ = ctx.merkle_roots(want, rp)
+    w1, _ = co.merkle_roots(want, rp)
+    assert np.array_equal(r1, w1)
+    r2, _ = ctx.merkle_roots(want, np.array([0, n], np.uint64))
+    w2, _ = co.merkle_roots(want, np.array([0, n], np.uint64))
+    assert np.array_equal(r2, w2)
+    par = np.zeros((n, 32), np.uint8); par[1:] = want[:-1]
+    kind = np.ones(n, np.uint8); kind[::1000] = 0
+    par[654_321, 7] ^= 0x40; kind[999_999] = 2                       # session 654 at 321; the very last delta's parent "other"
+    res = ctx.verify_chains(arena, offs, par, kind, rp, expected_roots=w1)
+    v, fb, _ = co.verify_chains(arena, offs, par, kind, rp)
+    assert np.array_equal(res["verdict"], v) and np.array_equal(res["first_bad"], fb) and res["root_match"].all()
+    assert list(np.nonzero(v == 0)[0]) == [654, 999] and fb[654] == 321 and fb[999] == 999
+
+
 def test_sha256_empty_batch(ctx):
     assert ctx.sha256_batch(np.zeros(0, np.uint8), np.zeros(1, np.uint64)).shape == (0, 32)
 
@@ -763,10 +800,12 @@ def test_sharded_single_tree_matches_whole_tree(ctx):
 
 
 # ------------------------------------------------------------------ full size (BASELINE config 2), properties
-def test_config2_full_size_properties(ctx):
-    """10k sessions x 1k x 256 B on the device: chain -> commit -> verify, checked through
-    size-independent properties plus a sample of sessions against the oracle."""
-    S, L, FL = 10_000, 1000, 256
+@pytest.mark.parametrize("S", [10_000, 12_500])
+def test_config2_full_size_properties(ctx, S):
+    """BASELINE configs[1] (10k sessions x 1k x 256 B) and the per-GPU share of configs[4] (12 500 sessions of the 10^8
+    deltas over 8 GPUs) on the device: chain -> commit -> verify, checked through size-independent properties plus
+    a sample of sessions against the oracle."""
+    L, FL = 1000, 256
     n = S * L
     arena = np.empty(n * FL, np.uint8)
     offs, hexpos, rp = workloads.config2_fill(arena, 0, S, L)
