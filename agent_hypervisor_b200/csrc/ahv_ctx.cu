@@ -169,8 +169,8 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_compress = 1;
     c->opt_sigma_variant = 1;
     c->opt_sigma_exact = 0;
-    c->opt_sigma_long_cut = 32;
-    c->opt_sigma_chunk = 1536;
+    c->opt_sigma_long_cut = 64;
+    c->opt_sigma_chunk = 1440;
     c->opt_sigma_share = 1;
     c->opt_sigma_heavy = 3072;
     c->opt_slash_variant = 0;
@@ -375,7 +375,7 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
         AHV_REQUIRE(value >= 256 && value <= 0x7fffffff, "sigma_heavy must be 256..2^31-1");
         ctx->opt_sigma_heavy = value;
     } else if (!strcmp(key, "sigma_chunk")) {
-        AHV_REQUIRE(value == 1024 || value == 1536 || value == 2048, "sigma_chunk must be 1024, 1536 or 2048");
+        AHV_REQUIRE(value == 1024 || value == 1296 || value == 1440 || value == 1536 || value == 2048, "sigma_chunk must be 1024, 1296, 1440, 1536 or 2048");
         ctx->opt_sigma_chunk = value;
     } else if (!strcmp(key, "compress")) {
         AHV_REQUIRE(value == 0 || value == 1, "compress must be 0 or 1");

@@ -36,10 +36,10 @@ k_sigma_eff_rings(const uint32_t *__restrict__ rowptr, const double *__restrict_
 }
 
 // Tiled form (default): a CTA of 128 threads owns 128 consecutive agent rows.  Their edges are one
-// contiguous CSR range; it arrives in shared memory in chunks of up to 2048 edges by THREE bulk
+// contiguous CSR range; it arrives in shared memory in chunks of up to 1440 edges by THREE bulk
 // asynchronous copies per chunk (cp.async.bulk, the 1-D TMA path: one thread issues them, the bytes land
 // without passing through registers and complete on an mbarrier), so the copy costs next to no issue
-// slots and six CTAs fit an SM, their copy and sum phases overlapping.  Most tiles fit one chunk: one
+// slots and eight CTAs fit an SM, their copy and sum phases overlapping.  Most tiles fit one chunk: one
 // wait, then every thread adds up its own row in CSR order.  The order of additions per row is exactly
 // the reference's (vouching.py:146-148), so results are bit-identical.  A record that is not live is
 // skipped, which equals adding +0.0: the running sum starts at +0.0 and can never become -0.0.
@@ -135,7 +135,7 @@ constexpr uint32_t SIG_AHEAD = 1024;            // look-ahead distance of the L2
 // MODE 0: sigma_eff + rings.  MODE 1: plain live sum of each row.  MODE 2: compensated live sum.
 // PAR (MODE 0 only): rows of more than long_cut edges take the fixed-shape warp sum.
 template <int MODE, bool PAR, int SIG_CHUNK>
-__global__ void __launch_bounds__(SIG_ROWS, SIG_CHUNK == 2048 ? 6 : (SIG_CHUNK == 1536 ? 8 : 10))
+__global__ void __launch_bounds__(SIG_ROWS, SIG_CHUNK == 2048 ? 6 : (SIG_CHUNK >= 1440 ? 8 : (SIG_CHUNK == 1296 ? 9 : 10)))
 k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict__ bonded,
                   const uint8_t *__restrict__ active, const int64_t *__restrict__ expiry, int64_t now,
                   const double *__restrict__ sigma, const double *__restrict__ omega,
@@ -707,8 +707,16 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
         k_sigma_eff_tiled<0, true, 1024><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1024>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
             d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
-    else if (ctx->opt_sigma_chunk != 2048)
+    else if (ctx->opt_sigma_chunk == 1296)
+        k_sigma_eff_tiled<0, true, 1296><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1296>), ctx->stream>>>(
+            d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+    else if (ctx->opt_sigma_chunk == 1536)
         k_sigma_eff_tiled<0, true, 1536><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1536>), ctx->stream>>>(
+            d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+    else if (ctx->opt_sigma_chunk != 2048)
+        k_sigma_eff_tiled<0, true, 1440><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1440>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
             d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
     else

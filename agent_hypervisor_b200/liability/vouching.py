@@ -97,7 +97,7 @@ class VouchingEngine:
     DEFAULT_MAX_EXPOSURE = 0.80
 
     # The drop-in class returns the reference's own bits: every row is summed left to right
-    # (vouching.py:146-148).  Set False to let rows of more than 32 records take the faster fixed-shape
+    # (vouching.py:146-148).  Set False to let rows of more than 64 records take the faster fixed-shape
     # warp sum of ahv_sigma_eff_rings (a few ulp away, inside the 1e-6 tolerance; same value every run).
     exact_order = True
 

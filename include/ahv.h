@@ -325,7 +325,7 @@ int ahv_gather_results_dev(ahv_ctx *ctx, const uint8_t *d_roots /* S*32 */, cons
  *   (vouching.py:34-38; times in microseconds since the epoch).
  *   sum is sequential fp64 from 0.0; sigma_eff = sigma + (omega * sum), two roundings;
  *   result = (1.0 < x) ? 1.0 : x  (Python min(), NaN kept).
- *   Rows of more than 32 records (option "sigma_long_cut") are summed in a fixed parallel shape instead
+ *   Rows of more than 64 records (option "sigma_long_cut") are summed in a fixed parallel shape instead
  *   (by one warp: 32 strided partials, then a fixed butterfly: deterministic, within a few ulp of the
  *   sequential sum; the run contract allows 1e-6 relative); option "sigma_exact" = 1 keeps the sequential order for every row.
  *   out_near[a] = 1 when sigma_eff lies within 1e-6 (relative) of 0.60 or 0.95: the agents whose ring could
@@ -457,10 +457,10 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "sigma_exact" 0/1   sigma_eff: 1 = every row summed left to right like the reference (bit-identical, but one very long
  *                   row then bounds the pass); 0 (default) = rows longer than "sigma_long_cut" edges are summed by a
  *                   warp in a fixed shape that depends on the row alone (a few ulp from the reference, same result every run)
- *   "sigma_long_cut" 4..  that row length (default 32)
+ *   "sigma_long_cut" 4..  that row length (default 64)
  *   "sigma_share" 0/1   CTAs of that kernel take over tiles with many more edges than a chunk from a shared queue (default 1)
  *   "sigma_heavy" 256..  a tile of that kernel with more edges than this is handed out through the shared queue (default 3072)
- *   "sigma_chunk" 1024/1536/2048  records per shared-memory chunk of that kernel (default 1536)
+ *   "sigma_chunk"   records per shared-memory chunk of that kernel: 1024 / 1296 / 1440 / 1536 / 2048 (default 1440: eight CTAs per SM)
  *   "leaf_timer" 0|base record CUDA-event timers base..base+15 around every leaf-kernel launch */
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value);
 

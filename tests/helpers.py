@@ -164,7 +164,7 @@ def check_slash_against_golden(cases, golden_cases, b, out):
 
 
 # ---- sigma_eff: the fixed-shape sum the CUDA path uses for rows longer than "sigma_long_cut" -------------
-SIGMA_LONG_CUT = 32
+SIGMA_LONG_CUT = 64
 
 
 def fixed_shape_row_sum(vals: np.ndarray) -> float:

@@ -643,14 +643,14 @@ def test_sigma_eff_long_and_empty_rows(ctx):
             (rng.random(A) < 0.5).astype(np.uint8), rng.integers(1, 4, A).astype(np.uint8))
     want = co.sigma_eff_rings(*args)
     _check_sigma_default_path(ctx, args, want)
-    for cut, chunk in ((4, 2048), (100, 1024), (512, 1536), (4096, 1024)):      # other cuts / chunk sizes: same contract
+    for cut, chunk in ((4, 2048), (32, 1296), (100, 1024), (512, 1536), (4096, 1440)):      # other cuts / chunk sizes: same contract
         ctx.set_option("sigma_long_cut", cut)
         ctx.set_option("sigma_chunk", chunk)
         try:
             got = ctx.sigma_eff_rings(*args)
         finally:
             ctx.set_option("sigma_long_cut", SIGMA_LONG_CUT)
-            ctx.set_option("sigma_chunk", 1536)
+            ctx.set_option("sigma_chunk", 1440)
         exp = sigma_expected_default_path(want, *args, cut=cut)
         assert np.array_equal(got[0], exp[0]) and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:4]))
     ctx.set_option("sigma_exact", 1)

@@ -73,6 +73,11 @@ def run_config4():
                             ("cut32_noshare", dict(sigma_long_cut=32, sigma_share=0)),
                             ("cut32_chunk1024", dict(sigma_long_cut=32, sigma_chunk=1024)),
                             ("cut32_chunk2048", dict(sigma_long_cut=32, sigma_chunk=2048)),
+                            ("cut32_chunk1440", dict(sigma_long_cut=32, sigma_chunk=1440)),
+                            ("cut64_chunk1440", dict(sigma_long_cut=64, sigma_chunk=1440)),
+                            ("cut32_chunk1296", dict(sigma_long_cut=32, sigma_chunk=1296)),
+                            ("cut64_chunk1296", dict(sigma_long_cut=64, sigma_chunk=1296)),
+                            ("cut64_chunk1440_heavy2048", dict(sigma_long_cut=64, sigma_chunk=1440, sigma_heavy=2048)),
                             ("heavy2048", dict(sigma_heavy=2048)), ("heavy3072", dict(sigma_heavy=3072)),
                             ("heavy6144", dict(sigma_heavy=6144)), ("heavy8192", dict(sigma_heavy=8192)),
                             ("stream_cut32", dict(sigma_long_cut=32, sigma_variant=2)),
@@ -80,7 +85,7 @@ def run_config4():
             for k, v in opts.items():
                 ctx.set_option(k, v)
             best, med = time_pass(d, A, gr["now"])
-            ctx.set_option("sigma_exact", 0); ctx.set_option("sigma_long_cut", 32); ctx.set_option("sigma_variant", 1); ctx.set_option("sigma_chunk", 1536); ctx.set_option("sigma_share", 1); ctx.set_option("sigma_heavy", 3072)
+            ctx.set_option("sigma_exact", 0); ctx.set_option("sigma_long_cut", 64); ctx.set_option("sigma_variant", 1); ctx.set_option("sigma_chunk", 1440); ctx.set_option("sigma_share", 1); ctx.set_option("sigma_heavy", 3072)
             res[label] = {"best_us": best * 1e3, "median_us": med * 1e3, "GBps_best": nbytes / best / 1e6,
                           "GBps_median": nbytes / med / 1e6}
             print(f"config4 {name:8s} {label:22s} best {best*1e3:7.1f} us  median {med*1e3:7.1f} us  {nbytes/med/1e6:7.0f} GB/s", flush=True)
