@@ -693,6 +693,9 @@ def run_cuda(args):
                 "h2d_ceiling_gbs": world * arena_bytes * e2e_steps / copy_s / 1e9,
                 "h2d_ceiling_note": "the same pinned arena copied host -> device with nothing else running, all ranks at once",
                 "frac_of_h2d_ceiling": (h2d / e2e_s) / (arena_bytes / copy_s),
+                # on boxes whose host side is one shared resource for both directions (8 ranks: uploads and the digests coming
+                # back do not overlap for free) the bytes of BOTH directions are what the ceiling has to carry
+                "frac_of_ceiling_both_directions": ((h2d + d2h) / e2e_s) / (arena_bytes / copy_s),
                 "without_digests": {"value": world * n * e2e_steps / e2e_nodig_s, "d2h_bytes_per_step": d2h - 32 * n,
                                     "note": "out_digests = NULL: roots, verdicts, first-bad indices and root matches only"}},
         "comm": ctx.comm_info(), "host": host, "configs": configs,
