@@ -680,8 +680,9 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
         const uint32_t g = ntiles < resident ? ntiles : resident;
         const size_t smem = 2 * sizeof(SigStage<SIG_SCH>);
         const uint32_t tick_epoch = ++ctx->sigma_tick_epoch;       // streaming launches alternate between two tile counters
-        static bool attr_set[2] = {false, false};
+        static bool attr_seen[64][2] = {};                    // per device: function attributes belong to a device's context
         const int which = ctx->opt_sigma_exact ? 0 : 1;
+        bool *attr_set = attr_seen[ctx->device & 63];
         if (!attr_set[which]) {
             if (which) AHV_CUDA(cudaFuncSetAttribute(k_sigma_eff_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             else AHV_CUDA(cudaFuncSetAttribute(k_sigma_eff_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -166,10 +166,11 @@ extern "C" int ahv_pack_deltas_dev(ahv_ctx *ctx, const ahv_delta_columns *cols, 
     }
     if (d_out_arena) {
         const size_t smem = (size_t)(PACK_THREADS / 32) * (PACK_WARP_SLOT + 16);
-        static bool attr_set = false;
-        if (!attr_set) {
+        static bool attr_set[64] = {};                        // per device: function attributes belong to a device's context
+        const int dev = ctx->device & 63;
+        if (!attr_set[dev]) {
             AHV_CUDA(cudaFuncSetAttribute(k_pack_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_set = true;
+            attr_set[dev] = true;
         }
         k_pack_write<<<grid_for(n, PACK_THREADS), PACK_THREADS, smem, ctx->stream>>>(c, d_out_offsets, d_out_arena, arena_capacity,
                                                                                       ctx->status_d);
