@@ -168,6 +168,7 @@ class Context:
         self.h = h
         self.device = int(device)
         self._lock = threading.Lock()   # one host thread per call
+        self._options: dict[str, int] = {}  # what set_option was last given (to restore after a per-call override)
         self._pinned: dict[int, int] = {}   # numpy data address -> pinned allocation
 
     # -- plumbing -----------------------------------------------------------
@@ -202,6 +203,7 @@ class Context:
 
     def set_option(self, key: str, value: int):
         self._check(self.lib.ahv_set_option(self.h, key.encode(), int(value)), f"ahv_set_option({key})")
+        self._options[key] = int(value)
 
     def dev_alloc(self, nbytes: int) -> int:
         p = _vp()
@@ -443,6 +445,7 @@ class Context:
         o_s = np.empty(A, np.float64); o_r = np.empty(A, np.uint8)
         o_d = np.empty(A, np.uint8); o_n = np.empty(A, np.uint8)
         with self._lock:
+            before = self._options.get("sigma_exact", 0)
             if exact is not None:
                 self.set_option("sigma_exact", 1 if exact else 0)
             try:
@@ -452,7 +455,7 @@ class Context:
                     "ahv_sigma_eff_rings")
             finally:
                 if exact is not None:
-                    self.set_option("sigma_exact", 0)
+                    self.set_option("sigma_exact", before)
         return o_s, o_r, o_d, o_n
 
     def exposure_sums(self, rowptr, bonded, active, expiry, now: int, compensated: Optional[bool] = None) -> np.ndarray:
