@@ -162,6 +162,8 @@ def test_product_never_imports_oracle():
                 assert "oracle" not in src.lower(), f"{fn} mentions the oracle"
                 if fn.endswith(".py"):
                     assert "hashlib" not in src.replace("no hashlib path", ""), f"{fn} uses hashlib"
+                    # the collective lives in the library (csrc/ahv_comm.cu): no torch anywhere in the package
+                    assert "import torch" not in src and "torch." not in src, f"{fn} uses torch"
 
 
 def test_cpp_packer_matches_reference_preimages(audit_golden):
