@@ -681,25 +681,52 @@ template <bool SC>
 __global__ void __launch_bounds__(128)
 k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint32_t *__restrict__ hexpos,
                 const uint64_t *__restrict__ rowptr, uint64_t S, uint8_t *__restrict__ out_digests,
-                uint8_t *__restrict__ out_parents, uint8_t *__restrict__ out_kind, uint32_t rc)
+                uint8_t *__restrict__ out_parents, uint8_t *__restrict__ out_kind, uint32_t rc, uint32_t lanes_per_warp)
 {
     const typename Pol<SC>::type cp = Pol<SC>::make(rc);
-    uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // lanes_per_warp < 32 spreads the sessions over more warps (only the first lanes of each carry one): an
+    // experiment, see ahv_chain_capture_dev
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = (uint32_t)(t & 31u);
+    if (lane >= lanes_per_warp) return;
+    const uint64_t s = (t >> 5) * lanes_per_warp + lane;
     if (s >= S) return;
     uint32_t prev[8];
-    for (uint64_t i = rowptr[s]; i < rowptr[s + 1]; ++i) {
-        const uint64_t off = offsets[i], len = offsets[i + 1] - off;
-        const uint32_t hp = hexpos[i];
-        if (i > rowptr[s] && hp != 0xffffffffu) {
+    const uint64_t i_begin = rowptr[s], i_end = rowptr[s + 1];
+    if (i_begin >= i_end) return;
+    // the next delta's extent and patch position are fetched while the current one is hashed: they do not depend
+    // on the chain, only the bytes do
+    uint64_t off = offsets[i_begin], off_next = offsets[i_begin + 1];
+    uint32_t hp = hexpos[i_begin];
+    for (uint64_t i = i_begin; i < i_end; ++i) {
+        const uint64_t len = off_next - off;
+        uint64_t off_after = 0;
+        uint32_t hp_next = 0xffffffffu;
+        if (i + 1 < i_end) {
+            off_after = __ldg(offsets + i + 2);
+            hp_next = __ldg(hexpos + i + 1);
+        }
+        if (i > i_begin && hp != 0xffffffffu) {
             uint8_t *dst = arena + off + hp;
+            if ((reinterpret_cast<uintptr_t>(dst) & 3u) == 0) {            // 16 word stores instead of 64 byte stores
+                uint32_t *d4 = reinterpret_cast<uint32_t *>(dst);
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                uint32_t w0, w1;
-                hex_expand(prev[q], w0, w1);
-                dst[8 * q + 0] = (uint8_t)(w0 >> 24); dst[8 * q + 1] = (uint8_t)(w0 >> 16);
-                dst[8 * q + 2] = (uint8_t)(w0 >> 8);  dst[8 * q + 3] = (uint8_t)w0;
-                dst[8 * q + 4] = (uint8_t)(w1 >> 24); dst[8 * q + 5] = (uint8_t)(w1 >> 16);
-                dst[8 * q + 6] = (uint8_t)(w1 >> 8);  dst[8 * q + 7] = (uint8_t)w1;
+                for (int q = 0; q < 8; ++q) {
+                    uint32_t w0, w1;
+                    hex_expand(prev[q], w0, w1);
+                    d4[2 * q] = bswap32(w0);                               // first character at the lowest address
+                    d4[2 * q + 1] = bswap32(w1);
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    uint32_t w0, w1;
+                    hex_expand(prev[q], w0, w1);
+                    dst[8 * q + 0] = (uint8_t)(w0 >> 24); dst[8 * q + 1] = (uint8_t)(w0 >> 16);
+                    dst[8 * q + 2] = (uint8_t)(w0 >> 8);  dst[8 * q + 3] = (uint8_t)w0;
+                    dst[8 * q + 4] = (uint8_t)(w1 >> 24); dst[8 * q + 5] = (uint8_t)(w1 >> 16);
+                    dst[8 * q + 6] = (uint8_t)(w1 >> 8);  dst[8 * q + 7] = (uint8_t)w1;
+                }
             }
             if (out_parents) store_digest(out_parents + 32 * i, prev);
             if (out_kind) out_kind[i] = AHV_PARENT_HEX;
@@ -712,6 +739,9 @@ k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint
         }
         sha256_message(arena + off, len, prev, cp);
         if (out_digests) store_digest(out_digests + 32 * i, prev);
+        off = off_next;
+        off_next = off_after;
+        hp = hp_next;
     }
 }
 
@@ -1109,12 +1139,20 @@ int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, 
     if (S == 0 || n == 0) return AHV_OK;
     // one lane per session: with fewer lanes than the chip can keep busy a lane's dependency chain is what
     // counts, and the plain-addition form has the shorter one (14.4 vs 15.4 ms for 10^4 sessions x 1000)
+    // sessions per warp: 32.  Spreading few sessions over more warps (option chain_lanes) was measured slower at every
+    // count (10^4 sessions: 14.0 ms with 32 lanes, 17.2 / 24.4 / 37.7 with 16 / 8 / 4): a warp instruction occupies its
+    // scheduler's integer pipe for two cycles whatever the number of active lanes, so the pass is bound by warp
+    // instructions, and a chain already issues one every ~3.8 cycles on its own
+    uint64_t lpw = ctx->opt_chain_lanes ? (uint64_t)ctx->opt_chain_lanes : 32;
+    lpw = lpw < 1 ? 1 : (lpw > 32 ? 32 : lpw);
+    const uint64_t warps = (S + lpw - 1) / lpw;
+    const unsigned g = grid_for(warps * 32, 64);
     if (ctx->opt_compress && S > 65536)
-        k_chain_capture<true><<<grid_for(S, 64), 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests,
-                                                                       d_parents, d_kind, SHA_SC);
+        k_chain_capture<true><<<g, 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests, d_parents, d_kind,
+                                                         SHA_SC, (uint32_t)lpw);
     else
-        k_chain_capture<false><<<grid_for(S, 64), 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests,
-                                                                        d_parents, d_kind, SHA_SC);
+        k_chain_capture<false><<<g, 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests, d_parents, d_kind,
+                                                          SHA_SC, (uint32_t)lpw);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

@@ -377,6 +377,9 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     } else if (!strcmp(key, "sigma_chunk")) {
         AHV_REQUIRE(value == 1024 || value == 1296 || value == 1440 || value == 1536 || value == 2048, "sigma_chunk must be 1024, 1296, 1440, 1536 or 2048");
         ctx->opt_sigma_chunk = value;
+    } else if (!strcmp(key, "chain_lanes")) {
+        AHV_REQUIRE(value >= 0 && value <= 32, "chain_lanes must be 0 (auto) or 1..32");
+        ctx->opt_chain_lanes = value;
     } else if (!strcmp(key, "compress")) {
         AHV_REQUIRE(value == 0 || value == 1, "compress must be 0 or 1");
         ctx->opt_compress = value;

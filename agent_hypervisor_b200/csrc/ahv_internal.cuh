@@ -44,6 +44,7 @@ struct ahv_ctx {
     int64_t opt_sigma_heavy;   // tiles with more edges than this go through the shared queue (default 3072)
     int64_t opt_sigma_share;   // 1 (default): heavy tiles of the tiled sigma_eff kernel go through a queue shared by the CTAs
     int64_t opt_sigma_chunk;   // edges per shared-memory chunk of the tiled sigma_eff kernel: 2048 (default) or 1024
+    int64_t opt_chain_lanes;   // sessions per warp in the chained-capture kernel (0 = 32)
     int64_t opt_compress;      // 1: scaled-sum compression (adds on the FMA pipe, default), 0: plain additions
     int64_t opt_top_max;       // level width at which the in-CTA tree kernel takes over (0 = auto from the session count, else 2..256; <= 64 uses the warp-per-session finish)
     int64_t opt_peak_ctas;     // CTAs of 256 threads per SM in the ahv_int_peak kernels (default 4)

@@ -447,6 +447,8 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "block" 64/128/256  threads per block of the leaf kernels (default 128)
  *   "fixed_variant" 0/1/2 fixed-size leaf kernel: direct 16-byte loads (default) / cp.async staged / TMA bulk-copy staged
  *   "compress" 0/1      plain additions / scaled-sum compression with additions on the FMA pipe (default 1)
+ *   "chain_lanes" 0..32 chained capture: sessions per warp (0 = 32; fewer spreads the sessions over more warps - measured
+ *                   slower at every session count, kept for the experiment)
  *   "top_max" 0,2..256  level width at which a session's tree is finished in one warp/CTA (0 = auto)
  *   "blocking_sync" 0/1 ahv_audit_sessions: spin (default 0, lowest latency) / sleep on an event while its pipeline
  *                   drains, leaving the host cores to a packer thread (1; what ReplayPipeline sets)
