@@ -28,17 +28,22 @@ async def terminate_sessions(hv, session_ids: Sequence[str], auditor: Optional[B
     managed, failure = [], None
     for sid in session_ids:
         try:
-            m = hv._get_session(sid)                  # core.py:199
-            m.sso.terminate()                         # :200
-        except Exception as e:                        # finish the sessions before this one, then re-raise
+            managed.append((sid, hv._get_session(sid)))       # core.py:199
+        except Exception as e:                        # unknown session: the ones before it are still done, then re-raise
             failure = e
             break
-        managed.append((sid, m))
+    # every root in ONE launch, before any state changes: compute_merkle_root (:204) reads the engines only, so
+    # doing it first is invisible to the per-session steps below and a device failure leaves every session as it was
     audited = [(sid, m) for sid, m in managed if m.sso.config.enable_audit]
     roots = dict(zip((sid for sid, _ in audited),
-                     auditor.roots_of_engines([m.delta_engine for _, m in audited]))) if audited else {}   # :204, all at once
+                     auditor.roots_of_engines([m.delta_engine for _, m in audited]))) if audited else {}
     out = []
     for sid, m in managed:
+        try:
+            m.sso.terminate()                         # :200
+        except Exception as e:                        # this session cannot be ended: stop here, like the loop would
+            failure = e
+            break
         root = roots.get(sid)
         if root:
             hv.commitment.commit(session_id=sid, merkle_root=root,
