@@ -80,6 +80,7 @@ SIGNATURES = {
     "ahv_timer_start": (C.c_int, [_vp, C.c_int]),
     "ahv_timer_stop": (C.c_int, [_vp, C.c_int]),
     "ahv_timer_elapsed_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
+    "ahv_timer_wait": (C.c_int, [_vp, C.c_int]),
     "ahv_sha256_batch": (C.c_int, [_vp, _vp, _vp, _u64, _u64, _vp]),
     "ahv_sha256_one": (C.c_int, [_vp, C.c_char_p, _u64, _vp]),
     "ahv_sha256_batch_dev": (C.c_int, [_vp, _vp, _u64, _vp, _u64, _u64, _vp]),

@@ -20,6 +20,13 @@ from .. import _native as nat
 from .packing import pack_columns
 
 
+def _roots_hex(roots, empty, S: int) -> list:
+    """[S] hex roots (None for an empty session): one hex conversion for the whole chunk, then slices."""
+    h = np.ascontiguousarray(roots).reshape(-1)[: 32 * S].tobytes().hex()
+    e = np.asarray(empty)[:S].astype(bool).tolist()
+    return [None if e[s] else h[64 * s: 64 * s + 64] for s in range(S)]
+
+
 class _BufferSet:
     def __init__(self, ctx: nat.Context, arena_bytes: int, max_deltas: int, max_sessions: int) -> None:
         n, S = max_deltas, max_sessions
@@ -108,7 +115,7 @@ class ReplayPipeline:
             o = self.ctx.audit_sessions(arena, offsets, None, None, bs.rowptr[: S + 1], parent_pos=ppos, out=out,
                                         expected_roots=exp)
             res = dict(digests=o["digests"], first_bad=o["first_bad"], verdict=o["verdict"].astype(bool),
-                       roots=[None if o["empty"][s] else o["roots"][s].tobytes().hex() for s in range(S)],
+                       roots=_roots_hex(o["roots"], o["empty"], S),
                        root_match=(o["root_match"].astype(bool) & ~o["empty"].astype(bool)) if exp is not None else None)
             if copy:
                 res["digests"] = np.array(res["digests"]); res["first_bad"] = np.array(res["first_bad"])
@@ -243,24 +250,41 @@ class DeviceReplay:
                              ("verdict", d["verdict"], S), ("first_bad", d["fb"], 8 * S), ("root_match", d["match"], S)):
             c._check(lib.ahv_memcpy_d2h(h, vp(o[key].ctypes.data), vp(ptr), nb), "ahv_memcpy_d2h")
 
+    # completion of a chunk = a CUDA event on the main stream (two of the context's timer slots, one per buffer set)
+    _EVENT_SLOT = 60
+
+    def _mark(self, ch: dict) -> None:
+        self.ctx.timer_stop(self._EVENT_SLOT + ch["b"])
+
+    def _wait(self, ch: dict) -> None:
+        c = self.ctx
+        c._check(c.lib.ahv_timer_wait(c.h, self._EVENT_SLOT + ch["b"]), "ahv_timer_wait")
+
     def run(self, chunks: Iterable[tuple], copy: bool = True) -> Iterator[dict]:
         """chunks: iterable of ``(cols, session_rowptr)`` / ``(cols, session_rowptr, committed_roots)`` as for
         ``ReplayPipeline.run``, or of ``StagedColumns`` (columns already in pinned memory: no host copy at all);
-        yields the same per-chunk dicts.  While the GPU works on chunk k the host stages chunk k+1 and its upload
-        runs on the second stream."""
+        yields the same per-chunk dicts.  While the GPU works on chunk k the host stages chunk k+1, its upload runs on
+        the second stream and its kernels are enqueued behind chunk k's, so the GPU never waits for the host between
+        chunks.  With ``copy=False`` the arrays are views into pinned buffers, valid until the next chunk is requested."""
         it = (ch if isinstance(ch, tuple) else (ch,) for ch in chunks)
         try:
             cur = self._stage_chunk(0, *next(it))
         except StopIteration:
             return
         k = 0
+        self._enqueue(cur)
+        self._mark(cur)
         while cur is not None:
-            self._enqueue(cur)
+            # chunk k+1 is staged, uploaded (second stream) and ENQUEUED behind chunk k before chunk k is waited for:
+            # the GPU goes from one chunk's kernels straight to the next one's (the work buffers are reused in
+            # stream order; the pinned result sets and the column buffers alternate)
             try:
-                nxt = self._stage_chunk(k + 1, *next(it))          # overlaps the kernels of chunk k
+                nxt = self._stage_chunk(k + 1, *next(it))
+                self._enqueue(nxt)
+                self._mark(nxt)
             except StopIteration:
                 nxt = None
-            self.ctx.sync()                                        # chunk k's results are in its pinned output set
+            self._wait(cur)                                        # chunk k's results are in its pinned output set
             n, S, o = cur["n"], cur["S"], self._out[cur["b"]]
             if n == 0:
                 res = dict(digests=np.zeros((0, 32), np.uint8), first_bad=np.full(S, -1, np.int64), verdict=np.ones(S, bool),
@@ -270,7 +294,7 @@ class DeviceReplay:
                 roots = o["roots"][: 32 * S].reshape(S, 32)
                 res = dict(digests=o["digests"][: 32 * n].reshape(n, 32), first_bad=o["first_bad"][:S],
                            verdict=o["verdict"][:S].astype(bool),
-                           roots=[None if empty[s] else roots[s].tobytes().hex() for s in range(S)],
+                           roots=_roots_hex(roots, empty, S),
                            root_match=(o["root_match"][:S].astype(bool) & ~empty) if cur["has_exp"] else None)
                 if copy:
                     res["digests"] = np.array(res["digests"]); res["first_bad"] = np.array(res["first_bad"])

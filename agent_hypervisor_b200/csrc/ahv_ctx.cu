@@ -345,6 +345,14 @@ int ahv_timer_elapsed_ms(ahv_ctx *ctx, int slot, float *out_ms)
     return AHV_OK;
 }
 
+int ahv_timer_wait(ahv_ctx *ctx, int slot)
+{
+    AHV_TRY(use_device(ctx));
+    AHV_REQUIRE(slot >= 0 && slot < AHV_MAX_TIMERS, "timer slot out of range");
+    AHV_CUDA(cudaEventSynchronize(ctx->t_stop[slot]));
+    return check_status(ctx);
+}
+
 int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
 {
     AHV_TRY(use_device(ctx));

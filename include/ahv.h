@@ -103,6 +103,9 @@ int ahv_upload_fence(ahv_ctx *ctx);
 int ahv_timer_start(ahv_ctx *ctx, int slot);
 int ahv_timer_stop(ahv_ctx *ctx, int slot);
 int ahv_timer_elapsed_ms(ahv_ctx *ctx, int slot, float *out_ms); /* synchronises on the stop event */
+/* Waits until everything enqueued on the ctx stream BEFORE ahv_timer_stop(slot) has finished (work enqueued after it may
+ * still be running): a completion marker for pipelines that keep the GPU fed.  Reports sticky device flags like ahv_sync. */
+int ahv_timer_wait(ahv_ctx *ctx, int slot);
 
 /* ------------------------------------------------------------------ audit path
  *
