@@ -50,7 +50,8 @@ k_sigma_eff_rings(const uint32_t *__restrict__ rowptr, const double *__restrict_
 //
 // A row of d edges is d dependent fp64 additions, so one long row holds its whole tile back (a row of
 // 14 017 edges alone costs more than the rest of a 10^7-edge graph).  With PAR, rows longer than
-// `long_cut` edges are therefore summed by one WARP each, in a FIXED shape that depends on the row alone
+// `long_cut` edges are therefore summed by the WARP that owns them (all 32 lanes on one row at a time, found
+// with a ballot, no shared list and no CTA barrier), in a FIXED shape that depends on the row alone
 // (not on tiling, chunking or scheduling, so it is the same run to run):
 //     partial[p] = live amounts at row positions p, p+32, p+64, ... added in that order   (p = 0..31)
 //     row sum    = xor-butterfly over the 32 partials with strides 16, 8, 4, 2, 1
@@ -146,12 +147,8 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
     extern __shared__ __align__(128) uint8_t sig_smem[];
     SigStage<SIG_CHUNK> &st = *reinterpret_cast<SigStage<SIG_CHUNK> *>(sig_smem);
     __shared__ __align__(8) uint64_t mbar_storage;
-    __shared__ double long_sum[SIG_ROWS];
-    __shared__ uint32_t long_r0[SIG_ROWS], long_r1[SIG_ROWS];
-    __shared__ uint16_t long_owner[SIG_ROWS];
-    __shared__ uint32_t wcount[SIG_WARPS];
     __shared__ uint32_t s_word;
-    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_storage);
     const uint32_t ntiles = gridDim.x;
     if (tid == 0) {
@@ -233,30 +230,11 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
             }
 
             RowSum<MODE == 2> acc;
-            // list of this tile's long rows, in row order (often empty); long row k belongs to warp k % 4
+            // long rows are taken by the warp that owns them, one after the other, all 32 lanes on each: found with
+            // a ballot, the row bounds passed round with shuffles - no shared list, no CTA barrier for them
             const bool is_long = PAR && (my1 - my0 > long_cut);
-            uint32_t n_long = 0;
-            if (PAR) {
-                const uint32_t bal = __ballot_sync(0xffffffffu, is_long);
-                if (lane == 0) wcount[wid] = __popc(bal);
-                __syncthreads();
-                uint32_t before = 0;
-#pragma unroll
-                for (int w = 0; w < SIG_WARPS; ++w) {
-                    const uint32_t c = wcount[w];
-                    if (w < (int)wid) before += c;
-                    n_long += c;
-                }
-                if (is_long) {
-                    const uint32_t k = before + __popc(bal & ((1u << lane) - 1u));
-                    long_r0[k] = my0;
-                    long_r1[k] = my1;
-                    long_owner[k] = (uint16_t)tid;
-                }
-                // (the list is read after the first chunk's conversion barrier: a long row has edges, so there is one)
-            }
-            uint32_t lk = wid;        // this warp's next long row
-            double part = 0.0;        // this lane's strided partial of it
+            uint32_t long_mask = PAR ? __ballot_sync(0xffffffffu, is_long) : 0u;     // the warp's long rows still to finish
+            double part = 0.0;        // this lane's strided partial of the long row in progress
 
             for (uint32_t k = 0; k < nchunk; ++k, ++phase) {
                 const uint32_t c0 = base + k * SIG_CHUNK;
@@ -296,8 +274,9 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
                     for (; e < hi; ++e) acc.add(st.b[e - c0]);
                 }
                 if (PAR) {
-                    while (lk < n_long) {
-                        const uint32_t r0 = long_r0[lk], r1 = long_r1[lk];
+                    while (long_mask) {                           // in row order
+                        const int owner = __ffs(long_mask) - 1;
+                        const uint32_t r0 = __shfl_sync(0xffffffffu, my0, owner), r1 = __shfl_sync(0xffffffffu, my1, owner);
                         if (r0 >= c1) break;                                   // starts in a later chunk
                         const uint32_t lo = r0 > c0 ? r0 : c0, hi = r1 < c1 ? r1 : c1;
                         // row positions congruent to lane (mod 32) inside [lo, hi)
@@ -307,9 +286,9 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
                         double x = part;
 #pragma unroll
                         for (int o = 16; o; o >>= 1) x = __dadd_rn(x, __shfl_xor_sync(0xffffffffu, x, o));
-                        if (lane == 0) long_sum[long_owner[lk]] = x;
+                        if ((int)lane == owner) acc.f = x;
                         part = 0.0;
-                        lk += SIG_WARPS;
+                        long_mask &= long_mask - 1u;
                     }
                 }
                 if (k + 1 < nchunk) {
@@ -317,9 +296,7 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
                     if (tid == 0) issue(k + 1);
                 }
             }
-            if (PAR && n_long) __syncthreads();                   // the warps' row sums are in long_sum
             if (valid) {
-                if (is_long) acc.f = long_sum[tid];
                 const double contrib = acc.result();
                 if (MODE != 0) {
                     out_sigma[a] = contrib;
