@@ -101,11 +101,13 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint3
                  ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes), "r"(mbar) : "memory");
 }
 
-// amount a record contributes: bonded when live (vouching.py:34-38,186-197), else +0.0
+// amount a record contributes: bonded when live (vouching.py:34-38,186-197), else +0.0.
+// "expiry is not None and now > expiry" with None encoded as INT64_MAX is just "now > expiry" (nothing is greater
+// than INT64_MAX), so live = active and expiry >= now: one 64-bit compare per record.
+static_assert(AHV_EXPIRY_NONE == INT64_MAX, "the live test relies on the encoding of 'no expiry'");
 __device__ __forceinline__ double live_amount(double b, uint32_t active, int64_t x, int64_t now)
 {
-    const bool live = active && !((x != AHV_EXPIRY_NONE) && (now > x));
-    return live ? b : 0.0;
+    return (active != 0u && x >= now) ? b : 0.0;
 }
 
 // Work sharing between the CTAs of one launch.  A tile whose rows hold far more edges than a chunk (one row of
@@ -254,7 +256,8 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
                                      "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(mbar), "r"(phase & 1u) : "memory");
                 }
                 if (cnt16 != c1 - c0) __syncthreads();            // the tail elements were written by other threads
-                // conversion pass, all lanes busy: b[i] <- the amount record i contributes (two records per step)
+                // conversion pass, all lanes busy: b[i] <- the amount record i contributes (two records per step: 16-byte
+                // shared-memory accesses at a 16-byte stride; four per step was measured slower - bank conflicts)
                 for (uint32_t i = 2 * tid; i < c1 - c0; i += 2 * SIG_ROWS) {
                     double2 b2 = *reinterpret_cast<const double2 *>(&st.b[i]);
                     const longlong2 x2 = *reinterpret_cast<const longlong2 *>(&st.x[i]);
