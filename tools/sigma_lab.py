@@ -12,6 +12,7 @@ import workloads
 from agent_hypervisor_b200 import Context
 ctx = Context(0)
 out = {}
+LAST_BATCH_MS = 0.0
 
 
 def upload(arrs):
@@ -32,6 +33,13 @@ def time_pass(d, A, now, reps=20):
     ts = []
     for _ in range(reps):
         ctx.timer_start(1); f(); ctx.timer_stop(1); ts.append(ctx.timer_ms(1))
+    # and 20 launches back to back between ONE pair of events (what bench.py reports): no per-launch event latency
+    ctx.timer_start(1)
+    for _ in range(reps):
+        f()
+    ctx.timer_stop(1)
+    global LAST_BATCH_MS
+    LAST_BATCH_MS = ctx.timer_ms(1) / reps
     for p in o:
         ctx.dev_free(p)
     return min(ts), float(np.median(ts))
@@ -87,8 +95,10 @@ def run_config4():
             best, med = time_pass(d, A, gr["now"])
             ctx.set_option("sigma_exact", 0); ctx.set_option("sigma_long_cut", 64); ctx.set_option("sigma_variant", 1); ctx.set_option("sigma_chunk", 1440); ctx.set_option("sigma_share", 1); ctx.set_option("sigma_heavy", 3072)
             res[label] = {"best_us": best * 1e3, "median_us": med * 1e3, "GBps_best": nbytes / best / 1e6,
-                          "GBps_median": nbytes / med / 1e6}
-            print(f"config4 {name:8s} {label:22s} best {best*1e3:7.1f} us  median {med*1e3:7.1f} us  {nbytes/med/1e6:7.0f} GB/s", flush=True)
+                          "GBps_median": nbytes / med / 1e6, "back_to_back_us": LAST_BATCH_MS * 1e3,
+                          "GBps_back_to_back": nbytes / LAST_BATCH_MS / 1e6}
+            print(f"config4 {name:8s} {label:22s} best {best*1e3:7.1f} us  median {med*1e3:7.1f} us  {nbytes/med/1e6:7.0f} GB/s   "
+                  f"back-to-back {LAST_BATCH_MS*1e3:7.1f} us {nbytes/LAST_BATCH_MS/1e6:7.0f} GB/s", flush=True)
         out.setdefault("config4", {})[name] = res
         for p in d.values():
             ctx.dev_free(p)
