@@ -34,6 +34,7 @@ AHV_SL_HDI uint64_t lane_group_bytes(uint64_t agents, uint64_t records)
 }
 
 constexpr uint8_t F_LIVE = 1, F_WAS_LIVE = 2, F_BAD_VOUCHER = 4;
+constexpr uint8_t F_ROW_DEAD = 8;   // lane walker, on the FIRST record of a row: no record of the row can be live any more
 
 struct SlashArgs {
     const uint32_t *rowptr;
@@ -110,12 +111,19 @@ struct LaneRun {
         u = (uint32_t)s_voucher[e] - la;
         return (s_flags[e] & F_LIVE) && u < ln;
     }
-    AHV_SL_HDI bool any_live(uint32_t v) const      // slashing.py:126-129
+    // slashing.py:126-129.  Only slash(v) changes the records of row v and it releases every live one, so a
+    // row found (or left) without a live record stays that way: remembered on the row's first record.  At a
+    // high risk weight most cascade candidates are agents slashed a moment ago; without the mark each of
+    // them costs a scan of the whole row.
+    AHV_SL_HDI bool any_live(uint32_t v)
     {
-        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {
+        const uint32_t e0 = s_rowptr[la + v], e1 = s_rowptr[la + v + 1];
+        if (e0 == e1 || (s_flags[e0] & F_ROW_DEAD)) return false;
+        for (uint32_t e = e0; e < e1; ++e) {
             uint32_t u;
             if (live(e, u)) return true;
         }
+        s_flags[e0] |= F_ROW_DEAD;
         return false;
     }
     // frame: the cascade-stack slot (0 / 1) whose clips this slash produces, or -1 when it will not cascade
@@ -125,7 +133,8 @@ struct LaneRun {
         s_score[la + v] = 0.0;                    // :88
         s_touched[la + v] = 1;
         const uint32_t me = n_slash++, c0 = n_clip;
-        for (uint32_t e = s_rowptr[la + v]; e < s_rowptr[la + v + 1]; ++e) {     // :92
+        const uint32_t e0 = s_rowptr[la + v], e1 = s_rowptr[la + v + 1];
+        for (uint32_t e = e0; e < e1; ++e) {                                     // :92
             uint32_t u;
             if (!live(e, u)) {
                 if ((s_flags[e] & F_LIVE) && u >= ln) status |= 2;              // voucher outside the session
@@ -146,6 +155,7 @@ struct LaneRun {
             q->sigma_before = before;
             q->sigma_after = after;
         }
+        if (e0 < e1) s_flags[e0] |= F_ROW_DEAD;
         ahv_slash_record *r = sl + me;            // :110-119
         r->agent = ga_lo + la + v;
         r->parent = parent;
@@ -240,7 +250,7 @@ AHV_SL_HDI void write_back_run(const LaneRun &r, const SlashArgs &k, uint32_t a_
             k.touched[a_lo + a] = 1;
         }
     for (uint32_t e = lane; e < E; e += stride)
-        if (r.s_flags[e] == F_WAS_LIVE) k.active[e_lo + e] = 0;
+        if ((r.s_flags[e] & (F_LIVE | F_WAS_LIVE)) == F_WAS_LIVE) k.active[e_lo + e] = 0;
 }
 
 // One session of a staged run (agents my_a0 .. my_a1, first record my_e0, events ev_lo .. ev_hi).
