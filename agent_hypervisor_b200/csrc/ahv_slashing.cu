@@ -252,19 +252,19 @@ k_slash_lanes(const SlashArgs k)
             // a session of which fewer than LANE_MIN_SESSIONS would fit a slice is k_slash_cascade's (a whole
             // warp for it)
             if (lane_group_bytes(__shfl_sync(FULL, my_a1, p) - a_lo, __shfl_sync(FULL, my_e1, p) - e_lo) >
-                LANE_SMEM_PER_WARP / LANE_MIN_SESSIONS) {
+                k.lane_slice / LANE_MIN_SESSIONS) {
                 if (lane == 0) k.big_sessions[1 + atomicAdd(k.big_sessions, 1u)] = (uint32_t)(s0 + p);
                 ++p;
                 continue;
             }
             // the longest run of sessions p .. q-1 whose state fits the slice (sizes grow with q: a prefix)
             const bool fit = (uint32_t)lane >= p && (uint32_t)lane < n &&
-                             lane_group_bytes(my_a1 - a_lo, my_e1 - e_lo) <= LANE_SMEM_PER_WARP;
+                             lane_group_bytes(my_a1 - a_lo, my_e1 - e_lo) <= k.lane_slice;
             const uint32_t cnt = __popc(__ballot_sync(FULL, fit));
             const uint32_t q = p + cnt;
             const uint32_t A = __shfl_sync(FULL, my_a1, q - 1) - a_lo, E = __shfl_sync(FULL, my_e1, q - 1) - e_lo;
             LaneRun r;
-            stage_run(r, slash_smem + (size_t)wib * LANE_SMEM_PER_WARP, k, a_lo, A, e_lo, E, (uint32_t)lane, 32u);
+            stage_run(r, slash_smem + (size_t)wib * k.lane_slice, k, a_lo, A, e_lo, E, (uint32_t)lane, 32u);
             __syncwarp();
             if ((uint32_t)lane >= p && (uint32_t)lane < q) run_session(r, k, s, a_lo, e_lo, my_a0, my_a1, my_e0, ev_lo, ev_hi);
             __syncwarp();
@@ -390,7 +390,9 @@ extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
         AHV_CUDA(cudaMemsetAsync(k.big_sessions, 0, 4, ctx->stream));
         const uint64_t groups = (b->n_sessions + 31) / 32;
         const uint64_t gwant = (groups + LANE_WARPS - 1) / LANE_WARPS;
-        k_slash_lanes<<<(unsigned)(gwant < cap ? gwant : cap), 32 * LANE_WARPS, LANE_WARPS * LANE_SMEM_PER_WARP, ctx->stream>>>(k);
+        k.lane_slice = (uint32_t)ctx->opt_slash_slice;
+        const uint64_t lcap = (uint64_t)ctx->sm_count * 32;
+        k_slash_lanes<<<(unsigned)(gwant < lcap ? gwant : lcap), 32 * LANE_WARPS, LANE_WARPS * k.lane_slice, ctx->stream>>>(k);
         AHV_CHECK_LAUNCH(ctx);
     }
     k_slash_cascade<true><<<grid, 32 * SLASH_WARPS, SLASH_WARPS * SLASH_SMEM_PER_WARP, ctx->stream>>>(k, lanes);

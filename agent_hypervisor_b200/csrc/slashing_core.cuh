@@ -30,11 +30,17 @@ constexpr int LANE_MIN_SESSIONS = 4;              // fewer sessions than this in
 
 AHV_SL_HDI uint64_t lane_group_bytes(uint64_t agents, uint64_t records)
 {
-    return 11 * agents + 3 * records + 16;      // < 65536 agents and records: 16-bit indices inside a group
+    return 11 * agents + 2 * records + 16;      // < 8191 agents and < 65536 records: 16-bit words inside a group
 }
 
 constexpr uint8_t F_LIVE = 1, F_WAS_LIVE = 2, F_BAD_VOUCHER = 4;
-constexpr uint8_t F_ROW_DEAD = 8;   // lane walker, on the FIRST record of a row: no record of the row can be live any more
+// The lane walker keeps ONE 16-bit word per staged record: the voucher's run-local agent index in the low 10
+// bits (a run holds fewer than 1000 agents; R_OUTSIDE = not an agent of the run) and three flags above it.
+constexpr uint16_t R_VOUCHER = 0x03ff, R_OUTSIDE = 0x03ff;
+constexpr uint16_t R_LIVE = 0x0400, R_WAS_LIVE = 0x0800;
+constexpr uint16_t R_CASCADE = 0x1000;    // the clip of this record left its voucher under the cascade threshold
+constexpr uint16_t R_ROW_DEAD = 0x2000;   // on the FIRST record of a row: no record of the row can be live any more
+static_assert(LANE_SMEM_PER_WARP / 11 < R_OUTSIDE, "run-local agent indices must fit 10 bits");
 
 struct SlashArgs {
     const uint32_t *rowptr;
@@ -57,6 +63,7 @@ struct SlashArgs {
     uint32_t *clip_count;
     uint8_t *status;
     uint32_t *big_sessions;       // scratch: [0] = count, [1..] = sessions k_slash_lanes left to k_slash_cascade
+    uint32_t lane_slice = LANE_SMEM_PER_WARP;   // k_slash_lanes: bytes of staged state per warp (<= LANE_SMEM_PER_WARP)
 };
 
 AHV_SL_HDI double clip_once(double x, double keep)
@@ -90,72 +97,71 @@ AHV_SL_HDI uint32_t live_flag(uint8_t active, int64_t expiry, int64_t now)
 
 // One lane = one session, serial, on the group's staged state.  Indices: agents and records are
 // group-local in shared memory; `la` is the first agent of this lane's session, `ln` their number.
+//
+// The cascade (slashing.py:122-138) walks the clips of a slash in order and slashes the vouchers whose
+// recorded sigma_after fell under the threshold.  Here a slash leaves that decision on the record it clipped
+// (R_CASCADE), so the walk re-reads the ROW it has just released instead of the clip log: the released
+// records of the row, in order, ARE the slash's clips (slash(v) releases every live record of row v, so
+// only the first slash of v that finds live records produces clips, and nothing else touches the row).
+// MAX_CASCADE_DEPTH is 2, so the reference's explicit stack becomes two nested loops with scalar cursors.
 struct LaneRun {
     double *s_score;
     uint16_t *s_rowptr;           // group-local record index
-    uint16_t *s_voucher;          // group-local agent index
-    uint8_t *s_flags;
+    uint16_t *s_rec;              // voucher (group-local agent index) | R_* flags
     uint8_t *s_touched;
     ahv_slash_record *sl;
     ahv_clip_record *cl;
     uint32_t la, ln;              // this session's agents inside the group
     uint32_t ga_lo, ge_lo;        // the group's first agent row / first record (global indices)
     uint32_t n_slash, n_clip, status;
-    // (sigma_after, voucher) of the first LANE_CLIP_CACHE clips of the slash at cascade depth 0 / 1: what the
-    // cascade loop needs, kept in (L1-resident) local memory instead of reading the clip records back
+    // sigma_after of the first LANE_CLIP_CACHE clips of the slash at cascade level 0 / 1 (the sigma_before of
+    // a cascaded slash), kept in (L1-resident) local memory instead of reading the clip records back
     double c_after[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
-    uint32_t c_voucher[MAX_CASCADE_DEPTH][LANE_CLIP_CACHE];
 
-    AHV_SL_HDI bool live(uint32_t e, uint32_t &u) const
-    {
-        u = (uint32_t)s_voucher[e] - la;
-        return (s_flags[e] & F_LIVE) && u < ln;
-    }
-    // slashing.py:126-129.  Only slash(v) changes the records of row v and it releases every live one, so a
-    // row found (or left) without a live record stays that way: remembered on the row's first record.  At a
-    // high risk weight most cascade candidates are agents slashed a moment ago; without the mark each of
-    // them costs a scan of the whole row.
+    // slashing.py:126-129.  A row found (or left) without a live record stays that way: remembered on the
+    // row's first record.  At a high risk weight most cascade candidates are agents slashed a moment ago;
+    // without the mark each of them costs a scan of the whole row.
     AHV_SL_HDI bool any_live(uint32_t v)
     {
         const uint32_t e0 = s_rowptr[la + v], e1 = s_rowptr[la + v + 1];
-        if (e0 == e1 || (s_flags[e0] & F_ROW_DEAD)) return false;
+        if (e0 == e1 || (s_rec[e0] & R_ROW_DEAD)) return false;
         for (uint32_t e = e0; e < e1; ++e) {
-            uint32_t u;
-            if (live(e, u)) return true;
+            const uint32_t x = s_rec[e];
+            if ((x & R_LIVE) && (x & R_VOUCHER) - la < ln) return true;
         }
-        s_flags[e0] |= F_ROW_DEAD;
+        s_rec[e0] |= R_ROW_DEAD;
         return false;
     }
-    // frame: the cascade-stack slot (0 / 1) whose clips this slash produces, or -1 when it will not cascade
-    AHV_SL_HDI uint32_t slash(uint32_t v, double sigma_before, double keep, uint32_t depth, int32_t parent, uint32_t ev,
-                              int frame)
+    // frame: the cascade level (0 / 1) whose clips this slash produces, or -1 when it will not cascade
+    AHV_SL_HDI uint32_t slash(uint32_t v, double sigma_before, double keep, double thresh, uint32_t depth, int32_t parent,
+                              uint32_t ev, int frame)
     {
         s_score[la + v] = 0.0;                    // :88
         s_touched[la + v] = 1;
         const uint32_t me = n_slash++, c0 = n_clip;
         const uint32_t e0 = s_rowptr[la + v], e1 = s_rowptr[la + v + 1];
         for (uint32_t e = e0; e < e1; ++e) {                                     // :92
-            uint32_t u;
-            if (!live(e, u)) {
-                if ((s_flags[e] & F_LIVE) && u >= ln) status |= 2;              // voucher outside the session
+            const uint32_t x = s_rec[e];
+            const uint32_t u = (x & R_VOUCHER) - la;
+            if (!(x & R_LIVE)) continue;
+            if (u >= ln) {
+                status |= 2;                                                    // voucher outside the session
                 continue;
             }
             const double before = s_score[la + u];                              // :94
             const double after = clip_once(before, keep);                       // :95-96
             s_score[la + u] = after;                                            // :97
             s_touched[la + u] = 1;
-            s_flags[e] = F_WAS_LIVE;                                            // :108 release_bond
-            if (frame >= 0 && n_clip - c0 < (uint32_t)LANE_CLIP_CACHE) {
-                c_after[frame][n_clip - c0] = after;
-                c_voucher[frame][n_clip - c0] = u;
-            }
+            // :108 release_bond, and :124 decided now: will this clip ask for a cascade?
+            s_rec[e] = (uint16_t)((x & ~(uint32_t)R_LIVE) | (after < thresh ? (uint32_t)R_CASCADE : 0u));
+            if (frame >= 0 && n_clip - c0 < (uint32_t)LANE_CLIP_CACHE) c_after[frame][n_clip - c0] = after;
             ahv_clip_record *q = cl + n_clip++;                                 // :99-105
             q->edge = ge_lo + e;
             q->slash = me;
             q->sigma_before = before;
             q->sigma_after = after;
         }
-        if (e0 < e1) s_flags[e0] |= F_ROW_DEAD;
+        if (e0 < e1) s_rec[e0] |= R_ROW_DEAD;
         ahv_slash_record *r = sl + me;            // :110-119
         r->agent = ga_lo + la + v;
         r->parent = parent;
@@ -166,9 +172,17 @@ struct LaneRun {
         r->sigma_before = sigma_before;
         return me;
     }
+    // the o-th clip's sigma_after of the slash whose clips start at c0 (cascade level `frame`)
+    AHV_SL_HDI double clip_after(int frame, uint32_t c0, uint32_t o) const
+    {
+        return o < (uint32_t)LANE_CLIP_CACHE ? c_after[frame][o] : cl[c0 + o].sigma_after;   // a long row: own earlier stores
+    }
+    static AHV_SL_HDI bool released(uint32_t x) { return (x & (uint32_t)(R_LIVE | R_WAS_LIVE)) == (uint32_t)R_WAS_LIVE; }
+
     AHV_SL_HDI void events(const SlashArgs &k, uint64_t ev_lo, uint64_t ev_hi)
     {
         const double thresh = add_rn(SIGMA_FLOOR, 0.01);                        // :124
+        static_assert(MAX_CASCADE_DEPTH == 2, "the cascade below is written out for two levels");
         for (uint64_t ev = ev_lo; ev < ev_hi; ++ev) {
             const uint32_t v0 = k.ev_agent[ev] - (ga_lo + la);
             if (v0 >= ln) {
@@ -177,36 +191,31 @@ struct LaneRun {
             }
             const double keep = add_rn(1.0, -k.ev_omega[ev]);                   // (1.0 - risk_weight), :95
             const uint32_t depth0 = k.ev_depth ? k.ev_depth[ev] : 0u;
-            uint32_t f_c0[MAX_CASCADE_DEPTH], f_cur[MAX_CASCADE_DEPTH], f_end[MAX_CASCADE_DEPTH], f_id[MAX_CASCADE_DEPTH];
-            int d = depth0 < (uint32_t)MAX_CASCADE_DEPTH ? 0 : -1;
-            f_c0[0] = f_cur[0] = n_clip;
-            f_id[0] = slash(v0, k.ev_sigma[ev], keep, depth0, -1, (uint32_t)ev, d);
-            f_end[0] = n_clip;
-            while (d >= 0) {                      // :122-138
-                if (f_cur[d] == f_end[d]) {
-                    --d;
-                    continue;
-                }
-                const uint32_t c = f_cur[d]++;
-                double after;
-                uint32_t u;
-                if (c - f_c0[d] < (uint32_t)LANE_CLIP_CACHE) {
-                    after = c_after[d][c - f_c0[d]];
-                    u = c_voucher[d][c - f_c0[d]];
-                } else {                          // a long row: this lane's own earlier stores
-                    after = cl[c].sigma_after;
-                    u = (uint32_t)s_voucher[cl[c].edge - ge_lo] - la;
-                }
-                if (!(after < thresh)) continue;
+            const bool level0 = depth0 < (uint32_t)MAX_CASCADE_DEPTH;
+            const uint32_t c0_0 = n_clip;
+            const uint32_t id0 = slash(v0, k.ev_sigma[ev], keep, thresh, depth0, -1, (uint32_t)ev, level0 ? 0 : -1);
+            if (!level0 || n_clip == c0_0) continue;
+            const bool level1 = depth0 + 1 < (uint32_t)MAX_CASCADE_DEPTH;
+            uint32_t o0 = 0;
+            for (uint32_t e = s_rowptr[la + v0], e_end = s_rowptr[la + v0 + 1]; e < e_end; ++e) {   // :122-138, level 0
+                const uint32_t x = s_rec[e];
+                if (!released(x)) continue;
+                const uint32_t o = o0++;
+                if (!(x & R_CASCADE)) continue;
+                const uint32_t u = (x & R_VOUCHER) - la;
                 if (!any_live(u)) continue;
-                const uint32_t c0 = n_clip;
-                const bool deeper = depth0 + d + 1 < (uint32_t)MAX_CASCADE_DEPTH;
-                const uint32_t id = slash(u, after, keep, depth0 + d + 1, (int32_t)f_id[d], (uint32_t)ev, deeper ? d + 1 : -1);
-                if (deeper) {
-                    ++d;
-                    f_c0[d] = f_cur[d] = c0;
-                    f_end[d] = n_clip;
-                    f_id[d] = id;
+                const uint32_t c0_1 = n_clip;
+                const uint32_t id1 = slash(u, clip_after(0, c0_0, o), keep, thresh, depth0 + 1, (int32_t)id0, (uint32_t)ev, level1 ? 1 : -1);
+                if (!level1 || n_clip == c0_1) continue;
+                uint32_t o1 = 0;
+                for (uint32_t f = s_rowptr[la + u], f_end = s_rowptr[la + u + 1]; f < f_end; ++f) {   // level 1
+                    const uint32_t y = s_rec[f];
+                    if (!released(y)) continue;
+                    const uint32_t p = o1++;
+                    if (!(y & R_CASCADE)) continue;
+                    const uint32_t w = (y & R_VOUCHER) - la;
+                    if (!any_live(w)) continue;
+                    slash(w, clip_after(1, c0_1, p), keep, thresh, depth0 + 2, (int32_t)id1, (uint32_t)ev, -1);
                 }
             }
         }
@@ -221,9 +230,8 @@ AHV_SL_HDI void stage_run(LaneRun &r, uint8_t *base, const SlashArgs &k, uint32_
 {
     r.s_score = reinterpret_cast<double *>(base);
     r.s_rowptr = reinterpret_cast<uint16_t *>(r.s_score + A);
-    r.s_voucher = r.s_rowptr + (A + 1);
-    r.s_flags = reinterpret_cast<uint8_t *>(r.s_voucher + E);
-    r.s_touched = r.s_flags + E;
+    r.s_rec = r.s_rowptr + (A + 1);
+    r.s_touched = reinterpret_cast<uint8_t *>(r.s_rec + E);
 #pragma unroll 8
     for (uint32_t a = lane; a <= A; a += stride) r.s_rowptr[a] = (uint16_t)(k.rowptr[a_lo + a] - e_lo);
 #pragma unroll 8
@@ -233,10 +241,10 @@ AHV_SL_HDI void stage_run(LaneRun &r, uint8_t *base, const SlashArgs &k, uint32_
     }
 #pragma unroll 8
     for (uint32_t e = lane; e < E; e += stride) {
-        // a voucher outside the run becomes 0xffff: outside every session of the run as well
+        // a voucher outside the run becomes R_OUTSIDE: outside every session of the run as well
         const uint32_t u = k.voucher[e_lo + e] - a_lo;
-        r.s_voucher[e] = (uint16_t)(u < A ? u : 0xffffu);
-        r.s_flags[e] = live_flag(k.active[e_lo + e], k.expiry[e_lo + e], k.now) ? (F_LIVE | F_WAS_LIVE) : 0;
+        r.s_rec[e] = (uint16_t)((u < A ? u : (uint32_t)R_OUTSIDE) |
+                                (live_flag(k.active[e_lo + e], k.expiry[e_lo + e], k.now) ? (R_LIVE | R_WAS_LIVE) : 0));
     }
 }
 
@@ -250,7 +258,7 @@ AHV_SL_HDI void write_back_run(const LaneRun &r, const SlashArgs &k, uint32_t a_
             k.touched[a_lo + a] = 1;
         }
     for (uint32_t e = lane; e < E; e += stride)
-        if ((r.s_flags[e] & (F_LIVE | F_WAS_LIVE)) == F_WAS_LIVE) k.active[e_lo + e] = 0;
+        if ((r.s_rec[e] & (R_LIVE | R_WAS_LIVE)) == R_WAS_LIVE) k.active[e_lo + e] = 0;
 }
 
 // One session of a staged run (agents my_a0 .. my_a1, first record my_e0, events ev_lo .. ev_hi).

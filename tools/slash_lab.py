@@ -16,9 +16,12 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--sessions", type=int, default=1_000_000)
 ap.add_argument("--out", default="")
 ap.add_argument("--no-cpu", action="store_true")
+ap.add_argument("--slice", type=int, default=0)
 ap.add_argument("--only", default="", help="agents,records[,omega]: run just this shape (for ncu)")
 args = ap.parse_args()
 ctx = Context(0)
+if args.slice:
+    ctx.set_option("slash_slice", args.slice)
 results = []
 
 
