@@ -543,7 +543,7 @@ int ahv_slash_cascade(ahv_ctx *ctx, const ahv_slash_batch *b)
     d.status = st.out(b->status, S);
     if (st.rc != AHV_OK) return st.rc;
     if (A) AHV_CUDA(cudaMemsetAsync(d.touched, 0, A, ctx->stream));
-    AHV_TRY(ahv_slash_cascade_dev(ctx, &d));
+    AHV_TRY(slash_cascade_launch(ctx, &d, E));      // E known here: the lane kernel's slice is sized for the average session
     st.back(b->active, d.active, E);
     st.back(b->scores, d.scores, A);
     st.back(b->touched, d.touched, A);

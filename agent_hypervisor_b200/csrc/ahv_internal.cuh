@@ -37,7 +37,7 @@ struct ahv_ctx {
     int64_t opt_block;         // threads per block for SHA kernels (default 128)
     int64_t opt_fixed_variant; // 0: direct LDG.128, 1: smem-staged (cp.async)
     int64_t opt_blocking_sync; // 1: ahv_audit_sessions sleeps on an event instead of spinning while the pipeline drains (default 0)
-    int64_t opt_slash_slice;   // k_slash_lanes: bytes of shared memory per warp (default 10752)
+    int64_t opt_slash_slice;   // k_slash_lanes: bytes of shared memory per warp; 0 = chosen per batch (default)
     int64_t opt_slash_variant; // 0: sessions that fit are staged in shared memory (default), 1: always global memory
     int64_t opt_sigma_variant; // 1: warp-tiled sigma_eff kernel (default), 0: one row per thread straight from global memory
     int64_t opt_sigma_exact;   // 1: every row summed in the reference's order (bit-identical); 0 (default): rows longer than opt_sigma_long_cut take the fixed-shape parallel sum
@@ -108,6 +108,8 @@ static inline uint64_t pad256(uint64_t b) { return (b + 255u) & ~(uint64_t)255u;
 int use_device(ahv_ctx *ctx);
 int check_status(ahv_ctx *ctx);                       // sticky device-side error flags -> error code (clears them)
 void comm_release(ahv_ctx *ctx);                     // ahv_comm.cu: destroys the communicator, if any
+// ahv_slashing.cu: the slashing pass on device arrays; n_records = rowptr[n_agents] when the caller knows it, else UINT64_MAX
+int slash_cascade_launch(ahv_ctx *ctx, const struct ahv_slash_batch *b, uint64_t n_records);
 
 static inline unsigned grid_for(uint64_t threads, unsigned block)
 {

@@ -357,7 +357,29 @@ k_slash_cascade(const SlashArgs k, const int from_list)
 
 using namespace ahv;
 
-extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
+namespace {
+
+// Bytes of shared memory per warp for k_slash_lanes.  A warp fills its slice with as many consecutive sessions
+// as fit (32 at most) and gives each a lane; the slices of the resident warps share the SM's 227 KB.  Measured
+// (tools/slash_lab.py --slice): when 32 average sessions fit 7 KB, or when not even 10.5 KB holds 32 of them,
+// the smaller slice wins (7 CTAs per SM instead of 5, the lanes per SM stay the same); in between the full
+// slice lets every lane of the warp have a session.
+uint32_t auto_lane_slice(uint64_t n_sessions, uint64_t n_agents, uint64_t n_records)
+{
+    constexpr uint64_t SMALL = 7168;
+    if (n_records == UINT64_MAX || n_sessions == 0) return LANE_SMEM_PER_WARP;   // records not known to the host
+    const uint64_t avg = lane_group_bytes((n_agents + n_sessions - 1) / n_sessions, (n_records + n_sessions - 1) / n_sessions);
+    if (32 * avg <= SMALL) return (uint32_t)SMALL;
+    if (32 * avg <= LANE_SMEM_PER_WARP) return LANE_SMEM_PER_WARP;
+    if (LANE_MIN_SESSIONS * avg <= SMALL) return (uint32_t)SMALL;
+    return LANE_SMEM_PER_WARP;
+}
+
+}  // namespace
+
+namespace ahv {
+
+int slash_cascade_launch(ahv_ctx *ctx, const ahv_slash_batch *b, uint64_t n_records)
 {
     AHV_TRY(use_device(ctx));
     AHV_REQUIRE(b, "batch is null");
@@ -390,7 +412,7 @@ extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
         AHV_CUDA(cudaMemsetAsync(k.big_sessions, 0, 4, ctx->stream));
         const uint64_t groups = (b->n_sessions + 31) / 32;
         const uint64_t gwant = (groups + LANE_WARPS - 1) / LANE_WARPS;
-        k.lane_slice = (uint32_t)ctx->opt_slash_slice;
+        k.lane_slice = ctx->opt_slash_slice ? (uint32_t)ctx->opt_slash_slice : auto_lane_slice(b->n_sessions, b->n_agents, n_records);
         const uint64_t lcap = (uint64_t)ctx->sm_count * 32;
         k_slash_lanes<<<(unsigned)(gwant < lcap ? gwant : lcap), 32 * LANE_WARPS, LANE_WARPS * k.lane_slice, ctx->stream>>>(k);
         AHV_CHECK_LAUNCH(ctx);
@@ -399,3 +421,7 @@ extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b)
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
+
+}  // namespace ahv
+
+extern "C" int ahv_slash_cascade_dev(ahv_ctx *ctx, const ahv_slash_batch *b) { return slash_cascade_launch(ctx, b, UINT64_MAX); }

@@ -111,6 +111,7 @@ struct LaneRun {
     uint8_t *s_touched;
     ahv_slash_record *sl;
     ahv_clip_record *cl;
+    ahv_clip_record *cl_next;     // cl + n_clip
     uint32_t la, ln;              // this session's agents inside the group
     uint32_t ga_lo, ge_lo;        // the group's first agent row / first record (global indices)
     uint32_t n_slash, n_clip, status;
@@ -150,12 +151,12 @@ struct LaneRun {
             }
             const double before = s_score[la + u];                              // :94
             const double after = clip_once(before, keep);                       // :95-96
-            s_score[la + u] = after;                                            // :97
-            s_touched[la + u] = 1;
+            s_score[la + u] = after;                                            // :97 (write_back_run marks u touched)
             // :108 release_bond, and :124 decided now: will this clip ask for a cascade?
             s_rec[e] = (uint16_t)((x & ~(uint32_t)R_LIVE) | (after < thresh ? (uint32_t)R_CASCADE : 0u));
             if (frame >= 0 && n_clip - c0 < (uint32_t)LANE_CLIP_CACHE) c_after[frame][n_clip - c0] = after;
-            ahv_clip_record *q = cl + n_clip++;                                 // :99-105
+            ahv_clip_record *q = cl_next++;                                     // :99-105
+            ++n_clip;
             q->edge = ge_lo + e;
             q->slash = me;
             q->sigma_before = before;
@@ -248,17 +249,27 @@ AHV_SL_HDI void stage_run(LaneRun &r, uint8_t *base, const SlashArgs &k, uint32_
     }
 }
 
-// What changed goes back: touched scores, released bonds.
+// What changed goes back: released bonds, touched scores.  The walker marks only the agents it slashed; the
+// vouchers it clipped are the vouchers of the released records, marked here (by all lanes, in parallel).
+// The caller synchronises the lanes before this (the walkers are done) - and once inside, between the two loops.
 AHV_SL_HDI void write_back_run(const LaneRun &r, const SlashArgs &k, uint32_t a_lo, uint32_t A, uint32_t e_lo, uint32_t E,
                                uint32_t lane, uint32_t stride)
 {
+    for (uint32_t e = lane; e < E; e += stride) {
+        const uint32_t x = r.s_rec[e];
+        if ((x & (R_LIVE | R_WAS_LIVE)) == R_WAS_LIVE) {
+            k.active[e_lo + e] = 0;
+            r.s_touched[x & R_VOUCHER] = 1;
+        }
+    }
+#if defined(__CUDA_ARCH__)
+    __syncwarp();
+#endif
     for (uint32_t a = lane; a < A; a += stride)
         if (r.s_touched[a]) {
             k.scores[a_lo + a] = r.s_score[a];
             k.touched[a_lo + a] = 1;
         }
-    for (uint32_t e = lane; e < E; e += stride)
-        if ((r.s_rec[e] & (R_LIVE | R_WAS_LIVE)) == R_WAS_LIVE) k.active[e_lo + e] = 0;
 }
 
 // One session of a staged run (agents my_a0 .. my_a1, first record my_e0, events ev_lo .. ev_hi).
@@ -270,7 +281,7 @@ AHV_SL_HDI void run_session(LaneRun &r, const SlashArgs &k, uint64_t s, uint32_t
     r.ga_lo = a_lo;
     r.ge_lo = e_lo;
     r.sl = k.slash_log + (ev_lo + my_e0);
-    r.cl = k.clip_log + my_e0;
+    r.cl = r.cl_next = k.clip_log + my_e0;
     r.n_slash = r.n_clip = r.status = 0;
     r.events(k, ev_lo, ev_hi);
     k.slash_count[s] = r.n_slash;

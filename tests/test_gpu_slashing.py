@@ -144,6 +144,30 @@ def test_large_batch_and_giant_session_vs_c_restatement(ctx, variant):
     assert_same_outputs(run_gpu(ctx, small), py, small)
 
 
+@pytest.mark.parametrize("slice_bytes", [0, 1024, 2064, 7168, 10752])
+def test_lane_slice_sizes(ctx, slice_bytes):
+    """k_slash_lanes with every size of its per-warp shared-memory slice (0 = chosen from the batch's average
+    session): the runs of sessions a warp stages are cut differently, the records must not change.  The
+    mid-size workload shape (32 agents x 256 records a session, where the auto choice is the 7 KB slice) and a
+    ragged batch whose sessions fall on both sides of every slice."""
+    import workloads
+    ctx.set_option("slash_slice", slice_bytes)
+    try:
+        mid = workloads.slash_sessions(600, 32, 256)
+        mid["event_depth"] = None
+        got = run_gpu(ctx, mid)
+        want = co.slash_cascade(*[mid[k] for k in ("rowptr", "voucher", "active", "expiry", "now", "session_agent_rowptr",
+                                                   "event_rowptr", "event_agent", "event_sigma", "event_omega", "scores")], None)
+        assert int(want[6].sum()) > 30000
+        assert_same_outputs(got, want, mid)
+        b = big_batch(21, 4000, giant=(90, 700))
+        assert_same_outputs(run_gpu(ctx, b), run_c(b), b)
+    finally:
+        ctx.set_option("slash_slice", 0)
+    with pytest.raises(Exception):
+        ctx.set_option("slash_slice", 1000)
+
+
 def test_edge_shapes_and_refusals(ctx):
     from agent_hypervisor_b200 import _native as nat
     z32, z64 = np.zeros(0, np.uint32), np.zeros(0, np.uint64)
