@@ -24,9 +24,9 @@
 //
 // Small sessions (a handful of records per row) would leave most of a warp's lanes idle, so k_slash_lanes
 // runs first: a warp takes 32 consecutive sessions, cuts them into runs that fit its slice of shared memory
-// (11 B per agent + 3 B per record), stages a run's contiguous rows, records and scores with coalesced
+// (11 B per agent + 2 B per record), stages a run's contiguous rows, records and scores with coalesced
 // reads, then every lane walks ITS session serially out of shared memory - the reference's loop as
-// written - and the warp writes back what changed.  Sessions so large that fewer than four fit a slice
+// written - and the warp writes back what changed.  Sessions so large that fewer than two fit a slice
 // are listed for k_slash_cascade, which then only visits that list.
 #include "ahv_internal.cuh"
 #include "slashing_core.cuh"
@@ -371,7 +371,7 @@ uint32_t auto_lane_slice(uint64_t n_sessions, uint64_t n_agents, uint64_t n_reco
     const uint64_t avg = lane_group_bytes((n_agents + n_sessions - 1) / n_sessions, (n_records + n_sessions - 1) / n_sessions);
     if (32 * avg <= SMALL) return (uint32_t)SMALL;
     if (32 * avg <= LANE_SMEM_PER_WARP) return LANE_SMEM_PER_WARP;
-    if (LANE_MIN_SESSIONS * avg <= SMALL) return (uint32_t)SMALL;
+    if (4 * avg <= SMALL) return (uint32_t)SMALL;
     return LANE_SMEM_PER_WARP;
 }
 

@@ -26,7 +26,7 @@ constexpr int LANE_WARPS = 4;                     // k_slash_lanes: warps per CT
 constexpr uint32_t LANE_SMEM_PER_WARP = 10752;    // bytes of staged state for a run of sessions (5 CTAs per SM)
 static_assert(LANE_WARPS * LANE_SMEM_PER_WARP <= 48 * 1024, "k_slash_lanes must fit the default dynamic shared-memory limit");
 constexpr int LANE_CLIP_CACHE = 12;
-constexpr int LANE_MIN_SESSIONS = 4;              // fewer sessions than this in a run: a warp per session instead
+constexpr int LANE_MIN_SESSIONS = 2;              // fewer sessions than this in a run: a warp per session instead
 
 AHV_SL_HDI uint64_t lane_group_bytes(uint64_t agents, uint64_t records)
 {

@@ -20,9 +20,18 @@ ap.add_argument("--slice", type=int, default=0)
 ap.add_argument("--only", default="", help="agents,records[,omega]: run just this shape (for ncu)")
 args = ap.parse_args()
 ctx = Context(0)
-if args.slice:
-    ctx.set_option("slash_slice", args.slice)
 results = []
+
+
+def host_entry_slice(S, A, E):
+    """The slice ahv_slash_cascade (host entry, which knows E) picks for a batch - auto_lane_slice in
+    csrc/ahv_slashing.cu; this tool times ahv_slash_cascade_dev on resident arrays and sets the same value."""
+    avg = 11 * -(-A // S) + 2 * -(-E // S) + 16
+    if 32 * avg <= 7168:
+        return 7168
+    if 32 * avg <= 10752:
+        return 10752
+    return 7168 if 4 * avg <= 7168 else 10752
 
 
 def run(name, b, cpu=True):
@@ -42,6 +51,8 @@ def run(name, b, cpu=True):
         setattr(sb, k, d[k])
     sb.event_depth = None
     lib, H = ctx.lib, ctx.h
+    slice_bytes = args.slice or host_entry_slice(S, A, E)
+    ctx.set_option("slash_slice", slice_bytes)
 
     def reset():
         ctx.h2d(d["active"], host["active"]); ctx.h2d(d["scores"], host["scores"])
@@ -60,7 +71,7 @@ def run(name, b, cpu=True):
     ms = float(np.median(times))
     n_slash, n_clip = int(ns.sum()), int(nc.sum())
     algo = workloads.slash_bytes(b, n_slash, n_clip)
-    r = dict(case=name, sessions=S, agents=A, records=E, slash_calls=n_slash, clips=n_clip, ms=ms, ms_min=float(min(times)),
+    r = dict(case=name, lane_slice=slice_bytes, sessions=S, agents=A, records=E, slash_calls=n_slash, clips=n_clip, ms=ms, ms_min=float(min(times)),
              sessions_per_s=S / (ms * 1e-3), clips_per_s=n_clip / (ms * 1e-3), algorithmic_bytes=algo,
              algorithmic_GBps=algo / (ms * 1e-3) / 1e9)
     if cpu and not args.no_cpu:
@@ -94,6 +105,8 @@ for variant in (1, 2, 0):
 run(f"{S} sessions x 16 agents x 48 records, omega 0.95", workloads.slash_sessions(S, 16, 48))
 run(f"{S} sessions x 16 agents x 48 records, omega 0.5 (no cascades)", workloads.slash_sessions(S, 16, 48, omega=0.5))
 run(f"{S // 4} sessions x 64 agents x 512 records, omega 0.95", workloads.slash_sessions(S // 4, 64, 512))
+run(f"{S // 2} sessions x 32 agents x 256 records, omega 0.95", workloads.slash_sessions(S // 2, 32, 256))
+run(f"{S // 8} sessions x 128 agents x 1024 records, omega 0.95 (warp per session)", workloads.slash_sessions(S // 8, 128, 1024))
 run("one session x 1e5 agents x 1e6 records, omega 0.95", workloads.slash_sessions(1, 100_000, 1_000_000))
 if args.out:
     with open(os.path.join(ROOT, args.out), "w") as f:
