@@ -16,7 +16,8 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--sessions", type=int, default=1_000_000)
 ap.add_argument("--out", default="")
 ap.add_argument("--no-cpu", action="store_true")
-ap.add_argument("--slice", type=int, default=0)
+ap.add_argument("--slice", type=int, default=0, help="lane kernel: bytes of shared memory per warp (0: what the host entry picks)")
+ap.add_argument("--variant", type=int, default=0, help="slash_variant for --only runs")
 ap.add_argument("--only", default="", help="agents,records[,omega]: run just this shape (for ncu)")
 args = ap.parse_args()
 ctx = Context(0)
@@ -92,6 +93,7 @@ def run(name, b, cpu=True):
 
 S = args.sessions
 if args.only:
+    ctx.set_option("slash_variant", args.variant)
     p = args.only.split(",")
     run(f"{S} sessions x {p[0]} agents x {p[1]} records", workloads.slash_sessions(S, int(p[0]), int(p[1]), omega=float(p[2]) if len(p) > 2 else 0.95), cpu=False)
     sys.exit(0)
