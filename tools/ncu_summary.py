@@ -21,10 +21,14 @@ KEYS = [("gpu__time_duration.sum", "duration"), ("dram__bytes_read.sum", "DRAM r
 lines = [f"# ncu --set full, {tag} (B200, --clock-control none; cold-cache, serialised launches)\n"]
 for name in ("sigma", "var", "chain", "tree"):
     rep = os.path.join(ROOT, "gpurun_out", f"prof_{tag}_{name}.ncu-rep")
-    if not os.path.exists(rep):
+    kept = os.path.join(outdir, f"prof_{name}_raw.csv")
+    if os.path.exists(rep):
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        open(kept, "w").write(raw)
+    elif os.path.exists(kept):                  # the report is scratch (gpurun_out/); its raw page was kept
+        raw = open(kept).read()
+    else:
         continue
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-    open(os.path.join(outdir, f"prof_{name}_raw.csv"), "w").write(raw)
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units, data = rows[0], rows[1], rows[2:]
     kn = hdr.index("Kernel Name")
