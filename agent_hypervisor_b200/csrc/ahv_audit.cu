@@ -718,14 +718,25 @@ k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint
                     d4[2 * q + 1] = bswap32(w1);
                 }
             } else {
+                // the field starts r = 1..3 bytes into a word (the usual case: its position moves with the digits of
+                // delta_id and turn_id): 15 whole words, each made of two neighbouring hex words, and the 4 bytes at
+                // the two ragged ends - not 64 byte stores, which kept the load/store unit busy for 3.5 us per delta
+                const uint32_t r = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 3u);
+                uint32_t *d4 = reinterpret_cast<uint32_t *>(dst - r);
+                uint32_t m[16];                                            // the field as little-endian words
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
                     uint32_t w0, w1;
                     hex_expand(prev[q], w0, w1);
-                    dst[8 * q + 0] = (uint8_t)(w0 >> 24); dst[8 * q + 1] = (uint8_t)(w0 >> 16);
-                    dst[8 * q + 2] = (uint8_t)(w0 >> 8);  dst[8 * q + 3] = (uint8_t)w0;
-                    dst[8 * q + 4] = (uint8_t)(w1 >> 24); dst[8 * q + 5] = (uint8_t)(w1 >> 16);
-                    dst[8 * q + 6] = (uint8_t)(w1 >> 8);  dst[8 * q + 7] = (uint8_t)w1;
+                    m[2 * q] = bswap32(w0);
+                    m[2 * q + 1] = bswap32(w1);
+                }
+#pragma unroll
+                for (int k = 1; k < 16; ++k) d4[k] = __funnelshift_l(m[k - 1], m[k], 8u * r);
+#pragma unroll
+                for (uint32_t t = 0; t < 3; ++t) {
+                    if (t < 4u - r) dst[t] = (uint8_t)(m[0] >> (8u * t));
+                    if (t < r) dst[64u - r + t] = (uint8_t)(m[15] >> (8u * (4u - r + t)));
                 }
             }
             if (out_parents) store_digest(out_parents + 32 * i, prev);
