@@ -677,10 +677,38 @@ k_sha256_one(const __grid_constant__ OneMsg m, uint8_t *out_mapped, uint32_t rc)
 // One thread per session walks its chain (audit/delta.py:101-114): hash delta i, write the
 // 64 hex characters into delta i+1's pre-image, continue.  Plain (coherent) loads only:
 // the thread re-reads bytes it has just written.
+// Blocks of a delta that lie wholly in front of its parent field do not depend on the chain.
+__device__ __forceinline__ uint64_t chain_prefix_blocks(uint32_t hp, uint64_t len)
+{
+    if (hp == 0xffffffffu) return 0;
+    const uint64_t a = hp >> 6, b = len >> 6;
+    return a < b ? a : b;
+}
+
+// Pre-pass of the chained capture, one thread per delta: the SHA-256 state after those blocks, left in the
+// delta's slot of out_digests (raw state words; k_chain_capture reads it before it stores the digest there).
 template <bool SC>
 __global__ void __launch_bounds__(128)
+k_chain_prefix(const uint8_t *__restrict__ arena, const uint64_t *__restrict__ offsets, const uint32_t *__restrict__ hexpos,
+               uint64_t n, uint8_t *__restrict__ out_digests, uint32_t rc)
+{
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t off = offsets[i];
+    const uint64_t nb = chain_prefix_blocks(hexpos[i], offsets[i + 1] - off);
+    if (nb == 0) return;
+    uint32_t st[8];
+    sha256_prefix(arena + off, nb, st, cp);
+    U4 *o = reinterpret_cast<U4 *>(out_digests + 32 * i);
+    o[0] = U4{st[0], st[1], st[2], st[3]};
+    o[1] = U4{st[4], st[5], st[6], st[7]};
+}
+
+template <bool SC, bool PREFIX>
+__global__ void __launch_bounds__(128)
 k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint32_t *__restrict__ hexpos,
-                const uint64_t *__restrict__ rowptr, uint64_t S, uint8_t *__restrict__ out_digests,
+                const uint64_t *__restrict__ rowptr, uint64_t S, uint8_t *out_digests,
                 uint8_t *__restrict__ out_parents, uint8_t *__restrict__ out_kind, uint32_t rc, uint32_t lanes_per_warp)
 {
     const typename Pol<SC>::type cp = Pol<SC>::make(rc);
@@ -698,13 +726,25 @@ k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint
     // on the chain, only the bytes do
     uint64_t off = offsets[i_begin], off_next = offsets[i_begin + 1];
     uint32_t hp = hexpos[i_begin];
+    U4 mid0 = {0, 0, 0, 0}, mid1 = {0, 0, 0, 0};       // PREFIX: the state k_chain_prefix left for delta i
+    if (PREFIX && chain_prefix_blocks(hp, off_next - off)) {
+        const U4 *m = reinterpret_cast<const U4 *>(out_digests + 32 * i_begin);
+        mid0 = m[0];
+        mid1 = m[1];
+    }
     for (uint64_t i = i_begin; i < i_end; ++i) {
         const uint64_t len = off_next - off;
         uint64_t off_after = 0;
         uint32_t hp_next = 0xffffffffu;
+        U4 nmid0 = {0, 0, 0, 0}, nmid1 = {0, 0, 0, 0};
         if (i + 1 < i_end) {
             off_after = __ldg(offsets + i + 2);
             hp_next = __ldg(hexpos + i + 1);
+            if (PREFIX && chain_prefix_blocks(hp_next, off_after - off_next)) {   // chain-independent as well: fetched a delta ahead
+                const U4 *m = reinterpret_cast<const U4 *>(out_digests + 32 * (i + 1));
+                nmid0 = m[0];
+                nmid1 = m[1];
+            }
         }
         if (i > i_begin && hp != 0xffffffffu) {
             uint8_t *dst = arena + off + hp;
@@ -748,11 +788,20 @@ k_chain_capture(uint8_t *arena, const uint64_t *__restrict__ offsets, const uint
             }
             if (out_kind) out_kind[i] = AHV_PARENT_NONE;
         }
-        sha256_message(arena + off, len, prev, cp);
+        const uint64_t nb = PREFIX ? chain_prefix_blocks(hp, len) : 0;
+        if (nb) {
+            prev[0] = mid0.x; prev[1] = mid0.y; prev[2] = mid0.z; prev[3] = mid0.w;
+            prev[4] = mid1.x; prev[5] = mid1.y; prev[6] = mid1.z; prev[7] = mid1.w;
+            sha256_message_from(arena + off, len, prev, nb, cp);
+        } else {
+            sha256_message(arena + off, len, prev, cp);
+        }
         if (out_digests) store_digest(out_digests + 32 * i, prev);
         off = off_next;
         off_next = off_after;
         hp = hp_next;
+        mid0 = nmid0;
+        mid1 = nmid1;
     }
 }
 
@@ -1149,21 +1198,41 @@ int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, 
     AHV_TRY(check_sizes(n, S));
     if (S == 0 || n == 0) return AHV_OK;
     // one lane per session: with fewer lanes than the chip can keep busy a lane's dependency chain is what
-    // counts, and the plain-addition form has the shorter one (14.4 vs 15.4 ms for 10^4 sessions x 1000)
+    // counts, and the plain-addition form has the shorter one.
     // sessions per warp: 32.  Spreading few sessions over more warps (option chain_lanes) was measured slower at every
-    // count (10^4 sessions: 14.0 ms with 32 lanes, 17.2 / 24.4 / 37.7 with 16 / 8 / 4): a warp instruction occupies its
-    // scheduler's integer pipe for two cycles whatever the number of active lanes, so the pass is bound by warp
-    // instructions, and a chain already issues one every ~3.8 cycles on its own
+    // count (10^4 sessions x 1000: 17 / 24 / 38 ms with 16 / 8 / 4 lanes against 14 with 32, before the changes of
+    // round 2): a warp instruction occupies its scheduler's integer pipe for two cycles whatever the number of
+    // active lanes, so the pass is bound by warp instructions, and a chain already issues one every ~3.8 cycles
     uint64_t lpw = ctx->opt_chain_lanes ? (uint64_t)ctx->opt_chain_lanes : 32;
     lpw = lpw < 1 ? 1 : (lpw > 32 ? 32 : lpw);
     const uint64_t warps = (S + lpw - 1) / lpw;
     const unsigned g = grid_for(warps * 32, 64);
-    if (ctx->opt_compress && S > 65536)
-        k_chain_capture<true><<<g, 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests, d_parents, d_kind,
-                                                         SHA_SC, (uint32_t)lpw);
-    else
-        k_chain_capture<false><<<g, 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests, d_parents, d_kind,
-                                                          SHA_SC, (uint32_t)lpw);
+    // The blocks in front of a delta's parent field do not depend on the chain: hashed first, all deltas in
+    // parallel, their state parked in the delta's digest slot (so only when digests are asked for).  For the
+    // 256-byte deltas of config 2 that is one compression of five, for benchmark-shaped deltas (the field
+    // sits behind the change list) three of six.
+    // Only while the pass is bound by the length of a chain: with more than 2^16 sessions every scheduler has several
+    // warps, the compressions themselves bound it, and the pre-pass is extra traffic (10^5 x 100: 4.3 ms without, 4.9 with).
+    const bool prefix = d_digests && (ctx->opt_chain_prefix == 2 || (ctx->opt_chain_prefix == 1 && S <= 65536));
+    if (prefix) {
+        AHV_REQUIRE((reinterpret_cast<uintptr_t>(d_digests) & 15u) == 0, "out_digests must be 16-byte aligned");
+        if (ctx->opt_compress)
+            k_chain_prefix<true><<<grid_for(n, 128), 128, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, n, d_digests, SHA_SC);
+        else
+            k_chain_prefix<false><<<grid_for(n, 128), 128, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, n, d_digests, SHA_SC);
+        AHV_CHECK_LAUNCH(ctx);
+    }
+#define AHV_CHAIN_LAUNCH(SC, PF)                                                                                          \
+    k_chain_capture<SC, PF><<<g, 64, 0, ctx->stream>>>(d_arena, d_offsets, d_hexpos, d_rowptr, S, d_digests, d_parents, d_kind, \
+                                                       SHA_SC, (uint32_t)lpw)
+    if (ctx->opt_compress && S > 65536) {
+        if (prefix) AHV_CHAIN_LAUNCH(true, true);
+        else AHV_CHAIN_LAUNCH(true, false);
+    } else {
+        if (prefix) AHV_CHAIN_LAUNCH(false, true);
+        else AHV_CHAIN_LAUNCH(false, false);
+    }
+#undef AHV_CHAIN_LAUNCH
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

@@ -175,6 +175,7 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_sigma_heavy = 3072;
     c->opt_slash_variant = 0;
     c->opt_slash_slice = 0;
+    c->opt_chain_prefix = 1;
     c->opt_blocking_sync = 0;
     *out_ctx = c;
     return AHV_OK;
@@ -367,6 +368,9 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "slash_variant")) {
         AHV_REQUIRE(value >= 0 && value <= 2, "slash_variant must be 0, 1 or 2");
         ctx->opt_slash_variant = value;
+    } else if (!strcmp(key, "chain_prefix")) {
+        AHV_REQUIRE(value >= 0 && value <= 2, "chain_prefix must be 0, 1 or 2");
+        ctx->opt_chain_prefix = value;
     } else if (!strcmp(key, "slash_slice")) {
         AHV_REQUIRE(value == 0 || (value >= 1024 && value <= 10752 && value % 16 == 0),
                     "slash_slice must be 0 (chosen per batch) or a multiple of 16 in 1024..10752");

@@ -492,19 +492,21 @@ AHV_HD void load_block_raw(const uint32_t *qb, bool aligned16, uint32_t a, uint3
 // SHA-256 of len bytes at p (any alignment).  One compress copy: full blocks take the fast word
 // path (next block's raw words are fetched before the current block is compressed), the final
 // one or two blocks build padding per word.
+//
+// sha256_message_from continues from the state after the first b0 (full) blocks - the chained capture
+// hashes the blocks in front of the parent field ahead of time (sha256_prefix), in parallel over all deltas.
 template <class P>
-AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8], const P &cp)
+AHV_HD void sha256_message_from(const uint8_t *p, uint64_t len, uint32_t st[8], uint64_t b0, const P &cp)
 {
     MsgReader rd;
     rd.init(p);
-    sha256_init(st);
     const uint64_t nfull = len >> 6;
     const uint32_t rem = (uint32_t)(len & 63u);
     const uint64_t nblk = nfull + ((rem + 9u > 64u) ? 2u : 1u);
     const bool aligned16 = ((reinterpret_cast<uintptr_t>(p) & 15u) == 0);
     uint32_t x[17];
-    if (nfull) load_block_raw(rd.q, aligned16, rd.a, x);
-    for (uint64_t b = 0; b < nblk; ++b) {
+    if (b0 < nfull) load_block_raw(rd.q + 16 * b0, aligned16, rd.a, x);
+    for (uint64_t b = b0; b < nblk; ++b) {
         uint32_t w[16];
         const uint32_t *qb = rd.q + 16 * b;
         if (b < nfull) {
@@ -538,6 +540,32 @@ AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8], const
                 w[15] = (uint32_t)bits;
             }
         }
+        cp.block(st, w);
+    }
+}
+
+template <class P>
+AHV_HD void sha256_message(const uint8_t *p, uint64_t len, uint32_t st[8], const P &cp)
+{
+    sha256_init(st);
+    sha256_message_from(p, len, st, 0, cp);
+}
+
+// State after the first nb full blocks of the message at p (nb * 64 <= its length).
+template <class P>
+AHV_HD void sha256_prefix(const uint8_t *p, uint64_t nb, uint32_t st[8], const P &cp)
+{
+    MsgReader rd;
+    rd.init(p);
+    sha256_init(st);
+    const bool aligned16 = ((reinterpret_cast<uintptr_t>(p) & 15u) == 0);
+    uint32_t x[17];
+    if (nb) load_block_raw(rd.q, aligned16, rd.a, x);
+    for (uint64_t b = 0; b < nb; ++b) {
+        uint32_t w[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[j] = prmt(x[j], x[j + 1], rd.sel);
+        if (b + 1 < nb) load_block_raw(rd.q + 16 * (b + 1), aligned16, rd.a, x);
         cp.block(st, w);
     }
 }

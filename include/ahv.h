@@ -236,7 +236,8 @@ int ahv_extract_parents_dev(ahv_ctx *ctx, const uint8_t *d_arena, uint64_t arena
  * chars into delta i+1's pre-image at byte hexpos[i+1] (the "parent_hash" value the
  * host left as a 64-char placeholder), then continue.  hexpos[i] = UINT32_MAX for a
  * delta whose parent is null.  The arena is patched in place; digests and the parent
- * side arrays (for ahv_verify_chains) are produced.
+ * side arrays (for ahv_verify_chains) are produced.  While the call runs, out_digests also
+ * holds intermediate hash states (option "chain_prefix"); every slot ends as its delta's digest.
  */
 int ahv_chain_capture(ahv_ctx *ctx, uint8_t *arena, const uint64_t *offsets, const uint32_t *hexpos,
                       const uint64_t *session_rowptr, uint64_t n_sessions, uint8_t *out_digests,
@@ -452,6 +453,9 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "compress" 0/1      plain additions / scaled-sum compression with additions on the FMA pipe (default 1)
  *   "chain_lanes" 0..32 chained capture: sessions per warp (0 = 32; fewer spreads the sessions over more warps - measured
  *                   slower at every session count, kept for the experiment)
+ *   "chain_prefix" 0/1/2  chained capture: the blocks in front of each delta's parent field are hashed in a parallel
+ *                   pre-pass: never / for up to 2^16 sessions, where the length of a chain bounds the pass (default 1) /
+ *                   always (2).  Needs out_digests, where the intermediate states are parked
  *   "top_max" 0,2..256  level width at which a session's tree is finished in one warp/CTA (0 = auto)
  *   "blocking_sync" 0/1 ahv_audit_sessions: spin (default 0, lowest latency) / sleep on an event while its pipeline
  *                   drains, leaving the host cores to a packer thread (1; what ReplayPipeline sets)

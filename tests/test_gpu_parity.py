@@ -501,6 +501,51 @@ def test_chain_capture_vs_python_chain(ctx):
     assert np.array_equal(digs, co.sha256_batch(wa, wo))
 
 
+@pytest.mark.parametrize("prefix", [1, 0, 2])
+def test_chain_capture_parent_field_anywhere(ctx, prefix):
+    """Chained capture over ragged messages with the 64-character parent field at every kind of position: in the
+    first block, straddling block boundaries, reaching the last byte, at all four byte alignments, absent in the
+    middle of a chain - with and without the parallel pre-pass over the blocks in front of the field
+    (option chain_prefix).  Checked against hashlib run link by link."""
+    rng = np.random.default_rng(77 + prefix)
+    S = 150
+    lens, hps, rp = [], [], [0]
+    for s in range(S):
+        L = int(rng.integers(0, 12))
+        for i in range(L):
+            n = int(rng.choice([64, 65, 100, 119, 120, 127, 128, 191, 192, 256, 300, 332, 640, 1000, 2048]))
+            if i == 0 or rng.random() < 0.1:
+                hp = 0xFFFFFFFF
+            else:
+                hp = int(rng.choice([0, 1, 2, 3, 60, 63, 64, 100, n - 64, max(0, n - 65), int(rng.integers(0, n - 63))]))
+                hp = min(hp, n - 64)
+            lens.append(n); hps.append(hp)
+        rp.append(len(lens))
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    arena = rng.integers(32, 127, int(offs[-1]), dtype=np.uint8)
+    want = arena.copy()
+    digs_w = np.zeros((len(lens), 32), np.uint8)
+    for s in range(S):
+        prev = None
+        for i in range(rp[s], rp[s + 1]):
+            o, n, hp = int(offs[i]), lens[i], hps[i]
+            if i > rp[s] and hp != 0xFFFFFFFF:
+                want[o + hp: o + hp + 64] = np.frombuffer(prev.hex().encode(), np.uint8)
+            prev = hashlib.sha256(want[o: o + n].tobytes()).digest()
+            digs_w[i] = np.frombuffer(prev, np.uint8)
+    ctx.set_option("chain_prefix", prefix)
+    try:
+        got = arena.copy()
+        digs, par, kind = ctx.chain_capture(got, offs, np.array(hps, np.uint32), np.array(rp, np.uint64))
+    finally:
+        ctx.set_option("chain_prefix", 1)
+    assert np.array_equal(digs, digs_w)
+    assert np.array_equal(got, want)
+    is_first = np.zeros(len(lens), bool); is_first[np.array(rp[:-1])[np.diff(rp) > 0]] = True
+    patched = (~is_first) & (np.array(hps, np.uint64) != 0xFFFFFFFF)
+    assert np.array_equal(kind != 0, patched)
+
+
 # ------------------------------------------------------------------ drop-in classes
 def test_delta_engine_dropin(ctx):
     from agent_hypervisor_b200 import DeltaEngine, VFSChange
