@@ -713,7 +713,8 @@ def run_cuda(args):
                 "frac_of_h2d_ceiling": (h2d / e2e_s) / (arena_bytes / copy_s),
                 # on boxes whose host side is one shared resource for both directions (8 ranks: uploads and the digests coming
                 # back do not overlap for free) the bytes of BOTH directions are what the ceiling has to carry
-                "frac_of_ceiling_both_directions": ((h2d + d2h) / e2e_s) / (arena_bytes / copy_s),
+                "both_directions_over_h2d_ceiling": ((h2d + d2h) / e2e_s) / (arena_bytes / copy_s),
+                "both_directions_note": "a ratio, not a fraction: above 1 where uploads and downloads overlap on a full-duplex link (one rank)",
                 "without_digests": {"value": world * n * e2e_steps / e2e_nodig_s, "d2h_bytes_per_step": d2h - 32 * n,
                                     "note": "out_digests = NULL: roots, verdicts, first-bad indices and root matches only"}},
         "comm": ctx.comm_info(), "host": host, "configs": configs,

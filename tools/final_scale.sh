@@ -6,5 +6,5 @@ timeout 300 python -m pytest tests/test_gpu_comm.py -m gpu -x -q 2>&1 | tail -2
 python - <<PY
 import json
 for n in (8,4,2):
-    d=json.load(open(f"gpurun_out/bench_r02c_n{n}.json")); print(n, d["value"], d["ms_per_step"], d["e2e"]["value"], d["e2e"]["h2d_ceiling_gbs"], d["e2e"]["frac_of_ceiling_both_directions"], d["verified"], d["clocks"]["sm_mhz"], d["clocks"]["reasons"])
+    d=json.load(open(f"gpurun_out/bench_r02c_n{n}.json")); print(n, d["value"], d["ms_per_step"], d["e2e"]["value"], d["e2e"]["h2d_ceiling_gbs"], d["e2e"].get("both_directions_over_h2d_ceiling", d["e2e"].get("frac_of_ceiling_both_directions")), d["verified"], d["clocks"]["sm_mhz"], d["clocks"]["reasons"])
 PY
