@@ -361,15 +361,16 @@ namespace {
 
 // Bytes of shared memory per warp for k_slash_lanes.  A warp fills its slice with as many consecutive sessions
 // as fit (32 at most) and gives each a lane; the slices of the resident warps share the SM's 227 KB.  Measured
-// (tools/slash_lab.py --slice): when 32 average sessions fit 7 KB, or when not even 10.5 KB holds 32 of them,
-// the smaller slice wins (7 CTAs per SM instead of 5, the lanes per SM stay the same); in between the full
-// slice lets every lane of the warp have a session.
+// (tools/slash_lab.py --slice): 7040 B lets 8 CTAs live on an SM (the register limit) and is the best
+// size whenever it still gives every lane a session, and again for sessions so large that a warp holds only a
+// few whatever the slice; in between the slice grows just enough for 32 average sessions (6 or 5 CTAs per SM).
 uint32_t auto_lane_slice(uint64_t n_sessions, uint64_t n_agents, uint64_t n_records)
 {
-    constexpr uint64_t SMALL = 7168;
+    constexpr uint64_t SMALL = 7040, MID = 9216;
     if (n_records == UINT64_MAX || n_sessions == 0) return LANE_SMEM_PER_WARP;   // records not known to the host
     const uint64_t avg = lane_group_bytes((n_agents + n_sessions - 1) / n_sessions, (n_records + n_sessions - 1) / n_sessions);
     if (32 * avg <= SMALL) return (uint32_t)SMALL;
+    if (32 * avg <= MID) return (uint32_t)MID;
     if (32 * avg <= LANE_SMEM_PER_WARP) return LANE_SMEM_PER_WARP;
     if (4 * avg <= SMALL) return (uint32_t)SMALL;
     return LANE_SMEM_PER_WARP;

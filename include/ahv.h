@@ -462,8 +462,8 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "slash_variant" 0/1/2 slashing: lane per small session + warp per larger one (default 0) / warp per session on
  *                   global memory only (1) / warp per session, staged in shared memory where it fits (2)
  *   "slash_slice" 0,1024..10752  slashing, lane kernel: bytes of shared memory per warp (multiple of 16).  0 (default):
- *                   ahv_slash_cascade picks 7168 or 10752 from the batch's average session size; ahv_slash_cascade_dev,
- *                   which does not know the record count, uses 10752 (set 7168 for sessions above ~16 agents x 48 records)
+ *                   ahv_slash_cascade picks 7040, 9216 or 10752 from the batch's average session size; ahv_slash_cascade_dev,
+ *                   which does not know the record count, uses 10752 (set 7040 for sessions above ~16 agents x 48 records)
  *   "sigma_variant" 0/1/2 sigma_eff: one row per thread from global memory / tiled through shared memory (default 1) /
  *                   persistent CTAs with a two-stage pipeline (2; measured slower, kept for comparison)
  *   "sigma_exact" 0/1   sigma_eff: 1 = every row summed left to right like the reference (bit-identical, but one very long

@@ -144,11 +144,11 @@ def test_large_batch_and_giant_session_vs_c_restatement(ctx, variant):
     assert_same_outputs(run_gpu(ctx, small), py, small)
 
 
-@pytest.mark.parametrize("slice_bytes", [0, 1024, 2064, 7168, 10752])
+@pytest.mark.parametrize("slice_bytes", [0, 1024, 2064, 7040, 10752])
 def test_lane_slice_sizes(ctx, slice_bytes):
     """k_slash_lanes with every size of its per-warp shared-memory slice (0 = chosen from the batch's average
     session): the runs of sessions a warp stages are cut differently, the records must not change.  The
-    mid-size workload shape (32 agents x 256 records a session, where the auto choice is the 7 KB slice) and a
+    mid-size workload shape (32 agents x 256 records a session, where the auto choice is the 7040-byte slice) and a
     ragged batch whose sessions fall on both sides of every slice."""
     import workloads
     ctx.set_option("slash_slice", slice_bytes)

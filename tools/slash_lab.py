@@ -28,11 +28,13 @@ def host_entry_slice(S, A, E):
     """The slice ahv_slash_cascade (host entry, which knows E) picks for a batch - auto_lane_slice in
     csrc/ahv_slashing.cu; this tool times ahv_slash_cascade_dev on resident arrays and sets the same value."""
     avg = 11 * -(-A // S) + 2 * -(-E // S) + 16
-    if 32 * avg <= 7168:
-        return 7168
+    if 32 * avg <= 7040:
+        return 7040
+    if 32 * avg <= 9216:
+        return 9216
     if 32 * avg <= 10752:
         return 10752
-    return 7168 if 4 * avg <= 7168 else 10752
+    return 7040 if 4 * avg <= 7040 else 10752
 
 
 def run(name, b, cpu=True):
@@ -108,7 +110,8 @@ run(f"{S} sessions x 16 agents x 48 records, omega 0.95", workloads.slash_sessio
 run(f"{S} sessions x 16 agents x 48 records, omega 0.5 (no cascades)", workloads.slash_sessions(S, 16, 48, omega=0.5))
 run(f"{S // 4} sessions x 64 agents x 512 records, omega 0.95", workloads.slash_sessions(S // 4, 64, 512))
 run(f"{S // 2} sessions x 32 agents x 256 records, omega 0.95", workloads.slash_sessions(S // 2, 32, 256))
-run(f"{S // 8} sessions x 128 agents x 1024 records, omega 0.95 (warp per session)", workloads.slash_sessions(S // 8, 128, 1024))
+run(f"{S // 8} sessions x 128 agents x 1024 records, omega 0.95 (3 sessions per warp slice)", workloads.slash_sessions(S // 8, 128, 1024))
+run(f"{S // 16} sessions x 256 agents x 2048 records, omega 0.95 (warp per session)", workloads.slash_sessions(S // 16, 256, 2048))
 run("one session x 1e5 agents x 1e6 records, omega 0.95", workloads.slash_sessions(1, 100_000, 1_000_000))
 if args.out:
     with open(os.path.join(ROOT, args.out), "w") as f:
