@@ -1199,11 +1199,14 @@ int ahv_chain_capture_dev(ahv_ctx *ctx, uint8_t *d_arena, uint64_t arena_bytes, 
     if (S == 0 || n == 0) return AHV_OK;
     // one lane per session: with fewer lanes than the chip can keep busy a lane's dependency chain is what
     // counts, and the plain-addition form has the shorter one.
-    // sessions per warp: 32.  Spreading few sessions over more warps (option chain_lanes) was measured slower at every
-    // count (10^4 sessions x 1000: 17 / 24 / 38 ms with 16 / 8 / 4 lanes against 14 with 32, before the changes of
-    // round 2): a warp instruction occupies its scheduler's integer pipe for two cycles whatever the number of
-    // active lanes, so the pass is bound by warp instructions, and a chain already issues one every ~3.8 cycles
-    uint64_t lpw = ctx->opt_chain_lanes ? (uint64_t)ctx->opt_chain_lanes : 32;
+    // Sessions per warp: as few as keep the number of warps within the number of warp schedulers (4 per SM).  A
+    // warp instruction occupies its scheduler's integer pipe for two cycles whatever the number of active lanes, so
+    // thinner warps do not run their chains faster by themselves - two warps on one scheduler take turns, which
+    // doubles the time (10^4 sessions x 1000: 9.3 ms with 17 lanes = 589 warps, 14.1 with 16 = 625 warps on 592
+    // schedulers) - but every load and store of a thinner warp touches fewer lines (10^3 sessions: 8.7 ms with 32
+    // lanes, 7.7 with 2).  Option chain_lanes fixes the number.
+    const uint64_t schedulers = 4ull * (uint64_t)ctx->sm_count;
+    uint64_t lpw = ctx->opt_chain_lanes ? (uint64_t)ctx->opt_chain_lanes : (S + schedulers - 1) / schedulers;
     lpw = lpw < 1 ? 1 : (lpw > 32 ? 32 : lpw);
     const uint64_t warps = (S + lpw - 1) / lpw;
     const unsigned g = grid_for(warps * 32, 64);

@@ -451,8 +451,8 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *   "block" 64/128/256  threads per block of the leaf kernels (default 128)
  *   "fixed_variant" 0/1/2 fixed-size leaf kernel: direct 16-byte loads (default) / cp.async staged / TMA bulk-copy staged
  *   "compress" 0/1      plain additions / scaled-sum compression with additions on the FMA pipe (default 1)
- *   "chain_lanes" 0..32 chained capture: sessions per warp (0 = 32; fewer spreads the sessions over more warps - measured
- *                   slower at every session count, kept for the experiment)
+ *   "chain_lanes" 0..32 chained capture: sessions per warp (0, default: as few as keep the warps within the number of
+ *                   warp schedulers - thinner warps touch fewer lines per load, but two warps on one scheduler take turns)
  *   "chain_prefix" 0/1/2  chained capture: the blocks in front of each delta's parent field are hashed in a parallel
  *                   pre-pass: never / for up to 2^16 sessions, where the length of a chain bounds the pass (default 1) /
  *                   always (2).  Needs out_digests, where the intermediate states are parked

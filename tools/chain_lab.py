@@ -14,7 +14,7 @@ for S, L in ((10000, 1000), (100000, 100), (1000, 1000)):
     d = {k: ctx.dev_alloc(v) for k, v in dict(arena=n * 256 + 16, offs=offs.nbytes, hp=hexpos.nbytes, rp=rp.nbytes,
                                               digs=32 * n, par=32 * n, kind=n).items()}
     ctx.h2d(d["offs"], offs); ctx.h2d(d["hp"], hexpos); ctx.h2d(d["rp"], rp)
-    for lanes in (0, 32, 16, 8, 4, 2, 1):                       # sessions per warp (0 = the library's choice)
+    for lanes in (0, 32, 24, 17, 16, 8, 4, 2, 1):                       # sessions per warp (0 = the library's choice)
         ctx.set_option("chain_lanes", lanes)
         best = 1e9
         for rep in range(3):
