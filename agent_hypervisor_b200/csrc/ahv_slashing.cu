@@ -16,18 +16,17 @@
 // stack over the clip log, which doubles as the output.
 //
 // The cascade is a chain of dependent look-ups (row bounds -> records -> scores -> next row ...), a DRAM
-// round trip each when done in global memory.  A session whose state fits the warp's slice of shared
-// memory (13 B per agent + 17 B per record) is therefore STAGED first: one coalesced read of its rows,
-// records and scores, the whole cascade out of shared memory, one write-back of what changed.  Larger
-// sessions run the same code on global memory (GlobalView), where rows are long enough to keep the lanes
-// busy.  Both views produce the same records.
+// round trip each when done in global memory.  The warp kernel has two views of a session: staged in its
+// warp's slice of shared memory when it fits (13 B per agent + 17 B per record; slash_variant 2 only, see
+// below) and on global memory (GlobalView), where rows are long enough to keep the lanes busy and the
+// number of resident warps hides the latency.  Both views produce the same records.
 //
-// Small sessions (a handful of records per row) would leave most of a warp's lanes idle, so k_slash_lanes
-// runs first: a warp takes 32 consecutive sessions, cuts them into runs that fit its slice of shared memory
-// (11 B per agent + 2 B per record), stages a run's contiguous rows, records and scores with coalesced
-// reads, then every lane walks ITS session serially out of shared memory - the reference's loop as
-// written - and the warp writes back what changed.  Sessions so large that fewer than two fit a slice
-// are listed for k_slash_cascade, which then only visits that list.
+// Small and mid-size sessions (a handful of records per row) would leave most of a warp's lanes idle, so
+// k_slash_lanes runs first: a warp takes 32 consecutive sessions, cuts them into runs that fit its slice of
+// shared memory (11 B per agent + 2 B per record), stages a run's contiguous rows, records and scores with
+// coalesced reads, then every lane walks ITS session serially out of shared memory (LaneRun in
+// slashing_core.cuh) and the warp writes back what changed.  Sessions so large that fewer than two fit a
+// slice are listed for k_slash_cascade, which then only visits that list, on global memory.
 #include "ahv_internal.cuh"
 #include "slashing_core.cuh"
 
