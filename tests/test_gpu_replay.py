@@ -132,6 +132,51 @@ def test_device_packer_is_byte_identical_to_the_host_packer(audit_golden):
             ctx.dev_free(p)
 
 
+def test_device_packer_long_batch_offsets():
+    """More deltas than the packer's one-CTA prefix scan handles (8 tiles of 4096): the three-launch scan must give
+    the host packer's offsets and bytes - 70 001 benchmark-shaped deltas with digits of every width in their ids."""
+    from agent_hypervisor_b200 import get_context
+    from agent_hypervisor_b200.audit.packing import (_str_col, column_bytes, device_columns_struct, pack_columns,
+                                                     stage_columns)
+    ctx = get_context()
+    n = 70001
+    idx = np.arange(n)
+    cols = {
+        "n": n,
+        "delta_id": _str_col([f"delta:{i}" for i in idx]),
+        "session_id": _str_col([f"session:{i // 1000:08d}" for i in idx]),
+        "agent_did": _str_col(["did:mesh:a" + "x" * (i % 7) for i in idx]),
+        "turn_id": (idx % 1000 + 1).astype(np.int64),
+        "timestamp_us": (1_767_225_600_000_000 + idx * 1_000_003).astype(np.int64),
+        "timestamp_utcoffset_s": np.zeros(n, np.int32),
+        "parent_kind": np.where(idx % 1000 == 0, 0, 1).astype(np.uint8),
+        "parent_digest": np.random.default_rng(5).integers(0, 256, 32 * n, dtype=np.uint8),
+        "parent_other": _str_col([""] * n),
+        "change_rowptr": np.arange(n + 1, dtype=np.uint64),
+        "change_path": _str_col([f"/f{i}" for i in idx]),
+        "change_op": _str_col(["add"] * n),
+        "change_content": _str_col([f"h{i}" for i in idx]),
+        "change_prev": _str_col([None] * n),
+    }
+    want_arena, want_offs, want_pos = pack_columns(cols, want_parent_pos=True)
+    stage = ctx.host_alloc(column_bytes(cols))
+    layout, used = stage_columns(cols, stage)
+    d_cols, d_offs, d_pos = ctx.dev_alloc(used), ctx.dev_alloc(8 * (n + 1)), ctx.dev_alloc(4 * n)
+    d_arena = ctx.dev_alloc(len(want_arena) + 64)
+    try:
+        ctx.h2d(d_cols, stage[:used])
+        st = device_columns_struct(n, layout, d_cols)
+        ctx.pack_deltas_dev(st, d_offs, d_arena, len(want_arena), d_pos)
+        got_arena, got_offs = np.empty(len(want_arena), np.uint8), np.empty(n + 1, np.uint64)
+        ctx.d2h(got_arena, d_arena); ctx.d2h(got_offs, d_offs); ctx.sync()
+        assert np.array_equal(got_offs, want_offs)
+        assert np.array_equal(got_arena, want_arena)
+    finally:
+        ctx.host_free(stage)
+        for p in (d_cols, d_offs, d_pos, d_arena):
+            ctx.dev_free(p)
+
+
 def test_device_replay_matches_the_host_packer_pipeline():
     from agent_hypervisor_b200 import DeviceReplay, ReplayPipeline
     from agent_hypervisor_b200.audit.packing import canonical_preimage, column_bytes
