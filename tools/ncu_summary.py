@@ -13,13 +13,15 @@ KEYS = [("gpu__time_duration.sum", "duration"), ("dram__bytes_read.sum", "DRAM r
         ("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "ALU pipe %"),
         ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "FMA pipe %"),
         ("sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active", "FP64 pipe %"),
+        ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "LSU pipe %"),
+        ("smsp__thread_inst_executed_per_inst_executed.ratio", "threads per warp instruction"),
         ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue slots %"),
         ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps active %"),
         ("launch__registers_per_thread", "registers"), ("launch__grid_size", "grid"), ("launch__block_size", "block"),
         ("launch__shared_mem_per_block_dynamic", "dyn smem / CTA"), ("smsp__inst_executed.sum", "warp instructions"),
         ("lts__t_sector_hit_rate.pct", "L2 hit %")]
 lines = [f"# ncu --set full, {tag} (B200, --clock-control none; cold-cache, serialised launches)\n"]
-for name in ("sigma", "var", "chain", "tree"):
+for name in ("sigma", "var", "chain", "tree", "slash_mid"):
     rep = os.path.join(ROOT, "gpurun_out", f"prof_{tag}_{name}.ncu-rep")
     kept = os.path.join(outdir, f"prof_{name}_raw.csv")
     if os.path.exists(rep):
