@@ -301,16 +301,34 @@ __global__ void k_len_hist(const uint64_t *__restrict__ offsets, uint64_t n, uin
         if (sh[k]) atomicAdd(&hist[k], sh[k]);
 }
 
-// cursor[b] = number of messages in bins > b  (longest first)
-__global__ void k_bin_scan(const uint32_t *__restrict__ hist, uint32_t *__restrict__ cursor)
+// cursor[b] = number of messages in bins > b  (longest first).  One CTA, one thread per bin: thread t takes bin
+// NBINS-1-t, so the exclusive prefix sum over t is the count in the longer bins.  (One thread walking the 1024
+// bins took 25 us - a dependent global load per bin - which showed in every chunk of a replay.)
+__global__ void __launch_bounds__(NBINS)
+k_bin_scan(const uint32_t *__restrict__ hist, uint32_t *__restrict__ cursor)
 {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        uint32_t acc = 0;
-        for (int b = NBINS - 1; b >= 0; --b) {
-            cursor[b] = acc;
-            acc += hist[b];
-        }
+    static_assert(NBINS == 1024, "one warp of warp totals");
+    __shared__ uint32_t warp_sum[32];
+    const uint32_t t = threadIdx.x, lane = t & 31u, wid = t >> 5;
+    const uint32_t b = (uint32_t)NBINS - 1u - t;
+    const uint32_t v = hist[b];
+    uint32_t x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= (uint32_t)o) x += y;
     }
+    if (lane == 31) warp_sum[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t ws = warp_sum[lane];
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, ws, o);
+            if (lane >= (uint32_t)o) ws += y;
+        }
+        warp_sum[lane] = ws;
+    }
+    __syncthreads();
+    cursor[b] = (wid ? warp_sum[wid - 1] : 0u) + x - v;
 }
 
 __global__ void k_len_scatter(const uint64_t *__restrict__ offsets, uint64_t n, uint32_t *__restrict__ cursor,
@@ -874,7 +892,7 @@ int run_leaves(ahv_ctx *ctx, const uint8_t *d_arena, const uint64_t *d_offsets, 
         unsigned g = (unsigned)(gfull < gmax ? gfull : gmax);
         k_len_hist<<<g, 256, 0, ctx->stream>>>(d_offsets, n, hist);
         AHV_CHECK_LAUNCH(ctx);
-        k_bin_scan<<<1, 32, 0, ctx->stream>>>(hist, cursor);
+        k_bin_scan<<<1, NBINS, 0, ctx->stream>>>(hist, cursor);
         AHV_CHECK_LAUNCH(ctx);
         k_len_scatter<<<grid_for(n, 256), 256, 0, ctx->stream>>>(d_offsets, n, cursor, p);
         AHV_CHECK_LAUNCH(ctx);
