@@ -11,6 +11,9 @@
 // is a few percent of peak.  One message (or one tree node) per thread, schedule in
 // registers, 16-byte vector loads; see DESIGN.md for the per-kernel rooflines.
 #include "ahv_internal.cuh"
+#include "scan.cuh"
+
+using namespace ahv::scan;
 #include "sha256_core.cuh"
 
 using namespace ahv;
@@ -369,6 +372,21 @@ __global__ void k_max_session(const uint64_t *__restrict__ rowptr, uint64_t S, u
     if ((threadIdx.x & 31) == 0 && v) atomicMax(out, v);
 }
 
+// Many sessions: the per-level node counts are written by one thread per (session, level) and turned into row
+// pointers by the tiled scan (scan.cuh); k_level_rowptrs below - one CTA per level - is for short session lists
+// (10^6 sessions: 1.04 ms there).
+__global__ void __launch_bounds__(256)
+k_level_counts(const uint64_t *__restrict__ rowptr, uint64_t S, uint64_t *__restrict__ lvl_rp /* L*(S+1) */)
+{
+    const uint32_t l = blockIdx.y + 1;
+    uint64_t *rp = lvl_rp + (uint64_t)blockIdx.y * (S + 1);
+    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    const uint64_t nn = rowptr[s + 1] - rowptr[s];
+    rp[s + 1] = (nn + ((1ull << l) - 1ull)) >> l;
+    if (s == 0) rp[0] = 0;
+}
+
 // per-level CSR: lvl_rp[l-1][s] = sum_{s'<s} ceil(n_s' / 2^l) for l = 1..L ; one block per level
 __global__ void __launch_bounds__(1024)
 k_level_rowptrs(const uint64_t *__restrict__ rowptr, uint64_t S, uint64_t *__restrict__ lvl_rp /* L*(S+1) */)
@@ -525,6 +543,46 @@ k_merkle_top(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const 
         for (int q = 0; q < 8; ++q) d[q] = buf[cur][0][q];
         store_digest(roots + 32 * s, d);
     }
+}
+
+// Same finish, one THREAD per session, for levels of <= 2 nodes: what is left when there are so many sessions
+// that the global level steps run to the end (tree_top = 2).  A warp per session would hash one node with one
+// lane (10^6 sessions: 5.5 ms; 0.2 ms here).
+template <bool UNIFORM, bool SC>
+__global__ void __launch_bounds__(128)
+k_merkle_top_lane(const uint8_t *__restrict__ in, uint64_t S, uint32_t c_in_u, const uint64_t *__restrict__ rp_in,
+                  uint8_t *__restrict__ roots, uint8_t *__restrict__ empty, uint32_t rc, uint32_t *__restrict__ status)
+{
+    const typename Pol<SC>::type cp = Pol<SC>::make(rc);
+    const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    uint64_t in0;
+    uint32_t c;
+    if (UNIFORM) {
+        in0 = s * c_in_u;
+        c = c_in_u;
+    } else {
+        in0 = rp_in[s];
+        c = (uint32_t)(rp_in[s + 1] - in0);
+    }
+    uint32_t d[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (c == 0 || c > 2u) {                               // c > 2: see k_merkle_top
+        store_digest(roots + 32 * s, d);
+        if (empty) empty[s] = (c == 0) ? 1 : 0;
+        if (c) atomicOr(status, AHV_STATUS_MAX_LEAVES);
+        return;
+    }
+    if (empty) empty[s] = 0;
+    uint32_t l[8];
+    load_digest(in + 32 * in0, l);
+    if (c == 1) {
+        store_digest(roots + 32 * s, l);
+        return;
+    }
+    uint32_t r[8];
+    load_digest(in + 32 * (in0 + 1), r);
+    merkle_node(l, r, d, cp);
+    store_digest(roots + 32 * s, d);
 }
 
 // Same finish, one WARP per session (4 sessions per CTA) for levels of <= 64 nodes: no idle
@@ -929,7 +987,7 @@ uint64_t tree_scratch_bytes(const ahv_ctx *ctx, uint64_t n, uint64_t S, uint64_t
     const uint32_t G = global_levels(ctx, S, max_leaves);
     if (G == 0) return 0;
     uint64_t b = 2 * pad256(32ull * (n / 2 + S + 1));
-    if (!uniform) b += pad256(8ull * G * (S + 1));
+    if (!uniform) b += pad256(8ull * G * (S + 1)) + scan_scratch_bytes(S, G) + 256;
     return b;
 }
 
@@ -953,7 +1011,11 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
             set_error("internal: scratch too small for tree levels");
             return AHV_E_NOMEM;
         }
-        if (!uniform) {
+        if (!uniform && S > 8ull * SCAN_TILE) {
+            k_level_counts<<<dim3(grid_for(S, 256), G), 256, 0, ctx->stream>>>(d_rowptr, S, lvl_rp);
+            AHV_CHECK_LAUNCH(ctx);
+            AHV_TRY(scan_u64_inplace(ctx, lvl_rp, S, G, S + 1, /*reserve=*/false));
+        } else if (!uniform) {
             k_level_rowptrs<<<G, 1024, 0, ctx->stream>>>(d_rowptr, S, lvl_rp);
             AHV_CHECK_LAUNCH(ctx);
         }
@@ -981,7 +1043,13 @@ int run_tree(ahv_ctx *ctx, const uint8_t *d_digests, const uint64_t *d_rowptr, u
         set_error("more than 2^31 - 1 sessions with an in-CTA tree finish (top_max > 64); use top_max <= 64 or split the batch");
         return AHV_E_TOOLARGE;
     }
-    if (top <= 64) {
+    if (top <= 2) {
+        const unsigned g = grid_for(S, 128);
+        if (uniform && sc) k_merkle_top_lane<true, true><<<g, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);
+        else if (uniform) k_merkle_top_lane<true, false><<<g, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);
+        else if (sc) k_merkle_top_lane<false, true><<<g, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc, ctx->status_d);
+        else k_merkle_top_lane<false, false><<<g, 128, 0, ctx->stream>>>(cur, S, 0, rp_cur, d_roots, d_empty, rc, ctx->status_d);
+    } else if (top <= 64) {
         const unsigned g4 = (unsigned)((S + 3) / 4);
         if (uniform && sc) k_merkle_top_warp<true, true><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);
         else if (uniform) k_merkle_top_warp<true, false><<<g4, 128, 0, ctx->stream>>>(cur, S, c_cur, nullptr, d_roots, d_empty, rc, ctx->status_d);

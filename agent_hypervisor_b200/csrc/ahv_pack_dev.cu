@@ -11,6 +11,9 @@
 // each lane's delta (a few instructions per output byte).
 #include "ahv_internal.cuh"
 #include "pack_core.cuh"
+#include "scan.cuh"
+
+using namespace ahv::scan;
 
 using namespace ahv;
 using namespace ahv_pack;
@@ -28,81 +31,6 @@ k_pack_sizes(const Cols c, uint64_t *__restrict__ offsets, uint32_t *__restrict_
     if (i == 0) offsets[0] = 0;
     // a position past 4 GiB cannot be stored: UINT32_MAX - 1 is never a valid one, so it reads as "other"
     if (ppos) ppos[i] = pp == 0xffffffffull ? 0xffffffffu : (uint32_t)(pp < 0xfffffffeull ? pp : 0xfffffffeull);
-}
-
-// Prefix sums in place: a[1..n] (lengths) -> inclusive prefix sums, a[0] stays 0.
-// A CTA of 1024 threads handles a tile of 4096 consecutive elements (4 per thread): thread totals are scanned
-// with shuffles inside each warp, the 32 warp totals by warp 0.  scan_tile returns, in every thread, the sum
-// of the tile; with WRITE it also stores carry + the inclusive prefix of every element.
-constexpr int SCAN_THREADS = 1024, SCAN_PER = 4, SCAN_TILE = SCAN_THREADS * SCAN_PER;
-
-template <bool WRITE>
-__device__ __forceinline__ uint64_t scan_tile(uint64_t *__restrict__ a, uint64_t n, uint64_t base, uint64_t carry,
-                                              uint64_t *warp_sum)
-{
-    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-    const uint64_t i0 = base + (uint64_t)threadIdx.x * SCAN_PER;
-    uint64_t v[SCAN_PER], t = 0;
-#pragma unroll
-    for (int k = 0; k < SCAN_PER; ++k) {
-        v[k] = (i0 + k <= n) ? a[i0 + k] : 0;
-        t += v[k];
-    }
-    uint64_t x = t;                                          // inclusive scan of the threads' totals
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
-        if (lane >= (uint32_t)o) x += y;
-    }
-    if (lane == 31) warp_sum[wid] = x;
-    __syncthreads();
-    if (wid == 0) {
-        uint64_t ws = warp_sum[lane];
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint64_t y = __shfl_up_sync(0xffffffffu, ws, o);
-            if (lane >= (uint32_t)o) ws += y;
-        }
-        warp_sum[lane] = ws;
-    }
-    __syncthreads();
-    const uint64_t total = warp_sum[31];
-    if (WRITE) {
-        uint64_t run = carry + (wid ? warp_sum[wid - 1] : 0) + (x - t);
-#pragma unroll
-        for (int k = 0; k < SCAN_PER; ++k) {
-            run += v[k];
-            if (i0 + k <= n) a[i0 + k] = run;
-        }
-    }
-    __syncthreads();                                         // warp_sum is reused by the caller's next tile
-    return total;
-}
-
-// one CTA walks the whole array (short arrays, and the tile totals of a long one)
-__global__ void __launch_bounds__(SCAN_THREADS)
-k_scan_u64(uint64_t *__restrict__ a, uint64_t n)
-{
-    __shared__ uint64_t warp_sum[32];
-    uint64_t carry = 0;
-    for (uint64_t base = 1; base <= n; base += SCAN_TILE) carry += scan_tile<true>(a, n, base, carry, warp_sum);
-}
-
-// long arrays, three launches: tile totals -> their prefix sums (k_scan_u64) -> every tile scanned with its carry
-__global__ void __launch_bounds__(SCAN_THREADS)
-k_scan_tile_totals(uint64_t *__restrict__ a, uint64_t n, uint64_t *__restrict__ totals)
-{
-    __shared__ uint64_t warp_sum[32];
-    const uint64_t t = scan_tile<false>(a, n, 1 + (uint64_t)blockIdx.x * SCAN_TILE, 0, warp_sum);
-    if (threadIdx.x == 0) {
-        totals[1 + blockIdx.x] = t;
-        if (blockIdx.x == 0) totals[0] = 0;
-    }
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS)
-k_scan_tiles(uint64_t *__restrict__ a, uint64_t n, const uint64_t *__restrict__ totals)
-{
-    __shared__ uint64_t warp_sum[32];
-    scan_tile<true>(a, n, 1 + (uint64_t)blockIdx.x * SCAN_TILE, totals[blockIdx.x], warp_sum);
 }
 
 // Pass 2.  The 32 deltas of a warp are neighbours in the arena, so the warp's output is ONE contiguous byte range:
@@ -191,21 +119,7 @@ extern "C" int ahv_pack_deltas_dev(ahv_ctx *ctx, const ahv_delta_columns *cols, 
     if (!((flags & AHV_PACK_OFFSETS_VALID) && d_out_arena)) {
         k_pack_sizes<<<grid_for(n, 256), 256, 0, ctx->stream>>>(c, d_out_offsets, d_out_parent_pos);
         AHV_CHECK_LAUNCH(ctx);
-        const uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-        if (tiles <= 8) {
-            k_scan_u64<<<1, SCAN_THREADS, 0, ctx->stream>>>(d_out_offsets, n);
-            AHV_CHECK_LAUNCH(ctx);
-        } else {
-            AHV_TRY(scratch_reserve(ctx, 8 * (tiles + 1) + 256));
-            uint64_t *totals = (uint64_t *)scratch_take(ctx, 8 * (tiles + 1));
-            AHV_REQUIRE(totals, "internal: scratch too small for the scan");
-            k_scan_tile_totals<<<(unsigned)tiles, SCAN_THREADS, 0, ctx->stream>>>(d_out_offsets, n, totals);
-            AHV_CHECK_LAUNCH(ctx);
-            k_scan_u64<<<1, SCAN_THREADS, 0, ctx->stream>>>(totals, tiles);
-            AHV_CHECK_LAUNCH(ctx);
-            k_scan_tiles<<<(unsigned)tiles, SCAN_THREADS, 0, ctx->stream>>>(d_out_offsets, n, totals);
-            AHV_CHECK_LAUNCH(ctx);
-        }
+        AHV_TRY(scan_u64_inplace(ctx, d_out_offsets, n, 1, 0));
     }
     if (d_out_arena) {
         const size_t smem = (size_t)(PACK_THREADS / 32) * (PACK_WARP_SLOT + 16);

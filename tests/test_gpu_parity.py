@@ -232,6 +232,25 @@ def _merkle_sizes(ctx):
     assert np.array_equal(roots[:40], pr) and np.array_equal(empty[:40], pe)
 
 
+def test_merkle_many_small_sessions(ctx):
+    """More sessions than the one-CTA row-pointer scan is used for (8 tiles of 4096): per-level node counts + the
+    tiled scan, every global level down to width 2, the thread-per-session finish - ragged (0..12 leaves, empties
+    included) and uniform - against the C oracle."""
+    rng = np.random.default_rng(8)
+    S = 40_001
+    sizes = rng.integers(0, 13, S)
+    rp = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+    digs = rng.integers(0, 256, (int(rp[-1]), 32), dtype=np.uint8)
+    roots, empty = ctx.merkle_roots(digs, rp)
+    wr, we = co.merkle_roots(digs, rp)
+    assert np.array_equal(empty, we) and np.array_equal(roots, wr)
+    rp3 = (np.arange(S + 1, dtype=np.uint64) * 3)
+    d3 = digs[: 3 * S]
+    r3, e3 = ctx.merkle_roots(d3, rp3)
+    w3, _ = co.merkle_roots(d3, rp3)
+    assert np.array_equal(r3, w3) and not e3.any()
+
+
 def test_merkle_single_big_tree(ctx):
     rng = np.random.default_rng(6)
     n = 100_003
