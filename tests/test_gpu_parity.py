@@ -958,6 +958,27 @@ def test_host_entries_reject_decreasing_offsets(ctx):
     roots = np.zeros((1, 32), np.uint8)
     assert ctx.lib.ahv_commit(ctx.h, vp(a.ctypes.data), vp(offs.ctypes.data), 0, vp(rp.ctypes.data), 1, 0, None,
                               vp(roots.ctypes.data), None) == -1
+    # the pipelined audit call checks its offsets chunk by chunk: a bad pair in a late chunk, and offsets that run
+    # past the arena's end before coming back, are both refused (and a good batch of the same shape passes)
+    S, L, FL = 12000, 1, 1024                                          # one-delta sessions: no parent, every chain verifies
+    n = S * L
+    big = ctx.host_alloc(n * FL); big[:] = 32
+    good = (np.arange(n + 1, dtype=np.uint64) * FL)
+    rp2 = (np.arange(S + 1, dtype=np.uint64) * L)
+    pos = np.full(n, 0xFFFFFFFF, np.uint32)
+    o = dict(roots=np.zeros(32 * S, np.uint8), verdict=np.zeros(S, np.uint8))
+
+    def call(offsets):
+        return ctx.lib.ahv_audit_sessions(ctx.h, vp(big.ctypes.data), vp(offsets.ctypes.data), 0, None, None, vp(pos.ctypes.data),
+                                          vp(rp2.ctypes.data), S, 0, None, None, vp(o["roots"].ctypes.data), None,
+                                          vp(o["verdict"].ctypes.data), None, None)
+    assert call(good) == 0 and o["verdict"].all()
+    bad = good.copy(); bad[n - 100] = bad[n - 101] - 1
+    assert call(bad) == -1 and b"non-decreasing" in ctx.lib.ahv_last_error()
+    bad = good.copy(); bad[50:60] += np.uint64(1 << 40)
+    assert call(bad) == -1 and b"non-decreasing" in ctx.lib.ahv_last_error()
+    assert call(good) == 0 and o["verdict"].all()                      # the context is still usable
+    ctx.host_free(big)
 
 
 def test_reads_stop_at_the_end_of_the_allocation(ctx):
