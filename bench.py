@@ -517,7 +517,7 @@ def run_cuda(args):
         step()
     ctx.sync()
     sampler = ClockSampler(local)
-    if rank == 0 and not args.no_clocks:
+    if not args.no_clocks:                     # every rank watches ITS GPU: one throttled GPU slows every step of all ranks
         sampler.start()
         time.sleep(0.1)
     ctx.sync(); ctx.barrier(); ctx.sync()      # every rank enters the timed region together
@@ -534,14 +534,28 @@ def run_cuda(args):
     launches = ctx.launch_count() - launches0
     ctx.set_option("leaf_timer", 0)
     ctx.barrier()
+    ms_own = ms_total
     ms_total = max_over_ranks(ms_total)
     if world > 1:
         launches = int(ctx.comm_all_gather(np.array([launches], np.int64)).sum())
-    clocks = None
-    if rank == 0:
-        time.sleep(0.15)
-        sampler.stop()
-        clocks = sampler.summary(t_wall0, t_wall1)
+    time.sleep(0.15)
+    sampler.stop()
+    clocks = sampler.summary(t_wall0, t_wall1)
+    if world > 1:
+        rnames = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        mask = sum(1 << i for i, nm in enumerate(rnames) if nm in clocks["reasons"])
+        other = (1 << 8) if any(r_ not in rnames for r_ in clocks["reasons"]) else 0
+        mine = np.array([clocks["sm_mhz"] or 0.0, float(mask | other), clocks.get("power_w_max") or 0.0, ms_own], np.float64)
+        allr = ctx.comm_all_gather(mine).reshape(world, 4)
+        if rank == 0:
+            clocks["per_rank_sm_mhz"] = [float(x) for x in allr[:, 0]]
+            clocks["sm_mhz"] = float(allr[:, 0].min())                        # the slowest GPU is the one that counts
+            union = int(np.bitwise_or.reduce(allr[:, 1].astype(np.int64)))
+            clocks["reasons"] = [nm for i, nm in enumerate(rnames) if union >> i & 1] + (["clock sampling unavailable on a rank"] if union >> 8 & 1 else [])
+            clocks["per_rank_power_w_max"] = [float(x) for x in allr[:, 2]]
+            clocks["per_rank_ms_total"] = [float(x) for x in allr[:, 3]]
+    if rank != 0:
+        clocks = None
 
     # leaf-kernel launch durations recorded live inside the timed region (CUDA events on the ctx stream)
     n_leaf = min(16, 2 * args.steps)
