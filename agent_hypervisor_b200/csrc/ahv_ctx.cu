@@ -176,6 +176,8 @@ int ahv_create(int device, ahv_ctx **out_ctx)
     c->opt_slash_variant = 0;
     c->opt_slash_slice = 0;
     c->opt_chain_prefix = 1;
+    c->opt_sigma_rows = 0;
+    c->sigma_edges_hint = 0;
     c->opt_blocking_sync = 0;
     *out_ctx = c;
     return AHV_OK;
@@ -368,6 +370,9 @@ int ahv_set_option(ahv_ctx *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "slash_variant")) {
         AHV_REQUIRE(value >= 0 && value <= 2, "slash_variant must be 0, 1 or 2");
         ctx->opt_slash_variant = value;
+    } else if (!strcmp(key, "sigma_rows")) {
+        AHV_REQUIRE(value == 0 || (value >= 1 && value <= 128 && (value & (value - 1)) == 0), "sigma_rows must be 0 or a power of two up to 128");
+        ctx->opt_sigma_rows = value;
     } else if (!strcmp(key, "chain_prefix")) {
         AHV_REQUIRE(value >= 0 && value <= 2, "chain_prefix must be 0, 1 or 2");
         ctx->opt_chain_prefix = value;

@@ -497,7 +497,10 @@ int ahv_sigma_eff_rings(ahv_ctx *ctx, const uint32_t *rowptr, const double *bond
     uint8_t *d_od = st.out(out_demote, A);
     uint8_t *d_on = st.out(out_near, A);
     if (st.rc != AHV_OK) return st.rc;
-    AHV_TRY(ahv_sigma_eff_rings_dev(ctx, d_rp, d_b, d_a, d_e, now, d_s, d_o, d_c, d_r, A, d_os, d_or, d_od, d_on));
+    ctx->sigma_edges_hint = E;                    // known here: the tiled kernel sizes its tiles for the average row
+    const int rc_dev = ahv_sigma_eff_rings_dev(ctx, d_rp, d_b, d_a, d_e, now, d_s, d_o, d_c, d_r, A, d_os, d_or, d_od, d_on);
+    ctx->sigma_edges_hint = 0;
+    AHV_TRY(rc_dev);
     st.back(out_sigma, d_os, A);
     st.back(out_ring, d_or, A);
     st.back(out_demote, d_od, A);

@@ -37,6 +37,8 @@ struct ahv_ctx {
     int64_t opt_block;         // threads per block for SHA kernels (default 128)
     int64_t opt_fixed_variant; // 0: direct LDG.128, 1: smem-staged (cp.async)
     int64_t opt_blocking_sync; // 1: ahv_audit_sessions sleeps on an event instead of spinning while the pipeline drains (default 0)
+    int64_t opt_sigma_rows;    // sigma_eff, tiled kernel: rows per tile (power of two, 1..128); 0 = from the average row length
+    uint64_t sigma_edges_hint; // set by the host entry around its call of the _dev entry: number of vouch records (0 = unknown)
     int64_t opt_chain_prefix;  // chained capture: hash the blocks in front of the parent field in a parallel pre-pass: 0 never, 1 up to 2^16 sessions (default), 2 always
     int64_t opt_slash_slice;   // k_slash_lanes: bytes of shared memory per warp; 0 = chosen per batch (default)
     int64_t opt_slash_variant; // 0: sessions that fit are staged in shared memory (default), 1: always global memory

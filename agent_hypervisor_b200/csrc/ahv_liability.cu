@@ -144,10 +144,14 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
                   const double *__restrict__ sigma, const double *__restrict__ omega,
                   const uint8_t *__restrict__ consensus, const uint8_t *__restrict__ current_ring, uint64_t A,
                   double *__restrict__ out_sigma, uint8_t *__restrict__ out_ring, uint8_t *__restrict__ out_demote,
-                  uint8_t *__restrict__ out_near, uint32_t long_cut, SigWork wk)
+                  uint8_t *__restrict__ out_near, uint32_t long_cut, SigWork wk, uint32_t rows_log2)
 {
     extern __shared__ __align__(128) uint8_t sig_smem[];
     SigStage<SIG_CHUNK> &st = *reinterpret_cast<SigStage<SIG_CHUNK> *>(sig_smem);
+    // Rows per tile: 128 (one per thread) unless the graph's rows are long on average - then a tile of 128 rows would
+    // be dozens of chunks walked by one CTA, and a small graph would not even fill the SMs - in which case a tile
+    // has R = 2^rows_log2 rows, owned by every (128 / R)-th thread so that they stay spread over the four warps.
+    const uint32_t R = 1u << rows_log2, own_shift = 7u - rows_log2;
     __shared__ __align__(8) uint64_t mbar_storage;
     __shared__ uint32_t s_word;
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
@@ -165,10 +169,10 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
     uint32_t phase = 0;                                   // chunks this CTA has waited for so far (mbarrier parity)
     uint32_t tile = blockIdx.x;
     while (tile != SIG_NONE) {
-        const uint64_t a0 = (uint64_t)tile * SIG_ROWS;
-        const uint64_t a = a0 + tid;
-        const bool valid = a < A;
-        const uint64_t a_last = (a0 + SIG_ROWS < A) ? a0 + SIG_ROWS : A;
+        const uint64_t a0 = (uint64_t)tile * R;
+        const uint64_t a = a0 + (tid >> own_shift);
+        const bool valid = (tid & ((1u << own_shift) - 1u)) == 0u && a < A;
+        const uint64_t a_last = (a0 + R < A) ? a0 + R : A;
         const uint32_t e_begin = __ldg(rowptr + a0), e_end = __ldg(rowptr + a_last);
         const uint32_t my0 = valid ? __ldg(rowptr + a) : 0u, my1 = valid ? __ldg(rowptr + a + 1) : 0u;
         // Look-ahead through L2 (first tile of each CTA; CTAs start roughly in tile order): the row pointers of
@@ -179,7 +183,7 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
         uint32_t f0 = 0, f1 = 0;
         const uint64_t tile_f = (uint64_t)tile + SIG_AHEAD;
         if (first && tid == 0 && tile_f < ntiles) {
-            const uint64_t r0 = tile_f * SIG_ROWS, r1 = (r0 + SIG_ROWS < A) ? r0 + SIG_ROWS : A;
+            const uint64_t r0 = tile_f * R, r1 = (r0 + R < A) ? r0 + R : A;
             f0 = __ldg(rowptr + r0);
             f1 = __ldg(rowptr + r1);
         }
@@ -213,7 +217,7 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
             // CTA b checks tiles b + i * SIG_SCAN_CTAS, one per thread
             if (wk.queue && first && blockIdx.x < SIG_SCAN_CTAS) {
                 for (uint32_t t = blockIdx.x + tid * SIG_SCAN_CTAS; t < ntiles; t += SIG_ROWS * SIG_SCAN_CTAS) {
-                    const uint64_t r0 = (uint64_t)t * SIG_ROWS, r1 = (r0 + SIG_ROWS < A) ? r0 + SIG_ROWS : A;
+                    const uint64_t r0 = (uint64_t)t * R, r1 = (r0 + R < A) ? r0 + R : A;
                     if (__ldg(rowptr + r1) - __ldg(rowptr + r0) > wk.heavy) {
                         const uint32_t slot = atomicAdd(&q_cnt[0], 1u);
                         if (slot < wk.cap) q_ent[slot] = t;
@@ -315,11 +319,11 @@ k_sigma_eff_tiled(const uint32_t *__restrict__ rowptr, const double *__restrict_
         if (first && tid < 8) {
             const uint64_t tile_ff = (uint64_t)tile + 2 * SIG_AHEAD;
             if (tid < 4 && tile_ff < ntiles) {                        // 128 row pointers = four 128-byte lines
-                const uint64_t r = tile_ff * SIG_ROWS + 32u * tid;
+                const uint64_t r = tile_ff * R + 32u * tid;
                 if (r <= A) asm volatile("prefetch.global.L2 [%0];" ::"l"(rowptr + r));
             }
             if (tile_f < ntiles) {
-                const uint64_t r0 = tile_f * SIG_ROWS;
+                const uint64_t r0 = tile_f * R;
                 if (tid == 0 && f1 > f0) {
                     const uint32_t p0 = f0 & ~15u;
                     uint32_t cnt = (f1 - p0) & ~15u;
@@ -652,7 +656,18 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
     const bool aligned = ((reinterpret_cast<uintptr_t>(d_bonded) | reinterpret_cast<uintptr_t>(d_expiry) |
                            reinterpret_cast<uintptr_t>(d_active)) & 15u) == 0;
     SigWork wk = {nullptr, nullptr, nullptr, 0, 0, 0};
-    if (ctx->opt_sigma_variant == 1 && aligned && ctx->opt_sigma_share) AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
+    // rows per tile of the tiled kernel: option sigma_rows, else from the average row length when the caller knows the
+    // record count (the host entry does), else 128
+    uint32_t rl = 7;
+    if (ctx->opt_sigma_rows) {
+        rl = 0;
+        while ((2u << rl) <= (uint32_t)ctx->opt_sigma_rows) ++rl;
+    } else if (ctx->sigma_edges_hint) {
+        const uint64_t avg = (ctx->sigma_edges_hint + A - 1) / A;
+        while (rl > 0 && ((uint64_t)avg << rl) > 2048) --rl;
+    }
+    const uint64_t R = 1ull << rl;
+    if (ctx->opt_sigma_variant == 1 && aligned && ctx->opt_sigma_share) AHV_TRY(sigma_work(ctx, grid_for(A, (unsigned)R), &wk));
     if (ctx->opt_sigma_variant == 2 && aligned) {
         AHV_TRY(sigma_work(ctx, grid_for(A, SIG_ROWS), &wk));
         const uint32_t ntiles = grid_for(A, SIG_ROWS);
@@ -681,29 +696,29 @@ int ahv_sigma_eff_rings_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double
                                                                      d_omega, d_consensus, d_current_ring, A, d_out_sigma,
                                                                      d_out_ring, d_out_demote, d_out_near);
     else if (ctx->opt_sigma_exact)
-        k_sigma_eff_tiled<0, false, 2048><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
+        k_sigma_eff_tiled<0, false, 2048><<<grid_for(A, (unsigned)R), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, 0u, wk);
+            d_out_ring, d_out_demote, d_out_near, 0u, wk, rl);
     else if (ctx->opt_sigma_chunk == 1024)
-        k_sigma_eff_tiled<0, true, 1024><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1024>), ctx->stream>>>(
+        k_sigma_eff_tiled<0, true, 1024><<<grid_for(A, (unsigned)R), SIG_ROWS, sizeof(SigStage<1024>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk, rl);
     else if (ctx->opt_sigma_chunk == 1296)
-        k_sigma_eff_tiled<0, true, 1296><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1296>), ctx->stream>>>(
+        k_sigma_eff_tiled<0, true, 1296><<<grid_for(A, (unsigned)R), SIG_ROWS, sizeof(SigStage<1296>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk, rl);
     else if (ctx->opt_sigma_chunk == 1536)
-        k_sigma_eff_tiled<0, true, 1536><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1536>), ctx->stream>>>(
+        k_sigma_eff_tiled<0, true, 1536><<<grid_for(A, (unsigned)R), SIG_ROWS, sizeof(SigStage<1536>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk, rl);
     else if (ctx->opt_sigma_chunk != 2048)
-        k_sigma_eff_tiled<0, true, 1440><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<1440>), ctx->stream>>>(
+        k_sigma_eff_tiled<0, true, 1440><<<grid_for(A, (unsigned)R), SIG_ROWS, sizeof(SigStage<1440>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk, rl);
     else
-        k_sigma_eff_tiled<0, true, 2048><<<grid_for(A, SIG_ROWS), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
+        k_sigma_eff_tiled<0, true, 2048><<<grid_for(A, (unsigned)R), SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(
             d_rowptr, d_bonded, d_active, d_expiry, now, d_sigma, d_omega, d_consensus, d_current_ring, A, d_out_sigma,
-            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk);
+            d_out_ring, d_out_demote, d_out_near, (uint32_t)ctx->opt_sigma_long_cut, wk, rl);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }
@@ -721,11 +736,11 @@ int ahv_exposure_sums_dev(ahv_ctx *ctx, const uint32_t *d_rowptr, const double *
     if (compensated)
         k_sigma_eff_tiled<2, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
-                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0, 0});
+                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0, 0}, 7u);
     else
         k_sigma_eff_tiled<1, false, 2048><<<g, SIG_ROWS, sizeof(SigStage<2048>), ctx->stream>>>(d_rowptr, d_bonded, d_active, d_expiry, now, nullptr,
                                                                      nullptr, nullptr, nullptr, n_rows, d_out_sum, nullptr,
-                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0, 0});
+                                                                     nullptr, nullptr, 0u, SigWork{nullptr, nullptr, nullptr, 0, 0, 0}, 7u);
     AHV_CHECK_LAUNCH(ctx);
     return AHV_OK;
 }

@@ -470,6 +470,9 @@ int ahv_int_peak(ahv_ctx *ctx, int mode, int iters, double *out_instr_per_s, flo
  *                   row then bounds the pass); 0 (default) = rows longer than "sigma_long_cut" edges are summed by a
  *                   warp in a fixed shape that depends on the row alone (a few ulp from the reference, same result every run)
  *   "sigma_long_cut" 4..  that row length (default 64)
+ *   "sigma_rows" 0,1..128  sigma_eff: agent rows per tile of the tiled kernel (a power of two).  0 (default): 128, or
+ *                   fewer when ahv_sigma_eff_rings sees rows of more than 16 records on average (a tile then stays within
+ *                   about one staging chunk); ahv_sigma_eff_rings_dev does not know the record count and uses 128
  *   "sigma_share" 0/1   CTAs of that kernel take over tiles with many more edges than a chunk from a shared queue (default 1)
  *   "sigma_heavy" 256..  a tile of that kernel with more edges than this is handed out through the shared queue (default 3072)
  *   "sigma_chunk"   records per shared-memory chunk of that kernel: 1024 / 1296 / 1440 / 1536 / 2048 (default 1440: eight CTAs per SM)

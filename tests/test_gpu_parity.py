@@ -717,6 +717,21 @@ def test_sigma_eff_long_and_empty_rows(ctx):
             ctx.set_option("sigma_chunk", 1440)
         exp = sigma_expected_default_path(want, *args, cut=cut)
         assert np.array_equal(got[0], exp[0]) and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:4]))
+    # rows per tile (the host entry picks 16 for this graph's average row of ~100 records): every size, same bits
+    exp = sigma_expected_default_path(want, *args)
+    for rows in (1, 2, 8, 32, 64, 128):
+        ctx.set_option("sigma_rows", rows)
+        try:
+            got = ctx.sigma_eff_rings(*args)
+            ctx.set_option("sigma_exact", 1)
+            got_exact = ctx.sigma_eff_rings(*args)
+        finally:
+            ctx.set_option("sigma_exact", 0)
+            ctx.set_option("sigma_rows", 0)
+        assert np.array_equal(got[0], exp[0]) and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:4])), rows
+        assert all(np.array_equal(a, b) for a, b in zip(got_exact, want)), rows
+    with pytest.raises(Exception):
+        ctx.set_option("sigma_rows", 3)
     ctx.set_option("sigma_exact", 1)
     try:
         for variant in (1, 0, 2):
